@@ -1,0 +1,166 @@
+/* libxvector.so -- C-ABI of the B200-native x-vector embedding hot path.
+ *
+ * The reference (entn-at/tf-kaldi-speaker) has no FFI/plugin interface: the path is Python
+ * that builds TensorFlow graph nodes.  This library sits one level below those Python
+ * signatures; each entry point names the reference code it replaces (paths relative to the
+ * reference root).  Plain pointers and sizes only; no torch / numpy types.
+ *
+ * Ownership : the caller owns every buffer it passes; the library copies weights at
+ *             xv_set_weight and owns all device memory; results are written into
+ *             caller-allocated buffers.
+ * Errors    : 0 on success, negative XV_E* otherwise; xv_last_error() gives the message.
+ * Threading : an xv_ctx is bound to one device and one CUDA stream and is NOT re-entrant;
+ *             multi-GPU = one ctx (one process or thread) per GPU.
+ * There is no CPU fallback: every compute entry point fails with XV_ECUDA without a GPU.
+ */
+#ifndef XVECTOR_H_
+#define XVECTOR_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define XV_OK            0
+#define XV_EINVAL       -1   /* bad argument / malformed config / utterance shorter than context */
+#define XV_ECUDA        -2   /* CUDA runtime or driver error (message has the CUDA string) */
+#define XV_ENOMEM       -3
+#define XV_ESTATE       -4   /* call order violated (e.g. forward before finalize_weights) */
+#define XV_ENOTFOUND    -5   /* unknown node / missing weight */
+#define XV_EUNSUPPORTED -6   /* network / pooling type not implemented (reference raises NotImplementedError:
+                                model/trainer.py:109-110, model/pooling.py:22-23) */
+#define XV_ECAPACITY    -7   /* output buffer too small */
+
+#define XV_DTYPE_F32  0
+#define XV_DTYPE_BF16 1
+
+typedef struct xv_ctx xv_ctx;
+
+/* ---- life cycle ------------------------------------------------------------------------
+ * Replaces Trainer.__init__ + Trainer.build("predict") (model/trainer.py:87-219, 325-338):
+ * config_json is the text of the reference nnet_conf JSON (misc/utils.py:13-41) extended with
+ *   "feature_dim": D            (nnet/feature_dim, extract.py:54-55)
+ *   "precision": "bf16"|"fp32"  (bf16 = tcgen05 path; fp32 = SIMT validation mode)
+ *   "batch_frames": int         (optional frame budget of one packed launch sequence)
+ * Lazily-injected defaults (num_nodes_pooling_layer=1500 model/tdnn.py:114-116, ...) are applied. */
+int  xv_create(int device, const char* config_json, xv_ctx** out);
+void xv_destroy(xv_ctx* ctx);
+/* ctx may be NULL: returns the calling thread's last error from xv_create. */
+const char* xv_last_error(xv_ctx* ctx);
+
+/* ---- weights ---------------------------------------------------------------------------
+ * Replaces Trainer.load() / tf.train.Saver.restore (model/trainer.py:277-295).  tf_name is the
+ * TensorFlow variable name ("tdnn/tdnn1_conv/kernel" [1,k,Cin,Cout], "tdnn/tdnn4_dense/kernel"
+ * [in,out], "tdnn/tdnn1_bn/moving_variance", "tdnn/attention/query" [H,dk], ...).  fp32, C order. */
+int  xv_set_weight(xv_ctx* ctx, const char* tf_name, const float* host, const int64_t* shape, int rank);
+/* Folds BN (eps 1e-3) + bias into per-channel scale/shift, pads K/N, casts to bf16 K-major,
+ * builds TMA descriptors.  Fails with XV_ENOTFOUND naming the first missing variable. */
+int  xv_finalize_weights(xv_ctx* ctx);
+
+/* ---- endpoints -------------------------------------------------------------------------
+ * endpoints[node] of model/tdnn.py:35-179 / model/pooling.py:24,198,220.  width = last-axis size;
+ * frame_level = 1 for [B,T',width] nodes; context = T - T' (frames lost to VALID convolutions). */
+int  xv_node_info(xv_ctx* ctx, const char* node, int32_t* width, int32_t* frame_level, int32_t* context);
+
+/* ---- the hot path ----------------------------------------------------------------------
+ * Replaces sess.run(self.embeddings, {features: x, is_training: False}) (model/trainer.py:909)
+ * for a ragged batch: feats = n_utts utterances packed back to back, [sum(lengths), D] fp32
+ * (host, pinned host or device memory), lengths[u] frames each.  node = "" -> the config's
+ * embedding_node.  Utterance-level nodes: out[n_utts, width] fp32 (host).  Each utterance is
+ * computed exactly as the reference computes a batch-of-one (no masking approximations). */
+int  xv_forward(xv_ctx* ctx, const float* feats, const int32_t* lengths, int32_t n_utts,
+                const char* node, float* out, int64_t out_capacity);
+/* Frame-level nodes (extract_frame.py / extract_attention.py readers): utterance u's
+ * [lengths[u]-context, width] block (attention_weights: [H, lengths[u]-context]) is written at
+ * out + out_offsets[u] (offsets in floats). */
+int  xv_forward_frames(xv_ctx* ctx, const float* feats, const int32_t* lengths, int32_t n_utts,
+                       const char* node, float* out, const int64_t* out_offsets, int64_t out_capacity);
+
+/* Same path split in three so a caller (bench.py) can time device-resident work:
+ * xv_stage  : H2D of features + length tables (kept on the device until the next xv_stage);
+ * xv_run    : launches every kernel of the forward pass asynchronously on the ctx stream;
+ * xv_fetch  : D2H of the utterance-level result of the last xv_run + stream sync. */
+int  xv_stage(xv_ctx* ctx, const float* feats, const int32_t* lengths, int32_t n_utts);
+int  xv_run(xv_ctx* ctx, const char* node);
+int  xv_fetch(xv_ctx* ctx, float* out, int64_t out_capacity);
+int  xv_sync(xv_ctx* ctx);
+
+/* ---- standalone pooling ----------------------------------------------------------------
+ * statistics_pooling(features,...) (model/pooling.py:27-52) for direct callers: x is a DEVICE
+ * (or host; then copied) buffer [cu_lens[n], C] of dtype XV_DTYPE_*, utterance u = rows
+ * cu_lens[u]..cu_lens[u+1]; out (host) [n, 2C] = [mean | std], population variance, floor 1e-12. */
+int  xv_stat_pooling(xv_ctx* ctx, const void* x, const int32_t* cu_lens, int32_t n, int32_t C,
+                     int dtype, float* out);
+/* As xv_stat_pooling but leaves the result on the device (out_dev [n,2C] fp32) and does not
+ * synchronise: the bandwidth-roofline entry point. cu_lens_dev is a device array [n+1]. */
+int  xv_stat_pooling_dev(xv_ctx* ctx, const void* x_dev, const int32_t* cu_lens_dev, int32_t n, int32_t C,
+                         int dtype, int32_t max_len, float* out_dev);
+/* The weighted-statistics core of self_attention (model/pooling.py:186-218): value [cu[n],Cv],
+ * key [cu[n],Ck] (dtype as above, device or host), query [H,dk] fp32 host.  out (host)
+ * [n, 2*H*dv]; weights_out (host, may be NULL) packed [H, L_u] per utterance at H*cu_lens[u]. */
+int  xv_attention_pooling(xv_ctx* ctx, const void* value, const void* key, const float* query,
+                          const int32_t* cu_lens, int32_t n, int32_t Cv, int32_t Ck, int32_t H,
+                          int split_value, int split_key, int use_scale, int dtype,
+                          float* out, float* weights_out);
+
+/* One affine (+BN +activation) layer of model/common.py:113-223 / model/tdnn.py:42-55 on fp32 HOST rows through
+ * the SIMT validation kernel, for direct array callers of dense_bn_relu()/dense()/dense_relu()/dense_tanh():
+ * out[r, n] = act(bn_scale[n] * (sum_{j<taps,c} x[r+j, c] * w[j*cin+c, n] + bias[n]) + bn_shift[n]); out has
+ * rows-taps+1 rows.  bn_scale/bn_shift (already folded with eps) and slope (negative-side slope per channel)
+ * may be NULL (= no BN / no activation). */
+int  xv_dense_rows_f32(xv_ctx* ctx, const float* x, int64_t rows, int32_t cin, int32_t taps, const float* w,
+                       int32_t n, const float* bias, const float* bn_scale, const float* bn_shift,
+                       const float* slope, int act_tanh, float* out);
+
+/* prelu() (model/common.py:27-42): out = relu(x) + alpha*(x-|x|)/2 per channel, x/out HOST [rows,width] fp32,
+ * alpha [width] (or [1] when shared != 0). */
+int  xv_prelu_f32(xv_ctx* ctx, const float* x, int64_t rows, int32_t width, const float* alpha, int shared, float* out);
+/* l2_scaling() (model/common.py:45-58): out = x * rsqrt(max(sum_row x^2, eps)) * factor, HOST [rows,width] fp32. */
+int  xv_l2_scaling_f32(xv_ctx* ctx, const float* x, int64_t rows, int32_t width, float factor, float eps, float* out);
+
+/* ---- measurement / plumbing --------------------------------------------------------------
+ * CUDA events on the ctx stream (the stream every kernel of this library is launched on). */
+int  xv_event_record(xv_ctx* ctx, int slot);                 /* slot in [0,16) */
+int  xv_event_elapsed_ms(xv_ctx* ctx, int slot_a, int slot_b, float* ms);
+/* Number of kernels of THIS library launched by the ctx so far, and a per-kernel-family
+ * breakdown written as "name=count;..." into buf. */
+int64_t xv_launch_count(xv_ctx* ctx);
+int  xv_launch_summary(xv_ctx* ctx, char* buf, size_t buf_size);
+/* Accumulated device time (ms) of a kernel family between xv_profile_begin/end (events around
+ * every launch of that family; serialises nothing else).  family: "gemm", "pool", "cast", ... */
+int  xv_profile_enable(xv_ctx* ctx, int on);
+int  xv_profile_query(xv_ctx* ctx, const char* family, float* total_ms, int64_t* launches);
+/* Pinned host memory for callers that want true async H2D. */
+void* xv_host_alloc(size_t bytes);
+void  xv_host_free(void* p);
+/* Raw device buffers (for the standalone pooling benches and tests). */
+void* xv_device_alloc(xv_ctx* ctx, size_t bytes);
+void  xv_device_free(xv_ctx* ctx, void* p);
+int   xv_memcpy_h2d(xv_ctx* ctx, void* dst_dev, const void* src_host, size_t bytes);
+int   xv_memcpy_d2h(xv_ctx* ctx, void* dst_host, const void* src_dev, size_t bytes);
+/* Converts fp32 host data to a bf16 device buffer (round-to-nearest-even). */
+int   xv_upload_bf16(xv_ctx* ctx, void* dst_dev, const float* src_host, size_t count);
+/* Writes `bytes` of a scratch buffer (> L2) to flush the L2 between timed iterations. */
+int   xv_flush_l2(xv_ctx* ctx);
+
+/* Generic C = act(scale*(A.W)+shift) on the tcgen05 path, for kernel-level tests and the GEMM
+ * roofline bench: A [M, taps-spliced view of Cin] bf16 device, Wt [N,K] bf16 device (K-major),
+ * out bf16 device [M, ldo].  See DESIGN.md "GEMM kernel". */
+int   xv_gemm_bf16(xv_ctx* ctx, const void* a_dev, int64_t a_rows, int32_t cin, int32_t taps, int32_t dilation,
+                   const void* wt_dev, int32_t n, const float* scale_dev, const float* shift_dev,
+                   float neg_slope, void* out_dev, int32_t ldo, int64_t m_rows);
+
+/* Bench variant of xv_gemm_bf16: caller supplies the per-channel negative-slope array, ldo == n, and
+ * nothing is synchronised (time it with xv_event_record on the ctx stream). */
+int   xv_gemm_bf16_async(xv_ctx* ctx, const void* a_dev, int64_t a_rows, int32_t cin, int32_t taps, int32_t dilation,
+                         const void* wt_dev, int32_t n, const float* scale_dev, const float* shift_dev,
+                         const float* slope_dev, void* out_dev, int64_t m_rows);
+
+const char* xv_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* XVECTOR_H_ */

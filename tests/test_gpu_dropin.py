@@ -1,0 +1,145 @@
+"""GPU: the Python drop-ins keep the reference's signatures and return the oracle's arrays."""
+import numpy as np
+import pytest
+
+from util import TOL, max_rel, tensor_rel
+
+pytestmark = pytest.mark.gpu
+
+
+class P(object):
+    def __init__(self, **kw):
+        self.__dict__.update(kw)
+
+    @property
+    def dict(self):
+        return self.__dict__
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_tdnn_function_signature_and_endpoints(precision):
+    from oracle import numpy_ref, synth
+    from xvector_b200.model import variables as V
+    from xvector_b200.model.tdnn import tdnn
+    cfg = dict(synth.TDNN_STAT_CONFIG)
+    w = synth.make_tdnn_weights(30, cfg, seed=2)
+    x = synth.config1_features(3, 60, 30, seed=9)
+    params = P(**cfg)
+    with V.variable_store(w, precision=precision):
+        out, endpoints = tdnn(x, params, is_training=False, reuse_variables=None, aux_features=None)
+        ref_out, ref_ep = numpy_ref.tdnn(x, numpy_ref.OracleParams(**cfg), w)
+        assert list(endpoints.keys()) == list(ref_ep.keys())
+        assert params.num_nodes_pooling_layer == 1500 and params.last_layer_no_bn is False
+        assert out.shape == ref_out.shape and max_rel(out, ref_out) <= TOL[precision]
+        for node in ("tdnn1_conv", "tdnn3_relu", "tdnn5_bn", "pooling", "tdnn6_dense"):
+            assert endpoints[node].shape == ref_ep[node].shape
+            assert tensor_rel(endpoints[node], ref_ep[node]) <= TOL[precision], node
+    V.clear_engines()
+
+
+def test_pooling_functions_on_arrays():
+    from oracle import numpy_ref, synth
+    from xvector_b200.model import variables as V
+    from xvector_b200.model.pooling import general_pooling, self_attention, statistics_pooling
+    rng = np.random.default_rng(4)
+    x = np.maximum(rng.standard_normal((4, 120, 1500)), 0).astype(np.float32)
+    params = P(pooling_type="statistics_pooling")
+    ep = {}
+    got = general_pooling(x, None, ep, params, False)
+    assert got.shape == (4, 3000) and ep["pooling"] is got
+    assert tensor_rel(got, numpy_ref.statistics_pooling(x)) < 1e-5
+    assert tensor_rel(statistics_pooling(x, None, {}, params, False), numpy_ref.statistics_pooling(x)) < 1e-5
+    with pytest.raises(NotImplementedError, match="Not implement lde pooling"):
+        general_pooling(x, None, {}, P(pooling_type="lde"), False)
+    # self_attention reads key/value from endpoints by name
+    cfg = dict(synth.TDNN_ATT_CONFIG, att_num_heads=4, att_key_num_nodes=[64, 48], att_key_input="k_in", att_value_input="v_in")
+    w = {}
+    r2 = np.random.default_rng(8)
+    for name, n_in, n_out in (("att_key0", 32, 64), ("att_key1", 64, 48)):
+        base = "tdnn/attention/%s/%s" % (name, name)
+        w[base + "_dense/kernel"] = (r2.standard_normal((n_in, n_out)) / 6).astype(np.float32)
+        w[base + "_dense/bias"] = (0.1 * r2.standard_normal(n_out)).astype(np.float32)
+    for k, v in (("gamma", r2.uniform(0.5, 1.5, 64)), ("beta", 0.1 * r2.standard_normal(64)),
+                 ("moving_mean", 0.1 * r2.standard_normal(64)), ("moving_variance", r2.uniform(0.5, 1.5, 64))):
+        w["tdnn/attention/att_key0/att_key0_bn/" + k] = v.astype(np.float32)
+    w["tdnn/attention/query"] = (0.3 * r2.standard_normal((4, 12))).astype(np.float32)
+    ep = {"k_in": r2.standard_normal((2, 50, 32)).astype(np.float32), "v_in": np.abs(r2.standard_normal((2, 50, 40))).astype(np.float32)}
+    ref_ep = dict(ep)
+    ref = numpy_ref.self_attention(None, None, ref_ep, numpy_ref.OracleParams(**cfg), w, scope="tdnn")
+    with V.variable_store(w):
+        with V.variable_scope("tdnn"):
+            got = self_attention(None, None, ep, P(**cfg), False)
+    assert tensor_rel(got, ref) < 1e-4
+    assert tensor_rel(ep["attention_weights"], ref_ep["attention_weights"]) < 1e-4
+    assert tensor_rel(ep["att_key0_relu"], ref_ep["att_key0_relu"]) < 1e-4
+    V.clear_engines()
+
+
+def test_common_helpers():
+    from oracle import numpy_ref
+    from xvector_b200.model import variables as V
+    from xvector_b200.model.common import combine_last_two_dimensions, l2_scaling, prelu, shape_list, split_heads
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal((5, 33)).astype(np.float32)
+    assert tensor_rel(l2_scaling(x, 4.0), numpy_ref.l2_scaling(x, 4.0)) < 1e-6
+    alpha = rng.uniform(0, 0.3, 33).astype(np.float32)
+    with V.variable_store({"s/act/alpha": alpha}):
+        with V.variable_scope("s"):
+            got = prelu(x, name="act")
+    np.testing.assert_allclose(got, np.maximum(x, 0) + alpha * (x - np.abs(x)) * 0.5, rtol=1e-6, atol=1e-7)
+    y = rng.standard_normal((2, 7, 12))
+    assert split_heads(y, 3).shape == (2, 3, 7, 4) and shape_list(y) == [2, 7, 12]
+    np.testing.assert_array_equal(combine_last_two_dimensions(split_heads(y, 3).transpose(0, 2, 1, 3)), y)
+    V.clear_engines()
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_trainer_predict_and_extractor(tmp_path, precision):
+    """Trainer.predict (model/trainer.py:886-913) and the extractor's chunk/average logic (extract.py:64-93)."""
+    import json
+    import os
+    from oracle import numpy_ref, synth
+    from xvector_b200.extract import extract_many, extract_one
+    from xvector_b200.misc.utils import Params
+    from xvector_b200.model.trainer import Trainer
+    cfg = dict(synth.TDNN_STAT_CONFIG)
+    w = synth.make_tdnn_weights(30, cfg, seed=6)
+    nnet = tmp_path / "nnet"
+    nnet.mkdir()
+    (nnet / "config.json").write_text(json.dumps(cfg))
+    np.savez(str(nnet / "weights.npz"), **w)
+    (nnet / "checkpoint").write_text('model_checkpoint_path: "model-1230000"\n')
+    params = Params(str(nnet / "config.json"))
+    trainer = Trainer(params, str(tmp_path), 30, single_cpu=True, precision=precision)
+    trainer.build("predict")
+    assert trainer.load() == 1230000
+    x = synth.config1_features(2, 80, 34, seed=12)               # wider than dim: sliced (trainer.py:906-907)
+    oparams = numpy_ref.OracleParams(**cfg)
+    tol = TOL[precision]
+    e3 = trainer.predict(x)
+    e2 = trainer.predict(x[0])
+    assert e3.shape == (2, 512) and e2.shape == (512,) and e3.dtype == np.float32
+    assert max_rel(e3, numpy_ref.predict(x, oparams, w, 30)) <= tol
+    assert max_rel(e2[None], e3[:1]) < 2e-3
+    trainer.set_embedding("tdnn4_relu")
+    f = trainer.predict(x[0])
+    assert f.shape == (66, 512) and tensor_rel(f, numpy_ref.predict(x[0], oparams, w, 30, node="tdnn4_relu")) <= tol
+    trainer.set_embedding("tdnn6_dense")
+    # extractor: skip / whole / chunked, with and without normalisation
+    lens = [20, 120, 530, 260]
+    feats = [synth.packed_features(np.array([n]), 30, seed=40 + n) for n in lens]
+    pred = lambda a: numpy_ref.predict(a, oparams, w, 30)
+    for norm in (False, True):
+        want = [numpy_ref.extract_embedding(ft, pred, chunk_size=200, min_chunk_size=25, normalize=norm) for ft in feats]
+        many = extract_many(trainer, feats, chunk_size=200, min_chunk_size=25, normalize=norm)
+        one = [extract_one(trainer, ft, chunk_size=200, min_chunk_size=25, normalize=norm) for ft in feats]
+        assert want[0] is None and many[0] is None and one[0] is None
+        for i in (1, 2, 3):
+            assert max_rel(many[i][None], want[i][None]) <= tol
+            assert max_rel(one[i][None], want[i][None]) <= tol
+    trainer.close()
+    t2 = Trainer(params, str(tmp_path / "missing"), 30, precision=precision)
+    t2.build("predict")
+    with pytest.raises(SystemExit):
+        t2.predict(x)                                            # "Cannot find model in ..." (trainer.py:891-895)
+    t2.close()

@@ -1,0 +1,118 @@
+"""CPU: the C-ABI library loads and exports every declared symbol; host-side logic (Params, scheduler, extractor
+planning, error behaviour).  No compute calls: there is no GPU here and no CPU fallback."""
+import ctypes as C
+import glob
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+
+import xvector_b200
+from xvector_b200 import _lib
+from xvector_b200 import scheduler
+from xvector_b200.extract import plan_many
+from xvector_b200.misc.utils import Params, ParamsPlain
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = xvector_b200.load()
+    header = open(os.path.join(ROOT, "include", "xvector.h")).read()
+    declared = set(re.findall(r"\b(xv_[a-z0-9_]+)\s*\(", header)) - {"xv_ctx"}
+    assert len(declared) >= 30
+    for name in sorted(declared):
+        assert hasattr(lib, name), "libxvector.so does not export %s" % name
+    assert declared == set(_lib.PROTOTYPES), "ctypes prototypes and include/xvector.h disagree: %s" % (
+        declared ^ set(_lib.PROTOTYPES))
+    assert b"sm_100a" in lib.xv_version()
+
+
+def test_create_fails_loudly_without_gpu_or_with_bad_config():
+    lib = xvector_b200.load()
+    ctx = C.c_void_p()
+    rc = lib.xv_create(0, b"{not json", C.byref(ctx))
+    assert rc != 0 and not ctx.value
+    assert len(lib.xv_last_error(None)) > 0
+    assert lib.xv_create(0, None, C.byref(ctx)) == _lib.XV_EINVAL
+
+
+def test_product_does_not_import_the_oracle():
+    pkg = os.path.join(ROOT, "tf-kaldi-speaker_b200")
+    for path in glob.glob(os.path.join(pkg, "**", "*.py"), recursive=True):
+        src = open(path).read()
+        assert not re.search(r"^\s*(from|import)\s+oracle\b", src, re.M), "%s imports the oracle" % path
+
+
+def test_params_interface(tmp_path):
+    p = tmp_path / "c.json"
+    p.write_text(json.dumps({"network_type": "tdnn", "pooling_type": "statistics_pooling", "weight_l2_regularizer": 1e-2}))
+    params = Params(str(p))
+    assert params.network_type == "tdnn" and "pooling_type" in params.dict
+    params.dict["num_nodes_pooling_layer"] = 1500
+    assert params.num_nodes_pooling_layer == 1500
+    params.last_layer_no_bn = False
+    assert "last_layer_no_bn" in params.dict
+    params.save(str(tmp_path / "d.json"))
+    assert Params(str(tmp_path / "d.json")).num_nodes_pooling_layer == 1500
+    pp = ParamsPlain()
+    pp.x = 3
+    assert pp.dict == {"x": 3}
+
+
+def test_config_json_drops_non_serialisable_values():
+    cfg = json.loads(xvector_b200.config_json({"network_type": "tdnn", "global_step": object()}, 30, "fp32", 4096))
+    assert cfg == {"network_type": "tdnn", "feature_dim": 30, "precision": "fp32", "batch_frames": 4096}
+
+
+def test_chunk_plan_matches_oracle():
+    from oracle import numpy_ref
+    for length, chunk in [(25000, 10000), (10001, 10000), (2501, 1001), (12345, 2000), (6000, 2000), (4001, 2000)]:
+        assert scheduler.chunk_plan(length, chunk) == numpy_ref.chunk_plan(length, chunk)
+
+
+def test_plan_many_skips_and_chunks():
+    work = plan_many([10, 300, 4500], chunk_size=2000, min_chunk_size=25)
+    assert work[0] == (1, 0, 300)
+    assert [w for w in work if w[0] == 2] == [(2, s, z) for s, z in scheduler.chunk_plan(4500, 2000)]
+    assert all(w[0] != 0 for w in work)
+
+
+def test_lpt_sharding_balances_flops():
+    from oracle import synth
+    lengths = synth.config2_lengths(4096)
+    for world in (1, 2, 4, 8):
+        shards = scheduler.shard_lpt(lengths, world)
+        all_idx = np.sort(np.concatenate(shards))
+        np.testing.assert_array_equal(all_idx, np.arange(len(lengths)))
+        loads = np.array([scheduler.utterance_flops(lengths[s], 30).sum() for s in shards])
+        assert loads.max() / loads.mean() < 1.01
+    assert abs(scheduler.utterance_flops(300, 30) / 1e9 - 2.4529) < 1e-3
+
+
+def test_trainer_error_behaviour(tmp_path):
+    from xvector_b200.model.trainer import Trainer
+    p = ParamsPlain()
+    p.network_type = "ftdnn"
+    with pytest.raises(NotImplementedError, match="Not implement ftdnn network"):
+        Trainer(p, str(tmp_path), 30)
+    p.network_type = "tdnn"
+    p.loss_func = "nope"
+    with pytest.raises(NotImplementedError, match="Not implement nope loss"):
+        Trainer(p, str(tmp_path), 30)
+    p.loss_func = "softmax"
+    t = Trainer(p, str(tmp_path), 30)
+    with pytest.raises(SystemExit):
+        t.load()                                           # graph not built (model/trainer.py:283-284)
+    with pytest.raises(AssertionError):
+        t.build("nonsense")
+
+
+def test_all_reference_style_configs_load(tmp_path):
+    from oracle import synth
+    for i, cfg in enumerate((synth.TDNN_STAT_CONFIG, synth.TDNN_ATT_CONFIG)):
+        f = tmp_path / ("c%d.json" % i)
+        f.write_text(json.dumps(cfg))
+        assert Params(str(f)).network_type == "tdnn"

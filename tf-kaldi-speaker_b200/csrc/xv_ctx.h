@@ -1,0 +1,178 @@
+// The xv_ctx object: model plan, weights, device buffers, staged job.  Internal to libxvector.so.
+#pragma once
+#include <string.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/xvector.h"
+#include "xv_internal.h"
+#include "xv_json.h"
+
+namespace xv {
+
+constexpr float kBnEpsilon = 1e-3f;     // tf.layers.batch_normalization default (TF 1.x)
+constexpr float kLreluAlpha = 0.2f;     // tf.nn.leaky_relu default
+constexpr int kNumEvents = 16;
+
+enum Stage { kStageDense = 0, kStageBn = 1, kStageAct = 2 };
+enum ActKind { kActNone = 0, kActRelu = 1, kActTanh = 2 };   // kActRelu = relu / lrelu / prelu per network_relu_type
+
+struct HostTensor {
+  std::vector<int64_t> shape;
+  std::vector<float> data;
+};
+
+// Grow-only device buffer.
+struct DevBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+};
+
+// One affine layer: y = act(bn(x.W + b)).  Frame level (applied to every packed row, optionally with a spliced
+// context of `taps` rows) or segment level (one row per utterance).
+struct Layer {
+  std::string name;          // "tdnn1" ... "att_key0"
+  std::string kernel_var, bias_var, bn_scope, alpha_var;
+  bool has_bn = false;
+  int act = kActNone;
+  int taps = 1, dil = 1, cin = 0, cout = 0;
+  int in_buf = -1;           // index of the frame buffer this layer reads (-1: the features)
+  std::string ep[3];         // endpoint name per stage ("" = stage does not exist)
+  // device-side parameters
+  int kpad = 0;              // padded K of the bf16 operand (multiple of 64)
+  int a_cin = 0;             // channel count of the bf16 A buffer this layer reads (taps*a_cin == kpad)
+  int a_taps = 1;            // taps used by the bf16 kernel (1 when the input is pre-spliced)
+  int n_alloc = 0;           // cout rounded up to a multiple of 256
+  DevBuf wt;                 // bf16 [n_alloc, kpad], K-major
+  DevBuf w32;                // fp32 [taps*cin, cout]
+  DevBuf bias, bn_scale, bn_shift, slope_raw;    // fp32 [cout] (validation path)
+  DevBuf f_scale[3], f_shift[3], f_slope[3];     // folded per-stage epilogue params, fp32 [n_alloc]
+  CUtensorMap tm_b;
+};
+
+struct NodeInfo {
+  int level = 0;     // 0 frame level, 1 utterance level, 2 attention weights
+  int layer = -1;    // index into frame_layers / seg_layers; -1 for pooling nodes
+  int stage = kStageAct;
+  int width = 0;
+  int context = 0;
+  int kind = 0;      // utterance level: 0 layer output, 1 "pooling", 2 "att_output_before_nonlinear", 3 att_post_bn, 4 att_post_relu, 5 "output"
+};
+
+struct Batch {
+  int32_t utt0 = 0, utt1 = 0;   // utterances [utt0, utt1)
+  int64_t row0 = 0;             // first packed row
+  int64_t rows = 0;
+  int32_t seg0 = 0;             // first entry of this batch in the tile_seg_ptr / segs tables
+  int32_t tile0 = 0;
+  int32_t m_tiles = 0;
+};
+
+struct ProfileSlot {
+  cudaEvent_t a, b;
+  int family;
+};
+
+}  // namespace xv
+
+struct xv_ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t events[xv::kNumEvents] = {};
+  cudaEvent_t h2d_done[2] = {}, buf_free[2] = {};
+  std::string err;
+
+  // ---- configuration (reference nnet_conf JSON + extensions) ----
+  xv::JValue cfg;
+  int dim = 0;
+  bool bf16 = true;
+  int64_t batch_frames = 65536;
+  std::string relu_type;         // "", "prelu", "lrelu"
+  std::string pooling_type;
+  std::string embedding_node;
+  int pool_nodes = 1500, last_nodes = 512;
+  bool last_layer_no_bn = false, last_layer_linear = false;
+  bool feature_norm = false;
+  float feature_scaling_factor = 1.f;
+  // attention
+  int att_heads = 1;
+  bool att_split_value = true, att_split_key = true, att_use_scale = true, att_apply_nonlinear = false;
+  int att_key_buf = -1, att_value_buf = -1;   // frame buffer indices feeding the key / value nets
+  int att_key_dim = 0, att_value_dim = 0, att_dk = 0, att_dv = 0;
+  int pooled_dim = 0;
+
+  // ---- model plan ----
+  std::vector<xv::Layer> frame_layers;    // tdnn1..5 then att_key*, att_value*
+  int n_main_frame = 0;                    // tdnn1..tdnn5
+  std::vector<int> key_layers, value_layers;
+  std::vector<xv::Layer> seg_layers;      // tdnn6, tdnn7
+  std::map<std::string, xv::NodeInfo> nodes;
+  int total_context = 14;
+  bool has_att_post = false;
+  xv::DevBuf att_query, att_post_scale, att_post_shift, att_post_slope;
+
+  std::map<std::string, xv::HostTensor> weights;
+  bool finalized = false;
+
+  // ---- device buffers ----
+  xv::DevBuf d_feats;                      // staged features (all utterances) fp32 [rows, dim]
+  xv::DevBuf d_feat_ring[2];               // pipelined H2D staging for xv_forward
+  xv::DevBuf a1;                           // spliced bf16 [batch rows, k1pad]
+  std::vector<xv::DevBuf> frame_out;       // per frame layer output (bf16 or fp32) [batch rows, n_alloc | cout]
+  xv::DevBuf scores;                       // attention scores/weights fp32 [H][batch rows]
+  xv::DevBuf pool_acc;                     // fused pooling accumulators
+  xv::DevBuf pool_ws;                      // launch_pool workspace
+  xv::DevBuf pooled_f32, pooled_bf16, pooled_pre_f32;
+  xv::DevBuf seg_out[2], seg_out_bf16;
+  xv::DevBuf d_cu, d_segs, d_tile_seg_ptr;
+  xv::DevBuf d_gather_meta, d_gather_out;
+  xv::DevBuf flush_buf;
+  void* h_pinned[2] = {nullptr, nullptr};
+  size_t h_pinned_bytes[2] = {0, 0};
+
+  // ---- staged job ----
+  bool staged = false;
+  int32_t n_utts = 0;
+  int64_t total_rows = 0;
+  std::vector<int32_t> lengths;
+  std::vector<int32_t> cu;                 // [n+1] packed row offsets
+  std::vector<xv::Batch> batches;
+  std::vector<xv::PoolSeg> segs;
+  std::vector<int32_t> tile_seg_ptr;
+  const float* host_feats = nullptr;       // xv_forward pipelined path
+  bool host_pinned = false;          // xv_forward source is pinned host memory
+  // result of the last run
+  const float* result = nullptr;
+  int result_ld = 0, result_width = 0;
+  bool ran = false;
+
+  // ---- accounting ----
+  int64_t launches = 0;
+  std::map<std::string, int64_t> launch_by_family;
+  bool profiling = false;
+  std::vector<xv::ProfileSlot> prof;
+  std::vector<std::string> prof_family_names;
+};
+
+namespace xv {
+// helpers implemented in xv_api.cu
+int fail(xv_ctx* c, int code, const char* fmt, ...);
+int cuda_fail(xv_ctx* c, cudaError_t e, const char* what);
+int ensure(xv_ctx* c, DevBuf* b, size_t bytes, bool zero = false);
+void release(DevBuf* b);
+void count_launch(xv_ctx* c, const char* family);
+struct ProfScope {
+  xv_ctx* c;
+  int idx;
+  ProfScope(xv_ctx* ctx, const char* family);
+  ~ProfScope();
+};
+// forward pieces (xv_forward.cu)
+int plan_job(xv_ctx* c, const int32_t* lengths, int32_t n_utts);
+int run_job(xv_ctx* c, const char* node, bool pipelined_h2d, float* frames_out, const int64_t* frames_off,
+            int64_t frames_cap);
+}  // namespace xv

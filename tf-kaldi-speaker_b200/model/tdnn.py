@@ -1,0 +1,105 @@
+"""tdnn() with the reference's signature and endpoint names (model/tdnn.py:10-181), executed by libxvector.
+
+There is no TF graph: `features` is a numpy array [batch, length, dim]; the variables tdnn() would create/read
+are taken from the installed variable store (model.variables.variable_store).  The returned `endpoints` is an
+OrderedDict in the reference's insertion order whose values are computed on first access (each access is one
+forward pass through the fused engine up to that node) and then cached."""
+from collections import OrderedDict
+
+import numpy as np
+
+from . import variables as V
+
+
+class Endpoints(OrderedDict):
+    """OrderedDict of lazily evaluated network outputs."""
+
+    def __init__(self, names, compute):
+        super(Endpoints, self).__init__()
+        self._compute = compute
+        for n in names:
+            OrderedDict.__setitem__(self, n, None)
+
+    def __getitem__(self, key):
+        v = OrderedDict.__getitem__(self, key)
+        if v is None and self._compute is not None:
+            v = self._compute(key)
+            OrderedDict.__setitem__(self, key, v)
+        return v
+
+    def items(self):
+        return [(k, self[k]) for k in self.keys()]
+
+    def values(self):
+        return [self[k] for k in self.keys()]
+
+
+def endpoint_names(params):
+    """Names tdnn() adds to endpoints, in order (model/tdnn.py:48-179, model/pooling.py:24,198,220,227-229)."""
+    names = []
+    for i in (1, 2, 3):
+        names += ["tdnn%d_conv" % i, "tdnn%d_bn" % i, "tdnn%d_relu" % i]
+    for i in (4, 5):
+        names += ["tdnn%d_dense" % i, "tdnn%d_bn" % i, "tdnn%d_relu" % i]
+    if params.pooling_type == "self_attention":
+        def side(prefix, nodes, last_type):
+            out = []
+            nodes = list(nodes)
+            for j in range(len(nodes)):
+                n = "%s%d" % (prefix, j)
+                last = j == len(nodes) - 1
+                out.append(n + "_dense")
+                if (not last) or last_type == 2:
+                    out.append(n + "_bn")
+                if (not last) or last_type in (1, 2):
+                    out.append(n + "_relu")
+                elif last_type == 3:
+                    out.append(n + "_tanh")
+            return out
+        names += side("att_key", params.att_key_num_nodes, params.att_key_network_type)
+        names += side("att_value", params.att_value_num_nodes, params.att_value_network_type)
+        names += ["attention_weights", "att_output_before_nonlinear"]
+        if params.att_apply_nonlinear:
+            names += ["att_post_bn", "att_post_relu"]
+    names += ["pooling", "tdnn6_dense", "tdnn6_bn", "tdnn6_relu", "tdnn7_dense"]
+    if not params.last_layer_no_bn:
+        names.append("tdnn7_bn")
+    if not params.last_layer_linear:
+        names.append("tdnn7_relu")
+    return names
+
+
+def tdnn(features, params, is_training=None, reuse_variables=None, aux_features=None):
+    """Build (= run) a TDNN network.  Same arguments and return value as the reference (model/tdnn.py:10):
+    returns (output of the last layer [batch, num_nodes_last_layer], endpoints).  `is_training` must be falsy:
+    this build covers the inference path; `reuse_variables` / `aux_features` are accepted and ignored."""
+    if is_training:
+        raise NotImplementedError("tdnn(is_training=True): the training graph is outside this build's scope")
+    # lazily injected defaults, exactly as the reference mutates params.dict (model/tdnn.py:114-116,152-154,163-164,173-174)
+    if "num_nodes_pooling_layer" not in params.dict:
+        params.dict["num_nodes_pooling_layer"] = 1500
+    if "num_nodes_last_layer" not in params.dict:
+        params.dict["num_nodes_last_layer"] = 512
+    if "last_layer_no_bn" not in params.dict:
+        params.last_layer_no_bn = False
+    if "last_layer_linear" not in params.dict:
+        params.last_layer_linear = False
+    if params.pooling_type not in ("statistics_pooling", "self_attention"):
+        raise NotImplementedError("Not implement %s pooling" % params.pooling_type)
+
+    x = np.ascontiguousarray(features, dtype=np.float32)
+    assert x.ndim == 3, "features must be [batch, length, dim]"
+    b, t, d = x.shape
+    eng = V.get_engine(params, d)
+    packed = x.reshape(b * t, d)
+    lengths = np.full(b, t, np.int32)
+
+    def compute(node):
+        _, frame_level, _ = eng.node_info(node)
+        if not frame_level:
+            return eng.forward(packed, lengths, node)
+        return np.stack(eng.forward_frames(packed, lengths, node), axis=0)
+
+    endpoints = Endpoints(endpoint_names(params), compute)
+    last = "tdnn7_relu" if not params.last_layer_linear else ("tdnn7_bn" if not params.last_layer_no_bn else "tdnn7_dense")
+    return endpoints[last], endpoints

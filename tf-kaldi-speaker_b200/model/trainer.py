@@ -1,0 +1,153 @@
+"""Trainer: the reference's predict/extract driver (model/trainer.py:87-219, 270-338, 379-405, 886-913) with the
+TF session replaced by one xv_ctx.  Signatures are kept; the body is a ctypes call into libxvector.so."""
+import os
+import re
+import sys
+
+import numpy as np
+
+from ..engine import Engine
+from .tdnn import tdnn  # noqa: F401  (kept importable from here like the reference)
+
+_NETWORKS = ("tdnn",)
+_KNOWN_NETWORKS = ("tdnn", "tdnn-s", "extended_tdnn", "resnet_18")
+_KNOWN_LOSSES = ("softmax", "asoftmax", "additive_margin_softmax", "additive_angular_margin_softmax",
+                 "semihard_triplet_loss", "angular_triplet_loss", "generalized_angular_triplet_loss")
+
+
+class Trainer(object):
+    """Handles network building, weight loading and prediction (the extraction half of the reference class)."""
+
+    def __init__(self, params, model_dir, dim, num_speakers=None, single_cpu=False, num_gpus=1,
+                 precision="bf16", device=0, batch_frames=None):
+        """Same leading arguments as the reference (model/trainer.py:87).  `single_cpu`/`num_gpus` are accepted
+        for call-site compatibility (extract.py:56 passes single_cpu=True) and ignored: the path runs on one B200
+        (`device`).  `precision` is 'bf16' (tcgen05 path) or 'fp32' (validation mode)."""
+        self.network_type = params.network_type
+        if params.network_type not in _KNOWN_NETWORKS:
+            raise NotImplementedError("Not implement %s network" % params.network_type)
+        if params.network_type not in _NETWORKS:
+            raise NotImplementedError("Not implement %s network (this build covers: %s)" %
+                                      (params.network_type, ", ".join(_NETWORKS)))
+        self.loss_func = params.dict.get("loss_func", "softmax")
+        if self.loss_func not in _KNOWN_LOSSES:
+            raise NotImplementedError("Not implement %s loss" % self.loss_func)
+        self.params = params
+        self.model = os.path.join(model_dir, "nnet")
+        self.dim = dim
+        self.num_speakers = num_speakers
+        self.precision = precision
+        self.device = device
+        self.batch_frames = batch_frames
+        self.is_built = False
+        self.is_loaded = False
+        self.first_feature_split_alert = True
+        self.engine = None
+        self.embeddings = None
+        self.endpoints = None
+        self._weights = None
+
+    def reset(self):
+        """model/trainer.py:248-268: drop the graph."""
+        self.close()
+        self.is_built = False
+        self.is_loaded = False
+
+    def close(self):
+        """model/trainer.py:270-275."""
+        if self.engine is not None:
+            self.engine.close()
+            self.engine = None
+
+    def build(self, mode, noupdate_var_list=None):
+        """model/trainer.py:309-338.  Only mode == "predict" is implemented in this build."""
+        assert (mode == "train" or mode == "valid" or mode == "predict")
+        if mode != "predict":
+            raise NotImplementedError("build(%r): the training/validation graph is outside this build's scope" % mode)
+        if self.engine is None:
+            self.engine = Engine(self.params.dict, self.dim, precision=self.precision, device=self.device,
+                                 batch_frames=self.batch_frames)
+        self.embeddings = self.params.embedding_node
+        self.is_built = True
+        self.is_loaded = False
+        if self._weights is not None:
+            self.set_weights(self._weights)
+
+    def set_embedding(self, embedding_node):
+        """model/trainer.py:305-307."""
+        self.params.embedding_node = embedding_node
+        self.embeddings = embedding_node
+
+    def set_weights(self, weights):
+        """Inject variables ({TF variable name: array}) instead of reading <model_dir>/nnet/weights.npz."""
+        self._weights = weights
+        if self.engine is not None:
+            self.engine.set_weights(weights)
+            self.is_loaded = True
+
+    def load(self):
+        """model/trainer.py:277-295.  Reads <model_dir>/nnet/weights.npz (variables keyed by TF name); returns the
+        step parsed from the TF `checkpoint` state file when one is present, else 0."""
+        if not self.is_built:
+            sys.exit("The graph has not been build. Cannot load the models.")
+        path = os.path.join(self.model, "weights.npz")
+        if not os.path.isfile(path):
+            sys.exit("Failed to find a checkpoint in {}".format(self.model))
+        with np.load(path) as z:
+            weights = {k: z[k] for k in z.files}
+        self.set_weights(weights)
+        step = 0
+        ckpt = os.path.join(self.model, "checkpoint")
+        if os.path.isfile(ckpt):
+            with open(ckpt) as f:
+                m = re.search(r'model_checkpoint_path:\s*"([^"]+)"', f.read())
+            if m:
+                digits = list(re.finditer(r"(\d+)(?!.*\d)", os.path.basename(m.group(1))))
+                if digits:
+                    step = int(digits[0].group(0))
+        self.is_loaded = True
+        return step
+
+    def predict(self, features):
+        """Output the embeddings (model/trainer.py:886-913): rank-2 [T, D] -> [E]; rank-3 [B, T, D] -> [B, E];
+        frame-level nodes give [T', N] / [B, T', N].  Features wider than `dim` are sliced."""
+        if not self.is_loaded:
+            if os.path.isfile(os.path.join(self.model, "weights.npz")):
+                self.load()
+            else:
+                sys.exit("Cannot find model in %s" % self.model)
+        features = np.asarray(features)
+        rank = len(features.shape)
+        assert (rank == 2 or rank == 3)
+        if rank == 2:
+            features = np.expand_dims(features, axis=0)
+        if self.first_feature_split_alert and features.shape[-1] != self.dim:
+            self.first_feature_split_alert = False
+        if features.shape[-1] != self.dim:
+            features = features[:, :, :self.dim]
+        b, t, d = features.shape
+        packed = np.ascontiguousarray(features, dtype=np.float32).reshape(b * t, d)
+        lengths = np.full(b, t, np.int32)
+        embeddings = self._run(packed, lengths)
+        if rank == 2:
+            embeddings = np.squeeze(embeddings, axis=0)
+        return embeddings
+
+    def _run(self, packed, lengths):
+        node = self.params.embedding_node
+        _, frame_level, _ = self.engine.node_info(node)
+        if frame_level:
+            return np.stack(self.engine.forward_frames(packed, lengths, node), axis=0)
+        return self.engine.forward(packed, lengths, node)
+
+    def predict_ragged(self, features_list):
+        """Extension of predict(): a list of [T_u, D] utterances of different lengths in ONE packed call.
+        Row u of the result equals predict(features_list[u]) (each utterance is computed as a batch of one)."""
+        if not self.is_loaded:
+            if os.path.isfile(os.path.join(self.model, "weights.npz")):
+                self.load()
+            else:
+                sys.exit("Cannot find model in %s" % self.model)
+        lengths = np.array([f.shape[0] for f in features_list], np.int32)
+        packed = np.concatenate([np.asarray(f, np.float32)[:, :self.dim] for f in features_list], axis=0)
+        return self.engine.forward(packed, lengths, self.params.embedding_node)

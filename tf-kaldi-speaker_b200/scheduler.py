@@ -1,0 +1,43 @@
+"""Host-side scheduling for extraction: chunk planning (extract.py:68-78) and sharding of utterances across GPUs.
+
+Utterances are packed back to back (no padding), so length bucketing is not needed for efficiency inside one GPU;
+across GPUs the work is balanced by longest-processing-time-first on the algorithmic FLOPs of each utterance.
+There is no collective on this path: every rank extracts its own shard."""
+import math
+
+import numpy as np
+
+
+def chunk_plan(length, chunk_size):
+    """[(start, size), ...] for an utterance longer than chunk_size (extract.py:68-78, Python-2 integer
+    division for chunk_size / 2)."""
+    half = chunk_size // 2
+    num_chunks = int(math.ceil(float(length - chunk_size) / half)) + 1
+    plan = []
+    for i in range(num_chunks):
+        start = i * half
+        size = chunk_size if length - start > chunk_size else length - start
+        plan.append((start, size))
+    return plan
+
+
+def utterance_flops(t, d, pool_nodes=1500):
+    """Algorithmic FLOPs up to tdnn6_dense."""
+    t = np.asarray(t, np.float64)
+    return (2 * 512 * (5 * d * (t - 4) + 2560 * (t - 8) + 3584 * (t - 14) + 512 * (t - 14))
+            + 2 * 512 * pool_nodes * (t - 14) + 2 * (2 * pool_nodes) * 512)
+
+
+def shard_lpt(lengths, world_size, dim=30):
+    """Longest-processing-time-first partition.  Returns a list (per rank) of utterance index arrays; within a
+    rank utterances are ordered by decreasing length (a deterministic length bucketing)."""
+    lengths = np.asarray(lengths)
+    cost = utterance_flops(lengths, dim)
+    order = np.argsort(-cost, kind="stable")
+    loads = np.zeros(world_size)
+    shards = [[] for _ in range(world_size)]
+    for i in order:
+        r = int(np.argmin(loads))
+        shards[r].append(int(i))
+        loads[r] += cost[i]
+    return [np.asarray(s, dtype=np.int64) for s in shards]
