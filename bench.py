@@ -1,0 +1,340 @@
+#!/usr/bin/env python
+"""bench.py -- x-vector extraction throughput (frames/s) of the B200-native hot path.
+
+  python bench.py --gpus 1 --steps 10 --warmup 3              (N=1)
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+         bench.py --gpus N --steps K --warmup W               (N>1, one rank per GPU)
+  python bench.py --impl reference ...                        (CPU restatement of the reference graph)
+
+Workload (BASELINE.json configs[1]): the standard x-vector TDNN (5x512 frame layers, 1500-dim pre-pool,
+statistics pooling, 512-dim tdnn6_dense embedding) on synthetic 30-dim MFCC utterances of log-uniform length
+200..6000 frames, 4096 utterances per GPU (weak scaling: a global list of 4096*N utterances is LPT-sharded over
+the N ranks; no collective on the data path).  A "step" = one pass of the hot path over the rank's shard.
+
+Printed JSON line (rank 0): `value` = whole-job input frames/s with features resident in HBM, timed with CUDA
+events on the library's stream, max over ranks; `e2e` = same metric through the public C-ABI call xv_forward from
+pinned HOST memory (H2D of features and D2H of embeddings inside the timed region); `roofline` = the tcgen05 GEMM
+family (algorithmic FLOPs / summed GEMM launch durations, events around every launch) against the measured bf16
+peak; `cpu_baseline` = the fp32 torch-CPU restatement run the way the reference deploys extraction.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+UTTS_PER_GPU = 4096
+DIM = 30
+METRIC = "xvector_extraction_frames_per_sec"
+UNIT = "frames/s"
+
+
+def read_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(path):
+        with open(path) as f:
+            p = json.load(f)
+        return {"bf16_burst": p["bf16_tflops"], "bf16_sustained": p.get("bf16_tflops_sustained", p["bf16_tflops"]),
+                "hbm": p["hbm_gbs"], "source": "measured"}
+    return {"bf16_burst": 1590.0, "bf16_sustained": 1400.0, "hbm": 6650.0, "source": "fallback"}
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi SM clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.rows = []
+        self.stop_flag = False
+        self.proc = None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                if self.stop_flag:
+                    break
+                self.rows.append([c.strip() for c in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self):
+        self.stop_flag = True
+        if self.proc is not None:
+            try:
+                self.proc.terminate()
+            except Exception:
+                pass
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except (ValueError, IndexError):
+                continue
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        busy = sorted(sm)[len(sm) // 2:]                     # the upper half = samples taken under load
+        return {"sm_mhz": float(np.median(busy)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def make_shard(rank, world):
+    from oracle import synth                                   # input generators only (no path computation)
+    from xvector_b200 import scheduler
+    lengths = synth.config2_lengths(UTTS_PER_GPU * world, seed=202)
+    mine = scheduler.shard_lpt(lengths, world, DIM)[rank]
+    my_len = lengths[mine].astype(np.int32)
+    return my_len
+
+
+def gemm_flops(lengths):
+    """Algorithmic FLOPs of the GEMM layers per step (unpadded shapes, 2 FLOPs/MAC)."""
+    from xvector_b200.scheduler import utterance_flops
+    return float(utterance_flops(lengths, DIM).sum())
+
+
+def run_ours(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import xvector_b200
+    from oracle import synth
+
+    lengths = make_shard(rank, world)
+    n_frames = int(lengths.sum())
+    cfg = dict(synth.TDNN_STAT_CONFIG)
+    weights = synth.make_tdnn_weights(DIM, cfg, seed=1234)
+    eng = xvector_b200.Engine(cfg, DIM, precision="bf16", device=local, batch_frames=args.batch_frames)
+    eng.set_weights(weights)
+    pin = xvector_b200.PinnedArray((n_frames, DIM))
+    rng = np.random.default_rng(1000 + rank)
+    scale = np.linspace(3.0, 0.5, DIM).astype(np.float32)
+    blk = 1 << 20
+    for s in range(0, n_frames, blk):                          # fill in blocks: avoids a second 0.8 GB temporary
+        e = min(n_frames, s + blk)
+        pin.array[s:e] = rng.standard_normal((e - s, DIM), dtype=np.float32) * scale
+    feats = pin.array
+
+    def barrier():
+        eng.sync()
+        if dist is not None:
+            import torch
+            torch.cuda.synchronize()
+            dist.barrier()
+
+    def max_over_ranks(v):
+        if dist is None:
+            return v
+        import torch
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(v):
+        if dist is None:
+            return v
+        import torch
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    # ---------------- device-resident timing (headline `value`) ----------------
+    eng.stage(feats, lengths)
+    for _ in range(args.warmup):
+        eng.run()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches0 = eng.launch_count()
+    eng.event_record(0)
+    for _ in range(args.steps):
+        eng.run()
+    eng.event_record(1)
+    eng.sync()
+    ms_dev = eng.elapsed_ms(0, 1)
+    launches = eng.launch_count() - launches0
+    barrier()
+    sampler.stop()
+    emb = eng.fetch()
+    assert np.isfinite(emb).all()
+    ms_dev = max_over_ranks(ms_dev)
+    total_frames = sum_over_ranks(float(n_frames))
+    total_launches = int(sum_over_ranks(float(launches)))
+    value = total_frames * args.steps / (ms_dev * 1e-3)
+
+    # ---------------- per-kernel-family device time (roofline) ----------------
+    eng.profile_enable(True)
+    prof_steps = max(1, min(3, args.steps))
+    for _ in range(prof_steps):
+        eng.run()
+    eng.sync()
+    fam = {}
+    for name in sorted(eng.launch_summary()):
+        ms, cnt = eng.profile_query(name)
+        if cnt:
+            fam[name] = {"ms_per_step": ms / prof_steps, "launches_per_step": cnt / prof_steps}
+    eng.profile_enable(False)
+    gemm_ms = sum(v["ms_per_step"] for k, v in fam.items() if k.startswith("gemm"))
+    gemm_launches = sum(v["launches_per_step"] for k, v in fam.items() if k.startswith("gemm"))
+    # per-layer tensor-pipe fraction (algorithmic FLOPs of that layer / its summed launch time)
+    t = lengths.astype(np.float64)
+    layer_flops = {"tdnn1": 2 * 512 * 5 * DIM * (t - 4), "tdnn2": 2 * 512 * 2560 * (t - 8), "tdnn3": 2 * 512 * 3584 * (t - 14),
+                   "tdnn4": 2 * 512 * 512 * (t - 14), "tdnn5": 2 * 512 * 1500 * (t - 14), "tdnn6": 2 * 3000 * 512 + 0 * t}
+    for k, v in fam.items():
+        lname = k.split(".")[-1]
+        if k.startswith("gemm") and lname in layer_flops and v["ms_per_step"] > 0:
+            v["tflops"] = float(layer_flops[lname].sum()) / (v["ms_per_step"] * 1e-3) / 1e12
+    flops = gemm_flops(lengths)
+    peaks = read_peaks()
+    achieved = flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
+    roofline = {
+        "kernel": "xv_tdnn_gemm_kernel (tcgen05 spliced GEMM + fused epilogue), all 6 layer launches of a step",
+        "bound": "tensor", "achieved": achieved, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
+        "frac": achieved / peaks["bf16_sustained"], "peak_kind": "sustained bf16, %s" % peaks["source"],
+        "frac_of_burst": achieved / peaks["bf16_burst"],
+        "algorithmic_flops_per_step": flops, "launches_per_step": gemm_launches,
+        "avg_launch_ms": gemm_ms / gemm_launches if gemm_launches else None,
+        "gemm_share_of_step": gemm_ms / (ms_dev / args.steps) if world == 1 else None,
+        "traffic": None,
+    }
+
+    # ---------------- end to end through the public C-ABI call (host buffers) ----------------
+    e2e_steps = max(1, min(args.steps, 5))
+    out = None
+    for _ in range(2):
+        out = eng.forward(feats, lengths)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        out = eng.forward(feats, lengths)                        # H2D (pinned) + kernels + D2H + sync inside
+    t1 = time.perf_counter()
+    barrier()
+    e2e_s = max_over_ranks(t1 - t0)
+    e2e_value = total_frames * e2e_steps / e2e_s
+    assert np.isfinite(out).all()
+
+    # ---------------- CPU baseline (rank 0, N=1 only) ----------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline(args.cpu_seconds)
+
+    if rank == 0:
+        clocks = sampler.summary()
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic",
+            "config": {
+                "workload": "configs[1]: standard x-vector TDNN (5x512 frame layers, 1500 pre-pool, stats pooling, "
+                            "tdnn6_dense 512-d) on 30-dim MFCC utterances of log-uniform length 200-6000 frames",
+                "utts_per_gpu": UTTS_PER_GPU, "frames_rank0": n_frames, "feature_dim": DIM, "node": "tdnn6_dense",
+                "batch_frames": args.batch_frames, "weights": "random init, seed 1234",
+                "parallelism": "utterance shards (LPT by FLOPs) over %d GPU(s), no collective" % world,
+                "l2_policy": "inputs larger than L2 (%.2f GB fp32 features per GPU vs 126 MB L2)" % (n_frames * DIM * 4 / 1e9),
+            },
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(n_frames * DIM * 4 + lengths.nbytes),
+                    "d2h_bytes_per_step": int(len(lengths) * 512 * 4), "steps": e2e_steps,
+                    "api": "xv_forward (pinned host features -> host embeddings)"},
+            "gpu_launches": total_launches,
+            "clocks": clocks,
+            "roofline": roofline,
+            "kernel_families_ms_per_step": fam,
+        }
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    pin.close()
+    eng.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def cpu_baseline(seconds):
+    """fp32 torch-CPU restatement (oracle/torch_ref.py), P single-thread processes, one utterance per call."""
+    from oracle import synth, torch_ref
+    cores = os.cpu_count() or 1
+    lengths = synth.config2_lengths(UTTS_PER_GPU, seed=202)
+    take = np.random.default_rng(0).permutation(len(lengths))[:max(4 * cores, 64)]
+    sub = lengths[take].astype(np.int32)
+    feats = synth.packed_features(sub, DIM, seed=202)
+    cfg = dict(synth.TDNN_STAT_CONFIG)
+    w = synth.make_tdnn_weights(DIM, cfg, seed=1234)
+    r = torch_ref.time_cpu_extraction(w, cfg, feats, sub, processes=cores, budget_s=seconds)
+    import torch
+    return {"value": r["frames_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+            "sample": "%d utterances (%d frames) drawn from the configs[1] length distribution, %.0f s budget per process, "
+                      "%d single-thread processes, one utterance per call; torch %s fp32 CPU restatement of the reference "
+                      "graph (reference TF unavailable on this box)" % (r["utts"], r["frames"], seconds, r["cores"],
+                                                                          torch.__version__)}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU extraction path (its TF code cannot run here; the fp32 torch-CPU
+    restatement stands in), all host cores, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return
+    per_step = max(2.0, min(args.cpu_seconds, 60.0 / max(1, args.steps + args.warmup)))
+    vals = []
+    cpu = None
+    for i in range(args.warmup + args.steps):
+        cpu = cpu_baseline(per_step)
+        if i >= args.warmup:
+            vals.append(cpu["value"])
+    v = float(np.mean(vals))
+    cpu["value"] = v
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": per_step * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "configs[1] length distribution, bounded sample per step (see cpu_baseline.sample)"},
+            "cpu_baseline": cpu,
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch-frames", type=int, default=65536)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

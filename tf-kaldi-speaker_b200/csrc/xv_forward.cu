@@ -119,7 +119,8 @@ static int gemm_layer(xv_ctx* c, const Layer& l, const void* a_base, int64_t a_r
   p.heads = 1;
   p.head_width = l.n_alloc;
   g.pool = pool;
-  ProfScope ps(c, pool ? "gemm_pool" : "gemm");
+  const std::string fam = std::string(pool ? "gemm_pool." : "gemm.") + l.name;
+  ProfScope ps(c, fam.c_str());
   cudaError_t e = launch_gemm(g, c->sm_count, c->stream);
   if (e != cudaSuccess) return cuda_fail(c, e, "tcgen05 GEMM launch");
   return XV_OK;
