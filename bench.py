@@ -97,10 +97,10 @@ class ClockSampler(threading.Thread):
                 "samples": len(sm)}
 
 
-def make_shard(rank, world):
+def make_shard(rank, world, utts_per_gpu=None):
     from oracle import synth                                   # input generators only (no path computation)
     from xvector_b200 import scheduler
-    lengths = synth.config2_lengths(UTTS_PER_GPU * world, seed=202)
+    lengths = synth.config2_lengths((utts_per_gpu or UTTS_PER_GPU) * world, seed=202)
     mine = scheduler.shard_lpt(lengths, world, DIM)[rank]
     my_len = lengths[mine].astype(np.int32)
     return my_len
@@ -125,7 +125,7 @@ def run_ours(args):
     import xvector_b200
     from oracle import synth
 
-    lengths = make_shard(rank, world)
+    lengths = make_shard(rank, world, args.utts)
     n_frames = int(lengths.sum())
     cfg = dict(synth.TDNN_STAT_CONFIG)
     weights = synth.make_tdnn_weights(DIM, cfg, seed=1234)
@@ -252,7 +252,7 @@ def run_ours(args):
             "config": {
                 "workload": "configs[1]: standard x-vector TDNN (5x512 frame layers, 1500 pre-pool, stats pooling, "
                             "tdnn6_dense 512-d) on 30-dim MFCC utterances of log-uniform length 200-6000 frames",
-                "utts_per_gpu": UTTS_PER_GPU, "frames_rank0": n_frames, "feature_dim": DIM, "node": "tdnn6_dense",
+                "utts_per_gpu": args.utts, "frames_rank0": n_frames, "feature_dim": DIM, "node": "tdnn6_dense",
                 "batch_frames": args.batch_frames, "weights": "random init, seed 1234",
                 "parallelism": "utterance shards (LPT by FLOPs) over %d GPU(s), no collective" % world,
                 "l2_policy": "inputs larger than L2 (%.2f GB fp32 features per GPU vs 126 MB L2)" % (n_frames * DIM * 4 / 1e9),
@@ -327,6 +327,8 @@ def main():
     ap.add_argument("--batch-frames", type=int, default=65536)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--utts", type=int, default=UTTS_PER_GPU, help="utterances per GPU (default = the configs[1] set; "
+                    "smaller values are for profiling runs only)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
