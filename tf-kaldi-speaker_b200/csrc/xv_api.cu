@@ -402,6 +402,8 @@ static int finalize_layer(xv_ctx* c, Layer& l) {
   if (l.has_bn && (rc = fold_bn(c, l.bn_scope, l.cout, &s, &h)) != XV_OK) return rc;
   std::vector<float> slope;
   if ((rc = act_slopes(c, l, l.cout, l.alpha_var, &slope)) != XV_OK) return rc;
+  l.plain_relu = l.act == kActRelu;
+  for (float s0 : slope) l.plain_relu = l.plain_relu && s0 == 0.f;
 
   // validation-path parameters (fp32, unpadded)
   if ((rc = upload(c, &l.w32, k->data.data(), sizeof(float) * K * l.cout)) != XV_OK) return rc;

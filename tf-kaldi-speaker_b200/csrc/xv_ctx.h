@@ -36,6 +36,7 @@ struct Layer {
   std::string name;          // "tdnn1" ... "att_key0"
   std::string kernel_var, bias_var, bn_scope, alpha_var;
   bool has_bn = false;
+  bool plain_relu = false;   // activation is max(x, 0) on every channel (fast epilogue path)
   int act = kActNone;
   int taps = 1, dil = 1, cin = 0, cout = 0;
   int in_buf = -1;           // index of the frame buffer this layer reads (-1: the features)

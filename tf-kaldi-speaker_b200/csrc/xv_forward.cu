@@ -90,11 +90,15 @@ int plan_job(xv_ctx* c, const int32_t* lengths, int32_t n_utts) {
 
 // ---- one tcgen05 layer launch -------------------------------------------------------------------
 static int gemm_layer(xv_ctx* c, const Layer& l, const void* a_base, int64_t a_rows_alloc, int stage,
-                      __nv_bfloat16* out_bf16, float* out_f32, int64_t m_rows, bool pool, float* pool_acc,
+                      __nv_bfloat16* out_bf16, float* out_f32, int64_t m_rows, bool pool, double* pool_acc,
                       const int32_t* tile_seg, const PoolSeg* segs) {
+  if (m_rows <= 0) return XV_OK;
   GemmPlan g;
   const char* err = make_tmap_bf16_2d(&g.tm_a, a_base, l.a_cin, a_rows_alloc, static_cast<uint64_t>(l.a_cin) * 2, kBK, kBM);
+  if (!err && out_bf16 != nullptr)
+    err = make_tmap_bf16_2d(&g.tm_out, out_bf16, l.n_alloc, m_rows, static_cast<uint64_t>(l.n_alloc) * 2, 32, 32, 64);
   if (err) return fail(c, XV_ECUDA, "%s", err);
+  if (out_bf16 == nullptr) g.tm_out = g.tm_a;   // never dereferenced
   g.tm_b = l.tm_b;
   GemmParams& p = g.p;
   p.m_rows = static_cast<int32_t>(m_rows);
@@ -108,6 +112,7 @@ static int gemm_layer(xv_ctx* c, const Layer& l, const void* a_base, int64_t a_r
   p.shift = static_cast<const float*>(l.f_shift[stage].p);
   p.slope = static_cast<const float*>(l.f_slope[stage].p);
   p.act_tanh = (l.act == kActTanh && stage == kStageAct) ? 1 : 0;
+  p.relu_only = (stage == kStageAct && l.plain_relu) ? 1 : 0;
   p.out_bf16 = out_bf16;
   p.out_f32 = out_f32;
   p.ldo = l.n_alloc;
@@ -232,7 +237,7 @@ int run_job(xv_ctx* c, const char* node_name, bool pipelined_h2d, float* frames_
     if ((rc = ensure(c, &c->seg_out[1], static_cast<size_t>(n_alloc_rows) * l7.n_alloc * 4)) != XV_OK) return rc;
     if ((rc = ensure(c, &c->seg_out_bf16, static_cast<size_t>(n_alloc_rows) * l7.kpad * 2, true)) != XV_OK) return rc;
     if (fuse_pool) {
-      const size_t bytes = static_cast<size_t>(std::max(n, 1)) * 2 * c->frame_layers[pool_layer].n_alloc * 4;
+      const size_t bytes = static_cast<size_t>(std::max(n, 1)) * 2 * c->frame_layers[pool_layer].n_alloc * sizeof(double);
       if ((rc = ensure(c, &c->pool_acc, bytes)) != XV_OK) return rc;
       cudaError_t e = cudaMemsetAsync(c->pool_acc.p, 0, bytes, c->stream);
       if (e != cudaSuccess) return cuda_fail(c, e, "cudaMemsetAsync(pool_acc)");
@@ -300,7 +305,7 @@ int run_job(xv_ctx* c, const char* node_name, bool pipelined_h2d, float* frames_
       if (c->bf16) {
         const void* a = L.in_buf < 0 ? c->a1.p : c->frame_out[L.in_buf].p;
         rc = gemm_layer(c, L, a, rows_alloc, stage_of[l], pool_here ? nullptr : static_cast<__nv_bfloat16*>(c->frame_out[l].p),
-                        nullptr, b.rows, pool_here, static_cast<float*>(c->pool_acc.p),
+                        nullptr, b.rows, pool_here, static_cast<double*>(c->pool_acc.p),
                         static_cast<const int32_t*>(c->d_tile_seg_ptr.p) + 2 * b.tile0, static_cast<const PoolSeg*>(c->d_segs.p));
       } else {
         const float* a = L.in_buf < 0 ? feats_b : static_cast<const float*>(c->frame_out[L.in_buf].p);
@@ -413,7 +418,7 @@ int run_job(xv_ctx* c, const char* node_name, bool pipelined_h2d, float* frames_
   if (fuse_pool) {
     const Layer& P = c->frame_layers[pool_layer];
     count_launch(c, "pool_finalize");
-    e = launch_pool_finalize(static_cast<const float*>(c->pool_acc.p), P.n_alloc, d_cu_global, c->total_context, n, P.cout,
+    e = launch_pool_finalize(static_cast<const double*>(c->pool_acc.p), P.n_alloc, d_cu_global, c->total_context, n, P.cout,
                              static_cast<float*>(c->pooled_f32.p), c->pooled_dim, static_cast<__nv_bfloat16*>(c->pooled_bf16.p),
                              l6.kpad, 0, c->stream);
     if (e != cudaSuccess) return cuda_fail(c, e, "pool finalize launch");

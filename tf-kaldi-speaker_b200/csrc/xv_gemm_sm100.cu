@@ -15,11 +15,14 @@
 // Rows past the end of the buffer are zero-filled by TMA.  Rows whose window straddles an utterance
 // boundary are computed but never consumed by valid rows (every layer is VALID) nor by pooling.
 //
-// Warp roles (192 threads, 1 CTA/SM, persistent over tiles):
-//   warp 0 : TMA producer (one lane)          -- fills the 4-stage smem ring (A 16 KB + B 32 KB per stage)
-//   warp 1 : TMEM allocator + MMA issuer      -- 4 x tcgen05.mma (128x256x16) per stage, commit -> mbarrier
-//   warps 2-5 : epilogue                      -- tcgen05.ld 32 lanes x 32 columns, affine+act, store/pool
-// TMEM holds two 128x256 fp32 accumulators so the epilogue of tile i overlaps the MMAs of tile i+1.
+// Warp roles (320 threads, 1 CTA/SM, persistent over tiles):
+//   warp 0    : TMA producer (one lane)        -- fills the 4-stage smem ring (A 16 KB + B 32 KB per stage)
+//   warp 1    : TMEM allocator + MMA issuer    -- 4 x tcgen05.mma (128x256x16) per stage, commit -> mbarrier
+//   warps 2-9 : epilogue, 2 warps per TMEM lane quarter (each takes 128 of the tile's 256 columns):
+//               tcgen05.ld 32 lanes x 32 columns -> affine + activation -> bf16 tile staged in 64B-swizzled
+//               smem -> TMA store (full-line writes), or fp32 direct store, or pooling partial sums.
+// TMEM holds two 128x256 fp32 accumulators so the epilogue of tile i overlaps the MMAs of tile i+1; the
+// accumulator is handed back to the MMA warp as soon as the last tcgen05.ld of the tile has completed.
 #include <stdio.h>
 
 #include "xv_internal.h"
@@ -29,32 +32,40 @@ namespace xv {
 
 namespace {
 
+constexpr int kEpiWarps = 8;
 constexpr uint32_t kABytes = kBM * kBK * 2;                  // 16384
 constexpr uint32_t kBBytes = kBN * kBK * 2;                  // 32768
 constexpr uint32_t kStageBytes = kABytes + kBBytes;          // 49152
 constexpr uint32_t kRingBytes = kStages * kStageBytes;       // 196608
-constexpr uint32_t kEpiParamBytes = kAccStages * kBN * 12;   // (scale,shift) float2 + slope float
-constexpr uint32_t kTransposeBytes = 4 * 32 * 33 * 4;        // per-epilogue-warp 32x33 fp32 (pooling only)
+constexpr uint32_t kEpiParamBytes = kAccStages * kBN * 12;   // (scale,shift) float2 + slope float = 6144
+constexpr uint32_t kStoreStageBytes = 32 * 64;               // per warp: 32 rows x 32 bf16, SWIZZLE_64B
+constexpr uint32_t kTrFloats = 32 * 17;                      // per warp: 32 rows x 16 columns (+1 pad) fp32
+constexpr uint32_t kEpiScratchBytes = kEpiWarps * (kTrFloats * 4 > kStoreStageBytes ? kTrFloats * 4 : kStoreStageBytes);
 constexpr uint32_t kBarrierBytes = 256;
 constexpr uint32_t kTmemCols = 512;
+constexpr uint32_t kSmemBytes = 1024 /*alignment slack (normally unused: the array is declared __align__(1024))*/ + kRingBytes + kEpiParamBytes + kEpiScratchBytes + kBarrierBytes;
+static_assert(kSmemBytes <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
+static_assert((kRingBytes + kEpiParamBytes) % 1024 == 0, "store staging must stay 1024-byte aligned");
 
-__host__ __device__ constexpr uint32_t gemm_smem_bytes(bool pool) {
-  return 1024 /*alignment slack*/ + kRingBytes + kEpiParamBytes + (pool ? kTransposeBytes : 0) + kBarrierBytes;
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
 }
 
 template <bool kPool>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
-                    const GemmParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  // 128-byte swizzle atoms need 1024-byte aligned stage buffers.
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+                    const __grid_constant__ CUtensorMap tm_out, const GemmParams p) {
+  // 128-byte swizzle atoms need 1024-byte aligned stage buffers.  The pad is added as an OFFSET to the
+  // __shared__ symbol (not via an integer round trip) so the compiler keeps the shared address space and emits
+  // LDS/STS rather than generic loads in the epilogue.
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* ring = smem;
   float2* ep_ss = reinterpret_cast<float2*>(smem + kRingBytes);                       // [2][256] scale,shift
   float* ep_sl = reinterpret_cast<float*>(smem + kRingBytes + kAccStages * kBN * 8);  // [2][256] slope
-  float* tr_base = reinterpret_cast<float*>(smem + kRingBytes + kEpiParamBytes);      // [4][32*33]
-  uint64_t* bars =
-      reinterpret_cast<uint64_t*>(smem + kRingBytes + kEpiParamBytes + (kPool ? kTransposeBytes : 0));
+  uint8_t* scratch = smem + kRingBytes + kEpiParamBytes;                              // per-warp staging / transpose
+  uint64_t* bars = reinterpret_cast<uint64_t*>(scratch + kEpiScratchBytes);
   uint64_t* full_bar = bars;                       // [kStages]   TMA -> MMA
   uint64_t* empty_bar = bars + kStages;            // [kStages]   MMA -> TMA
   uint64_t* tfull_bar = bars + 2 * kStages;        // [kAccStages] MMA -> epilogue
@@ -67,13 +78,14 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&tm_a);
     ptx::prefetch_tensormap(&tm_b);
+    if (!kPool && p.out_bf16 != nullptr) ptx::prefetch_tensormap(&tm_out);
     for (int s = 0; s < kStages; ++s) {
       ptx::mbar_init(&full_bar[s], 1);
       ptx::mbar_init(&empty_bar[s], 1);
     }
     for (int s = 0; s < kAccStages; ++s) {
       ptx::mbar_init(&tfull_bar[s], 1);
-      ptx::mbar_init(&tempty_bar[s], 4);   // one arrive per epilogue warp
+      ptx::mbar_init(&tempty_bar[s], kEpiWarps);   // one arrive per epilogue warp
     }
     ptx::fence_mbar_init();
   }
@@ -138,10 +150,15 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       }
     }
   } else {
-    // ===================== epilogue (warps 2..5) =====================
+    // ===================== epilogue (warps 2..9) =====================
+    const uint32_t e = warp - 2;                 // 0..7
     const uint32_t q = warp & 3;                 // TMEM lane quarter this warp may access
-    const uint32_t etid = threadIdx.x - 64;      // 0..127
-    float* tr = tr_base + q * (32 * 33);
+    const uint32_t half = e >> 2;                // which 128 of the tile's 256 columns
+    const uint32_t etid = threadIdx.x - 64;      // 0..255
+    uint8_t* stage_buf = scratch + e * kStoreStageBytes;                       // bf16 store staging (non-pool)
+    float* tr = reinterpret_cast<float*>(scratch) + e * kTrFloats;             // transpose buffer (pool)
+    const bool relu_only = p.relu_only != 0;
+    const bool store_bf16 = !kPool && p.out_bf16 != nullptr;
     uint32_t as = 0, aphase = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       const int mt = t / p.n_tiles;
@@ -150,103 +167,159 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       // per-tile epilogue parameters -> smem (double buffered by accumulator stage)
       float2* ss = ep_ss + as * kBN;
       float* sl = ep_sl + as * kBN;
-      for (int i = etid; i < kBN; i += 128) {
-        ss[i] = make_float2(__ldg(p.scale + n0 + i), __ldg(p.shift + n0 + i));
-        sl[i] = __ldg(p.slope + n0 + i);
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      ss[etid] = make_float2(__ldg(p.scale + n0 + etid), __ldg(p.shift + n0 + etid));
+      sl[etid] = __ldg(p.slope + n0 + etid);
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after();
 
       const int mw = m0 + q * 32;                // first row of this warp
       const int row = mw + lane;
       const bool row_ok = row < p.m_rows;
-      int seg_lo = 0, seg_hi = 0;
+      // segments (utterance valid-row ranges) that intersect this warp's 32 rows: [w_first, w_last]
+      int w_first = 0, w_last = -1;
+      bool w_full = false;
+      PoolSeg w_sg = {0, 0, 0, 0};
       if (kPool) {
-        seg_lo = __ldg(p.tile_seg_ptr + 2 * mt);       // [lo, hi) utterance range intersecting this tile
-        seg_hi = __ldg(p.tile_seg_ptr + 2 * mt + 1);
+        const int seg_lo = __ldg(p.tile_seg_ptr + 2 * mt);       // [lo, hi) utterance range intersecting this tile
+        const int seg_hi = __ldg(p.tile_seg_ptr + 2 * mt + 1);
+        for (int s = seg_lo; s < seg_hi; ++s) {
+          const PoolSeg sg = p.segs[s];
+          if (max(sg.r0, mw) < min(sg.r1, mw + 32)) {
+            if (w_last < w_first) { w_first = s; w_sg = sg; }
+            w_last = s;
+          }
+        }
+        w_full = w_first == w_last && w_sg.r0 <= mw && w_sg.r1 >= mw + 32 && p.row_weight == nullptr;
       }
 #pragma unroll 1
-      for (int c = 0; c < kBN / 32; ++c) {
+      for (int ci = 0; ci < 4; ++ci) {
+        const int c = half * 4 + ci;             // 32-column chunk of the tile
         uint32_t r[32];
         ptx::tmem_ld_32x32(tmem_base + ((q * 32) << 16) + as * kBN + c * 32, r);
         ptx::tmem_ld_wait();
+        if (ci == 3) {
+          // last TMEM read of this tile by this warp: hand the accumulator back to the MMA warp now
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
+        }
         float y[32];
+        const float4* ss4 = reinterpret_cast<const float4*>(ss + c * 32);
+        if (relu_only) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const float2 sh = ss[c * 32 + j];
-          float v = fmaf(__uint_as_float(r[j]), sh.x, sh.y);
-          v = v >= 0.f ? v : v * sl[c * 32 + j];
-          y[j] = v;
-        }
-        if (p.act_tanh) {
+          for (int j = 0; j < 16; ++j) {
+            const float4 sh = ss4[j];            // (scale, shift) of two columns in one broadcast LDS.128
+            y[2 * j] = fmaxf(fmaf(__uint_as_float(r[2 * j]), sh.x, sh.y), 0.f);
+            y[2 * j + 1] = fmaxf(fmaf(__uint_as_float(r[2 * j + 1]), sh.z, sh.w), 0.f);
+          }
+        } else {
+          const float2* sl2 = reinterpret_cast<const float2*>(sl + c * 32);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) y[j] = tanhf(y[j]);
-        }
-        if (p.out_bf16 != nullptr && row_ok) {
-          uint4* dst = reinterpret_cast<uint4*>(p.out_bf16 + static_cast<size_t>(row) * p.ldo + n0 + c * 32);
+          for (int j = 0; j < 16; ++j) {
+            const float4 sh = ss4[j];
+            const float2 ng = sl2[j];
+            float v0 = fmaf(__uint_as_float(r[2 * j]), sh.x, sh.y);
+            float v1 = fmaf(__uint_as_float(r[2 * j + 1]), sh.z, sh.w);
+            y[2 * j] = v0 >= 0.f ? v0 : v0 * ng.x;
+            y[2 * j + 1] = v1 >= 0.f ? v1 : v1 * ng.y;
+          }
+          if (p.act_tanh) {
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            __nv_bfloat162 b0 = __floats2bfloat162_rn(y[g * 8 + 0], y[g * 8 + 1]);
-            __nv_bfloat162 b1 = __floats2bfloat162_rn(y[g * 8 + 2], y[g * 8 + 3]);
-            __nv_bfloat162 b2 = __floats2bfloat162_rn(y[g * 8 + 4], y[g * 8 + 5]);
-            __nv_bfloat162 b3 = __floats2bfloat162_rn(y[g * 8 + 6], y[g * 8 + 7]);
-            uint4 v;
-            v.x = *reinterpret_cast<uint32_t*>(&b0);
-            v.y = *reinterpret_cast<uint32_t*>(&b1);
-            v.z = *reinterpret_cast<uint32_t*>(&b2);
-            v.w = *reinterpret_cast<uint32_t*>(&b3);
-            dst[g] = v;
+            for (int j = 0; j < 32; ++j) y[j] = tanhf(y[j]);
           }
         }
-        if (p.out_f32 != nullptr && row_ok) {
+        if (store_bf16) {
+          // stage this warp's 32 rows x 32 bf16 in the TMA SWIZZLE_64B layout (16-byte chunk index XOR
+          // ((row >> 1) & 3)): conflict-free 16-byte shared stores, then one TMA store writes full lines.
+          if (lane == 0) ptx::tma_store_wait_read<0>();        // previous store has finished reading the buffer
+          __syncwarp();
+          uint8_t* rowp = stage_buf + lane * 64;
+          const uint32_t sw = (lane >> 1) & 3;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            uint4 v;
+            v.x = pack_bf16(y[g * 8 + 0], y[g * 8 + 1]);
+            v.y = pack_bf16(y[g * 8 + 2], y[g * 8 + 3]);
+            v.z = pack_bf16(y[g * 8 + 4], y[g * 8 + 5]);
+            v.w = pack_bf16(y[g * 8 + 6], y[g * 8 + 7]);
+            *reinterpret_cast<uint4*>(rowp + ((g ^ sw) << 4)) = v;
+          }
+          ptx::fence_proxy_async_smem();                        // generic-proxy writes -> visible to the TMA engine
+          __syncwarp();
+          if (lane == 0) {
+            ptx::tma_store_2d(&tm_out, stage_buf, n0 + c * 32, mw);   // rows >= m_rows are clipped by the tensor map
+            ptx::tma_store_commit();
+          }
+        }
+        if (!kPool && p.out_f32 != nullptr && row_ok) {
           float4* dst = reinterpret_cast<float4*>(p.out_f32 + static_cast<size_t>(row) * p.ldo + n0 + c * 32);
 #pragma unroll
           for (int g = 0; g < 8; ++g) dst[g] = make_float4(y[g * 4], y[g * 4 + 1], y[g * 4 + 2], y[g * 4 + 3]);
         }
         if (kPool) {
-          // Transpose the warp's 32 rows x 32 columns through padded smem, then lane = column sums the
-          // valid rows of every utterance segment that intersects this warp's rows.
-          const int col = n0 + c * 32 + lane;
-          const int head = p.row_weight != nullptr ? col / p.head_width : 0;
+          // Column sums over the valid rows of every utterance segment intersecting this warp's 32 rows.
+          // 16 columns at a time through a [32][17] fp32 transpose buffer: lane (cl = lane & 15, rh = lane >> 4)
+          // sums column cl over row half rh (conflict-free both ways), halves are combined with one shuffle,
+          // lanes 0-15 add the sums and lanes 16-31 the sums of squares (fp64 atomics: order-independent to
+          // fp32 precision, and no cancellation noise in E[x^2] - mean^2).
+          const int cl = lane & 15, rh = lane >> 4;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) tr[lane * 33 + j] = y[j];
-          __syncwarp();
-          for (int s = seg_lo; s < seg_hi; ++s) {
-            const PoolSeg sg = p.segs[s];
-            const int lo = max(sg.r0, mw) - mw;
-            const int hi = min(sg.r1, mw + 32) - mw;
-            if (lo < hi) {
-              float s1 = 0.f, s2 = 0.f;
-              if (p.row_weight == nullptr) {
-                for (int rr = lo; rr < hi; ++rr) {
-                  const float v = tr[rr * 33 + lane];
-                  s1 += v;
-                  s2 = fmaf(v, v, s2);
-                }
-              } else {
-                const float* wrow = p.row_weight + static_cast<size_t>(min(head, p.heads - 1)) * p.m_rows + mw;
-                for (int rr = lo; rr < hi; ++rr) {
-                  const float v = tr[rr * 33 + lane];
-                  const float w = __ldg(wrow + rr);
-                  s1 = fmaf(w, v, s1);
-                  s2 = fmaf(w * v, v, s2);
-                }
+          for (int hc = 0; hc < 2; ++hc) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) tr[lane * 17 + j] = y[hc * 16 + j];
+            __syncwarp();
+            const int col = n0 + c * 32 + hc * 16 + cl;
+            const float* trc = tr + (rh * 16) * 17 + cl;
+            if (w_full) {
+              // common case: one utterance covers all 32 rows of this warp
+              float s1 = 0.f, s2 = 0.f, s1b = 0.f, s2b = 0.f;
+#pragma unroll
+              for (int i = 0; i < 16; i += 2) {
+                const float v0 = trc[i * 17], v1 = trc[(i + 1) * 17];
+                s1 += v0; s2 = fmaf(v0, v0, s2);
+                s1b += v1; s2b = fmaf(v1, v1, s2b);
               }
-              float* acc = p.pool_acc + static_cast<size_t>(sg.utt) * 2 * p.pool_ld + col;
-              atomicAdd(acc, s1);
-              atomicAdd(acc + p.pool_ld, s2);
+              s1 += s1b; s2 += s2b;
+              s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+              s2 += __shfl_xor_sync(0xffffffffu, s2, 16);
+              atomicAdd(p.pool_acc + (static_cast<size_t>(w_sg.utt) * 2 + rh) * p.pool_ld + col,
+                        static_cast<double>(rh ? s2 : s1));
+            } else {
+              for (int s = w_first; s <= w_last; ++s) {
+                const PoolSeg sg = s == w_first ? w_sg : p.segs[s];
+                const int lo = max(sg.r0, mw) - mw;
+                const int hi = min(sg.r1, mw + 32) - mw;
+                if (lo >= hi) continue;
+                const float* wrow = nullptr;
+                if (p.row_weight != nullptr) {
+                  const int head = min(col / p.head_width, p.heads - 1);
+                  wrow = p.row_weight + static_cast<size_t>(head) * p.m_rows + mw + rh * 16;
+                }
+                float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                  const int rr = rh * 16 + i;
+                  if (rr >= lo && rr < hi) {
+                    const float v = trc[i * 17];
+                    const float w = wrow ? __ldg(wrow + i) : 1.f;
+                    s1 = fmaf(w, v, s1);
+                    s2 = fmaf(w * v, v, s2);
+                  }
+                }
+                s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+                s2 += __shfl_xor_sync(0xffffffffu, s2, 16);
+                atomicAdd(p.pool_acc + (static_cast<size_t>(sg.utt) * 2 + rh) * p.pool_ld + col,
+                          static_cast<double>(rh ? s2 : s1));
+              }
             }
+            __syncwarp();
           }
-          __syncwarp();
         }
       }
-      // release the accumulator stage back to the MMA warp
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
       if (++as == kAccStages) { as = 0; aphase ^= 1; }
     }
+    if (store_bf16 && lane == 0) ptx::tma_store_wait<0>();      // all bulk stores of this warp have completed
   }
 
   ptx::tc_fence_before();
@@ -278,10 +351,9 @@ const char* gemm_init() {
     g_encode = reinterpret_cast<EncodeTiledFn>(fn);
   }
   cudaError_t e = cudaFuncSetAttribute(xv_tdnn_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       gemm_smem_bytes(false));
+                                       kSmemBytes);
   if (e == cudaSuccess)
-    e = cudaFuncSetAttribute(xv_tdnn_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             gemm_smem_bytes(true));
+    e = cudaFuncSetAttribute(xv_tdnn_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
   if (e != cudaSuccess) {
     snprintf(g_err, sizeof(g_err), "cudaFuncSetAttribute(max dynamic smem) failed: %s", cudaGetErrorString(e));
     return g_err;
@@ -290,14 +362,15 @@ const char* gemm_init() {
 }
 
 const char* make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t rows,
-                              uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_rows) {
+                              uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_rows, int swizzle_bytes) {
   if (g_encode == nullptr) return "gemm_init() not called";
   cuuint64_t dims[2] = {inner, rows};
   cuuint64_t strides[1] = {row_stride_bytes};
   cuuint32_t box[2] = {box_inner, box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     snprintf(g_err, sizeof(g_err),
@@ -314,9 +387,9 @@ cudaError_t launch_gemm(const GemmPlan& plan, int sm_count, cudaStream_t stream)
   if (tiles <= 0) return cudaSuccess;
   const int grid = tiles < sm_count ? tiles : sm_count;
   if (plan.pool) {
-    xv_tdnn_gemm_kernel<true><<<grid, kGemmThreads, gemm_smem_bytes(true), stream>>>(plan.tm_a, plan.tm_b, plan.p);
+    xv_tdnn_gemm_kernel<true><<<grid, kGemmThreads, kSmemBytes, stream>>>(plan.tm_a, plan.tm_b, plan.tm_out, plan.p);
   } else {
-    xv_tdnn_gemm_kernel<false><<<grid, kGemmThreads, gemm_smem_bytes(false), stream>>>(plan.tm_a, plan.tm_b, plan.p);
+    xv_tdnn_gemm_kernel<false><<<grid, kGemmThreads, kSmemBytes, stream>>>(plan.tm_a, plan.tm_b, plan.tm_out, plan.p);
   }
   return cudaGetLastError();
 }

@@ -14,7 +14,7 @@ constexpr int kBK = 64;         // K per pipeline stage = one 128-byte swizzle a
 constexpr int kUK = 16;         // UMMA K for 16-bit inputs
 constexpr int kStages = 4;      // TMA->MMA smem ring depth
 constexpr int kAccStages = 2;   // TMEM accumulator double buffer (2 x 256 columns = all 512)
-constexpr int kGemmThreads = 192;  // warp0 TMA, warp1 MMA+TMEM alloc, warps2-5 epilogue
+constexpr int kGemmThreads = 320;  // warp0 TMA, warp1 MMA+TMEM alloc, warps2-9 epilogue
 
 // One valid-row range of one utterance inside the packed row space: rows [r0, r1) belong to
 // utterance `utt` and are valid outputs of the pooled layer.
@@ -38,11 +38,12 @@ struct GemmParams {
   const float* shift;  // [N_alloc]
   const float* slope;  // [N_alloc] negative-side slope (0 relu, 0.2 lrelu, alpha prelu, 1 linear)
   int32_t act_tanh;
+  int32_t relu_only;   // every slope is 0 (plain ReLU) and no tanh: fast epilogue path
   __nv_bfloat16* out_bf16;  // [m_rows, ldo] or null
   float* out_f32;           // [m_rows, ldo] or null
   int32_t ldo;
   // fused statistics-pooling partial sums (tdnn5): acc[utt][0|1][pool_ld] += sum x | sum x^2
-  float* pool_acc;
+  double* pool_acc;    // fp64: atomics become order-independent at fp32 precision
   int32_t pool_ld;
   const int32_t* tile_seg_ptr;  // [2 * m_tiles]: (lo, hi) index range into segs per tile
   const PoolSeg* segs;
@@ -55,6 +56,7 @@ struct GemmParams {
 struct GemmPlan {
   CUtensorMap tm_a;
   CUtensorMap tm_b;
+  CUtensorMap tm_out;  // bf16 output [m_rows, ldo], box 32x32, SWIZZLE_64B (unused for fp32 / pooled outputs)
   GemmParams p;
   bool pool;
 };
@@ -62,7 +64,7 @@ struct GemmPlan {
 // Host-side helpers (xv_gemm_sm100.cu)
 const char* gemm_init();   // resolves cuTensorMapEncodeTiled, sets smem attributes; returns error text or null
 const char* make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t rows,
-                              uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_rows);
+                              uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_rows, int swizzle_bytes = 128);
 cudaError_t launch_gemm(const GemmPlan& plan, int sm_count, cudaStream_t stream);
 
 // ---- SIMT / elementwise kernels (xv_kernels.cu) ----
@@ -112,7 +114,7 @@ size_t pool_workspace_bytes(int32_t n, int32_t hout, int32_t c);
 cudaError_t launch_pool(const PoolArgs& a, int sm_count, cudaStream_t stream);
 
 // Finalize the fused (GEMM-epilogue) pooling accumulators: acc [n][2][acc_ld] (sum, sumsq) -> mean|std.
-cudaError_t launch_pool_finalize(const float* acc, int acc_ld, const int32_t* cu, int context, int n, int c,
+cudaError_t launch_pool_finalize(const double* acc, int acc_ld, const int32_t* cu, int context, int n, int c,
                                  float* out_f32, int ldo_f32, __nv_bfloat16* out_bf16, int ldo_bf16, int weighted,
                                  cudaStream_t stream);
 

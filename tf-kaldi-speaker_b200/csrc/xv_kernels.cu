@@ -28,17 +28,26 @@ __global__ void splice_cast_kernel(const float* __restrict__ in, int64_t rows, i
     const int64_t r = i / vec_per_row;
     const int k0 = static_cast<int>(i - r * vec_per_row) << 3;
     float v[8];
+    if (dil == 1) {
+      // rows are contiguous with stride d, so the spliced row is the contiguous slab in[r*d .. r*d + taps*d)
+      const int64_t base = r * d + k0;
+      const int64_t total_in = rows * d;
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const int k = k0 + e;
-      float x = 0.f;
-      if (k < k_real) {
-        const int j = k / d;
-        const int c = k - j * d;
-        const int64_t rr = r + static_cast<int64_t>(j) * dil;
-        if (rr < rows) x = __ldg(in + rr * d + c);
+      for (int e = 0; e < 8; ++e)
+        v[e] = (k0 + e < k_real && base + e < total_in) ? __ldg(in + base + e) : 0.f;
+    } else {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int k = k0 + e;
+        float x = 0.f;
+        if (k < k_real) {
+          const int j = k / d;
+          const int c = k - j * d;
+          const int64_t rr = r + static_cast<int64_t>(j) * dil;
+          if (rr < rows) x = __ldg(in + rr * d + c);
+        }
+        v[e] = x;
       }
-      v[e] = x;
     }
     __nv_bfloat162 b0 = __floats2bfloat162_rn(v[0], v[1]);
     __nv_bfloat162 b1 = __floats2bfloat162_rn(v[2], v[3]);

@@ -194,8 +194,10 @@ int xv_gemm_bf16(xv_ctx* c, const void* a_dev, int64_t a_rows, int32_t cin, int3
   cudaSetDevice(c->device);
   const int kpad = taps * cin;
   GemmPlan g;
+  if (m_rows <= 0) return XV_OK;
   const char* err = make_tmap_bf16_2d(&g.tm_a, a_dev, cin, a_rows, static_cast<uint64_t>(cin) * 2, kBK, kBM);
   if (!err) err = make_tmap_bf16_2d(&g.tm_b, wt_dev, kpad, n, static_cast<uint64_t>(kpad) * 2, kBK, kBN);
+  if (!err) err = make_tmap_bf16_2d(&g.tm_out, out_dev, n, m_rows, static_cast<uint64_t>(n) * 2, 32, 32, 64);
   if (err) return fail(c, XV_ECUDA, "%s", err);
   DevBuf slope;
   int rc = ensure(c, &slope, sizeof(float) * n);
@@ -211,6 +213,7 @@ int xv_gemm_bf16(xv_ctx* c, const void* a_dev, int64_t a_rows, int32_t cin, int3
   p.n_tiles = n / kBN;
   p.taps = taps; p.dilation = dilation; p.kb_per_tap = cin / kBK; p.cin = cin;
   p.scale = scale_dev; p.shift = shift_dev; p.slope = static_cast<const float*>(slope.p);
+  p.relu_only = neg_slope == 0.f ? 1 : 0;
   p.out_bf16 = static_cast<__nv_bfloat16*>(out_dev); p.ldo = ldo; p.heads = 1; p.head_width = n;
   g.pool = false;
   {
@@ -236,8 +239,10 @@ int xv_gemm_bf16_async(xv_ctx* c, const void* a_dev, int64_t a_rows, int32_t cin
     return fail(c, XV_EINVAL, "xv_gemm_bf16_async: bad geometry");
   const int kpad = taps * cin;
   GemmPlan g;
+  if (m_rows <= 0) return XV_OK;
   const char* err = make_tmap_bf16_2d(&g.tm_a, a_dev, cin, a_rows, static_cast<uint64_t>(cin) * 2, kBK, kBM);
   if (!err) err = make_tmap_bf16_2d(&g.tm_b, wt_dev, kpad, n, static_cast<uint64_t>(kpad) * 2, kBK, kBN);
+  if (!err) err = make_tmap_bf16_2d(&g.tm_out, out_dev, n, m_rows, static_cast<uint64_t>(n) * 2, 32, 32, 64);
   if (err) return fail(c, XV_ECUDA, "%s", err);
   GemmParams& p = g.p;
   memset(&p, 0, sizeof(p));

@@ -175,8 +175,9 @@ __global__ void __launch_bounds__(512) pool_accum_kernel(const PoolAccumParams a
   }
 }
 
+template <typename AccT>
 struct PoolFinalizeParams {
-  const float* acc;      // [n][hout][2][acc_ld]
+  const AccT* acc;       // [n][hout][2][acc_ld]
   int32_t acc_ld, n, hout, c;
   const int32_t* cu;
   int32_t context;
@@ -187,7 +188,8 @@ struct PoolFinalizeParams {
   __nv_bfloat16* out_bf16; int32_t ldout_bf16;
 };
 
-__global__ void pool_finalize_kernel(const PoolFinalizeParams a) {
+template <typename AccT>
+__global__ void pool_finalize_kernel(const PoolFinalizeParams<AccT> a) {
   const int64_t total = static_cast<int64_t>(a.n) * a.hout * a.c;
   for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
@@ -195,12 +197,13 @@ __global__ void pool_finalize_kernel(const PoolFinalizeParams a) {
     const int64_t t = i / a.c;
     const int hh = static_cast<int>(t % a.hout);
     const int u = static_cast<int>(t / a.hout);
-    const float* p = a.acc + ((static_cast<int64_t>(u) * a.hout + hh) * 2) * a.acc_ld + c;
+    const AccT* p = a.acc + ((static_cast<int64_t>(u) * a.hout + hh) * 2) * a.acc_ld + c;
     const int32_t cs = a.cu[u];
     const int32_t len = a.cu[u + 1] - cs - a.context;
-    const float inv = a.weighted ? 1.f : 1.f / static_cast<float>(len);
-    const float m = p[0] * inv;
-    float var = p[a.acc_ld] * inv - m * m;
+    const AccT inv = a.weighted ? AccT(1) : AccT(1) / static_cast<AccT>(len);
+    const AccT m_acc = p[0] * inv;
+    const float m = static_cast<float>(m_acc);
+    float var = static_cast<float>(p[a.acc_ld] * inv - m_acc * m_acc);
     float piv = 0.f;
     if (a.x != nullptr) {
       piv = a.dtype == 1 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(a.x)[static_cast<int64_t>(cs) * a.ldx + c])
@@ -367,29 +370,29 @@ cudaError_t launch_pool(const PoolArgs& a, int sm_count, cudaStream_t stream) {
     }
   }
   if (e != cudaSuccess) return e;
-  PoolFinalizeParams f;
+  PoolFinalizeParams<float> f;
   f.acc = a.acc; f.acc_ld = a.c; f.n = a.n; f.hout = hout; f.c = a.c; f.cu = a.cu; f.context = a.context;
   f.weighted = a.weights != nullptr; f.x = a.x; f.dtype = a.dtype; f.ldx = a.ldx;
   f.out = a.out; f.ldout = a.ldout; f.out_bf16 = a.out_bf16; f.ldout_bf16 = a.ldout_bf16;
   const int64_t total = static_cast<int64_t>(a.n) * hout * a.c;
   int64_t blocks = (total + 255) / 256;
   if (blocks > sm_count * 8) blocks = sm_count * 8;
-  pool_finalize_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(f);
+  pool_finalize_kernel<float><<<static_cast<int>(blocks), 256, 0, stream>>>(f);
   return cudaGetLastError();
 }
 
-cudaError_t launch_pool_finalize(const float* acc, int acc_ld, const int32_t* cu, int context, int n, int c,
+cudaError_t launch_pool_finalize(const double* acc, int acc_ld, const int32_t* cu, int context, int n, int c,
                                  float* out_f32, int ldo_f32, __nv_bfloat16* out_bf16, int ldo_bf16, int weighted,
                                  cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
-  PoolFinalizeParams f;
+  PoolFinalizeParams<double> f;
   f.acc = acc; f.acc_ld = acc_ld; f.n = n; f.hout = 1; f.c = c; f.cu = cu; f.context = context;
   f.weighted = weighted; f.x = nullptr; f.dtype = 0; f.ldx = 0;
   f.out = out_f32; f.ldout = ldo_f32; f.out_bf16 = out_bf16; f.ldout_bf16 = ldo_bf16;
   const int64_t total = static_cast<int64_t>(n) * c;
   int64_t blocks = (total + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
-  pool_finalize_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(f);
+  pool_finalize_kernel<double><<<static_cast<int>(blocks), 256, 0, stream>>>(f);
   return cudaGetLastError();
 }
 
