@@ -324,7 +324,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch-frames", type=int, default=65536)
+    ap.add_argument("--batch-frames", type=int, default=262144)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--utts", type=int, default=UTTS_PER_GPU, help="utterances per GPU (default = the configs[1] set; "

@@ -490,7 +490,7 @@ int xv_create(int device, const char* config_json, xv_ctx** out) {
     return XV_EINVAL;
   }
   c->bf16 = prec == "bf16";
-  c->batch_frames = jint(c->cfg, "batch_frames", 65536);
+  c->batch_frames = jint(c->cfg, "batch_frames", 262144);
   if (c->batch_frames < 1024) c->batch_frames = 1024;
   int rc = build_plan(c);
   if (rc != XV_OK) {

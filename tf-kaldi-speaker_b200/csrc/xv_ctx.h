@@ -91,7 +91,7 @@ struct xv_ctx {
   xv::JValue cfg;
   int dim = 0;
   bool bf16 = true;
-  int64_t batch_frames = 65536;
+  int64_t batch_frames = 262144;
   std::string relu_type;         // "", "prelu", "lrelu"
   std::string pooling_type;
   std::string embedding_node;

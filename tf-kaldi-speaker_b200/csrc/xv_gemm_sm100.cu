@@ -39,8 +39,7 @@ constexpr uint32_t kStageBytes = kABytes + kBBytes;          // 49152
 constexpr uint32_t kRingBytes = kStages * kStageBytes;       // 196608
 constexpr uint32_t kEpiParamBytes = kAccStages * kBN * 12;   // (scale,shift) float2 + slope float = 6144
 constexpr uint32_t kStoreStageBytes = 32 * 64;               // per warp: 32 rows x 32 bf16, SWIZZLE_64B
-constexpr uint32_t kTrFloats = 32 * 17;                      // per warp: 32 rows x 16 columns (+1 pad) fp32
-constexpr uint32_t kEpiScratchBytes = kEpiWarps * (kTrFloats * 4 > kStoreStageBytes ? kTrFloats * 4 : kStoreStageBytes);
+constexpr uint32_t kEpiScratchBytes = kEpiWarps * kStoreStageBytes;
 constexpr uint32_t kBarrierBytes = 256;
 constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kSmemBytes = 1024 /*alignment slack (normally unused: the array is declared __align__(1024))*/ + kRingBytes + kEpiParamBytes + kEpiScratchBytes + kBarrierBytes;
@@ -156,7 +155,6 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     const uint32_t half = e >> 2;                // which 128 of the tile's 256 columns
     const uint32_t etid = threadIdx.x - 64;      // 0..255
     uint8_t* stage_buf = scratch + e * kStoreStageBytes;                       // bf16 store staging (non-pool)
-    float* tr = reinterpret_cast<float*>(scratch) + e * kTrFloats;             // transpose buffer (pool)
     const bool relu_only = p.relu_only != 0;
     const bool store_bf16 = !kPool && p.out_bf16 != nullptr;
     uint32_t as = 0, aphase = 0;
@@ -190,8 +188,117 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
             w_last = s;
           }
         }
-        w_full = w_first == w_last && w_sg.r0 <= mw && w_sg.r1 >= mw + 32 && p.row_weight == nullptr;
+        w_full = w_first == w_last && w_sg.r0 <= mw && w_sg.r1 >= mw + 32;
       }
+      if (kPool) {
+        // ---- pooled layer: nothing is stored; per-utterance column sums of y and y^2 ----
+        // tcgen05.ld.16x256b gives each thread 4 rows x 8 columns of the warp's 32x32 block (rows rq+{0,8,16,24},
+        // columns 8i + 2(lane&3) + {0,1}), so the row reduction is 3 in-thread adds per column followed by a
+        // 14-shuffle butterfly over the 8 lanes that share (lane & 3): no shared-memory traffic at all (the smem
+        // pipe is what the UMMA operand reads and TMA fills need).  After the butterfly every lane owns two
+        // adjacent columns of either the sum (lane bit 4 = 0) or the sum of squares (bit 4 = 1) and issues two fp64
+        // atomics (order-independent at fp32 precision; no cancellation noise in E[x^2] - mean^2).
+        const int rq = lane >> 2, cq = (lane & 3) * 2;
+#pragma unroll 1
+        for (int ci = 0; ci < 4; ++ci) {
+          const int c = half * 4 + ci;
+          uint32_t ra[16], rb[16];
+          const uint32_t tcol = as * kBN + c * 32;
+          ptx::tmem_ld_16x256b_x4(tmem_base + ((q * 32) << 16) + tcol, ra);
+          ptx::tmem_ld_16x256b_x4(tmem_base + ((q * 32 + 16) << 16) + tcol, rb);
+          ptx::tmem_ld_wait();
+          if (ci == 3) {
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
+          }
+          float y[4][8];                           // [row k: rq + 8k][column slot 2i + e]
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 sh = *reinterpret_cast<const float4*>(ss + c * 32 + 8 * i + cq);
+            const float2 ng = *reinterpret_cast<const float2*>(sl + c * 32 + 8 * i + cq);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const uint32_t* src = k < 2 ? ra : rb;
+              float v0 = fmaf(__uint_as_float(src[4 * i + 2 * (k & 1)]), sh.x, sh.y);
+              float v1 = fmaf(__uint_as_float(src[4 * i + 2 * (k & 1) + 1]), sh.z, sh.w);
+              if (relu_only) {
+                v0 = fmaxf(v0, 0.f);
+                v1 = fmaxf(v1, 0.f);
+              } else {
+                v0 = v0 >= 0.f ? v0 : v0 * ng.x;
+                v1 = v1 >= 0.f ? v1 : v1 * ng.y;
+                if (p.act_tanh) { v0 = tanhf(v0); v1 = tanhf(v1); }
+              }
+              y[k][2 * i] = v0;
+              y[k][2 * i + 1] = v1;
+            }
+          }
+          for (int s = w_first; s <= w_last; ++s) {
+            const PoolSeg sg = s == w_first ? w_sg : p.segs[s];
+            float v[16];
+            if (w_full) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                v[j] = (y[0][j] + y[1][j]) + (y[2][j] + y[3][j]);
+                v[8 + j] = fmaf(y[0][j], y[0][j], y[1][j] * y[1][j]) + fmaf(y[2][j], y[2][j], y[3][j] * y[3][j]);
+              }
+            } else {
+              const int lo = max(sg.r0, mw) - mw;
+              const int hi = min(sg.r1, mw + 32) - mw;
+              if (lo >= hi) continue;
+              float m[4];
+#pragma unroll
+              for (int k = 0; k < 4; ++k) m[k] = (rq + 8 * k >= lo && rq + 8 * k < hi) ? 1.f : 0.f;
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                float a1 = 0.f, a2 = 0.f;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  const float t = m[k] * y[k][j];
+                  a1 += t;
+                  a2 = fmaf(t, y[k][j], a2);
+                }
+                v[j] = a1;
+                v[8 + j] = a2;
+              }
+            }
+            // butterfly over lane bits 4, 3, 2: halves the live values each step
+            {
+              const bool up = (lane & 16) != 0;
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float send = up ? v[j] : v[j + 8];
+                const float keep = up ? v[j + 8] : v[j];
+                v[j] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+              }
+            }
+            {
+              const bool up = (lane & 8) != 0;
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float send = up ? v[j] : v[j + 4];
+                const float keep = up ? v[j + 4] : v[j];
+                v[j] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+              }
+            }
+            {
+              const bool up = (lane & 4) != 0;
+#pragma unroll
+              for (int j = 0; j < 2; ++j) {
+                const float send = up ? v[j] : v[j + 2];
+                const float keep = up ? v[j + 2] : v[j];
+                v[j] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+              }
+            }
+            const int kind = (lane >> 4) & 1;                      // 0: sum, 1: sum of squares
+            const int ii = ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+            double* dst = p.pool_acc + (static_cast<size_t>(sg.utt) * 2 + kind) * p.pool_ld + n0 + c * 32 + 8 * ii + cq;
+            atomicAdd(dst, static_cast<double>(v[0]));
+            atomicAdd(dst + 1, static_cast<double>(v[1]));
+          }
+        }
+      } else {
 #pragma unroll 1
       for (int ci = 0; ci < 4; ++ci) {
         const int c = half * 4 + ci;             // 32-column chunk of the tile
@@ -257,65 +364,7 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
 #pragma unroll
           for (int g = 0; g < 8; ++g) dst[g] = make_float4(y[g * 4], y[g * 4 + 1], y[g * 4 + 2], y[g * 4 + 3]);
         }
-        if (kPool) {
-          // Column sums over the valid rows of every utterance segment intersecting this warp's 32 rows.
-          // 16 columns at a time through a [32][17] fp32 transpose buffer: lane (cl = lane & 15, rh = lane >> 4)
-          // sums column cl over row half rh (conflict-free both ways), halves are combined with one shuffle,
-          // lanes 0-15 add the sums and lanes 16-31 the sums of squares (fp64 atomics: order-independent to
-          // fp32 precision, and no cancellation noise in E[x^2] - mean^2).
-          const int cl = lane & 15, rh = lane >> 4;
-#pragma unroll
-          for (int hc = 0; hc < 2; ++hc) {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) tr[lane * 17 + j] = y[hc * 16 + j];
-            __syncwarp();
-            const int col = n0 + c * 32 + hc * 16 + cl;
-            const float* trc = tr + (rh * 16) * 17 + cl;
-            if (w_full) {
-              // common case: one utterance covers all 32 rows of this warp
-              float s1 = 0.f, s2 = 0.f, s1b = 0.f, s2b = 0.f;
-#pragma unroll
-              for (int i = 0; i < 16; i += 2) {
-                const float v0 = trc[i * 17], v1 = trc[(i + 1) * 17];
-                s1 += v0; s2 = fmaf(v0, v0, s2);
-                s1b += v1; s2b = fmaf(v1, v1, s2b);
-              }
-              s1 += s1b; s2 += s2b;
-              s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
-              s2 += __shfl_xor_sync(0xffffffffu, s2, 16);
-              atomicAdd(p.pool_acc + (static_cast<size_t>(w_sg.utt) * 2 + rh) * p.pool_ld + col,
-                        static_cast<double>(rh ? s2 : s1));
-            } else {
-              for (int s = w_first; s <= w_last; ++s) {
-                const PoolSeg sg = s == w_first ? w_sg : p.segs[s];
-                const int lo = max(sg.r0, mw) - mw;
-                const int hi = min(sg.r1, mw + 32) - mw;
-                if (lo >= hi) continue;
-                const float* wrow = nullptr;
-                if (p.row_weight != nullptr) {
-                  const int head = min(col / p.head_width, p.heads - 1);
-                  wrow = p.row_weight + static_cast<size_t>(head) * p.m_rows + mw + rh * 16;
-                }
-                float s1 = 0.f, s2 = 0.f;
-#pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                  const int rr = rh * 16 + i;
-                  if (rr >= lo && rr < hi) {
-                    const float v = trc[i * 17];
-                    const float w = wrow ? __ldg(wrow + i) : 1.f;
-                    s1 = fmaf(w, v, s1);
-                    s2 = fmaf(w * v, v, s2);
-                  }
-                }
-                s1 += __shfl_xor_sync(0xffffffffu, s1, 16);
-                s2 += __shfl_xor_sync(0xffffffffu, s2, 16);
-                atomicAdd(p.pool_acc + (static_cast<size_t>(sg.utt) * 2 + rh) * p.pool_ld + col,
-                          static_cast<double>(rh ? s2 : s1));
-              }
-            }
-            __syncwarp();
-          }
-        }
+      }
       }
       if (++as == kAccStages) { as = 0; aphase ^= 1; }
     }
