@@ -223,6 +223,11 @@ def run_ours(args):
         "traffic": None,
     }
 
+    # ---------------- standalone statistics pooling (HBM roofline; rank 0 at N=1) ----------------
+    pooling = None
+    if rank == 0 and world == 1 and not args.no_pool_bench:
+        pooling = pooling_roofline(eng, peaks)
+
     # ---------------- end to end through the public C-ABI call (host buffers) ----------------
     e2e_steps = max(1, min(args.steps, 5))
     out = None
@@ -265,6 +270,8 @@ def run_ours(args):
             "roofline": roofline,
             "kernel_families_ms_per_step": fam,
         }
+        if pooling is not None:
+            line["pooling_roofline"] = pooling
         if cpu is not None:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
@@ -272,6 +279,58 @@ def run_ours(args):
     eng.close()
     if dist is not None:
         dist.destroy_process_group()
+
+
+def pooling_roofline(eng, peaks, channels=1500, iters=10):
+    """xv_stat_pooling_dev (the drop-in for direct statistics_pooling() callers, model/pooling.py:27-52) on a bf16
+    [rows, 1500] matrix of 1.26 GB (10x the L2) cut into utterances with the configs[1] length distribution.
+    Algorithmic bytes = rows*C*2 read + n*2C*4 written; time = events around every pooling call
+    (memset of the accumulators + accumulate kernel + finalize kernel)."""
+    import ctypes as C
+    from oracle import synth
+    from xvector_b200 import _lib
+    lengths = synth.config2_lengths(4096, seed=202).astype(np.int64)
+    target = 420000
+    k = int(np.searchsorted(np.cumsum(lengths), target))
+    lengths = lengths[:max(k, 1)]
+    cu = np.concatenate([[0], np.cumsum(lengths)]).astype(np.int32)
+    rows, n = int(cu[-1]), len(lengths)
+    x_dev = eng.device_alloc(rows * channels * 2)
+    cu_dev = eng.device_alloc(cu.nbytes)
+    out_dev = eng.device_alloc(n * 2 * channels * 4)
+    try:
+        blk_rows = 16384
+        blk = (np.random.default_rng(5).standard_normal((blk_rows, channels), dtype=np.float32)).clip(min=0)
+        for r0 in range(0, rows, blk_rows):                   # values do not matter for bandwidth; reuse one block
+            r1 = min(rows, r0 + blk_rows)
+            eng.upload_bf16(C.c_void_p(x_dev.value + r0 * channels * 2), blk[:r1 - r0])
+        eng.h2d(cu_dev, cu)
+        call = lambda: eng._check(eng.lib.xv_stat_pooling_dev(eng._ctx, x_dev, C.cast(cu_dev, C.POINTER(C.c_int32)), n,
+                                                               channels, _lib.DTYPE_BF16, int(lengths.max()),
+                                                               C.cast(out_dev, C.POINTER(C.c_float))))
+        for _ in range(3):
+            call()
+        eng.sync()
+        eng.profile_enable(True)
+        for _ in range(iters):
+            call()
+        eng.sync()
+        ms, cnt = eng.profile_query("pool")
+        eng.profile_enable(False)
+        out = np.empty((n, 2 * channels), np.float32)
+        eng.d2h(out, out_dev)
+        assert np.isfinite(out).all()
+    finally:
+        eng.device_free(x_dev)
+        eng.device_free(cu_dev)
+        eng.device_free(out_dev)
+    nbytes = rows * channels * 2 + n * 2 * channels * 4
+    gbs = nbytes / (ms / cnt * 1e-3) / 1e9
+    return {"kernel": "pool_accum_bulk_kernel<bf16,4> (cp.async.bulk-staged) + pool_finalize_kernel (xv_stat_pooling_dev)", "bound": "hbm",
+            "achieved": gbs, "peak": peaks["hbm"], "unit": "GB/s", "frac": gbs / peaks["hbm"],
+            "peak_kind": "copy bandwidth, %s" % peaks["source"], "algorithmic_bytes_per_launch": nbytes,
+            "rows": rows, "utterances": n, "channels": channels, "avg_launch_ms": ms / cnt, "launches": cnt,
+            "traffic": None}
 
 
 def cpu_baseline(seconds):
@@ -327,6 +386,7 @@ def main():
     ap.add_argument("--batch-frames", type=int, default=262144)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-pool-bench", action="store_true")
     ap.add_argument("--utts", type=int, default=UTTS_PER_GPU, help="utterances per GPU (default = the configs[1] set; "
                     "smaller values are for profiling runs only)")
     args = ap.parse_args()

@@ -14,7 +14,10 @@
 // vector load per row) and `rl` row lanes stride the rows; loads are unrolled x4 for memory-level parallelism.
 #include <float.h>
 
+#include <stdlib.h>
+
 #include "xv_internal.h"
+#include "xv_ptx.cuh"
 
 namespace xv {
 
@@ -84,6 +87,46 @@ struct PoolAccumParams {
   float* acc;             // [n][hout][2][c]
   int32_t hout;
   int32_t rows_per_chunk, threads_x, rl;
+  // bulk (TMA-staged) variant
+  int32_t rows_per_stage;   // even; stage = rows_per_stage * ldx * sizeof(T) bytes <= kPoolStageBytes
+  int32_t span;             // rows per CTA (multiple of rows_per_stage)
+  int64_t bulk_end;         // rows [0, bulk_end) may be fetched with 16-byte-granular bulk copies
+};
+
+constexpr int kPoolStages = 3;
+constexpr uint32_t kPoolStageBytes = 32768;
+constexpr uint32_t kPoolBulkSmem = kPoolStages * kPoolStageBytes + 64;
+
+template <typename T, int V>
+struct SmemLoad;
+template <>
+struct SmemLoad<float, 4> {
+  static __device__ __forceinline__ void ld(const float* p, float (&o)[4]) {
+    const float4 v = *reinterpret_cast<const float4*>(p);
+    o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
+  }
+};
+template <>
+struct SmemLoad<float, 2> {
+  static __device__ __forceinline__ void ld(const float* p, float (&o)[2]) {
+    const float2 v = *reinterpret_cast<const float2*>(p);
+    o[0] = v.x; o[1] = v.y;
+  }
+};
+template <>
+struct SmemLoad<__nv_bfloat16, 8> {
+  static __device__ __forceinline__ void ld(const __nv_bfloat16* p, float (&o)[8]) {
+    const uint4 v = *reinterpret_cast<const uint4*>(p);
+    unpack_bf16x2(v.x, o[0], o[1]); unpack_bf16x2(v.y, o[2], o[3]);
+    unpack_bf16x2(v.z, o[4], o[5]); unpack_bf16x2(v.w, o[6], o[7]);
+  }
+};
+template <>
+struct SmemLoad<__nv_bfloat16, 4> {
+  static __device__ __forceinline__ void ld(const __nv_bfloat16* p, float (&o)[4]) {
+    const uint2 v = *reinterpret_cast<const uint2*>(p);
+    unpack_bf16x2(v.x, o[0], o[1]); unpack_bf16x2(v.y, o[2], o[3]);
+  }
 };
 
 template <typename T, int V>
@@ -173,6 +216,160 @@ __global__ void __launch_bounds__(512) pool_accum_kernel(const PoolAccumParams a
       }
     }
   }
+}
+
+// Bulk-staged variant of pool_accum_kernel for the HBM roofline: a persistent CTA owns a contiguous span of
+// packed rows; warp 0 streams it through a 3-stage shared-memory ring with 1-D bulk copies (cp.async.bulk,
+// 30 KB per request, completion on an mbarrier) so ~90 KB per CTA (two CTAs per SM) are always in flight
+// without any per-thread load instruction; the consumer warps (one thread per V columns) reduce each stage
+// from shared memory with conflict-free vector loads, walk the utterance segments the span crosses and flush
+// one fp32 atomicAdd per (segment, column).  Same pivot-shifted sums as pool_accum_kernel.
+template <typename T, int V>
+__global__ void __launch_bounds__(544) pool_accum_bulk_kernel(const PoolAccumParams a) {
+  extern __shared__ __align__(128) uint8_t pool_smem[];
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(pool_smem + kPoolStages * kPoolStageBytes);
+  uint64_t* empty_bar = full_bar + kPoolStages;
+  const T* __restrict__ x = reinterpret_cast<const T*>(a.x);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_cons_warps = (blockDim.x >> 5) - 1;
+  const int64_t R0 = static_cast<int64_t>(blockIdx.x) * a.span;
+  const int64_t R1 = min(R0 + a.span, a.rows);
+  if (R0 >= R1) return;
+  const int n_chunks = static_cast<int>((R1 - R0 + a.rows_per_stage - 1) / a.rows_per_stage);
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kPoolStages; ++s) {
+      ptx::mbar_init(&full_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], n_cons_warps);
+    }
+    ptx::fence_mbar_init();
+  }
+  __syncthreads();
+  const uint32_t row_bytes = static_cast<uint32_t>(a.ldx) * sizeof(T);
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t st = 0, ph = 0;
+      for (int i = 0; i < n_chunks; ++i) {
+        const int64_t c0 = R0 + static_cast<int64_t>(i) * a.rows_per_stage;
+        int64_t c1 = min(c0 + a.rows_per_stage, R1);
+        c1 = min(c1, a.bulk_end);                       // a trailing odd row is read straight from global memory
+        ptx::mbar_wait(&empty_bar[st], ph ^ 1);
+        if (c1 > c0) {
+          const uint32_t bytes = static_cast<uint32_t>(c1 - c0) * row_bytes;
+          ptx::mbar_arrive_expect_tx(&full_bar[st], bytes);
+          ptx::bulk_load_1d(pool_smem + st * kPoolStageBytes, x + c0 * a.ldx, bytes, &full_bar[st]);
+        } else {
+          ptx::mbar_arrive(&full_bar[st]);
+        }
+        if (++st == kPoolStages) { st = 0; ph ^= 1; }
+      }
+    }
+    return;
+  }
+  const int cvi = threadIdx.x - 32;
+  const int col0 = cvi * V;
+  const bool col_ok = col0 < a.c;
+  const int hz = blockIdx.y;
+  const float* wrow = nullptr;
+  if (a.weights != nullptr) {
+    const int h = a.head_width > 0 ? (col_ok ? col0 / a.head_width : 0) : hz;
+    wrow = a.weights + static_cast<int64_t>(h) * a.rows;
+  }
+  // first utterance whose end lies beyond R0
+  int u = 0;
+  {
+    int lo = 0, hi = a.n;
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (static_cast<int64_t>(__ldg(a.cu + mid + 1)) > R0) hi = mid; else lo = mid + 1;
+    }
+    u = lo;
+  }
+  float s[V], q[V], piv[V];
+  int64_t cs = 0, ve = 0, ue = 0;            // utterance start, valid end, end
+  bool dirty = false;
+  auto open_utt = [&]() {
+#pragma unroll
+    for (int e = 0; e < V; ++e) { s[e] = 0.f; q[e] = 0.f; piv[e] = 0.f; }
+    dirty = false;
+    if (u < a.n) {
+      cs = __ldg(a.cu + u);
+      ue = __ldg(a.cu + u + 1);
+      ve = ue - a.context;
+      if (col_ok && cs < ve) VecLoad<T, V>::ld(x + cs * a.ldx + col0, piv);
+    } else {
+      cs = ve = ue = a.rows + 1;
+    }
+  };
+  auto flush = [&]() {
+    if (dirty && col_ok) {
+      float* dst = a.acc + ((static_cast<int64_t>(u) * a.hout + hz) * 2) * a.c + col0;
+#pragma unroll
+      for (int e = 0; e < V; ++e) {
+        atomicAdd(dst + e, s[e]);
+        atomicAdd(dst + a.c + e, q[e]);
+      }
+    }
+  };
+  open_utt();
+  uint32_t st = 0, ph = 0;
+  for (int i = 0; i < n_chunks; ++i) {
+    const int64_t c0 = R0 + static_cast<int64_t>(i) * a.rows_per_stage;
+    const int64_t c1 = min(c0 + a.rows_per_stage, R1);
+    ptx::mbar_wait(&full_bar[st], ph);
+    const T* sbase = reinterpret_cast<const T*>(pool_smem + st * kPoolStageBytes) + col0;
+    if (c0 >= cs && c1 <= ve && c1 <= a.bulk_end) {
+      // fast path: the whole stage lies inside the current utterance's valid rows
+      if (col_ok) {
+        const int nr = static_cast<int>(c1 - c0);
+        if (wrow == nullptr) {
+#pragma unroll 5
+          for (int r = 0; r < nr; ++r) {
+            float v[V];
+            SmemLoad<T, V>::ld(sbase + r * a.ldx, v);
+#pragma unroll
+            for (int e = 0; e < V; ++e) {
+              const float d = v[e] - piv[e];
+              s[e] += d;
+              q[e] = fmaf(d, d, q[e]);
+            }
+          }
+        } else {
+          for (int r = 0; r < nr; ++r) {
+            float v[V];
+            SmemLoad<T, V>::ld(sbase + r * a.ldx, v);
+            const float w = __ldg(wrow + c0 + r);
+#pragma unroll
+            for (int e = 0; e < V; ++e) {
+              const float d = v[e] - piv[e];
+              s[e] = fmaf(w, d, s[e]);
+              q[e] = fmaf(w * d, d, q[e]);
+            }
+          }
+        }
+        dirty = true;
+      }
+    } else {
+      for (int64_t r = c0; r < c1; ++r) {
+        while (r >= ue && u < a.n) { flush(); ++u; open_utt(); }
+        if (r < cs || r >= ve || !col_ok) continue;
+        float v[V];
+        if (r < a.bulk_end) SmemLoad<T, V>::ld(sbase + (r - c0) * a.ldx, v);
+        else VecLoad<T, V>::ld(x + r * a.ldx + col0, v);
+        const float w = wrow ? __ldg(wrow + r) : 1.f;
+#pragma unroll
+        for (int e = 0; e < V; ++e) {
+          const float d = v[e] - piv[e];
+          s[e] = fmaf(w, d, s[e]);
+          q[e] = fmaf(w * d, d, q[e]);
+        }
+        dirty = true;
+      }
+    }
+    __syncwarp();
+    if (lane == 0) ptx::mbar_arrive(&empty_bar[st]);
+    if (++st == kPoolStages) { st = 0; ph ^= 1; }
+  }
+  flush();
 }
 
 template <typename AccT>
@@ -325,6 +522,18 @@ cudaError_t launch_accum_v(const PoolAccumParams& p, dim3 grid, int block, cudaS
 
 }  // namespace
 
+static cudaError_t launch_pool_finalize_f32(const PoolArgs& a, int hout, int sm_count, cudaStream_t stream) {
+  PoolFinalizeParams<float> f;
+  f.acc = a.acc; f.acc_ld = a.c; f.n = a.n; f.hout = hout; f.c = a.c; f.cu = a.cu; f.context = a.context;
+  f.weighted = a.weights != nullptr; f.x = a.x; f.dtype = a.dtype; f.ldx = a.ldx;
+  f.out = a.out; f.ldout = a.ldout; f.out_bf16 = a.out_bf16; f.ldout_bf16 = a.ldout_bf16;
+  const int64_t total = static_cast<int64_t>(a.n) * hout * a.c;
+  int64_t blocks = (total + 255) / 256;
+  if (blocks > sm_count * 8) blocks = sm_count * 8;
+  pool_finalize_kernel<float><<<static_cast<int>(blocks), 256, 0, stream>>>(f);
+  return cudaGetLastError();
+}
+
 size_t pool_workspace_bytes(int32_t n, int32_t hout, int32_t c) {
   return static_cast<size_t>(n) * hout * 2 * c * sizeof(float);
 }
@@ -342,6 +551,42 @@ cudaError_t launch_pool(const PoolArgs& a, int sm_count, cudaStream_t stream) {
   if (a.dtype == 1) v = pick_vec<__nv_bfloat16>(a.x, a.ldx, a.c, head_width, 8);
   else v = pick_vec<float>(a.x, a.ldx, a.c, head_width, 4);
   const int nv = (a.c + v - 1) / v;
+  // ---- bulk-staged kernel whenever the layout allows 16-byte-granular bulk copies ----
+  {
+    static const bool force_ldg = getenv("XV_POOL_IMPL") != nullptr && getenv("XV_POOL_IMPL")[0] == 'l';
+    const size_t esz = a.dtype == 1 ? 2 : 4;
+    const size_t row_bytes = static_cast<size_t>(a.ldx) * esz;
+    const bool v_ok = a.dtype == 1 ? (v == 8 || v == 4) : (v == 4 || v == 2);
+    if (!force_ldg && v_ok && nv <= 512 && row_bytes % 8 == 0 && 2 * row_bytes <= kPoolStageBytes &&
+        reinterpret_cast<uintptr_t>(a.x) % 16 == 0) {
+      int rps = static_cast<int>(kPoolStageBytes / row_bytes) & ~1;
+      if (rps > 64) rps = 64;
+      const int ctas = sm_count * 2;
+      int64_t span = (a.rows + ctas - 1) / ctas;
+      span = ((span + rps - 1) / rps) * rps;
+      p.rows_per_stage = rps;
+      p.span = static_cast<int32_t>(span);
+      p.bulk_end = row_bytes % 16 == 0 ? a.rows : (a.rows & ~int64_t(1));
+      p.threads_x = 0; p.rl = 1; p.rows_per_chunk = 0;
+      dim3 grid(static_cast<unsigned>((a.rows + span - 1) / span), static_cast<unsigned>(hout));
+      const int block = 32 + ((nv + 31) / 32) * 32;
+      static bool attr_done = false;
+      if (!attr_done) {
+        cudaFuncSetAttribute(pool_accum_bulk_kernel<__nv_bfloat16, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPoolBulkSmem);
+        cudaFuncSetAttribute(pool_accum_bulk_kernel<__nv_bfloat16, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPoolBulkSmem);
+        cudaFuncSetAttribute(pool_accum_bulk_kernel<float, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPoolBulkSmem);
+        cudaFuncSetAttribute(pool_accum_bulk_kernel<float, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPoolBulkSmem);
+        attr_done = true;
+      }
+      if (a.dtype == 1 && v == 8) pool_accum_bulk_kernel<__nv_bfloat16, 8><<<grid, block, kPoolBulkSmem, stream>>>(p);
+      else if (a.dtype == 1) pool_accum_bulk_kernel<__nv_bfloat16, 4><<<grid, block, kPoolBulkSmem, stream>>>(p);
+      else if (v == 4) pool_accum_bulk_kernel<float, 4><<<grid, block, kPoolBulkSmem, stream>>>(p);
+      else pool_accum_bulk_kernel<float, 2><<<grid, block, kPoolBulkSmem, stream>>>(p);
+      e = cudaGetLastError();
+      if (e != cudaSuccess) return e;
+      return launch_pool_finalize_f32(a, hout, sm_count, stream);
+    }
+  }
   int tx = nv < 512 ? ((nv + 31) / 32) * 32 : 512;
   int rl = tx >= 256 ? 1 : 256 / tx;
   // keep the cross-row-lane reduction buffer within its 16 KB cap
@@ -370,15 +615,7 @@ cudaError_t launch_pool(const PoolArgs& a, int sm_count, cudaStream_t stream) {
     }
   }
   if (e != cudaSuccess) return e;
-  PoolFinalizeParams<float> f;
-  f.acc = a.acc; f.acc_ld = a.c; f.n = a.n; f.hout = hout; f.c = a.c; f.cu = a.cu; f.context = a.context;
-  f.weighted = a.weights != nullptr; f.x = a.x; f.dtype = a.dtype; f.ldx = a.ldx;
-  f.out = a.out; f.ldout = a.ldout; f.out_bf16 = a.out_bf16; f.ldout_bf16 = a.ldout_bf16;
-  const int64_t total = static_cast<int64_t>(a.n) * hout * a.c;
-  int64_t blocks = (total + 255) / 256;
-  if (blocks > sm_count * 8) blocks = sm_count * 8;
-  pool_finalize_kernel<float><<<static_cast<int>(blocks), 256, 0, stream>>>(f);
-  return cudaGetLastError();
+  return launch_pool_finalize_f32(a, hout, sm_count, stream);
 }
 
 cudaError_t launch_pool_finalize(const double* acc, int acc_ld, const int32_t* cu, int context, int n, int c,
