@@ -252,11 +252,167 @@ def tdnn(features, params, w):
     return x, ep
 
 
+def _tail_layers(x, params, w, scope, ep, first, second):
+    """Segment-level layers shared by every network: <first>_dense/bn/relu then <second>_dense[/bn][/relu]
+    (model/tdnn.py:137-179, :521-589; model/resnet.py:307-349)."""
+    x = dense_layer(x, w["%s/%s_dense/kernel" % (scope, first)], w["%s/%s_dense/bias" % (scope, first)])
+    ep["%s_dense" % first] = x
+    x = batch_norm_infer(x, w, "%s/%s_bn" % (scope, first))
+    ep["%s_bn" % first] = x
+    x = activation(x, params, w, "%s/%s_relu" % (scope, first))
+    ep["%s_relu" % first] = x
+    if "num_nodes_last_layer" not in params.dict:
+        params.dict["num_nodes_last_layer"] = 512
+    x = dense_layer(x, w["%s/%s_dense/kernel" % (scope, second)], w["%s/%s_dense/bias" % (scope, second)])
+    ep["%s_dense" % second] = x
+    if "last_layer_no_bn" not in params.dict:
+        params.last_layer_no_bn = False
+    if not params.last_layer_no_bn:
+        x = batch_norm_infer(x, w, "%s/%s_bn" % (scope, second))
+        ep["%s_bn" % second] = x
+    if "last_layer_linear" not in params.dict:
+        params.last_layer_linear = False
+    if not params.last_layer_linear:
+        x = activation(x, params, w, "%s/%s_relu" % (scope, second))
+        ep["%s_relu" % second] = x
+    return x
+
+
+def conv1d_valid(x, kernel, bias):
+    """tf.layers.conv1d(filters, k) on [B,T,C], VALID, stride 1 (model/tdnn.py:378-383); kernel [k,C,O]."""
+    return conv_1xk(x, np.asarray(kernel)[None], bias)
+
+
+# frame-level layer table of etdnn (model/tdnn.py:376-518): (name, conv kernel width or 0 for dense)
+ETDNN_FRAME_LAYERS = (("tdnn1", 5), ("tdnn2", 0), ("tdnn3", 5), ("tdnn4", 0), ("tdnn5", 7), ("tdnn6", 0),
+                      ("tdnn7", 9), ("tdnn8", 0), ("tdnn9", 0), ("tdnn10", 0))
+
+
+def etdnn(features, params, w):
+    """model/tdnn.py:343-591, inference: conv1d k=5,5,7,9 interleaved with 512-dense, tdnn9 dense, tdnn10 dense
+    (num_nodes_pooling_layer), pooling, tdnn12, tdnn13.  Variable scope "etdnn"."""
+    ep = OrderedDict()
+    x = np.asarray(features, np.float64)
+    if "num_nodes_pooling_layer" not in params.dict:
+        params.dict["num_nodes_pooling_layer"] = 1500
+    for name, k in ETDNN_FRAME_LAYERS:
+        if k:
+            x = conv1d_valid(x, w["etdnn/%s_conv/kernel" % name], w["etdnn/%s_conv/bias" % name])
+            ep["%s_conv" % name] = x
+        else:
+            x = dense_layer(x, w["etdnn/%s_dense/kernel" % name], w["etdnn/%s_dense/bias" % name])
+            ep["%s_dense" % name] = x
+        x = batch_norm_infer(x, w, "etdnn/%s_bn" % name)
+        ep["%s_bn" % name] = x
+        x = activation(x, params, w, "etdnn/%s_relu" % name)
+        ep["%s_relu" % name] = x
+    x = general_pooling(x, None, ep, params, w, "etdnn")
+    x = _tail_layers(x, params, w, "etdnn", ep, "tdnn12", "tdnn13")
+    return x, ep
+
+
+# --------------------------------------------------------------------------- ResNet-18
+def same_pads(n_in, k, s):
+    """TensorFlow 'SAME' padding split: out = ceil(in/s); total = max((out-1)*s + k - in, 0); before = total//2."""
+    n_out = -(-n_in // s)
+    total = max((n_out - 1) * s + k - n_in, 0)
+    return n_out, total // 2, total - total // 2
+
+
+def conv2d_same(x, kernel, strides=(1, 1), bias=None):
+    """tf.layers.conv2d(padding='same', use_bias=False) on NHWC [B,T,F,C] (model/resnet.py:25-32);
+    kernel [kh,kw,Cin,Cout], cross-correlation, TF asymmetric SAME padding."""
+    x = np.asarray(x, np.float64)
+    k = np.asarray(kernel, np.float64)
+    kh, kw = k.shape[:2]
+    st, sf = strides
+    b, t, f, c = x.shape
+    to, pt0, pt1 = same_pads(t, kh, st)
+    fo, pf0, pf1 = same_pads(f, kw, sf)
+    xp = np.zeros((b, t + pt0 + pt1, f + pf0 + pf1, c), np.float64)
+    xp[:, pt0:pt0 + t, pf0:pf0 + f] = x
+    y = np.zeros((b, to, fo, k.shape[3]), np.float64)
+    for dh in range(kh):
+        for dw in range(kw):
+            y += xp[:, dh:dh + (to - 1) * st + 1:st, dw:dw + (fo - 1) * sf + 1:sf] @ k[dh, dw]
+    if bias is not None:
+        y = y + np.asarray(bias, np.float64)
+    return y
+
+
+def max_pool_3x3_same(x):
+    """tf.layers.max_pooling2d(x, (3,3), (1,1), padding='same') (model/resnet.py:230-231)."""
+    b, t, f, c = x.shape
+    xp = np.full((b, t + 2, f + 2, c), -np.inf)
+    xp[:, 1:t + 1, 1:f + 1] = x
+    y = np.full_like(x, -np.inf)
+    for dh in range(3):
+        for dw in range(3):
+            y = np.maximum(y, xp[:, dh:dh + t, dw:dw + f])
+    return y
+
+
+def _res_block(x, filters, strides, params, w, name, project):
+    """conv_block (project=True, model/resnet.py:9-87) / identity_block (:90-149) with two 3x3 convs."""
+    s = "resnet_18/" + name
+    y = conv2d_same(x, w[s + "_conv0/kernel"], strides)
+    y = batch_norm_infer(y, w, s + "_bn0")
+    y = activation(y, params, w, s + "_relu0")
+    y = conv2d_same(y, w[s + "_conv1/kernel"])
+    y = batch_norm_infer(y, w, s + "_bn1")
+    if project:
+        sc = conv2d_same(x, w[s + "_conv_short/kernel"], strides)
+        sc = batch_norm_infer(sc, w, s + "_bn_short")
+    else:
+        sc = x
+    return activation(y + sc, params, w, s + "_relu_final")
+
+
+def resnet_18(features, params, w, require_dim=None):
+    """model/resnet.py:152-351, inference.  The reference asserts a 40-dim input (:190); pass require_dim=40 to
+    keep that check (BASELINE.json config 4 also names 64-dim fbank, so the default accepts any F % 8 == 0)."""
+    x = np.asarray(features, np.float64)
+    if require_dim is not None:
+        assert x.shape[-1] == require_dim
+    assert x.shape[-1] % 8 == 0
+    time_stride = 2 if params.resnet_time_stride else 1
+    if "resnet_blocks" not in params.dict:
+        params.dict["resnet_blocks"] = [2, 2, 2, 2]
+    ep = OrderedDict()
+    x = x[:, :, :, None]
+    x = conv2d_same(x, w["resnet_18/conv0_1/kernel"])
+    x = batch_norm_infer(x, w, "resnet_18/conv0_bn")
+    x = activation(x, params, w, "resnet_18/conv0_relu")
+    if params.resnet_maxpooling:
+        x = max_pool_3x3_same(x)
+    for stage, filt in enumerate((64, 128, 256, 512)):
+        strides = (1, 1) if stage == 0 else (time_stride, 2)
+        x = _res_block(x, filt, strides, params, w, "conv%da" % (stage + 1), True)
+        for i in range(params.resnet_blocks[stage] - 1):
+            x = _res_block(x, filt, (1, 1), params, w, "conv%db_%d" % (stage + 1, i), False)
+    # conv5: (1, F') VALID with bias (model/resnet.py:256-267)
+    k5 = np.asarray(w["resnet_18/conv5/kernel"], np.float64)          # [1, F', 512, 512]
+    assert k5.shape[1] == x.shape[2]
+    x = np.einsum("btfc,fco->bto", x, k5[0]) + np.asarray(w["resnet_18/conv5/bias"], np.float64)
+    x = batch_norm_infer(x, w, "resnet_18/conv5_bn")
+    x = activation(x, params, w, "resnet_18/conv5_relu")
+    for name in ("dense1", "dense2"):
+        x = dense_layer(x, w["resnet_18/%s/kernel" % name], w["resnet_18/%s/bias" % name])
+        x = batch_norm_infer(x, w, "resnet_18/%s_bn" % name)
+        x = activation(x, params, w, "resnet_18/%s_relu" % name)
+    x = general_pooling(x, None, ep, params, w, "resnet_18")
+    x = _tail_layers(x, params, w, "resnet_18", ep, "tdnn6", "tdnn7")
+    return x, ep
+
+
+NETWORKS = {"tdnn": tdnn, "etdnn": etdnn, "resnet_18": resnet_18}
+
+
 def entire_network(features, params, w):
     """model/trainer.py:385-405."""
-    if params.network_type != "tdnn":
+    if params.network_type not in NETWORKS:
         raise NotImplementedError("Not implement %s network" % params.network_type)
-    x, ep = tdnn(features, params, w)
+    x, ep = NETWORKS[params.network_type](features, params, w)
     ep["output"] = x
     if "feature_norm" in params.dict and params.feature_norm:
         assert "feature_scaling_factor" in params.dict

@@ -149,3 +149,113 @@ def packed_features(lengths, dim=30, seed=202):
     """Ragged utterances packed back to back: [sum(lengths), dim] fp32."""
     rng = np.random.default_rng(seed + 1)
     return mfcc_like(rng, int(np.sum(lengths)), dim)
+
+
+# ----------------------------------------------------------------------------- etdnn / resnet_18
+ETDNN_STAT_CONFIG = dict(TDNN_STAT_CONFIG, network_type="etdnn", embedding_node="tdnn12_dense")
+
+# egs/voxceleb/v3/nnet_conf/resnet18_softmax_1e-2.json (keys the forward path reads); v3/run.sh extracts
+# --node tdnn6_dense.
+RESNET_CONFIG = {
+    "network_type": "resnet_18",
+    "resnet_time_stride": False,
+    "resnet_maxpooling": False,
+    "last_layer_linear": False,
+    "loss_func": "softmax",
+    "pooling_type": "statistics_pooling",
+    "embedding_node": "tdnn6_dense",
+    "weight_l2_regularizer": 1e-2,
+    "batchnorm_momentum": 0.99,
+}
+
+ETDNN_LAYERS = (("tdnn1", 5), ("tdnn2", 0), ("tdnn3", 5), ("tdnn4", 0), ("tdnn5", 7), ("tdnn6", 0), ("tdnn7", 9),
+                ("tdnn8", 0), ("tdnn9", 0), ("tdnn10", 0))
+
+
+def make_etdnn_weights(dim, config=None, seed=1234, hidden=512):
+    """All variables etdnn() creates (model/tdnn.py:343-591; conv1d kernels are [k, Cin, Cout])."""
+    cfg = dict(ETDNN_STAT_CONFIG if config is None else config)
+    rng = np.random.default_rng(seed)
+    w = {}
+    pool_nodes = cfg.get("num_nodes_pooling_layer", 1500)
+    last_nodes = cfg.get("num_nodes_last_layer", 512)
+    prelu = cfg.get("network_relu_type", None) == "prelu"
+    cin = dim
+    for name, k in ETDNN_LAYERS:
+        cout = pool_nodes if name == "tdnn10" else hidden
+        if k:
+            w["etdnn/%s_conv/kernel" % name] = _glorot(rng, (k, cin, cout), k * cin, k * cout)
+            w["etdnn/%s_conv/bias" % name] = (0.1 * rng.standard_normal(cout)).astype(np.float32)
+        else:
+            _dense(rng, w, "etdnn/%s_dense" % name, cin, cout)
+        _bn(rng, w, "etdnn/%s_bn" % name, cout)
+        if prelu:
+            w["etdnn/%s_relu/alpha" % name] = rng.uniform(0.0, 0.3, cout).astype(np.float32)
+        cin = cout
+    _dense(rng, w, "etdnn/tdnn12_dense", 2 * pool_nodes, 512)
+    _bn(rng, w, "etdnn/tdnn12_bn", 512)
+    _dense(rng, w, "etdnn/tdnn13_dense", 512, last_nodes)
+    _bn(rng, w, "etdnn/tdnn13_bn", last_nodes)
+    if prelu:
+        w["etdnn/tdnn12_relu/alpha"] = rng.uniform(0.0, 0.3, 512).astype(np.float32)
+        w["etdnn/tdnn13_relu/alpha"] = rng.uniform(0.0, 0.3, last_nodes).astype(np.float32)
+    return w
+
+
+def make_resnet_weights(dim, config=None, seed=1234):
+    """All variables resnet_18() creates (model/resnet.py:209-349): 3x3 kernels [3,3,Cin,Cout] without bias,
+    1x1 projection shortcuts, conv5 [1, dim/8, 512, 512] with bias, dense1/dense2, tdnn6/tdnn7."""
+    cfg = dict(RESNET_CONFIG if config is None else config)
+    rng = np.random.default_rng(seed)
+    w = {}
+    prelu = cfg.get("network_relu_type", None) == "prelu"
+    blocks = cfg.get("resnet_blocks", [2, 2, 2, 2])
+    last_nodes = cfg.get("num_nodes_last_layer", 512)
+
+    def conv(name, kh, kw, cin, cout):
+        w["resnet_18/%s/kernel" % name] = _glorot(rng, (kh, kw, cin, cout), kh * kw * cin, kh * kw * cout)
+
+    def alpha(name, n):
+        if prelu:
+            w["resnet_18/%s/alpha" % name] = rng.uniform(0.0, 0.3, n).astype(np.float32)
+
+    conv("conv0_1", 3, 3, 1, 64)
+    _bn(rng, w, "resnet_18/conv0_bn", 64)
+    alpha("conv0_relu", 64)
+    cin = 64
+    for stage, filt in enumerate((64, 128, 256, 512)):
+        names = ["conv%da" % (stage + 1)] + ["conv%db_%d" % (stage + 1, i) for i in range(blocks[stage] - 1)]
+        for bi, name in enumerate(names):
+            conv(name + "_conv0", 3, 3, cin, filt)
+            _bn(rng, w, "resnet_18/%s_bn0" % name, filt)
+            alpha(name + "_relu0", filt)
+            conv(name + "_conv1", 3, 3, filt, filt)
+            _bn(rng, w, "resnet_18/%s_bn1" % name, filt)
+            if bi == 0:
+                conv(name + "_conv_short", 1, 1, cin, filt)
+                _bn(rng, w, "resnet_18/%s_bn_short" % name, filt)
+            alpha(name + "_relu_final", filt)
+            cin = filt
+    fq = dim // 8
+    conv("conv5", 1, fq, 512, 512)
+    w["resnet_18/conv5/bias"] = (0.1 * rng.standard_normal(512)).astype(np.float32)
+    _bn(rng, w, "resnet_18/conv5_bn", 512)
+    alpha("conv5_relu", 512)
+    _dense(rng, w, "resnet_18/dense1", 512, 512)
+    _bn(rng, w, "resnet_18/dense1_bn", 512)
+    alpha("dense1_relu", 512)
+    _dense(rng, w, "resnet_18/dense2", 512, 1500)
+    _bn(rng, w, "resnet_18/dense2_bn", 1500)
+    alpha("dense2_relu", 1500)
+    _dense(rng, w, "resnet_18/tdnn6_dense", 3000, 512)
+    _bn(rng, w, "resnet_18/tdnn6_bn", 512)
+    alpha("tdnn6_relu", 512)
+    _dense(rng, w, "resnet_18/tdnn7_dense", 512, last_nodes)
+    _bn(rng, w, "resnet_18/tdnn7_bn", last_nodes)
+    alpha("tdnn7_relu", last_nodes)
+    return w
+
+
+def fbank_like(n_frames, dim, seed):
+    """CMN'd log-mel-like rows: N(0,1) (SURVEY.md 8(d) cfg 3/4)."""
+    return np.random.default_rng(seed).standard_normal((n_frames, dim), dtype=np.float32)

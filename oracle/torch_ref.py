@@ -142,6 +142,102 @@ class TorchTdnn(object):
         return e[0] if squeeze else e
 
 
+class TorchEtdnn(TorchTdnn):
+    """etdnn() up to `tdnn12_dense` (model/tdnn.py:343-536), fp32, statistics pooling."""
+
+    LAYERS = (("tdnn1", 5), ("tdnn2", 0), ("tdnn3", 5), ("tdnn4", 0), ("tdnn5", 7), ("tdnn6", 0), ("tdnn7", 9),
+              ("tdnn8", 0), ("tdnn9", 0), ("tdnn10", 0))
+
+    def __init__(self, weights, config):
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32))
+        self.cfg = dict(config)
+        self.w = {k: t(v) for k, v in weights.items()}
+        self.kind = self.cfg.get("network_relu_type", None)
+
+    @torch.no_grad()
+    def embed(self, feats):
+        x = torch.from_numpy(np.ascontiguousarray(feats, dtype=np.float32))
+        squeeze = x.dim() == 2
+        if squeeze:
+            x = x.unsqueeze(0)
+        x = x.transpose(1, 2)                                    # [B,C,T]
+        for name, k in self.LAYERS:
+            if k:
+                # TF conv1d kernel [k,Cin,Cout] -> torch [Cout,Cin,k]
+                x = F.conv1d(x, self.w["etdnn/%s_conv/kernel" % name].permute(2, 1, 0).contiguous(),
+                             self.w["etdnn/%s_conv/bias" % name])
+            else:
+                x = F.linear(x.transpose(1, 2), self.w["etdnn/%s_dense/kernel" % name].t(),
+                             self.w["etdnn/%s_dense/bias" % name]).transpose(1, 2)
+            x = self._bn(x, "etdnn/%s_bn" % name)
+            x = self._act(x, "etdnn/%s_relu" % name, 1)
+        p = self.stat_pool(x)
+        e = F.linear(p, self.w["etdnn/tdnn12_dense/kernel"].t(), self.w["etdnn/tdnn12_dense/bias"]).numpy()
+        return e[0] if squeeze else e
+
+
+class TorchResnet18(TorchTdnn):
+    """resnet_18() up to `tdnn6_dense` (model/resnet.py:152-312), fp32, NCHW with H=time, W=freq.
+    TF 'SAME' padding is applied explicitly (asymmetric for stride 2: SURVEY.md 7.3-i)."""
+
+    def __init__(self, weights, config):
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32))
+        self.cfg = dict(config)
+        self.w = {k: t(v) for k, v in weights.items()}
+        self.kind = self.cfg.get("network_relu_type", None)
+
+    def _conv_same(self, x, name, strides=(1, 1)):
+        k = self.w["resnet_18/%s/kernel" % name]                 # [kh,kw,Cin,Cout]
+        kh, kw = k.shape[0], k.shape[1]
+        pads = []
+        for n_in, kk, s in ((x.shape[3], kw, strides[1]), (x.shape[2], kh, strides[0])):   # F.pad: last dim first
+            n_out = -(-n_in // s)
+            total = max((n_out - 1) * s + kk - n_in, 0)
+            pads += [total // 2, total - total // 2]
+        x = F.pad(x, pads)
+        return F.conv2d(x, k.permute(3, 2, 0, 1).contiguous(), None, stride=strides)
+
+    def _block(self, x, name, strides, project):
+        s = "resnet_18/" + name
+        y = self._conv_same(x, name + "_conv0", strides)
+        y = self._act(self._bn(y, s + "_bn0"), s + "_relu0", 1)
+        y = self._bn(self._conv_same(y, name + "_conv1"), s + "_bn1")
+        sc = self._bn(self._conv_same(x, name + "_conv_short", strides), s + "_bn_short") if project else x
+        return self._act(y + sc, s + "_relu_final", 1)
+
+    @torch.no_grad()
+    def embed(self, feats):
+        x = torch.from_numpy(np.ascontiguousarray(feats, dtype=np.float32))
+        squeeze = x.dim() == 2
+        if squeeze:
+            x = x.unsqueeze(0)
+        x = x.unsqueeze(1)                                       # [B,1,T,F]
+        x = self._act(self._bn(self._conv_same(x, "conv0_1"), "resnet_18/conv0_bn"), "resnet_18/conv0_relu", 1)
+        if self.cfg.get("resnet_maxpooling", False):
+            x = F.max_pool2d(x, 3, 1, 1)
+        ts = 2 if self.cfg.get("resnet_time_stride", False) else 1
+        blocks = self.cfg.get("resnet_blocks", [2, 2, 2, 2])
+        for stage in range(4):
+            x = self._block(x, "conv%da" % (stage + 1), (1, 1) if stage == 0 else (ts, 2), True)
+            for i in range(blocks[stage] - 1):
+                x = self._block(x, "conv%db_%d" % (stage + 1, i), (1, 1), False)
+        k5 = self.w["resnet_18/conv5/kernel"]                    # [1,F',512,512]
+        x = F.conv2d(x, k5.permute(3, 2, 0, 1).contiguous(), self.w["resnet_18/conv5/bias"])
+        x = self._act(self._bn(x, "resnet_18/conv5_bn"), "resnet_18/conv5_relu", 1).squeeze(3)   # [B,512,T]
+        for name in ("dense1", "dense2"):
+            x = F.linear(x.transpose(1, 2), self.w["resnet_18/%s/kernel" % name].t(),
+                         self.w["resnet_18/%s/bias" % name]).transpose(1, 2)
+            x = self._act(self._bn(x, "resnet_18/%s_bn" % name), "resnet_18/%s_relu" % name, 1)
+        p = self.stat_pool(x)
+        e = F.linear(p, self.w["resnet_18/tdnn6_dense/kernel"].t(), self.w["resnet_18/tdnn6_dense/bias"]).numpy()
+        return e[0] if squeeze else e
+
+
+def make_net(weights, config):
+    kind = config.get("network_type", "tdnn")
+    return {"tdnn": TorchTdnn, "etdnn": TorchEtdnn, "resnet_18": TorchResnet18}[kind](weights, config)
+
+
 # ------------------------------------------------------------------- timed CPU baseline
 def _worker(args):
     weights, config, feats, lengths, idx, budget_s = args
@@ -150,7 +246,7 @@ def _worker(args):
         torch.set_num_interop_threads(1)
     except RuntimeError:
         pass
-    net = TorchTdnn(weights, config)
+    net = make_net(weights, config)
     offs = np.concatenate([[0], np.cumsum(lengths)])
     net.embed(feats[offs[idx[0]]:offs[idx[0] + 1]])            # warm-up, untimed
     frames = 0

@@ -122,3 +122,48 @@ def test_extract_embedding_chunk_average():
 def test_flops_model():
     assert abs(numpy_ref.tdnn_flops(300, 30) / 1e9 - 2.4529) < 1e-3
     assert abs(numpy_ref.tdnn_flops(200, 30) / 1e9 - 1.6023) < 1e-3
+
+
+@pytest.mark.parametrize("dim,ts,mp,relu,frames", [
+    (40, False, False, None, 33),            # the shipped resnet18_softmax_1e-2.json
+    (16, True, True, "prelu", 37),           # time stride (odd T -> asymmetric SAME padding) + max pooling
+    (24, True, False, "lrelu", 30),
+], ids=["v3_config", "tstride_maxpool_prelu", "tstride_lrelu"])
+def test_resnet18_restatements_agree(dim, ts, mp, relu, frames):
+    cfg = dict(synth.RESNET_CONFIG, resnet_time_stride=ts, resnet_maxpooling=mp)
+    if relu:
+        cfg["network_relu_type"] = relu
+    w = synth.make_resnet_weights(dim, cfg, seed=11)
+    x = synth.fbank_like(2 * frames, dim, seed=5).reshape(2, frames, dim)
+    e64 = numpy_ref.predict(x, numpy_ref.OracleParams(**cfg), w, dim)
+    e32 = torch_ref.make_net(w, cfg).embed(x)
+    assert e64.shape == (2, 512)
+    assert np.abs(e64 - e32).max() / np.abs(e64).max() < 1e-5
+
+
+def test_same_padding_is_tensorflow_asymmetric():
+    # 40 -> 20 with k=3, s=2: TF pads (0, 1), not the symmetric (1, 1) of other frameworks
+    assert numpy_ref.same_pads(40, 3, 2) == (20, 0, 1)
+    assert numpy_ref.same_pads(5, 3, 2) == (3, 1, 1)
+    assert numpy_ref.same_pads(37, 3, 1) == (37, 1, 1)
+    assert numpy_ref.same_pads(37, 1, 2) == (19, 0, 0)
+    x = np.arange(2 * 6 * 4, dtype=np.float64).reshape(1, 6, 4, 2)
+    k = np.zeros((3, 3, 2, 1))
+    k[0, 0, 0, 0] = 1.0                       # picks input (t-pt0+0, f-pf0+0), channel 0
+    y = numpy_ref.conv2d_same(x, k, (1, 2))
+    # time: pad (1,1) -> row t-1; freq: pad (0,1) with stride 2 -> column 2*fo
+    assert y.shape == (1, 6, 2, 1)
+    np.testing.assert_array_equal(y[0, 1:, :, 0], x[0, :-1, ::2, 0])
+    np.testing.assert_array_equal(y[0, 0], 0.0)
+
+
+def test_etdnn_restatements_agree():
+    cfg = dict(synth.ETDNN_STAT_CONFIG)
+    w = synth.make_etdnn_weights(30, cfg, seed=4)
+    x = synth.config1_features(2, 90, 30, seed=3)
+    e64 = numpy_ref.predict(x, numpy_ref.OracleParams(**cfg), w, 30)
+    e32 = torch_ref.make_net(w, cfg).embed(x)
+    assert e64.shape == (2, 512)
+    assert np.abs(e64 - e32).max() / np.abs(e64).max() < 1e-5
+    _, ep = numpy_ref.entire_network(x, numpy_ref.OracleParams(**cfg), w)
+    assert ep["tdnn10_relu"].shape == (2, 90 - 22, 1500)          # context 4+4+6+8
