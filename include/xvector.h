@@ -158,6 +158,17 @@ int   xv_gemm_bf16_async(xv_ctx* ctx, const void* a_dev, int64_t a_rows, int32_t
                          const void* wt_dev, int32_t n, const float* scale_dev, const float* shift_dev,
                          const float* slope_dev, void* out_dev, int64_t m_rows);
 
+/* One 2-D convolution of the ResNet-18 front end on the implicit-GEMM tcgen05 path (kernel-level tests and the
+ * conv roofline bench): replaces tf.layers.conv2d(padding='same', use_bias=False) + batch_normalization
+ * [+ shortcut] + activation of model/resnet.py:25-86.  x [nb,t,f,cin] bf16 NHWC (device), wt [cout][kh*kw*cin]
+ * bf16 K-major (device; TF kernel [kh,kw,cin,cout] transposed), strides st/sf in {1,2} (TensorFlow SAME padding),
+ * out [nb,ceil(t/st),ceil(f/sf),cout] bf16 = act(scale*conv + shift + residual); residual may be NULL.
+ * cin % 64 == 0, cout % 64 == 0.  Asynchronous on the ctx stream. */
+int   xv_conv2d_bf16_async(xv_ctx* ctx, const void* x_dev, int32_t nb, int32_t t, int32_t f, int32_t cin,
+                           const void* wt_dev, int32_t kh, int32_t kw, int32_t st, int32_t sf, int32_t cout,
+                           const float* scale_dev, const float* shift_dev, const float* slope_dev,
+                           const void* residual_dev, void* out_dev);
+
 const char* xv_version(void);
 
 #ifdef __cplusplus

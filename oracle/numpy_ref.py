@@ -405,7 +405,7 @@ def resnet_18(features, params, w, require_dim=None):
     return x, ep
 
 
-NETWORKS = {"tdnn": tdnn, "etdnn": etdnn, "resnet_18": resnet_18}
+NETWORKS = {"tdnn": tdnn, "extended_tdnn": etdnn, "resnet_18": resnet_18}      # model/trainer.py:101-108
 
 
 def entire_network(features, params, w):

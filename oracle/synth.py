@@ -152,7 +152,7 @@ def packed_features(lengths, dim=30, seed=202):
 
 
 # ----------------------------------------------------------------------------- etdnn / resnet_18
-ETDNN_STAT_CONFIG = dict(TDNN_STAT_CONFIG, network_type="etdnn", embedding_node="tdnn12_dense")
+ETDNN_STAT_CONFIG = dict(TDNN_STAT_CONFIG, network_type="extended_tdnn", embedding_node="tdnn12_dense")
 
 # egs/voxceleb/v3/nnet_conf/resnet18_softmax_1e-2.json (keys the forward path reads); v3/run.sh extracts
 # --node tdnn6_dense.

@@ -235,7 +235,7 @@ class TorchResnet18(TorchTdnn):
 
 def make_net(weights, config):
     kind = config.get("network_type", "tdnn")
-    return {"tdnn": TorchTdnn, "etdnn": TorchEtdnn, "resnet_18": TorchResnet18}[kind](weights, config)
+    return {"tdnn": TorchTdnn, "extended_tdnn": TorchEtdnn, "resnet_18": TorchResnet18}[kind](weights, config)
 
 
 # ------------------------------------------------------------------- timed CPU baseline

@@ -65,6 +65,8 @@ PROTOTYPES = {
                                _p, C.c_int32, C.c_int64]),
     "xv_gemm_bf16_async": (C.c_int, [_p, _p, C.c_int64, C.c_int32, C.c_int32, C.c_int32, _p, C.c_int32, _p, _p, _p,
                                      _p, C.c_int64]),
+    "xv_conv2d_bf16_async": (C.c_int, [_p, _p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _p, C.c_int32, C.c_int32,
+                                       C.c_int32, C.c_int32, C.c_int32, _p, _p, _p, _p, _p]),
     "xv_version": (C.c_char_p, []),
 }
 

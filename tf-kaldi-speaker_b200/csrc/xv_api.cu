@@ -85,7 +85,7 @@ ProfScope::~ProfScope() {
 
 static int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
-static uint16_t f32_to_bf16_rne(float f) {
+uint16_t f32_to_bf16_rne(float f) {
   uint32_t u;
   memcpy(&u, &f, 4);
   if ((u & 0x7fffffffu) > 0x7f800000u) return static_cast<uint16_t>((u >> 16) | 0x40);   // NaN
@@ -139,6 +139,7 @@ static int last_stage(const Layer& l) {
 
 static int build_side_net(xv_ctx* c, const char* prefix, const JValue* nodes, int last_type, int in_buf, int in_dim,
                           std::vector<int>* out_layers, int* out_dim) {
+  const std::string att_scope = c->scope + "/attention";
   *out_dim = in_dim;
   if (!nodes || nodes->type != JValue::Arr) return XV_OK;
   const int n = static_cast<int>(nodes->arr.size());
@@ -157,7 +158,7 @@ static int build_side_net(xv_ctx* c, const char* prefix, const JValue* nodes, in
     }
     char name[64];
     snprintf(name, sizeof(name), "%s%d", prefix, i);
-    Layer l = make_layer("tdnn/attention", name, false, has_bn, act, 1, *out_dim, width, in_buf, true);
+    Layer l = make_layer(att_scope, name, false, has_bn, act, 1, *out_dim, width, in_buf, true);
     c->frame_layers.push_back(l);
     in_buf = static_cast<int>(c->frame_layers.size()) - 1;
     out_layers->push_back(in_buf);
@@ -169,12 +170,15 @@ static int build_side_net(xv_ctx* c, const char* prefix, const JValue* nodes, in
 static int build_plan(xv_ctx* c) {
   const JValue& cfg = c->cfg;
   const std::string net = jstr(cfg, "network_type", "");
-  if (net != "tdnn")
+  // model/trainer.py:101-110: tdnn | tdnn-s (dead: quit() at model/tdnn.py:201-202) | extended_tdnn | resnet_18
+  if (net != "tdnn" && net != "extended_tdnn" && net != "resnet_18")
     return fail(c, XV_EUNSUPPORTED, "Not implement %s network", net.c_str());   // model/trainer.py:109-110
+  c->resnet = net == "resnet_18";
+  c->scope = net == "tdnn" ? "tdnn" : (net == "extended_tdnn" ? "etdnn" : "resnet_18");
   c->relu_type = cfg.has("network_relu_type") ? jstr(cfg, "network_relu_type", "") : "";
   if (c->relu_type != "prelu" && c->relu_type != "lrelu") c->relu_type = "";
   c->pooling_type = jstr(cfg, "pooling_type", "");
-  c->embedding_node = jstr(cfg, "embedding_node", "tdnn6_dense");
+  c->embedding_node = jstr(cfg, "embedding_node", net == "extended_tdnn" ? "tdnn12_dense" : "tdnn6_dense");
   c->pool_nodes = jint(cfg, "num_nodes_pooling_layer", 1500);      // model/tdnn.py:114-116
   c->last_nodes = jint(cfg, "num_nodes_last_layer", 512);          // model/tdnn.py:152-154
   c->last_layer_no_bn = jbool(cfg, "last_layer_no_bn", false);     // :163-164
@@ -187,25 +191,55 @@ static int build_plan(xv_ctx* c) {
     c->feature_scaling_factor = static_cast<float>(f->num);
   }
   const int hidden = 512;
-  const int taps[3] = {5, 5, 7};
-  int ctx_sum = 0;
-  int cin = c->dim;
-  for (int i = 0; i < 3; ++i) {
-    char name[16];
-    snprintf(name, sizeof(name), "tdnn%d", i + 1);
-    c->frame_layers.push_back(make_layer("tdnn", name, true, true, kActRelu, taps[i], cin, hidden, i - 1, false));
-    cin = hidden;
+  std::vector<int> ctx_of;
+  const char* seg_names[2] = {"tdnn6", "tdnn7"};
+  if (c->resnet) {
+    // model/resnet.py:152-351.  The 2-D convolution stack (conv0_1 .. conv4b) is planned in xv_resnet.cu; its
+    // output [B, T', F', 512] viewed as rows of F'*512 values feeds conv5 (a (1,F') VALID conv = one GEMM),
+    // dense1 and dense2, which run on the same spliced-GEMM kernel as the TDNN frame layers.
+    c->resnet_pool_nodes = 1500;     // model/resnet.py:281-282 hard-codes 1500 (num_nodes_pooling_layer is not read)
+    c->pool_nodes = c->resnet_pool_nodes;
+    int rc = resnet_build_plan(c);
+    if (rc != XV_OK) return rc;
+    const int fq = c->resnet_f_out;
+    auto named = [&](const char* name, int cin, int cout, int in_buf) {
+      Layer l = make_layer("resnet_18", name, false, true, kActRelu, 1, cin, cout, in_buf, false);
+      l.kernel_var = std::string("resnet_18/") + name + "/kernel";
+      l.bias_var = std::string("resnet_18/") + name + "/bias";
+      l.ep[0] = l.ep[1] = l.ep[2] = "";      // resnet_18 publishes no frame-level endpoints (model/resnet.py:303-349)
+      return l;
+    };
+    c->frame_layers.push_back(named("conv5", fq * 512, hidden, -1));
+    c->frame_layers.push_back(named("dense1", hidden, hidden, 0));
+    c->frame_layers.push_back(named("dense2", hidden, c->pool_nodes, 1));
+    c->n_main_frame = 3;
+    c->total_context = 0;
+    ctx_of.assign(3, 0);
+  } else {
+    // (name, conv kernel width | 0 = dense) per frame layer: model/tdnn.py:38-130 and :376-518
+    struct Row { const char* name; int taps; };
+    static const Row tdnn_rows[] = {{"tdnn1", 5}, {"tdnn2", 5}, {"tdnn3", 7}, {"tdnn4", 0}, {"tdnn5", 0}};
+    static const Row etdnn_rows[] = {{"tdnn1", 5}, {"tdnn2", 0}, {"tdnn3", 5}, {"tdnn4", 0}, {"tdnn5", 7},
+                                     {"tdnn6", 0}, {"tdnn7", 9}, {"tdnn8", 0}, {"tdnn9", 0}, {"tdnn10", 0}};
+    const bool ext = net == "extended_tdnn";
+    const Row* rows = ext ? etdnn_rows : tdnn_rows;
+    const int n_rows = ext ? 10 : 5;
+    if (ext) { seg_names[0] = "tdnn12"; seg_names[1] = "tdnn13"; }
+    int ctx_sum = 0;
+    int cin = c->dim;
+    for (int i = 0; i < n_rows; ++i) {
+      const bool conv = rows[i].taps > 0;
+      const int cout = i == n_rows - 1 ? c->pool_nodes : hidden;
+      c->frame_layers.push_back(make_layer(c->scope, rows[i].name, conv, true, kActRelu, conv ? rows[i].taps : 1, cin,
+                                           cout, i - 1, false));
+      cin = cout;
+      ctx_sum += c->frame_layers[i].taps - 1;
+      ctx_of.push_back(ctx_sum);
+    }
+    c->n_main_frame = n_rows;
+    c->total_context = ctx_sum;
   }
-  c->frame_layers.push_back(make_layer("tdnn", "tdnn4", false, true, kActRelu, 1, hidden, hidden, 2, false));
-  c->frame_layers.push_back(make_layer("tdnn", "tdnn5", false, true, kActRelu, 1, hidden, c->pool_nodes, 3, false));
-  c->n_main_frame = 5;
-  std::vector<int> ctx_of(5);
-  for (int i = 0; i < 5; ++i) {
-    ctx_sum += c->frame_layers[i].taps - 1;
-    ctx_of[i] = ctx_sum;
-  }
-  c->total_context = ctx_sum;
-  for (int i = 0; i < 5; ++i) {
+  for (int i = 0; i < c->n_main_frame; ++i) {
     const Layer& l = c->frame_layers[i];
     for (int s = 0; s < 3; ++s) {
       if (l.ep[s].empty()) continue;
@@ -288,8 +322,8 @@ static int build_plan(xv_ctx* c) {
   p.level = 1; p.kind = 1; p.width = c->pooled_dim;
   c->nodes["pooling"] = p;
   // ---- segment level ----
-  c->seg_layers.push_back(make_layer("tdnn", "tdnn6", false, true, kActRelu, 1, c->pooled_dim, 512, -1, false));
-  c->seg_layers.push_back(make_layer("tdnn", "tdnn7", false, !c->last_layer_no_bn,
+  c->seg_layers.push_back(make_layer(c->scope, seg_names[0], false, true, kActRelu, 1, c->pooled_dim, 512, -1, false));
+  c->seg_layers.push_back(make_layer(c->scope, seg_names[1], false, !c->last_layer_no_bn,
                                      c->last_layer_linear ? kActNone : kActRelu, 1, 512, c->last_nodes, -1, false));
   for (int i = 0; i < 2; ++i) {
     const Layer& l = c->seg_layers[i];
@@ -328,12 +362,12 @@ static int build_plan(xv_ctx* c) {
 }
 
 // ---- weight folding ---------------------------------------------------------------------------
-static const HostTensor* find_weight(xv_ctx* c, const std::string& name) {
+const HostTensor* find_weight(xv_ctx* c, const std::string& name) {
   auto it = c->weights.find(name);
   return it == c->weights.end() ? nullptr : &it->second;
 }
 
-static int upload(xv_ctx* c, DevBuf* b, const void* host, size_t bytes) {
+int upload(xv_ctx* c, DevBuf* b, const void* host, size_t bytes) {
   int rc = ensure(c, b, bytes);
   if (rc != XV_OK) return rc;
   cudaError_t e = cudaMemcpy(b->p, host, bytes, cudaMemcpyHostToDevice);
@@ -351,7 +385,7 @@ static int need_vec(xv_ctx* c, const std::string& name, int n, const HostTensor*
 }
 
 // s = gamma / sqrt(var + eps), h = beta - s * mean   (inference BN, eps = 1e-3)
-static int fold_bn(xv_ctx* c, const std::string& scope, int n, std::vector<double>* s, std::vector<double>* h) {
+int fold_bn(xv_ctx* c, const std::string& scope, int n, std::vector<double>* s, std::vector<double>* h) {
   const HostTensor *g, *b, *m, *v;
   int rc;
   if ((rc = need_vec(c, scope + "/gamma", n, &g)) != XV_OK) return rc;
@@ -388,8 +422,11 @@ static int finalize_layer(xv_ctx* c, Layer& l) {
   if (!k) return fail(c, XV_ENOTFOUND, "missing variable '%s'", l.kernel_var.c_str());
   const int K = l.taps * l.cin;
   bool shape_ok;
-  if (k->shape.size() == 4)
-    shape_ok = k->shape[0] == 1 && k->shape[1] == l.taps && k->shape[2] == l.cin && k->shape[3] == l.cout;
+  if (k->shape.size() == 4)        // conv2d (1,k): [1,k,Cin,Cout]; resnet conv5 (1,F') over [F',512] rows: [1,F',512,Cout]
+    shape_ok = k->shape[0] == 1 && k->shape[1] * k->shape[2] == static_cast<int64_t>(l.taps) * l.cin && k->shape[3] == l.cout &&
+               (k->shape[1] == l.taps || l.taps == 1);
+  else if (k->shape.size() == 3)   // conv1d: [k,Cin,Cout] (model/tdnn.py:378-383)
+    shape_ok = k->shape[0] == l.taps && k->shape[1] == l.cin && k->shape[2] == l.cout;
   else
     shape_ok = k->shape.size() == 2 && l.taps == 1 && k->shape[0] == l.cin && k->shape[1] == l.cout;
   if (!shape_ok)
@@ -498,7 +535,9 @@ int xv_create(int device, const char* config_json, xv_ctx** out) {
     delete c;
     return rc;
   }
+  if (c->resnet && !c->cfg.has("batch_frames")) c->batch_frames = 16384;   // keeps a stage's activations L2-sized
   const char* ge = gemm_init();
+  if (!ge && c->resnet) ge = conv_gemm_init();
   if (ge) {
     fail(nullptr, XV_ECUDA, "%s", ge);
     delete c;
@@ -531,6 +570,7 @@ void xv_destroy(xv_ctx* c) {
   };
   for (Layer& l : c->frame_layers) rel_layer(l);
   for (Layer& l : c->seg_layers) rel_layer(l);
+  resnet_release(c);
   for (DevBuf& b : c->frame_out) release(&b);
   DevBuf* bufs[] = {&c->att_query, &c->att_post_scale, &c->att_post_shift, &c->att_post_slope, &c->d_feats,
                     &c->d_feat_ring[0], &c->d_feat_ring[1], &c->a1, &c->scores, &c->pool_acc, &c->pool_ws,
@@ -572,24 +612,26 @@ int xv_finalize_weights(xv_ctx* c) {
   if (!c) return XV_EINVAL;
   cudaSetDevice(c->device);
   int rc;
+  if (c->resnet && (rc = resnet_finalize(c)) != XV_OK) return rc;
   for (Layer& l : c->frame_layers)
     if ((rc = finalize_layer(c, l)) != XV_OK) return rc;
   for (Layer& l : c->seg_layers)
     if ((rc = finalize_layer(c, l)) != XV_OK) return rc;
   if (c->pooling_type == "self_attention") {
-    const HostTensor* q = find_weight(c, "tdnn/attention/query");
-    if (!q) return fail(c, XV_ENOTFOUND, "missing variable 'tdnn/attention/query'");
+    const std::string qname = c->scope + "/attention/query";
+    const HostTensor* q = find_weight(c, qname);
+    if (!q) return fail(c, XV_ENOTFOUND, "missing variable '%s'", qname.c_str());
     if (q->shape.size() != 2 || q->shape[0] != c->att_heads || q->shape[1] != c->att_dk)
-      return fail(c, XV_EINVAL, "variable 'tdnn/attention/query' must be [%d, %d]", c->att_heads, c->att_dk);
+      return fail(c, XV_EINVAL, "variable '%s' must be [%d, %d]", qname.c_str(), c->att_heads, c->att_dk);
     if ((rc = upload(c, &c->att_query, q->data.data(), q->data.size() * sizeof(float))) != XV_OK) return rc;
     if (c->has_att_post) {
       std::vector<double> s, h;
-      if ((rc = fold_bn(c, "tdnn/attention/att_post_bn", c->pooled_dim, &s, &h)) != XV_OK) return rc;
+      if ((rc = fold_bn(c, c->scope + "/attention/att_post_bn", c->pooled_dim, &s, &h)) != XV_OK) return rc;
       std::vector<float> sf(c->pooled_dim), hf(c->pooled_dim), sl;
       for (int i = 0; i < c->pooled_dim; ++i) { sf[i] = static_cast<float>(s[i]); hf[i] = static_cast<float>(h[i]); }
       Layer fake;
       fake.act = kActRelu;
-      if ((rc = act_slopes(c, fake, c->pooled_dim, "tdnn/attention/att_post_relu/alpha", &sl)) != XV_OK) return rc;
+      if ((rc = act_slopes(c, fake, c->pooled_dim, c->scope + "/attention/att_post_relu/alpha", &sl)) != XV_OK) return rc;
       if ((rc = upload(c, &c->att_post_scale, sf.data(), sf.size() * 4)) != XV_OK) return rc;
       if ((rc = upload(c, &c->att_post_shift, hf.data(), hf.size() * 4)) != XV_OK) return rc;
       if ((rc = upload(c, &c->att_post_slope, sl.data(), sl.size() * 4)) != XV_OK) return rc;

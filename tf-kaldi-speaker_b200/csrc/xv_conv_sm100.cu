@@ -1,0 +1,291 @@
+// 2-D convolution of the ResNet-18 front end as an implicit GEMM on sm_100a: the im2col operand never exists.
+//
+// Replaces tf.layers.conv2d(padding='same', use_bias=False) -> tf.layers.batch_normalization [-> + shortcut]
+// [-> relu] of conv_block / identity_block (model/resnet.py:9-149).
+//
+// Activations are NHWC bf16 [B, T, F, C] (H = time, W = frequency).  An output tile is a box of tb time steps x
+// fb frequency bins of ONE utterance (fb*tb <= 128 rows of the UMMA M dimension); for kernel tap (dt, df) and
+// channel block cb the A operand of that tile is the same box shifted by the tap, which is exactly one TMA box
+// of a 5-D tensor map over the input viewed as [B][T/st][st][F/sf][sf*C] (st, sf = strides; the parity split
+// turns a strided read into a dense box).  Coordinates that fall outside the utterance (TensorFlow 'SAME'
+// padding, asymmetric for stride 2) are zero-filled by the TMA unit, so padding costs nothing and utterances
+// never see each other's frames.  B = bf16 weights [Cout][kh*kw*Cin] (K-major), accumulators in TMEM.
+//
+// Warp roles as in xv_gemm_sm100.cu: warp 0 TMA producer, warp 1 MMA issuer, warps 2-9 epilogue
+// (tcgen05.ld -> folded BN affine -> + residual -> activation -> bf16).  The four warps that share a column
+// half stage their 128 rows x 32 columns in one SWIZZLE_64B buffer and ONE 4-D TMA store writes the
+// (32 ch, fb, tb) box; rows beyond the utterance end are clipped by the tensor map.
+#include <stdio.h>
+
+#include "xv_internal.h"
+#include "xv_ptx.cuh"
+
+namespace xv {
+
+namespace {
+
+constexpr int kConvEpiWarps = 8;
+constexpr uint32_t kConvABytes = kBM * kBK * 2;   // 16384
+
+template <int BN>
+struct ConvSmem {
+  static constexpr uint32_t kBBytes = BN * kBK * 2;
+  static constexpr uint32_t kStage = kConvABytes + kBBytes;
+  static constexpr uint32_t kRing = kStages * kStage;
+  static constexpr uint32_t kParams = kAccStages * BN * 12;
+  static constexpr uint32_t kStaging = 2 * 128 * 64;          // one 128-row x 32-column bf16 buffer per column half
+  static constexpr uint32_t kTotal = 1024 + kRing + kParams + kStaging + 256;
+};
+static_assert(ConvSmem<256>::kTotal <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
+
+__device__ __forceinline__ uint32_t pack2(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ void unpack2(uint32_t u, float& a, float& b) {
+  a = __uint_as_float(u << 16);
+  b = __uint_as_float(u & 0xffff0000u);
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
+                    const __grid_constant__ CUtensorMap tm_out, const __grid_constant__ ConvGemmParams p) {
+  using S = ConvSmem<BN>;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* ring = smem;
+  float2* ep_ss = reinterpret_cast<float2*>(smem + S::kRing);
+  float* ep_sl = reinterpret_cast<float*>(smem + S::kRing + kAccStages * BN * 8);
+  uint8_t* staging = smem + S::kRing + S::kParams;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(staging + S::kStaging);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + kStages;
+  uint64_t* tfull_bar = bars + 2 * kStages;
+  uint64_t* tempty_bar = tfull_bar + kAccStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + kAccStages);
+
+  const uint32_t warp = threadIdx.x >> 5;
+  const uint32_t lane = threadIdx.x & 31;
+  constexpr uint32_t kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tensormap(&tm_a);
+    ptx::prefetch_tensormap(&tm_b);
+    ptx::prefetch_tensormap(&tm_out);
+    for (int s = 0; s < kStages; ++s) {
+      ptx::mbar_init(&full_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < kAccStages; ++s) {
+      ptx::mbar_init(&tfull_bar[s], 1);
+      ptx::mbar_init(&tempty_bar[s], kConvEpiWarps);
+    }
+    ptx::fence_mbar_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_slot, kTmemCols);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int total_tiles = p.m_tiles * p.n_tiles;
+  const int num_kb = p.taps * p.kb_per_tap;
+  const int tiles_per_utt = p.tiles_t * p.tiles_f;
+  const uint32_t a_bytes = static_cast<uint32_t>(p.tile_rows) * kBK * 2;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int mt = t / p.n_tiles;
+        const int n0 = (t - mt * p.n_tiles) * BN;
+        const int b = mt / tiles_per_utt;
+        const int rem = mt - b * tiles_per_utt;
+        const int tt = rem / p.tiles_f;
+        const int to0 = tt * p.tb;
+        const int fo0 = (rem - tt * p.tiles_f) * p.fb;
+        for (int tap = 0; tap < p.taps; ++tap) {
+          const ConvTap tp = p.tap[tap];
+          for (int cb = 0; cb < p.kb_per_tap; ++cb) {
+            ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+            uint8_t* sa = ring + stage * S::kStage;
+            uint8_t* sb = sa + kConvABytes;
+            ptx::mbar_arrive_expect_tx(&full_bar[stage], a_bytes + S::kBBytes);
+            ptx::tma_load_5d(sa, &tm_a, &full_bar[stage], tp.c0 + cb * kBK, fo0 + tp.c1, tp.c2, to0 + tp.c3, b);
+            ptx::tma_load_2d(sb, &tm_b, &full_bar[stage], tap * p.cin + cb * kBK, n0);
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::make_idesc_bf16(kBM, BN);
+      uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
+        ptx::tc_fence_after();
+        const uint32_t tmem_d = tmem_base + as * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          ptx::mbar_wait(&full_bar[stage], phase);
+          ptx::tc_fence_after();
+          const uint32_t a_addr = ptx::smem_u32(ring + stage * S::kStage);
+          const uint64_t adesc = ptx::make_kmajor_sw128_desc(a_addr);
+          const uint64_t bdesc = ptx::make_kmajor_sw128_desc(a_addr + kConvABytes);
+#pragma unroll
+          for (int k = 0; k < kBK / kUK; ++k)
+            ptx::umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          ptx::umma_commit(&empty_bar[stage]);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+        ptx::umma_commit(&tfull_bar[as]);
+        if (++as == kAccStages) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..9) =====================
+    const uint32_t e = warp - 2;
+    const uint32_t q = warp & 3;                 // TMEM lane quarter
+    const uint32_t half = e >> 2;                // column half
+    const uint32_t etid = threadIdx.x - 64;
+    constexpr int kChunks = BN / 64;             // 32-column chunks per warp
+    uint8_t* stage_buf = staging + half * (128 * 64);
+    const bool issuer = q == 0 && lane == 0;
+    const bool relu_only = p.relu_only != 0;
+    const int r = q * 32 + lane;                 // row of the tile = TMEM lane
+    const int t_l = r / p.fb;
+    const int f_l = r - t_l * p.fb;
+    uint32_t as = 0, aphase = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      const int mt = t / p.n_tiles;
+      const int n0 = (t - mt * p.n_tiles) * BN;
+      const int b = mt / tiles_per_utt;
+      const int rem = mt - b * tiles_per_utt;
+      const int tt = rem / p.tiles_f;
+      const int to0 = tt * p.tb;
+      const int fo0 = (rem - tt * p.tiles_f) * p.fb;
+      float2* ss = ep_ss + as * BN;
+      float* sl = ep_sl + as * BN;
+      if (etid < BN) {
+        ss[etid] = make_float2(__ldg(p.scale + n0 + etid), __ldg(p.shift + n0 + etid));
+        sl[etid] = __ldg(p.slope + n0 + etid);
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      ptx::mbar_wait(&tfull_bar[as], aphase);
+      ptx::tc_fence_after();
+      const bool row_ok = r < p.tile_rows && (to0 + t_l) < p.t_out;
+      const __nv_bfloat16* res_row = nullptr;
+      if (p.residual != nullptr && row_ok)
+        res_row = p.residual + ((static_cast<size_t>(b) * p.t_alloc_res + to0 + t_l) * p.f_out + fo0 + f_l) * p.cout + n0;
+#pragma unroll 1
+      for (int ci = 0; ci < kChunks; ++ci) {
+        const int c = half * kChunks + ci;
+        uint32_t acc[32];
+        ptx::tmem_ld_32x32(tmem_base + ((q * 32) << 16) + as * BN + c * 32, acc);
+        uint4 rv[4];
+        if (res_row != nullptr) {
+          const uint4* rp = reinterpret_cast<const uint4*>(res_row + c * 32);
+#pragma unroll
+          for (int g = 0; g < 4; ++g) rv[g] = __ldg(rp + g);
+        } else {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) rv[g] = make_uint4(0, 0, 0, 0);
+        }
+        ptx::tmem_ld_wait();
+        if (ci == kChunks - 1) {
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
+        }
+        float y[32];
+        const float4* ss4 = reinterpret_cast<const float4*>(ss + c * 32);
+        const float2* sl2 = reinterpret_cast<const float2*>(sl + c * 32);
+        const uint32_t* rw = reinterpret_cast<const uint32_t*>(rv);
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const float4 sh = ss4[j];
+          float r0, r1;
+          unpack2(rw[j], r0, r1);
+          float v0 = fmaf(__uint_as_float(acc[2 * j]), sh.x, sh.y) + r0;
+          float v1 = fmaf(__uint_as_float(acc[2 * j + 1]), sh.z, sh.w) + r1;
+          if (relu_only) {
+            v0 = fmaxf(v0, 0.f);
+            v1 = fmaxf(v1, 0.f);
+          } else {
+            const float2 ng = sl2[j];
+            v0 = v0 >= 0.f ? v0 : v0 * ng.x;
+            v1 = v1 >= 0.f ? v1 : v1 * ng.y;
+          }
+          y[2 * j] = v0;
+          y[2 * j + 1] = v1;
+        }
+        // the previous chunk's bulk store must have finished reading the staging buffer
+        if (issuer) ptx::tma_store_wait_read<0>();
+        asm volatile("bar.sync %0, 128;" ::"r"(2 + half) : "memory");
+        uint8_t* rowp = stage_buf + r * 64;
+        const uint32_t sw = (r >> 1) & 3;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint4 v;
+          v.x = pack2(y[g * 8 + 0], y[g * 8 + 1]);
+          v.y = pack2(y[g * 8 + 2], y[g * 8 + 3]);
+          v.z = pack2(y[g * 8 + 4], y[g * 8 + 5]);
+          v.w = pack2(y[g * 8 + 6], y[g * 8 + 7]);
+          *reinterpret_cast<uint4*>(rowp + ((g ^ sw) << 4)) = v;
+        }
+        ptx::fence_proxy_async_smem();
+        asm volatile("bar.sync %0, 128;" ::"r"(2 + half) : "memory");
+        if (issuer) {
+          ptx::tma_store_4d(&tm_out, stage_buf, n0 + c * 32, fo0, to0, b);
+          ptx::tma_store_commit();
+        }
+      }
+      if (++as == kAccStages) { as = 0; aphase ^= 1; }
+    }
+    if (issuer) ptx::tma_store_wait<0>();
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+}  // namespace
+
+const char* conv_gemm_init() {
+  static char err[160];
+  cudaError_t e = cudaFuncSetAttribute(xv_conv_gemm_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, ConvSmem<64>::kTotal);
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(xv_conv_gemm_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, ConvSmem<128>::kTotal);
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(xv_conv_gemm_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, ConvSmem<256>::kTotal);
+  if (e != cudaSuccess) {
+    snprintf(err, sizeof(err), "cudaFuncSetAttribute(conv max dynamic smem) failed: %s", cudaGetErrorString(e));
+    return err;
+  }
+  return nullptr;
+}
+
+cudaError_t launch_conv_gemm(const ConvGemmPlan& plan, int sm_count, cudaStream_t stream) {
+  const int tiles = plan.p.m_tiles * plan.p.n_tiles;
+  if (tiles <= 0) return cudaSuccess;
+  const int grid = tiles < sm_count ? tiles : sm_count;
+  if (plan.bn == 64)
+    xv_conv_gemm_kernel<64><<<grid, kGemmThreads, ConvSmem<64>::kTotal, stream>>>(plan.tm_a, plan.tm_b, plan.tm_out, plan.p);
+  else if (plan.bn == 128)
+    xv_conv_gemm_kernel<128><<<grid, kGemmThreads, ConvSmem<128>::kTotal, stream>>>(plan.tm_a, plan.tm_b, plan.tm_out, plan.p);
+  else
+    xv_conv_gemm_kernel<256><<<grid, kGemmThreads, ConvSmem<256>::kTotal, stream>>>(plan.tm_a, plan.tm_b, plan.tm_out, plan.p);
+  return cudaGetLastError();
+}
+
+}  // namespace xv

@@ -62,10 +62,35 @@ struct NodeInfo {
   int kind = 0;      // utterance level: 0 layer output, 1 "pooling", 2 "att_output_before_nonlinear", 3 att_post_bn, 4 att_post_relu, 5 "output"
 };
 
+// One 2-D convolution of the ResNet-18 front end (model/resnet.py:9-149, 217-251): conv (no bias) -> BN
+// [-> + residual] [-> activation], NHWC.  Activations live in "slots" (ActSlot) that rotate over four buffers.
+struct ActSlot {
+  int buf = 0;            // index into xv_ctx::res_buf
+  int f = 0, c = 0;       // frequency bins, channels
+  int tshift = 0;         // number of stride-2 time reductions applied so far
+  bool pad_even = false;  // allocate an even number of time rows (zero pad row): read by a time-strided conv
+};
+struct ConvLayer {
+  std::string name, kernel_var, bn_scope, alpha_var;
+  int kh = 3, kw = 3, st = 1, sf = 1;
+  int cin = 0, cout = 0;
+  bool act = true;        // activation after (BN + residual)
+  int in_slot = -1, out_slot = -1, res_slot = -1;
+  bool plain_relu = false;
+  int bn_tile = 64;       // UMMA N of the tile: 64 | 128 | 256
+  DevBuf wt;              // bf16 [cout][kh*kw*cin], K-major
+  DevBuf w32;             // fp32 [kh*kw*cin][cout]
+  DevBuf scale, shift, slope;   // fp32 [cout]
+  CUtensorMap tm_b;
+};
+
 struct Batch {
   int32_t utt0 = 0, utt1 = 0;   // utterances [utt0, utt1)
-  int64_t row0 = 0;             // first packed row
+  int64_t row0 = 0;             // first packed row (rows of the frame-level tail: T' per utterance)
   int64_t rows = 0;
+  int64_t in_row0 = 0;          // first packed INPUT frame and number of input frames (differ from row0/rows only
+  int64_t in_rows = 0;          // for resnet_18 with time stride)
+  int32_t t_in = 0;             // resnet_18: the common utterance length of the batch
   int32_t seg0 = 0;             // first entry of this batch in the tile_seg_ptr / segs tables
   int32_t tile0 = 0;
   int32_t m_tiles = 0;
@@ -92,6 +117,8 @@ struct xv_ctx {
   int dim = 0;
   bool bf16 = true;
   int64_t batch_frames = 262144;
+  bool resnet = false;
+  std::string scope = "tdnn";    // variable scope: "tdnn" | "etdnn" | "resnet_18"
   std::string relu_type;         // "", "prelu", "lrelu"
   std::string pooling_type;
   std::string embedding_node;
@@ -115,6 +142,19 @@ struct xv_ctx {
   int total_context = 14;
   bool has_att_post = false;
   xv::DevBuf att_query, att_post_scale, att_post_shift, att_post_slope;
+
+  // ---- resnet_18 front end (xv_resnet.cu) ----
+  bool resnet_time_stride = false, resnet_maxpool = false;
+  int resnet_blocks[4] = {2, 2, 2, 2};
+  int resnet_pool_nodes = 1500;
+  int resnet_f_out = 0;                    // F' = dim / 8
+  int resnet_out_slot = -1;                // slot holding the stage-4 output
+  int resnet_conv0_slot = -1, resnet_pool_slot = -1;
+  std::vector<xv::ActSlot> slots;
+  std::vector<xv::ConvLayer> convs;        // conv1a_conv0 ... conv4b_conv1 (conv0_1 is the SIMT stem)
+  xv::DevBuf conv0_w, conv0_scale, conv0_shift, conv0_slope;   // stem: fp32 [9][64] + folded BN
+  xv::DevBuf res_buf[4];
+  std::vector<int32_t> cu_in;              // [n+1] packed input-frame offsets (== cu unless time stride)
 
   std::map<std::string, xv::HostTensor> weights;
   bool finalized = false;
@@ -172,6 +212,19 @@ struct ProfScope {
   ProfScope(xv_ctx* ctx, const char* family);
   ~ProfScope();
 };
+// resnet_18 front end (xv_resnet.cu)
+int resnet_build_plan(xv_ctx* c);
+int resnet_finalize(xv_ctx* c);
+int resnet_out_len(const xv_ctx* c, int t);      // frames after the (optional) three time strides
+// runs conv0_1 .. conv4b on `nb` utterances of `t` frames each (feats fp32 [nb*t, dim] on the device); *out points at
+// the stage-4 activations [nb*T', F'*512] (bf16, or fp32 in validation mode) inside a ctx-owned buffer.
+int resnet_run_batch(xv_ctx* c, const float* feats, int nb, int t, const void** out);
+void resnet_release(xv_ctx* c);
+// shared with xv_api.cu
+const HostTensor* find_weight(xv_ctx* c, const std::string& name);
+int upload(xv_ctx* c, DevBuf* b, const void* host, size_t bytes);
+int fold_bn(xv_ctx* c, const std::string& scope, int n, std::vector<double>* s, std::vector<double>* h);
+uint16_t f32_to_bf16_rne(float f);
 // forward pieces (xv_forward.cu)
 int plan_job(xv_ctx* c, const int32_t* lengths, int32_t n_utts);
 int run_job(xv_ctx* c, const char* node, bool pipelined_h2d, float* frames_out, const int64_t* frames_off,

@@ -21,14 +21,17 @@ int plan_job(xv_ctx* c, const int32_t* lengths, int32_t n_utts) {
   c->n_utts = n_utts;
   c->lengths.assign(lengths, lengths + n_utts);
   c->cu.assign(n_utts + 1, 0);
-  int64_t rows = 0;
+  c->cu_in.assign(n_utts + 1, 0);
+  int64_t rows = 0, tail_rows = 0;
   for (int u = 0; u < n_utts; ++u) {
-    if (lengths[u] <= c->total_context)
+    if (lengths[u] <= c->total_context || lengths[u] < 1)
       return fail(c, XV_EINVAL, "utterance %d has %d frames; the network context needs more than %d", u, lengths[u],
                   c->total_context);
     rows += lengths[u];
+    tail_rows += resnet_out_len(c, lengths[u]);     // == lengths[u] unless resnet_18 with time stride
     if (rows >= (int64_t(1) << 31) - 4096) return fail(c, XV_EINVAL, "more than 2^31 frames in one call");
-    c->cu[u + 1] = static_cast<int32_t>(rows);
+    c->cu_in[u + 1] = static_cast<int32_t>(rows);
+    c->cu[u + 1] = static_cast<int32_t>(tail_rows);
   }
   c->total_rows = rows;
   c->batches.clear();
@@ -39,11 +42,15 @@ int plan_job(xv_ctx* c, const int32_t* lengths, int32_t n_utts) {
     Batch b;
     b.utt0 = u;
     b.row0 = c->cu[u];
+    b.in_row0 = c->cu_in[u];
+    b.t_in = lengths[u];
     int64_t r = 0;
-    while (u < n_utts && (r == 0 || r + lengths[u] <= c->batch_frames)) r += lengths[u++];
+    // resnet_18: a batch is a run of EQUAL-length utterances (one 5-D tensor map describes [B,T,F,C])
+    while (u < n_utts && (r == 0 || (r + lengths[u] <= c->batch_frames && (!c->resnet || lengths[u] == b.t_in)))) r += lengths[u++];
     b.utt1 = u;
-    b.rows = r;
-    b.m_tiles = static_cast<int32_t>((r + kBM - 1) / kBM);
+    b.in_rows = r;
+    b.rows = c->cu[u] - b.row0;
+    b.m_tiles = static_cast<int32_t>((b.rows + kBM - 1) / kBM);
     b.tile0 = static_cast<int32_t>(c->tile_seg_ptr.size() / 2);
     // segment table: one valid-row range per utterance (batch-local rows); per tile the [lo,hi) range of
     // utterances whose valid rows intersect the tile.
@@ -51,7 +58,7 @@ int plan_job(xv_ctx* c, const int32_t* lengths, int32_t n_utts) {
       PoolSeg s;
       s.utt = v;
       s.r0 = static_cast<int32_t>(c->cu[v] - b.row0);
-      s.r1 = s.r0 + lengths[v] - c->total_context;
+      s.r1 = s.r0 + (c->cu[v + 1] - c->cu[v]) - c->total_context;
       s.pad = 0;
       c->segs[v] = s;
     }
@@ -211,8 +218,11 @@ int run_job(xv_ctx* c, const char* node_name, bool pipelined_h2d, float* frames_
   const int pool_layer = c->n_main_frame - 1;
 
   // ---- buffers ----
-  int64_t max_rows = 0;
-  for (const Batch& b : c->batches) max_rows = std::max(max_rows, b.rows);
+  int64_t max_rows = 0, max_in_rows = 0;
+  for (const Batch& b : c->batches) {
+    max_rows = std::max(max_rows, b.rows);
+    max_in_rows = std::max(max_in_rows, b.in_rows);
+  }
   const int64_t rows_alloc = round_up64(std::max<int64_t>(max_rows, 1), kBM);
   const size_t esz = c->bf16 ? 2 : 4;
   for (int l = 0; l < nl; ++l) {
@@ -222,10 +232,10 @@ int run_job(xv_ctx* c, const char* node_name, bool pipelined_h2d, float* frames_
     if ((rc = ensure(c, &c->frame_out[l], static_cast<size_t>(rows_alloc) * w * esz, true)) != XV_OK) return rc;
   }
   const Layer& l0 = c->frame_layers[0];
-  if (c->bf16 && (rc = ensure(c, &c->a1, static_cast<size_t>(rows_alloc) * l0.kpad * 2, true)) != XV_OK) return rc;
+  if (c->bf16 && !c->resnet && (rc = ensure(c, &c->a1, static_cast<size_t>(rows_alloc) * l0.kpad * 2, true)) != XV_OK) return rc;
   if (pipelined_h2d)
     for (int s = 0; s < 2; ++s)
-      if ((rc = ensure(c, &c->d_feat_ring[s], static_cast<size_t>(max_rows) * c->dim * 4)) != XV_OK) return rc;
+      if ((rc = ensure(c, &c->d_feat_ring[s], static_cast<size_t>(max_in_rows) * c->dim * 4)) != XV_OK) return rc;
   const Layer& l6 = c->seg_layers[0];
   const Layer& l7 = c->seg_layers[1];
   const int64_t n_alloc_rows = round_up64(std::max(n, 1), kBM);
@@ -266,8 +276,8 @@ int run_job(xv_ctx* c, const char* node_name, bool pipelined_h2d, float* frames_
     const float* feats_b;
     const int slot = static_cast<int>(bi & 1);
     if (pipelined_h2d) {
-      const float* src = c->host_feats + b.row0 * c->dim;
-      const size_t bytes = static_cast<size_t>(b.rows) * c->dim * 4;
+      const float* src = c->host_feats + b.in_row0 * c->dim;
+      const size_t bytes = static_cast<size_t>(b.in_rows) * c->dim * 4;
       if (bi >= 2 && (e = cudaStreamWaitEvent(c->copy_stream, c->buf_free[slot], 0)) != cudaSuccess)
         return cuda_fail(c, e, "cudaStreamWaitEvent");
       const void* from = src;
@@ -290,25 +300,33 @@ int run_job(xv_ctx* c, const char* node_name, bool pipelined_h2d, float* frames_
       if ((e = cudaStreamWaitEvent(c->stream, c->h2d_done[slot], 0)) != cudaSuccess) return cuda_fail(c, e, "cudaStreamWaitEvent");
       feats_b = static_cast<const float*>(c->d_feat_ring[slot].p);
     } else {
-      feats_b = static_cast<const float*>(c->d_feats.p) + b.row0 * c->dim;
+      feats_b = static_cast<const float*>(c->d_feats.p) + b.in_row0 * c->dim;
     }
     // ---- frame layers ----
-    if (c->bf16) {
+    const void* a_first = nullptr;          // operand of the first frame layer
+    if (c->resnet) {
+      // conv0_1 .. conv4b: [nb, T, F] -> [nb*T', F'*512]; conv5 then reads these rows as a plain GEMM operand
+      if ((rc = resnet_run_batch(c, feats_b, nb, b.t_in, &a_first)) != XV_OK) return rc;
+    } else if (c->bf16) {
       ProfScope ps(c, "splice_cast");
       e = launch_splice_cast(feats_b, b.rows, c->dim, l0.taps, l0.dil, static_cast<__nv_bfloat16*>(c->a1.p), l0.kpad, c->stream);
       if (e != cudaSuccess) return cuda_fail(c, e, "splice_cast launch");
+      a_first = c->a1.p;
+    } else {
+      a_first = feats_b;
     }
     for (int l = 0; l < nl; ++l) {
       if (stage_of[l] < 0) continue;
       const Layer& L = c->frame_layers[l];
       const bool pool_here = fuse_pool && l == pool_layer;
       if (c->bf16) {
-        const void* a = L.in_buf < 0 ? c->a1.p : c->frame_out[L.in_buf].p;
-        rc = gemm_layer(c, L, a, rows_alloc, stage_of[l], pool_here ? nullptr : static_cast<__nv_bfloat16*>(c->frame_out[l].p),
+        const void* a = L.in_buf < 0 ? a_first : c->frame_out[L.in_buf].p;
+        const int64_t a_rows = (L.in_buf < 0 && c->resnet) ? b.rows : rows_alloc;
+        rc = gemm_layer(c, L, a, a_rows, stage_of[l], pool_here ? nullptr : static_cast<__nv_bfloat16*>(c->frame_out[l].p),
                         nullptr, b.rows, pool_here, static_cast<double*>(c->pool_acc.p),
                         static_cast<const int32_t*>(c->d_tile_seg_ptr.p) + 2 * b.tile0, static_cast<const PoolSeg*>(c->d_segs.p));
       } else {
-        const float* a = L.in_buf < 0 ? feats_b : static_cast<const float*>(c->frame_out[L.in_buf].p);
+        const float* a = L.in_buf < 0 ? static_cast<const float*>(a_first) : static_cast<const float*>(c->frame_out[L.in_buf].p);
         rc = simt_layer(c, L, a, b.rows, stage_of[l], static_cast<float*>(c->frame_out[l].p), b.rows);
       }
       if (rc != XV_OK) return rc;

@@ -431,6 +431,26 @@ const char* make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t inner
   return nullptr;
 }
 
+const char* make_tmap_bf16_nd(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                              const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes) {
+  if (g_encode == nullptr) return "gemm_init() not called";
+  cuuint64_t d[5];
+  cuuint64_t st[4];
+  cuuint32_t bx[5], es[5];
+  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; bx[i] = box[i]; es[i] = 1; }
+  for (int i = 1; i < rank; ++i) st[i - 1] = strides_bytes[i];
+  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), d, st, bx, es,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    snprintf(g_err, sizeof(g_err), "cuTensorMapEncodeTiled(rank %d) failed (CUresult %d): dims=%llu,%llu,%llu box=%u,%u,%u base=%p",
+             rank, static_cast<int>(r), (unsigned long long)dims[0], (unsigned long long)dims[1],
+             (unsigned long long)(rank > 2 ? dims[2] : 0), box[0], box[1], rank > 2 ? box[2] : 0, base);
+    return g_err;
+  }
+  return nullptr;
+}
+
 cudaError_t launch_gemm(const GemmPlan& plan, int sm_count, cudaStream_t stream) {
   const int tiles = plan.p.m_tiles * plan.p.n_tiles;
   if (tiles <= 0) return cudaSuccess;

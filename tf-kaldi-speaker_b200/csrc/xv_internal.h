@@ -67,6 +67,38 @@ const char* make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t inner
                               uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_rows, int swizzle_bytes = 128);
 cudaError_t launch_gemm(const GemmPlan& plan, int sm_count, cudaStream_t stream);
 
+// ---- implicit-GEMM 2-D convolution (xv_conv_sm100.cu), ResNet-18 front end ----
+// Per-tap coordinate offsets into the 5-D input map (sf*C, F/sf, st, T/st, B): see xv_conv_sm100.cu.
+struct ConvTap {
+  int32_t c0, c1, c2, c3;
+};
+struct ConvGemmParams {
+  int32_t n_utts, t_out, f_out;
+  int32_t fb, tb;            // output tile = tb time steps x fb frequency bins (fb*tb <= 128)
+  int32_t tiles_f, tiles_t;  // f_out / fb, ceil(t_out / tb)
+  int32_t tile_rows;         // fb * tb
+  int32_t m_tiles, n_tiles;  // n_utts * tiles_t * tiles_f, cout / BN
+  int32_t taps, kb_per_tap, cin;
+  ConvTap tap[9];
+  const float* scale;        // folded BN: y = scale*acc + shift
+  const float* shift;
+  const float* slope;        // negative-side slope per channel (1 = no activation)
+  int32_t relu_only;
+  const __nv_bfloat16* residual;   // [n_utts][t_alloc_res][f_out][cout] added before the activation, or null
+  int32_t t_alloc_res;
+  int32_t cout;
+};
+struct ConvGemmPlan {
+  CUtensorMap tm_a, tm_b, tm_out;
+  ConvGemmParams p;
+  int bn;                    // 64 | 128 | 256
+};
+const char* conv_gemm_init();
+cudaError_t launch_conv_gemm(const ConvGemmPlan& plan, int sm_count, cudaStream_t stream);
+// rank-N bf16 tensor map (dims/strides innermost first; strides[0] is implied = 2 bytes).
+const char* make_tmap_bf16_nd(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                              const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes);
+
 // ---- SIMT / elementwise kernels (xv_kernels.cu) ----
 // features fp32 [rows, D] -> spliced bf16 [rows, kpad]: out[r, j*D + c] = in[r + j*dil, c] (0 beyond rows / kpad)
 cudaError_t launch_splice_cast(const float* feats, int64_t rows, int d, int taps, int dil, __nv_bfloat16* out,

@@ -34,13 +34,18 @@ class Endpoints(OrderedDict):
         return [self[k] for k in self.keys()]
 
 
-def endpoint_names(params):
-    """Names tdnn() adds to endpoints, in order (model/tdnn.py:48-179, model/pooling.py:24,198,220,227-229)."""
+TDNN_FRAME_LAYERS = (("tdnn1", True), ("tdnn2", True), ("tdnn3", True), ("tdnn4", False), ("tdnn5", False))
+# etdnn: conv1d k=5,5,7,9 interleaved with dense layers (model/tdnn.py:376-518)
+ETDNN_FRAME_LAYERS = (("tdnn1", True), ("tdnn2", False), ("tdnn3", True), ("tdnn4", False), ("tdnn5", True),
+                      ("tdnn6", False), ("tdnn7", True), ("tdnn8", False), ("tdnn9", False), ("tdnn10", False))
+
+
+def endpoint_names(params, frame_layers=TDNN_FRAME_LAYERS, seg=("tdnn6", "tdnn7")):
+    """Names tdnn()/etdnn() add to endpoints, in order (model/tdnn.py:48-179, :384-589,
+    model/pooling.py:24,198,220,227-229)."""
     names = []
-    for i in (1, 2, 3):
-        names += ["tdnn%d_conv" % i, "tdnn%d_bn" % i, "tdnn%d_relu" % i]
-    for i in (4, 5):
-        names += ["tdnn%d_dense" % i, "tdnn%d_bn" % i, "tdnn%d_relu" % i]
+    for name, conv in frame_layers:
+        names += ["%s_%s" % (name, "conv" if conv else "dense"), "%s_bn" % name, "%s_relu" % name]
     if params.pooling_type == "self_attention":
         def side(prefix, nodes, last_type):
             out = []
@@ -61,22 +66,17 @@ def endpoint_names(params):
         names += ["attention_weights", "att_output_before_nonlinear"]
         if params.att_apply_nonlinear:
             names += ["att_post_bn", "att_post_relu"]
-    names += ["pooling", "tdnn6_dense", "tdnn6_bn", "tdnn6_relu", "tdnn7_dense"]
+    names += ["pooling", "%s_dense" % seg[0], "%s_bn" % seg[0], "%s_relu" % seg[0], "%s_dense" % seg[1]]
     if not params.last_layer_no_bn:
-        names.append("tdnn7_bn")
+        names.append("%s_bn" % seg[1])
     if not params.last_layer_linear:
-        names.append("tdnn7_relu")
+        names.append("%s_relu" % seg[1])
     return names
 
 
-def tdnn(features, params, is_training=None, reuse_variables=None, aux_features=None):
-    """Build (= run) a TDNN network.  Same arguments and return value as the reference (model/tdnn.py:10):
-    returns (output of the last layer [batch, num_nodes_last_layer], endpoints).  `is_training` must be falsy:
-    this build covers the inference path; `reuse_variables` / `aux_features` are accepted and ignored."""
-    if is_training:
-        raise NotImplementedError("tdnn(is_training=True): the training graph is outside this build's scope")
-    # lazily injected defaults, exactly as the reference mutates params.dict (model/tdnn.py:114-116,152-154,163-164,173-174)
-    if "num_nodes_pooling_layer" not in params.dict:
+def _inject_defaults(params, pooling_layer=True):
+    """Defaults the reference injects lazily by mutating params.dict (model/tdnn.py:114-116,152-154,163-164,173-174)."""
+    if pooling_layer and "num_nodes_pooling_layer" not in params.dict:
         params.dict["num_nodes_pooling_layer"] = 1500
     if "num_nodes_last_layer" not in params.dict:
         params.dict["num_nodes_last_layer"] = 512
@@ -87,10 +87,14 @@ def tdnn(features, params, is_training=None, reuse_variables=None, aux_features=
     if params.pooling_type not in ("statistics_pooling", "self_attention"):
         raise NotImplementedError("Not implement %s pooling" % params.pooling_type)
 
+
+def _run_network(features, params, network_type, names, last_prefix):
     x = np.ascontiguousarray(features, dtype=np.float32)
     assert x.ndim == 3, "features must be [batch, length, dim]"
     b, t, d = x.shape
-    eng = V.get_engine(params, d)
+    cfg = dict(params.dict)
+    cfg["network_type"] = network_type
+    eng = V.get_engine(params, d, config=cfg)
     packed = x.reshape(b * t, d)
     lengths = np.full(b, t, np.int32)
 
@@ -100,6 +104,27 @@ def tdnn(features, params, is_training=None, reuse_variables=None, aux_features=
             return eng.forward(packed, lengths, node)
         return np.stack(eng.forward_frames(packed, lengths, node), axis=0)
 
-    endpoints = Endpoints(endpoint_names(params), compute)
-    last = "tdnn7_relu" if not params.last_layer_linear else ("tdnn7_bn" if not params.last_layer_no_bn else "tdnn7_dense")
+    endpoints = Endpoints(names, compute)
+    last = last_prefix + "_relu" if not params.last_layer_linear else (
+        last_prefix + "_bn" if not params.last_layer_no_bn else last_prefix + "_dense")
     return endpoints[last], endpoints
+
+
+def tdnn(features, params, is_training=None, reuse_variables=None, aux_features=None):
+    """Build (= run) a TDNN network.  Same arguments and return value as the reference (model/tdnn.py:10):
+    returns (output of the last layer [batch, num_nodes_last_layer], endpoints).  `is_training` must be falsy:
+    this build covers the inference path; `reuse_variables` / `aux_features` are accepted and ignored."""
+    if is_training:
+        raise NotImplementedError("tdnn(is_training=True): the training graph is outside this build's scope")
+    _inject_defaults(params)
+    return _run_network(features, params, "tdnn", endpoint_names(params), "tdnn7")
+
+
+def etdnn(features, params, is_training=None, reuse_variables=None, aux_features=None):
+    """Extended TDNN (model/tdnn.py:343-591): 10 frame layers, pooling, tdnn12, tdnn13; variable scope "etdnn".
+    Same arguments and return value as the reference."""
+    if is_training:
+        raise NotImplementedError("etdnn(is_training=True): the training graph is outside this build's scope")
+    _inject_defaults(params)
+    return _run_network(features, params, "extended_tdnn",
+                        endpoint_names(params, ETDNN_FRAME_LAYERS, ("tdnn12", "tdnn13")), "tdnn13")

@@ -7,9 +7,10 @@ import sys
 import numpy as np
 
 from ..engine import Engine
-from .tdnn import tdnn  # noqa: F401  (kept importable from here like the reference)
+from .tdnn import tdnn, etdnn  # noqa: F401  (kept importable from here like the reference)
+from .resnet import resnet_18  # noqa: F401
 
-_NETWORKS = ("tdnn",)
+_NETWORKS = ("tdnn", "extended_tdnn", "resnet_18")      # "tdnn-s" is dead code in the reference (quit() at model/tdnn.py:201)
 _KNOWN_NETWORKS = ("tdnn", "tdnn-s", "extended_tdnn", "resnet_18")
 _KNOWN_LOSSES = ("softmax", "asoftmax", "additive_margin_softmax", "additive_angular_margin_softmax",
                  "semihard_triplet_loss", "angular_triplet_loss", "generalized_angular_triplet_loss")

@@ -79,16 +79,18 @@ def _config_key(params_dict):
     return json.dumps(clean, sort_keys=True)
 
 
-def get_engine(params, dim, weights=None, prec=None, dev=None):
-    """Engine for (config, dim, precision, weight dict identity); built and weight-loaded on first use."""
+def get_engine(params, dim, weights=None, prec=None, dev=None, config=None):
+    """Engine for (config, dim, precision, weight dict identity); built and weight-loaded on first use.
+    `config` overrides params.dict (the network functions force their own network_type)."""
     from ..engine import Engine
     weights = current_weights() if weights is None else weights
     prec = prec or precision()
     dev = device() if dev is None else dev
-    key = (_config_key(params.dict), int(dim), prec, dev, id(weights))
+    cfg = params.dict if config is None else config
+    key = (_config_key(cfg), int(dim), prec, dev, id(weights))
     eng = _engines.get(key)
     if eng is None:
-        eng = Engine(params.dict, dim, precision=prec, device=dev)
+        eng = Engine(cfg, dim, precision=prec, device=dev)
         eng.set_weights(weights)
         eng._weights_ref = weights          # keep the dict alive so id() stays unique
         _engines[key] = eng
