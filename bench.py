@@ -112,6 +112,58 @@ def gemm_flops(lengths):
     return float(utterance_flops(lengths, DIM).sum())
 
 
+class Workload(object):
+    """What one bench step runs.  tdnn = BASELINE.json configs[1] (the headline); resnet18 = configs[3]
+    (secondary line, `--workload resnet18`): ResNet-18 + statistics pooling on fbank x 400 frames."""
+
+    def __init__(self, args, rank, world):
+        from oracle import synth                               # input/weight generators only (no path computation)
+        from xvector_b200 import scheduler
+        self.name = args.workload
+        if self.name == "tdnn":
+            self.dim = DIM
+            self.cfg = dict(synth.TDNN_STAT_CONFIG)
+            self.weights = synth.make_tdnn_weights(DIM, self.cfg, seed=1234)
+            self.utts = args.utts or UTTS_PER_GPU
+            self.lengths = make_shard(rank, world, self.utts)
+            self.batch_frames = args.batch_frames or 262144
+            self.scale = np.linspace(3.0, 0.5, DIM).astype(np.float32)
+            t = self.lengths.astype(np.float64)
+            self.layer_flops = {"gemm.tdnn1": 2 * 512 * 5 * DIM * (t - 4), "gemm.tdnn2": 2 * 512 * 2560 * (t - 8),
+                                "gemm.tdnn3": 2 * 512 * 3584 * (t - 14), "gemm.tdnn4": 2 * 512 * 512 * (t - 14),
+                                "gemm_pool.tdnn5": 2 * 512 * 1500 * (t - 14), "gemm.tdnn6": 2 * 3000 * 512 + 0 * t}
+            self.layer_flops = {k: float(v.sum()) for k, v in self.layer_flops.items()}
+            self.flops = float(scheduler.utterance_flops(self.lengths, DIM).sum())
+            self.tensor_prefixes = ("gemm",)
+            self.kernel = "xv_tdnn_gemm_kernel (tcgen05 spliced GEMM + fused epilogue), all 6 layer launches of a step"
+            self.workload = Workload.describe(args)
+        else:
+            self.dim = args.dim or 64
+            self.cfg = dict(synth.RESNET_CONFIG)
+            self.weights = synth.make_resnet_weights(self.dim, self.cfg, seed=1234)
+            self.utts = args.utts or 1024
+            self.lengths = np.full(self.utts, 400, np.int32)      # fixed 400-frame segments: every rank gets the same shard
+            self.batch_frames = args.batch_frames or 16384
+            self.scale = np.ones(self.dim, np.float32)
+            per = scheduler.resnet_layer_flops(400, self.dim)
+            per["gemm_pool.dense2"] = per.pop("gemm.dense2")          # statistics pooling is fused into dense2's epilogue
+            self.layer_flops = {k: v * self.utts for k, v in per.items()}
+            self.flops = float(sum(v for k, v in self.layer_flops.items() if k != "stem"))
+            self.tensor_prefixes = ("gemm", "conv")
+            self.kernel = ("xv_conv_gemm_kernel (tcgen05 implicit-GEMM 3x3/1x1 convolutions, fused BN+residual+ReLU) + "
+                           "xv_tdnn_gemm_kernel (conv5, dense1, dense2+pooling, tdnn6)")
+            self.workload = Workload.describe(args)
+        self.n_frames = int(self.lengths.sum())
+
+    @staticmethod
+    def describe(args):
+        if getattr(args, "workload", "tdnn") == "resnet18":
+            return ("configs[3]: ResNet-18 + statistics pooling (egs/voxceleb/v3) embedding extraction, "
+                    "%d-dim fbank x 400 frames" % (args.dim or 64))
+        return ("configs[1]: standard x-vector TDNN (5x512 frame layers, 1500 pre-pool, stats pooling, "
+                "tdnn6_dense 512-d) on 30-dim MFCC utterances of log-uniform length 200-6000 frames")
+
+
 def run_ours(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -125,15 +177,13 @@ def run_ours(args):
     import xvector_b200
     from oracle import synth
 
-    lengths = make_shard(rank, world, args.utts)
-    n_frames = int(lengths.sum())
-    cfg = dict(synth.TDNN_STAT_CONFIG)
-    weights = synth.make_tdnn_weights(DIM, cfg, seed=1234)
-    eng = xvector_b200.Engine(cfg, DIM, precision="bf16", device=local, batch_frames=args.batch_frames)
+    wl = Workload(args, rank, world)
+    lengths, n_frames, cfg, weights, DIM = wl.lengths, wl.n_frames, wl.cfg, wl.weights, wl.dim
+    eng = xvector_b200.Engine(cfg, DIM, precision="bf16", device=local, batch_frames=wl.batch_frames)
     eng.set_weights(weights)
     pin = xvector_b200.PinnedArray((n_frames, DIM))
     rng = np.random.default_rng(1000 + rank)
-    scale = np.linspace(3.0, 0.5, DIM).astype(np.float32)
+    scale = wl.scale
     blk = 1 << 20
     for s in range(0, n_frames, blk):                          # fill in blocks: avoids a second 0.8 GB temporary
         e = min(n_frames, s + blk)
@@ -199,21 +249,18 @@ def run_ours(args):
         if cnt:
             fam[name] = {"ms_per_step": ms / prof_steps, "launches_per_step": cnt / prof_steps}
     eng.profile_enable(False)
-    gemm_ms = sum(v["ms_per_step"] for k, v in fam.items() if k.startswith("gemm"))
-    gemm_launches = sum(v["launches_per_step"] for k, v in fam.items() if k.startswith("gemm"))
-    # per-layer tensor-pipe fraction (algorithmic FLOPs of that layer / its summed launch time)
-    t = lengths.astype(np.float64)
-    layer_flops = {"tdnn1": 2 * 512 * 5 * DIM * (t - 4), "tdnn2": 2 * 512 * 2560 * (t - 8), "tdnn3": 2 * 512 * 3584 * (t - 14),
-                   "tdnn4": 2 * 512 * 512 * (t - 14), "tdnn5": 2 * 512 * 1500 * (t - 14), "tdnn6": 2 * 3000 * 512 + 0 * t}
+    is_tensor = lambda k: k.startswith(wl.tensor_prefixes)
+    gemm_ms = sum(v["ms_per_step"] for k, v in fam.items() if is_tensor(k))
+    gemm_launches = sum(v["launches_per_step"] for k, v in fam.items() if is_tensor(k))
+    # per-family tensor-pipe throughput (algorithmic FLOPs of that family / its summed launch time)
     for k, v in fam.items():
-        lname = k.split(".")[-1]
-        if k.startswith("gemm") and lname in layer_flops and v["ms_per_step"] > 0:
-            v["tflops"] = float(layer_flops[lname].sum()) / (v["ms_per_step"] * 1e-3) / 1e12
-    flops = gemm_flops(lengths)
+        if k in wl.layer_flops and is_tensor(k) and v["ms_per_step"] > 0:
+            v["tflops"] = wl.layer_flops[k] / (v["ms_per_step"] * 1e-3) / 1e12
+    flops = wl.flops
     peaks = read_peaks()
     achieved = flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
     roofline = {
-        "kernel": "xv_tdnn_gemm_kernel (tcgen05 spliced GEMM + fused epilogue), all 6 layer launches of a step",
+        "kernel": wl.kernel,
         "bound": "tensor", "achieved": achieved, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
         "frac": achieved / peaks["bf16_sustained"], "peak_kind": "sustained bf16, %s" % peaks["source"],
         "frac_of_burst": achieved / peaks["bf16_burst"],
@@ -225,7 +272,7 @@ def run_ours(args):
 
     # ---------------- standalone statistics pooling (HBM roofline; rank 0 at N=1) ----------------
     pooling = None
-    if rank == 0 and world == 1 and not args.no_pool_bench:
+    if rank == 0 and world == 1 and not args.no_pool_bench and wl.name == "tdnn":
         pooling = pooling_roofline(eng, peaks)
 
     # ---------------- end to end through the public C-ABI call (host buffers) ----------------
@@ -246,7 +293,7 @@ def run_ours(args):
     # ---------------- CPU baseline (rank 0, N=1 only) ----------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu = cpu_baseline(args.cpu_seconds)
+        cpu = cpu_baseline(args.cpu_seconds, args)
 
     if rank == 0:
         clocks = sampler.summary()
@@ -255,10 +302,9 @@ def run_ours(args):
             "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
             "config": {
-                "workload": "configs[1]: standard x-vector TDNN (5x512 frame layers, 1500 pre-pool, stats pooling, "
-                            "tdnn6_dense 512-d) on 30-dim MFCC utterances of log-uniform length 200-6000 frames",
-                "utts_per_gpu": args.utts, "frames_rank0": n_frames, "feature_dim": DIM, "node": "tdnn6_dense",
-                "batch_frames": args.batch_frames, "weights": "random init, seed 1234",
+                "workload": wl.workload,
+                "utts_per_gpu": wl.utts, "frames_rank0": n_frames, "feature_dim": DIM, "node": "tdnn6_dense",
+                "batch_frames": wl.batch_frames, "weights": "random init, seed 1234",
                 "parallelism": "utterance shards (LPT by FLOPs) over %d GPU(s), no collective" % world,
                 "l2_policy": "inputs larger than L2 (%.2f GB fp32 features per GPU vs 126 MB L2)" % (n_frames * DIM * 4 / 1e9),
             },
@@ -333,22 +379,32 @@ def pooling_roofline(eng, peaks, channels=1500, iters=10):
             "traffic": None}
 
 
-def cpu_baseline(seconds):
+def cpu_baseline(seconds, args=None):
     """fp32 torch-CPU restatement (oracle/torch_ref.py), P single-thread processes, one utterance per call."""
     from oracle import synth, torch_ref
-    cores = os.cpu_count() or 1
-    lengths = synth.config2_lengths(UTTS_PER_GPU, seed=202)
-    take = np.random.default_rng(0).permutation(len(lengths))[:max(4 * cores, 64)]
-    sub = lengths[take].astype(np.int32)
-    feats = synth.packed_features(sub, DIM, seed=202)
-    cfg = dict(synth.TDNN_STAT_CONFIG)
-    w = synth.make_tdnn_weights(DIM, cfg, seed=1234)
-    r = torch_ref.time_cpu_extraction(w, cfg, feats, sub, processes=cores, budget_s=seconds)
     import torch
+    cores = os.cpu_count() or 1
+    workload = getattr(args, "workload", "tdnn") if args is not None else "tdnn"
+    if workload == "resnet18":
+        dim = (args.dim or 64)
+        sub = np.full(max(cores, 8), 400, np.int32)
+        feats = synth.fbank_like(int(sub.sum()), dim, seed=404)
+        cfg = dict(synth.RESNET_CONFIG)
+        w = synth.make_resnet_weights(dim, cfg, seed=1234)
+        what = "%d-dim fbank x 400-frame utterances of configs[3]" % dim
+    else:
+        lengths = synth.config2_lengths(UTTS_PER_GPU, seed=202)
+        take = np.random.default_rng(0).permutation(len(lengths))[:max(4 * cores, 64)]
+        sub = lengths[take].astype(np.int32)
+        feats = synth.packed_features(sub, DIM, seed=202)
+        cfg = dict(synth.TDNN_STAT_CONFIG)
+        w = synth.make_tdnn_weights(DIM, cfg, seed=1234)
+        what = "utterances drawn from the configs[1] length distribution"
+    r = torch_ref.time_cpu_extraction(w, cfg, feats, sub, processes=cores, budget_s=seconds)
     return {"value": r["frames_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port",
-            "sample": "%d utterances (%d frames) drawn from the configs[1] length distribution, %.0f s budget per process, "
+            "sample": "%d %s (%d frames), %.0f s budget per process, "
                       "%d single-thread processes, one utterance per call; torch %s fp32 CPU restatement of the reference "
-                      "graph (reference TF unavailable on this box)" % (r["utts"], r["frames"], seconds, r["cores"],
+                      "graph (reference TF unavailable on this box)" % (r["utts"], what, r["frames"], seconds, r["cores"],
                                                                           torch.__version__)}
 
 
@@ -363,7 +419,7 @@ def run_reference(args):
     vals = []
     cpu = None
     for i in range(args.warmup + args.steps):
-        cpu = cpu_baseline(per_step)
+        cpu = cpu_baseline(per_step, args)
         if i >= args.warmup:
             vals.append(cpu["value"])
     v = float(np.mean(vals))
@@ -371,7 +427,8 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": per_step * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "configs[1] length distribution, bounded sample per step (see cpu_baseline.sample)"},
+            "config": {"workload": Workload.describe(args), "node": "tdnn6_dense", "weights": "random init, seed 1234",
+                       "sample": "bounded sample of that workload per step (see cpu_baseline.sample)"},
             "cpu_baseline": cpu,
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
@@ -383,11 +440,14 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch-frames", type=int, default=262144)
+    ap.add_argument("--workload", default="tdnn", choices=["tdnn", "resnet18"],
+                    help="tdnn = BASELINE.json configs[1] (the headline metric); resnet18 = configs[3] (secondary)")
+    ap.add_argument("--dim", type=int, default=0, help="feature dim of the resnet18 workload (default 64; 40 = reference-legal)")
+    ap.add_argument("--batch-frames", type=int, default=0)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-pool-bench", action="store_true")
-    ap.add_argument("--utts", type=int, default=UTTS_PER_GPU, help="utterances per GPU (default = the configs[1] set; "
+    ap.add_argument("--utts", type=int, default=0, help="utterances per GPU (default = the configs[1] set; "
                     "smaller values are for profiling runs only)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":

@@ -68,13 +68,18 @@ __global__ void __launch_bounds__(256) resnet_stem_kernel(const float* __restric
       }
     }
     T* dst = out + static_cast<int64_t>(b) * out_utt_stride + (static_cast<int64_t>(ti) * f + fi) * 64 + cg * 8;
+    T y[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const int ch = cg * 8 + k;
       float v = fmaf(acc[k], ss[ch], ss[64 + ch]);
       v = v >= 0.f ? v : v * ss[128 + ch];
-      dst[k] = cvt_out<T>(v);
+      y[k] = cvt_out<T>(v);
     }
+    // 8 channels = one 16-byte (bf16) or two 16-byte (fp32) stores; consecutive threads write consecutive chunks
+    const uint4* src = reinterpret_cast<const uint4*>(y);
+#pragma unroll
+    for (int k = 0; k < static_cast<int>(sizeof(T) * 8 / 16); ++k) reinterpret_cast<uint4*>(dst)[k] = src[k];
   }
 }
 

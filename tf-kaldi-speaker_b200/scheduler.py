@@ -41,3 +41,31 @@ def shard_lpt(lengths, world_size, dim=30):
         shards[r].append(int(i))
         loads[r] += cost[i]
     return [np.asarray(s, dtype=np.int64) for s in shards]
+
+
+def resnet_layer_flops(t, f, blocks=(2, 2, 2, 2), time_stride=False):
+    """Algorithmic FLOPs of one resnet_18 utterance of t frames x f bins up to tdnn6_dense, per kernel family
+    (2 FLOPs per MAC, SAME convolutions count every output position; SURVEY.md section 8(d):
+    65.46 GFLOP at (400, 40), 104.25 GFLOP at (400, 64))."""
+    out = {"stem": 2.0 * t * f * 9 * 64}
+    cin, tt, ff = 64, t, f
+    for stage, filt in enumerate((64, 128, 256, 512)):
+        if stage > 0:
+            ff = ff // 2
+            if time_stride:
+                tt = (tt + 1) // 2
+        pos = float(tt) * ff
+        fam = "conv.c%d" % filt
+        fl = 2 * pos * 9 * cin * filt + 2 * pos * cin * filt + 2 * pos * 9 * filt * filt      # conv0, 1x1 shortcut, conv1
+        fl += (blocks[stage] - 1) * 2 * (2 * pos * 9 * filt * filt)
+        out[fam] = out.get(fam, 0.0) + fl
+        cin = filt
+    out["gemm.conv5"] = 2.0 * tt * ff * 512 * 512
+    out["gemm.dense1"] = 2.0 * tt * 512 * 512
+    out["gemm.dense2"] = 2.0 * tt * 512 * 1500
+    out["gemm.tdnn6"] = 2.0 * 3000 * 512
+    return out
+
+
+def resnet_flops(t, f, blocks=(2, 2, 2, 2), time_stride=False):
+    return sum(resnet_layer_flops(t, f, blocks, time_stride).values())
