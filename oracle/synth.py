@@ -259,3 +259,46 @@ def make_resnet_weights(dim, config=None, seed=1234):
 def fbank_like(n_frames, dim, seed):
     """CMN'd log-mel-like rows: N(0,1) (SURVEY.md 8(d) cfg 3/4)."""
     return np.random.default_rng(seed).standard_normal((n_frames, dim), dtype=np.float32)
+
+
+# ----------------------------------------------------------------------------- training step (config 5)
+# egs/voxceleb/v1/nnet_conf/tdnn_amsoftmax_m0.20_linear_bn_1e-2.json (keys the training step reads)
+TDNN_AMSOFTMAX_CONFIG = {
+    "network_type": "tdnn",
+    "last_layer_no_bn": False,
+    "last_layer_linear": True,
+    "feature_norm": False,
+    "loss_func": "additive_margin_softmax",
+    "amsoftmax_m": 0.20,
+    "amsoftmax_lambda_min": 0,
+    "amsoftmax_lambda_base": 1000,
+    "amsoftmax_lambda_gamma": 0.0001,
+    "amsoftmax_lambda_power": 5,
+    "pooling_type": "statistics_pooling",
+    "embedding_node": "tdnn6_dense",
+    "learning_rate": 0.01,
+    "clip_gradient": False,
+    "clip_gradient_norm": 3,
+    "weight_l2_regularizer": 1e-2,
+    "batchnorm_momentum": 0.99,
+    "num_speakers_per_batch": 64,
+    "num_segments_per_speaker": 1,
+}
+
+
+def add_softmax_weights(w, num_speakers, embed_dim=512, seed=77, bias=False):
+    """softmax/output/kernel [E, S], Xavier-uniform (model/loss.py:236-239) (+ bias for plain softmax :29-34)."""
+    rng = np.random.default_rng(seed)
+    w = dict(w)
+    w["softmax/output/kernel"] = _glorot(rng, (embed_dim, num_speakers), embed_dim, num_speakers)
+    if bias:
+        w["softmax/output/bias"] = np.zeros(num_speakers, np.float32)
+    return w
+
+
+def config5_batch(batch=64, frames=200, dim=30, num_speakers=5994, seed=505):
+    """cfg 5: features [batch, frames, dim] fp32 + labels [batch] int32."""
+    rng = np.random.default_rng(seed)
+    x = mfcc_like(rng, batch * frames, dim).reshape(batch, frames, dim)
+    y = rng.integers(0, num_speakers, batch).astype(np.int32)
+    return x, y

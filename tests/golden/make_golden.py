@@ -10,6 +10,10 @@ Runs ONLY in the build container (needs /root/reference).  Two kinds of fixture:
    reshape arguments) before exec; nothing from the reference is copied into the repo.
    This is the only reference-authored numeric pin on the hot path.
 
+1b. amsoftmax_golden.npz -- outputs of the REFERENCE's own numpy statement `compute_amsoftmax`
+   (model/test_utils.py:229-270), executed from the file where it lies: pins the loss VALUE of
+   additive_margin_softmax (model/loss.py:201-286) for the training-step oracle (oracle/train_ref.py).
+
 2. tdnn_small_golden.npz -- fp64 oracle (oracle/numpy_ref.py) outputs on small seeded
    inputs.  These are regression fixtures for the oracle itself ("parity unpinned":
    the reference has no runnable implementation or fixture for tdnn/stat pooling).
@@ -45,6 +49,21 @@ def load_reference_attention():
     return mod.compute_self_attention
 
 
+def load_reference_amsoftmax():
+    src = open(REF).read()
+    mod = types.ModuleType("ref_test_utils_am")
+    mod.np = np
+    m = re.search(r"^def softmax\(.*?(?=^def )", src, re.S | re.M)
+    if m:
+        exec(compile(m.group(0), REF, "exec"), mod.__dict__)
+    else:
+        from scipy.special import softmax as _sm
+        mod.softmax = lambda x: _sm(x, axis=1)
+    m = re.search(r"^def compute_amsoftmax\(.*?(?=^def )", src, re.S | re.M)
+    exec(compile(m.group(0), REF, "exec"), mod.__dict__)
+    return mod.compute_amsoftmax
+
+
 class P(object):
     pass
 
@@ -76,6 +95,29 @@ def main():
         out[name + "/att"] = att
     np.savez_compressed(os.path.join(HERE, "attention_golden.npz"), **out)
     print("wrote attention_golden.npz with", len(cases), "cases")
+
+    # --- additive margin softmax loss values from the reference's numpy statement ---
+    am = load_reference_amsoftmax()
+    a = {}
+    am_cases = [("m020_step0", 8, 16, 11, 0.20, 0), ("m020_step30000", 8, 16, 11, 0.20, 30000),
+                ("m035_step200000", 5, 24, 7, 0.35, 200000), ("m015_lmin", 6, 12, 9, 0.15, 10 ** 7)]
+    for name, b, e, s_, m_, step in am_cases:
+        p = P()
+        p.feature_norm = False
+        p.amsoftmax_m = m_
+        p.amsoftmax_lambda_min = 0.0 if "lmin" not in name else 0.5
+        p.amsoftmax_lambda_base, p.amsoftmax_lambda_gamma, p.amsoftmax_lambda_power = 1000.0, 0.0001, 5.0
+        p.global_step = step
+        emb = rng.standard_normal((b, e))
+        wmat = rng.standard_normal((e, s_)) * 0.3
+        lab = rng.integers(0, s_, b)
+        a[name + "/embeddings"] = emb
+        a[name + "/w"] = wmat
+        a[name + "/labels"] = lab.astype(np.int32)
+        a[name + "/hyper"] = np.array([m_, p.amsoftmax_lambda_min, 1000.0, 0.0001, 5.0, step], np.float64)
+        a[name + "/loss"] = np.float64(am(emb.copy(), lab, p, wmat.copy()))
+    np.savez_compressed(os.path.join(HERE, "amsoftmax_golden.npz"), **a)
+    print("wrote amsoftmax_golden.npz with", len(am_cases), "cases")
 
     # --- oracle regression fixtures (small) ---
     g = {}

@@ -1,0 +1,70 @@
+"""CPU: the training-step oracle (config 5) -- AM-softmax loss pinned on the reference's own numpy statement,
+hand-derived backward pass cross-checked against torch autograd, tower semantics of TrainerMGPU."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import numpy_ref, synth, torch_train_ref, train_ref
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def test_amsoftmax_loss_matches_reference_numpy_statement():
+    """Pinned: model/test_utils.py:229-270 compute_amsoftmax executed from the reference tree (make_golden.py)."""
+    g = np.load(os.path.join(GOLDEN, "amsoftmax_golden.npz"))
+    names = sorted({k.split("/")[0] for k in g.files})
+    assert len(names) == 4
+    for n in names:
+        m, lmin, lb, lg, lp, step = g[n + "/hyper"]
+        p = numpy_ref.OracleParams(loss_func="additive_margin_softmax", amsoftmax_m=m, amsoftmax_lambda_min=lmin,
+                                   amsoftmax_lambda_base=lb, amsoftmax_lambda_gamma=lg, amsoftmax_lambda_power=lp)
+        loss, _, _ = train_ref.loss_forward_backward(g[n + "/embeddings"], g[n + "/labels"],
+                                                     {"softmax/output/kernel": g[n + "/w"]}, p, step, want_grad=False)
+        assert abs(loss - float(g[n + "/loss"])) < 1e-10
+
+
+@pytest.mark.parametrize("loss_func,relu,linear,no_bn,step", [
+    ("additive_margin_softmax", None, True, False, 0),           # tdnn_amsoftmax_m0.20_linear_bn_1e-2.json
+    ("additive_margin_softmax", "prelu", False, False, 30000),
+    ("softmax", "lrelu", True, True, 0),                          # last layer without BN: its bias gradient is non-zero
+], ids=["amsoftmax_cfg5", "amsoftmax_prelu_step30000", "softmax_lrelu_nobn"])
+def test_manual_backward_matches_autograd(loss_func, relu, linear, no_bn, step):
+    cfg = dict(synth.TDNN_AMSOFTMAX_CONFIG, loss_func=loss_func, last_layer_linear=linear, last_layer_no_bn=no_bn)
+    if relu:
+        cfg["network_relu_type"] = relu
+    s = 37
+    w = synth.add_softmax_weights(synth.make_tdnn_weights(20, cfg, seed=3), s, bias=(loss_func == "softmax"))
+    x, y = synth.config5_batch(6, 40, 20, s, seed=1)
+    out = train_ref.tower_forward_backward(x, y, w, numpy_ref.OracleParams(**cfg), step)
+    loss, reg, grads = torch_train_ref.total_loss_and_grads(x, y, w, cfg, step)
+    assert abs(out["loss"] - loss) < 1e-10 and abs(out["reg"] - reg) < 1e-9
+    scale = max(np.abs(v).max() for v in grads.values() if v is not None)
+    for k, v in grads.items():
+        if no_bn and k.startswith("tdnn/tdnn7_bn"):
+            continue
+        assert v is not None, k
+        mine = out["grads"][k].reshape(v.shape)
+        # biases in front of a batch norm have an exactly-zero gradient: compare on the global scale
+        assert np.abs(mine - v).max() <= 1e-9 * max(np.abs(v).max(), 1e-3 * scale), k
+
+
+def test_tower_semantics_and_sgd_update():
+    cfg = dict(synth.TDNN_AMSOFTMAX_CONFIG)
+    s = 23
+    w = synth.add_softmax_weights(synth.make_tdnn_weights(16, cfg, seed=5), s)
+    x, y = synth.config5_batch(8, 36, 16, s, seed=2)
+    p = numpy_ref.OracleParams(**cfg)
+    new1, info1 = train_ref.train_step(x, y, w, p, 0.01, 0, num_towers=1)
+    new2, info2 = train_ref.train_step(x, y, w, p, 0.01, 0, num_towers=2)
+    # per-tower BN statistics make the 2-tower gradient differ from the full-batch one, but not by much
+    k = "tdnn/tdnn3_conv/kernel"
+    rel = np.abs(info1["grads"][k] - info2["grads"][k]).max() / np.abs(info1["grads"][k]).max()
+    assert 1e-6 < rel < 1.0
+    np.testing.assert_allclose(new1[k], np.asarray(w[k], np.float64) - 0.01 * info1["grads"][k].reshape(w[k].shape))
+    # moving averages: tower 0 only, momentum 0.99, unbiased variance for the fused (conv) layers
+    o0 = train_ref.tower_forward_backward(x[:4], y[:4], w, p, 0, want_grad=False)
+    np.testing.assert_allclose(new2["tdnn/tdnn1_bn/moving_mean"], o0["moving"]["tdnn/tdnn1_bn/moving_mean"])
+    mv = np.asarray(w["tdnn/tdnn4_bn/moving_variance"], np.float64)
+    assert np.all(np.abs(new1["tdnn/tdnn4_bn/moving_variance"] - mv) <= 0.0100001 * np.maximum(mv, 5.0))
+    assert info2["loss"] == pytest.approx(np.mean(info2["tower_losses"]))
