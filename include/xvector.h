@@ -158,6 +158,30 @@ int   xv_gemm_bf16_async(xv_ctx* ctx, const void* a_dev, int64_t a_rows, int32_t
                          const void* wt_dev, int32_t n, const float* scale_dev, const float* shift_dev,
                          const float* slope_dev, void* out_dev, int64_t m_rows);
 
+/* ---- training step (BASELINE.json config 5) ------------------------------------------------------------
+ * Replaces sess.run(train_op, {features, labels, is_training: True, global_step, learning_rate}) of
+ * Trainer.train / TrainerMGPU (model/trainer.py:590-673, 1133-1248) for network_type tdnn + statistics_pooling with
+ * loss_func softmax | additive_margin_softmax (model/loss.py:9-48, 201-286), optimizer sgd | momentum.
+ * The context must be created with "precision":"fp32"; every variable the reference's graph would hold
+ * (tdnn/..., softmax/output/kernel [512, num_speakers] (+ /bias for softmax), BN moving statistics) is first given
+ * with xv_set_weight; xv_train_init copies them into the flat parameter buffer that the step updates in place. */
+int  xv_train_init(xv_ctx* ctx, int32_t num_speakers);
+/* One step on this rank's slice of the batch: feats [batch, frames, D] fp32 (host or device), labels [batch]
+ * int32 (host).  Forward in training mode (BN batch statistics of THIS rank, model/trainer.py:1183-1190), loss +
+ * L2 regularisation, backward, gradient average over ranks (one ncclAllReduce when xv_comm_init was called with
+ * world > 1; == add_n/N of model/trainer.py:1240-1244), optimizer update, BN moving averages from rank 0.
+ * loss_out (may be NULL): [0] = mean tower loss, [1] = [0] + regularisation loss. */
+int  xv_train_step(xv_ctx* ctx, const float* feats, const int32_t* labels, int32_t batch, int32_t frames,
+                   float learning_rate, int64_t global_step, float* loss_out);
+/* Current value / last averaged gradient (including the wd*W regularisation term) of a variable, by TF name. */
+int  xv_train_get_weight(xv_ctx* ctx, const char* tf_name, float* host, int64_t capacity);
+int  xv_train_get_grad(xv_ctx* ctx, const char* tf_name, float* host, int64_t capacity);
+/* Data parallelism: rank 0 creates a 128-byte ncclUniqueId (xv_comm_unique_id), the launcher hands it to every
+ * rank, each rank calls xv_comm_init(ctx, id, rank, world) after xv_train_init.  NCCL is loaded at run time
+ * (libnccl.so.2, the copy already mapped by the process if there is one).  world == 1 needs no NCCL. */
+int  xv_comm_unique_id(xv_ctx* ctx, void* out128);
+int  xv_comm_init(xv_ctx* ctx, const void* nccl_unique_id, int rank, int world);
+
 /* One 2-D convolution of the ResNet-18 front end on the implicit-GEMM tcgen05 path (kernel-level tests and the
  * conv roofline bench): replaces tf.layers.conv2d(padding='same', use_bias=False) + batch_normalization
  * [+ shortcut] + activation of model/resnet.py:25-86.  x [nb,t,f,cin] bf16 NHWC (device), wt [cout][kh*kw*cin]

@@ -100,7 +100,12 @@ class _Affine(object):
             self.xhat = (z - self.mu) * self.rstd
             y = self.gamma * self.xhat + self.beta
         self.pre_act = y
+        self.near_zero = 0
         if self.act:
+            # pre-activations within fp32 rounding of 0: an fp32 implementation may take the other branch of the
+            # activation's derivative there (tests use this count to choose between the strict and the loose bar)
+            mag = (np.abs(self.gamma * self.xhat) + np.abs(self.beta)) if self.has_bn else np.abs(z)
+            self.near_zero = int(np.sum(np.abs(y) < 2e-6 * np.maximum(mag, 1e-30)))
             y = _act_fwd(y, self.relu_kind, self.alpha)
         return y
 
@@ -246,7 +251,8 @@ def tower_forward_backward(features, labels, w, params, global_step=0, want_grad
     for l in frame + seg:
         reg += wd * 0.5 * float(np.sum(l.k * l.k))
     reg += wd_out * 0.5 * float(np.sum(np.asarray(w["softmax/output/kernel"], np.float64) ** 2))
-    out = {"loss": loss, "reg": reg, "total": loss + reg, "endpoints": ep, "grads": None, "moving": {}}
+    out = {"loss": loss, "reg": reg, "total": loss + reg, "endpoints": ep, "grads": None, "moving": {},
+           "near_zero": sum(l.near_zero for l in frame + seg)}
     momentum = float(params.batchnorm_momentum)
     for l in frame + seg:
         l.moving_updates(w, momentum, out["moving"])
@@ -298,6 +304,6 @@ def train_step(features, labels, w, params, learning_rate, global_step=0, num_to
     for k, v in outs[0]["moving"].items():
         new_w[k] = v
     info = {"loss": float(np.mean([o["loss"] for o in outs])), "reg": outs[0]["reg"], "grads": grads,
-            "tower_losses": [o["loss"] for o in outs], "opt_state": state}
+            "tower_losses": [o["loss"] for o in outs], "opt_state": state, "near_zero": sum(o["near_zero"] for o in outs)}
     info["total"] = info["loss"] + info["reg"]
     return new_w, info

@@ -1,0 +1,129 @@
+"""GPU: one training step (BASELINE.json config 5) through the C-ABI against the fp64 oracle: loss, every gradient,
+the SGD / momentum update and the BN moving averages."""
+import numpy as np
+import pytest
+
+from util import tensor_rel
+
+pytestmark = pytest.mark.gpu
+
+GRAD_TOL = 1e-4          # fp32 path, L2 error per variable relative to its norm (north_star's fp32 bar)
+# ReLU-family derivatives are discontinuous at 0.  Among the ~4e5 frame-level pre-activations of a step a few lie
+# within fp32 rounding of 0 (their batch-normalised value carries an absolute error of ~1e-6), and the fp32 path then
+# takes the other branch of the derivative for that ONE element: its channel's gamma/beta gradient moves by one term
+# (observed: error ratio gamma/beta == xhat of the element) and everything upstream of it by ~1e-3.  The strict bar
+# therefore applies to the variables downstream of every frame-level activation (tdnn6, tdnn7, softmax) and the
+# looser one to the frame-level variables.
+FLIP_TOL = 5e-3
+
+
+def _setup(cfg, dim, speakers, batch, frames, seed):
+    import xvector_b200
+    from oracle import synth
+    w = synth.add_softmax_weights(synth.make_tdnn_weights(dim, cfg, seed=seed), speakers, bias=(cfg["loss_func"] == "softmax"))
+    x, y = synth.config5_batch(batch, frames, dim, speakers, seed=seed + 1)
+    eng = xvector_b200.Engine(cfg, dim, precision="fp32")
+    eng.set_weights(w)
+    eng.train_init(speakers)
+    return eng, w, x, y
+
+
+@pytest.mark.parametrize("loss_func,relu,linear,no_bn,opt,step,seed", [
+    ("additive_margin_softmax", None, True, False, "sgd", 0, 31),          # tdnn_amsoftmax_m0.20_linear_bn_1e-2.json
+    ("additive_margin_softmax", "prelu", False, False, "momentum", 30000, 41),
+    ("additive_margin_softmax", "prelu", False, False, "momentum", 30000, 42),
+    ("softmax", "lrelu", True, True, "sgd", 0, 31),
+], ids=["amsoftmax_cfg5", "amsoftmax_prelu_momentum", "amsoftmax_prelu_seed42", "softmax_lrelu_nobn"])
+def test_train_step_matches_oracle(loss_func, relu, linear, no_bn, opt, step, seed):
+    from oracle import numpy_ref, synth, train_ref
+    cfg = dict(synth.TDNN_AMSOFTMAX_CONFIG, loss_func=loss_func, last_layer_linear=linear, last_layer_no_bn=no_bn)
+    if relu:
+        cfg["network_relu_type"] = relu
+    if opt == "momentum":
+        cfg.update(optimizer="momentum", momentum=0.9, use_nesterov=False)
+    dim, speakers, batch, frames, lr = 24, 101, 8, 50, 0.05
+    eng, w, x, y = _setup(cfg, dim, speakers, batch, frames, seed=seed)
+    try:
+        loss, total = eng.train_step(x, y, lr, step)
+        new_ref, info = train_ref.train_step(x, y, w, numpy_ref.OracleParams(**cfg), lr, step)
+        assert abs(loss - info["loss"]) <= 1e-5 * abs(info["loss"])
+        assert abs(total - info["total"]) <= 1e-5 * abs(info["total"])
+        gscale = max(np.abs(g).max() for g in info["grads"].values())
+        frame_level = lambda nm: nm.split("/")[1][:5] in ("tdnn1", "tdnn2", "tdnn3", "tdnn4", "tdnn5")
+        for name, g_ref in info["grads"].items():
+            g = eng.train_grad(name, np.asarray(w[name]).shape)
+            g_ref = g_ref.reshape(g.shape)
+            tol = FLIP_TOL if frame_level(name) else GRAD_TOL
+            # a bias in front of a BN has an exactly-zero gradient (a sum of cancelling terms): judge it on the global scale
+            exact_zero = name.endswith("/bias") and np.abs(g_ref).max() < 1e-12
+            denom = gscale if exact_zero else max(np.abs(g_ref).max(), 1e-3 * gscale)
+            # an activation whose pre-activation is ~1e-7 can fall on different sides of 0 in fp32 and fp64: isolated
+            # elements may then differ by one term of the sum, so the 1e-4 bar is applied to the L2 error of the tensor
+            # and a looser bar to its worst element.  beta / bias gradients are sums of the SAME terms g as the layer's
+            # gamma gradient (sum g vs sum g*xhat) but cancel almost completely (the incoming gradient sums to zero
+            # over the batch after a later BN), so their rounding error is judged on the gamma gradient's scale.
+            floor = 1e-3 * gscale * np.sqrt(g.size)
+            layer = name.rsplit("/", 2)[0] + "/" + name.split("/")[1].split("_")[0] + "_bn/gamma"
+            if name.endswith(("/beta", "/bias")) and layer in info["grads"]:
+                floor = max(floor, np.linalg.norm(info["grads"][layer]))
+            l2 = np.linalg.norm(g - g_ref) / max(np.linalg.norm(g_ref), floor) if not exact_zero else 0.0
+            assert l2 <= tol, "%s: L2 %.3e" % (name, l2)
+            denom = max(denom, floor / np.sqrt(g.size))
+            assert np.abs(g - g_ref).max() / denom <= 20 * tol, "%s: %.3e" % (name, np.abs(g - g_ref).max() / denom)
+        for name, v_ref in new_ref.items():
+            if no_bn and name.startswith("tdnn/tdnn7_bn"):
+                continue                                   # variables the graph does not create with last_layer_no_bn
+            v = eng.train_weight(name, np.asarray(w[name]).shape)
+            v_ref = v_ref.reshape(v.shape)
+            if frame_level(name):       # one flipped activation derivative moves a whole kernel column: L2 criterion
+                assert np.linalg.norm(v - v_ref) <= FLIP_TOL * np.linalg.norm(v_ref), name
+            else:
+                assert tensor_rel(v, v_ref) <= 1e-5, name
+        # a second step runs on the updated parameters (momentum accumulators, moving averages chained)
+        new_ref2, info2 = train_ref.train_step(x, y, new_ref, numpy_ref.OracleParams(**cfg), lr, step + 1,
+                                               opt_state=info["opt_state"])
+        loss2, _ = eng.train_step(x, y, lr, step + 1)
+        assert abs(loss2 - info2["loss"]) <= FLIP_TOL * abs(info2["loss"])
+        k = "tdnn/tdnn3_conv/kernel"
+        v2 = eng.train_weight(k, w[k].shape)
+        assert np.linalg.norm(v2 - new_ref2[k].reshape(v2.shape)) <= 2 * FLIP_TOL * np.linalg.norm(new_ref2[k])
+        assert eng.launch_count() > 0
+    finally:
+        eng.close()
+
+
+def test_train_step_config5_shapes_run():
+    """The real config-5 shapes (64 x 200 frames x 30 dims, 5994 speakers): finite loss that goes down."""
+    from oracle import synth
+    cfg = dict(synth.TDNN_AMSOFTMAX_CONFIG)
+    eng, w, x, y = _setup(cfg, 30, 5994, 64, 200, seed=505)
+    try:
+        losses = [eng.train_step(x, y, 0.01, i)[0] for i in range(4)]
+        assert np.isfinite(losses).all()
+        assert abs(losses[0] - np.log(5994)) < 1.5          # random init: cross entropy near ln(S)
+        assert losses[-1] < losses[0]
+    finally:
+        eng.close()
+
+
+def test_train_init_errors():
+    import xvector_b200
+    from oracle import synth
+    cfg = dict(synth.TDNN_AMSOFTMAX_CONFIG)
+    w = synth.make_tdnn_weights(24, cfg, seed=1)
+    eng = xvector_b200.Engine(cfg, 24, precision="fp32")
+    try:
+        eng.set_weights(w)
+        with pytest.raises(xvector_b200.XVectorError, match="softmax/output/kernel"):
+            eng.train_init(50)
+        with pytest.raises(xvector_b200.XVectorError, match="xv_train_init"):
+            eng.train_step(np.zeros((2, 40, 24), np.float32), np.zeros(2, np.int32), 0.1)
+    finally:
+        eng.close()
+    eng = xvector_b200.Engine(dict(cfg, loss_func="asoftmax"), 24, precision="fp32")
+    try:
+        eng.set_weights(w)
+        with pytest.raises(xvector_b200.XVectorError, match="Not implement asoftmax loss"):
+            eng.train_init(50)
+    finally:
+        eng.close()

@@ -570,6 +570,7 @@ void xv_destroy(xv_ctx* c) {
   };
   for (Layer& l : c->frame_layers) rel_layer(l);
   for (Layer& l : c->seg_layers) rel_layer(l);
+  train_release(c);
   resnet_release(c);
   for (DevBuf& b : c->frame_out) release(&b);
   DevBuf* bufs[] = {&c->att_query, &c->att_post_scale, &c->att_post_shift, &c->att_post_slope, &c->d_feats,

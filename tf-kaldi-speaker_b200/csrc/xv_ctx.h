@@ -96,6 +96,8 @@ struct Batch {
   int32_t m_tiles = 0;
 };
 
+struct TrainState;   // xv_train.cu
+
 struct ProfileSlot {
   cudaEvent_t a, b;
   int family;
@@ -155,6 +157,8 @@ struct xv_ctx {
   xv::DevBuf conv0_w, conv0_scale, conv0_shift, conv0_slope;   // stem: fp32 [9][64] + folded BN
   xv::DevBuf res_buf[4];
   std::vector<int32_t> cu_in;              // [n+1] packed input-frame offsets (== cu unless time stride)
+
+  xv::TrainState* train = nullptr;         // training step state (xv_train_init)
 
   std::map<std::string, xv::HostTensor> weights;
   bool finalized = false;
@@ -220,6 +224,7 @@ int resnet_out_len(const xv_ctx* c, int t);      // frames after the (optional) 
 // the stage-4 activations [nb*T', F'*512] (bf16, or fp32 in validation mode) inside a ctx-owned buffer.
 int resnet_run_batch(xv_ctx* c, const float* feats, int nb, int t, const void** out);
 void resnet_release(xv_ctx* c);
+void train_release(xv_ctx* c);                   // xv_train.cu
 // shared with xv_api.cu
 const HostTensor* find_weight(xv_ctx* c, const std::string& name);
 int upload(xv_ctx* c, DevBuf* b, const void* host, size_t bytes);

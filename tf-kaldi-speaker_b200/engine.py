@@ -241,6 +241,40 @@ class Engine(object):
                                                _fptr(out)))
         return out.reshape(x.shape)
 
+    # -- training step (config 5)
+    def train_init(self, num_speakers):
+        self._check(self.lib.xv_train_init(self._ctx, int(num_speakers)))
+        self._train_shapes = {}
+
+    def train_step(self, feats, labels, learning_rate, global_step=0):
+        """feats [B, T, D] fp32, labels [B] int32 -> (loss, total_loss)."""
+        x = _f32(feats)
+        y = np.ascontiguousarray(labels, dtype=np.int32)
+        assert x.ndim == 3 and y.shape == (x.shape[0],)
+        out = np.zeros(2, np.float32)
+        self._check(self.lib.xv_train_step(self._ctx, _fptr(x), _i32ptr(y), x.shape[0], x.shape[1], float(learning_rate),
+                                           int(global_step), _fptr(out)))
+        return float(out[0]), float(out[1])
+
+    def _train_read(self, fn, name, shape):
+        out = np.empty(shape, np.float32)
+        self._check(fn(self._ctx, name.encode("utf-8"), _fptr(out), out.size))
+        return out
+
+    def train_weight(self, name, shape):
+        return self._train_read(self.lib.xv_train_get_weight, name, shape)
+
+    def train_grad(self, name, shape):
+        return self._train_read(self.lib.xv_train_get_grad, name, shape)
+
+    def comm_unique_id(self):
+        buf = C.create_string_buffer(128)
+        self._check(self.lib.xv_comm_unique_id(self._ctx, buf))
+        return buf.raw
+
+    def comm_init(self, unique_id, rank, world):
+        self._check(self.lib.xv_comm_init(self._ctx, C.create_string_buffer(bytes(unique_id), 128), int(rank), int(world)))
+
     # -- measurement / memory
     def event_record(self, slot):
         self._check(self.lib.xv_event_record(self._ctx, slot))
