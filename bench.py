@@ -379,6 +379,104 @@ def pooling_roofline(eng, peaks, channels=1500, iters=10):
             "traffic": None}
 
 
+def run_train(args):
+    """--workload train: BASELINE.json configs[4] -- one TDNN + AM-softmax training step (fwd + bwd + update) per
+    step, data parallel with ONE ncclAllReduce over the flat gradient buffer.  Weak scaling: 64 utterances x 200
+    frames per GPU (the reference-faithful "global 64 split over N" is --train-global-batch 64)."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    import xvector_b200
+    from oracle import synth
+    from xvector_b200 import train_dp
+    speakers, frames, dim = 5994, 200, DIM
+    gbatch = args.train_global_batch or 64 * world
+    cfg = dict(synth.TDNN_AMSOFTMAX_CONFIG)
+    w = synth.add_softmax_weights(synth.make_tdnn_weights(dim, cfg, seed=1234), speakers)
+    x, y = synth.config5_batch(gbatch, frames, dim, speakers, seed=505)
+    eng = xvector_b200.Engine(cfg, dim, precision="fp32", device=local)
+    eng.set_weights(w)
+    eng.train_init(speakers)
+    uid = train_dp.exchange_unique_id_torch(eng, rank, world) if world > 1 else b"\0" * 128
+    eng.comm_init(uid, rank, world)
+    xs, ys = train_dp.slice_batch(x, y, rank, world)
+    pin = xvector_b200.PinnedArray(xs.shape)
+    pin.array[...] = xs
+
+    def barrier():
+        eng.sync()
+        if dist is not None:
+            import torch
+            torch.cuda.synchronize()
+            dist.barrier()
+
+    def max_over_ranks(v):
+        if dist is None:
+            return v
+        import torch
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    losses = []
+    for i in range(args.warmup):
+        losses.append(eng.train_step(pin.array, ys, 0.01, i)[0])
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches0 = eng.launch_count()
+    eng.event_record(0)
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        # the public call: H2D of this step's features/labels, all kernels, the allreduce, D2H of the loss
+        losses.append(eng.train_step(pin.array, ys, 0.01, args.warmup + i)[0])
+    t1 = time.perf_counter()
+    eng.event_record(1)
+    eng.sync()
+    ms_dev = max_over_ranks(eng.elapsed_ms(0, 1))
+    wall = max_over_ranks(t1 - t0)
+    launches = eng.launch_count() - launches0
+    barrier()
+    sampler.stop()
+    assert np.isfinite(losses).all()
+    total_frames = float(gbatch * frames)
+    flops = train_dp.train_flops(gbatch, frames, dim, speakers)
+    peaks = read_peaks()
+    if rank == 0:
+        achieved = flops * args.steps / (ms_dev * 1e-3) / 1e12
+        line = {
+            "metric": "tdnn_amsoftmax_train_frames_per_sec", "value": total_frames * args.steps / (ms_dev * 1e-3), "unit": UNIT,
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps,
+            "higher_is_better": True, "scaling": "weak" if not args.train_global_batch else "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "configs[4]: TDNN x-vector + AM-softmax training step fwd+bwd+update, %d x %d frames x %d dims, "
+                                   "%d speakers, SGD" % (gbatch, frames, dim, speakers), "global_batch": gbatch,
+                       "per_gpu_batch": gbatch // world, "weights": "random init, seed 1234",
+                       "parallelism": "dp%d: one ncclAllReduce(sum) of the flat gradient buffer (9.13 M fp32) per step" % world,
+                       "l2_policy": "activations + gradients of a step (0.4 GB) exceed the L2"},
+            "e2e": {"value": total_frames * args.steps / wall, "unit": UNIT, "h2d_bytes_per_step": int(xs.nbytes + ys.nbytes),
+                    "d2h_bytes_per_step": 16, "steps": args.steps, "api": "xv_train_step (pinned host batch -> loss on the host)"},
+            "gpu_launches": int(launches) * world, "clocks": sampler.summary(),
+            "roofline": {"kernel": "fp32 SIMT GEMMs of the validation-grade training path (forward, dgrad, wgrad)",
+                         "bound": "tensor", "achieved": achieved, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
+                         "frac": achieved / peaks["bf16_sustained"], "peak_kind": "sustained bf16, %s" % peaks["source"],
+                         "algorithmic_flops_per_step": flops, "traffic": None,
+                         "note": "whole-step FLOPs / whole-step time; this path runs on FFMA, not on the tensor cores"},
+            "loss_first_last": [losses[0], losses[-1]],
+        }
+        print(json.dumps(line), flush=True)
+    pin.close()
+    eng.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def cpu_baseline(seconds, args=None):
     """fp32 torch-CPU restatement (oracle/torch_ref.py), P single-thread processes, one utterance per call."""
     from oracle import synth, torch_ref
@@ -440,10 +538,12 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="tdnn", choices=["tdnn", "resnet18"],
+    ap.add_argument("--workload", default="tdnn", choices=["tdnn", "resnet18", "train"],
                     help="tdnn = BASELINE.json configs[1] (the headline metric); resnet18 = configs[3] (secondary)")
     ap.add_argument("--dim", type=int, default=0, help="feature dim of the resnet18 workload (default 64; 40 = reference-legal)")
     ap.add_argument("--batch-frames", type=int, default=0)
+    ap.add_argument("--train-global-batch", type=int, default=0, help="train workload: fixed global batch (strong scaling); "
+                    "default 64 per GPU (weak scaling)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-pool-bench", action="store_true")
@@ -454,6 +554,8 @@ def main():
         args.warmup = 3
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "train":
+        run_train(args)
     else:
         run_ours(args)
 
