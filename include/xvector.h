@@ -193,6 +193,13 @@ int   xv_conv2d_bf16_async(xv_ctx* ctx, const void* x_dev, int32_t nb, int32_t t
                            const float* scale_dev, const float* shift_dev, const float* slope_dev,
                            const void* residual_dev, void* out_dev);
 
+/* Weight gradient of a spliced (1 x taps) layer on the tcgen05 path (kernel-level tests; used by xv_train_step in
+ * bf16 mode): dW[j*cin + c, n] = sum_{m<rows} a[m + j, c] * dz[m, n] -- what tf.gradients produces for the kernels of
+ * model/tdnn.py:42-103 under model/trainer.py:501-527.  a [a_rows, lda] bf16, dz [rows, ldz] bf16, out fp32
+ * [taps*cin, ldo] (zeroed by the call), all device pointers; lda, ldz multiples of 8, ldo a multiple of 4. */
+int   xv_wgrad_bf16_async(xv_ctx* ctx, const void* a_dev, int64_t a_rows, int32_t lda, const void* dz_dev, int32_t ldz,
+                          int64_t rows, int32_t taps, int32_t cin, int32_t n_valid, float* out_dev, int32_t ldo);
+
 const char* xv_version(void);
 
 #ifdef __cplusplus

@@ -67,6 +67,8 @@ PROTOTYPES = {
                                      _p, C.c_int64]),
     "xv_conv2d_bf16_async": (C.c_int, [_p, _p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _p, C.c_int32, C.c_int32,
                                        C.c_int32, C.c_int32, C.c_int32, _p, _p, _p, _p, _p]),
+    "xv_wgrad_bf16_async": (C.c_int, [_p, _p, C.c_int64, C.c_int32, _p, C.c_int32, C.c_int64, C.c_int32, C.c_int32,
+                                      C.c_int32, _p, C.c_int32]),
     "xv_train_init": (C.c_int, [_p, C.c_int32]),
     "xv_train_step": (C.c_int, [_p, _p, _p, C.c_int32, C.c_int32, C.c_float, C.c_int64, _p]),
     "xv_train_get_weight": (C.c_int, [_p, C.c_char_p, _p, C.c_int64]),

@@ -99,6 +99,22 @@ cudaError_t launch_conv_gemm(const ConvGemmPlan& plan, int sm_count, cudaStream_
 const char* make_tmap_bf16_nd(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                               const uint64_t* strides_bytes, const uint32_t* box, int swizzle_bytes);
 
+// ---- tensor-core weight gradient (xv_wgrad_sm100.cu), training step ----
+struct WgradParams {
+  int64_t rows;              // packed frames contracted over
+  int64_t rows_per_split;    // multiple of 64
+  int32_t splits;
+  int32_t taps, cin;         // dW rows = taps * cin
+  int32_t n_valid;           // dW columns written
+  int32_t m_tiles_per_tap, m_tiles, n_tiles;
+  int32_t ldo;
+  float* out;
+};
+const char* wgrad_init();
+// dW[j*cin + c, n] += sum_m a[m + j, c] * dz[m, n]; a [a_rows, lda] bf16, dz [rows, ldz] bf16, out fp32 pre-zeroed.
+const char* launch_wgrad(const void* a, int64_t a_rows, int lda, const void* dz, int ldz, int64_t rows, int taps, int cin,
+                         int n_valid, float* out, int ldo, int sm_count, cudaStream_t stream, cudaError_t* cuda_err);
+
 // ---- SIMT / elementwise kernels (xv_kernels.cu) ----
 // features fp32 [rows, D] -> spliced bf16 [rows, kpad]: out[r, j*D + c] = in[r + j*dil, c] (0 beyond rows / kpad)
 cudaError_t launch_splice_cast(const float* feats, int64_t rows, int d, int taps, int dil, __nv_bfloat16* out,
