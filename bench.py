@@ -400,7 +400,8 @@ def run_train(args):
     cfg = dict(synth.TDNN_AMSOFTMAX_CONFIG)
     w = synth.add_softmax_weights(synth.make_tdnn_weights(dim, cfg, seed=1234), speakers)
     x, y = synth.config5_batch(gbatch, frames, dim, speakers, seed=505)
-    eng = xvector_b200.Engine(cfg, dim, precision="fp32", device=local)
+    mixed = args.train_precision == "bf16"
+    eng = xvector_b200.Engine(cfg, dim, precision=args.train_precision, device=local)
     eng.set_weights(w)
     eng.train_init(speakers)
     uid = train_dp.exchange_unique_id_torch(eng, rank, world) if world > 1 else b"\0" * 128
@@ -454,7 +455,7 @@ def run_train(args):
             "metric": "tdnn_amsoftmax_train_frames_per_sec", "value": total_frames * args.steps / (ms_dev * 1e-3), "unit": UNIT,
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps,
             "higher_is_better": True, "scaling": "weak" if not args.train_global_batch else "strong", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
+            "dtype": "bf16 operands / f32 accumulate + f32 master weights" if mixed else "f32", "data": "synthetic",
             "config": {"workload": "configs[4]: TDNN x-vector + AM-softmax training step fwd+bwd+update, %d x %d frames x %d dims, "
                                    "%d speakers, SGD" % (gbatch, frames, dim, speakers), "global_batch": gbatch,
                        "per_gpu_batch": gbatch // world, "weights": "random init, seed 1234",
@@ -463,11 +464,13 @@ def run_train(args):
             "e2e": {"value": total_frames * args.steps / wall, "unit": UNIT, "h2d_bytes_per_step": int(xs.nbytes + ys.nbytes),
                     "d2h_bytes_per_step": 16, "steps": args.steps, "api": "xv_train_step (pinned host batch -> loss on the host)"},
             "gpu_launches": int(launches) * world, "clocks": sampler.summary(),
-            "roofline": {"kernel": "fp32 SIMT GEMMs of the validation-grade training path (forward, dgrad, wgrad)",
+            "roofline": {"kernel": ("tcgen05 GEMMs of the frame layers (forward + tap-step -1 dgrad on xv_tdnn_gemm_kernel, MN-major "
+                                    "xv_wgrad_kernel) inside the whole step" if mixed else
+                                    "fp32 SIMT GEMMs of the validation-grade training path (forward, dgrad, wgrad)"),
                          "bound": "tensor", "achieved": achieved, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
                          "frac": achieved / peaks["bf16_sustained"], "peak_kind": "sustained bf16, %s" % peaks["source"],
                          "algorithmic_flops_per_step": flops, "traffic": None,
-                         "note": "whole-step FLOPs / whole-step time; this path runs on FFMA, not on the tensor cores"},
+                         "note": "whole-step FLOPs / whole-step time" + ("" if mixed else "; this path runs on FFMA, not on the tensor cores")},
             "loss_first_last": [losses[0], losses[-1]],
         }
         print(json.dumps(line), flush=True)
@@ -544,6 +547,8 @@ def main():
     ap.add_argument("--batch-frames", type=int, default=0)
     ap.add_argument("--train-global-batch", type=int, default=0, help="train workload: fixed global batch (strong scaling); "
                     "default 64 per GPU (weak scaling)")
+    ap.add_argument("--train-precision", default="bf16", choices=["bf16", "fp32"],
+                    help="train workload: bf16 = tcgen05 GEMMs with bf16 operands and fp32 master weights; fp32 = validation path")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-pool-bench", action="store_true")

@@ -296,9 +296,14 @@ def add_softmax_weights(w, num_speakers, embed_dim=512, seed=77, bias=False):
     return w
 
 
-def config5_batch(batch=64, frames=200, dim=30, num_speakers=5994, seed=505):
-    """cfg 5: features [batch, frames, dim] fp32 + labels [batch] int32."""
+def config5_batch(batch=64, frames=200, dim=30, num_speakers=5994, seed=505, speaker_signal=0.0):
+    """cfg 5: features [batch, frames, dim] fp32 + labels [batch] int32.  speaker_signal > 0 adds a
+    per-speaker cepstral offset (so that utterance-level statistics differ between speakers the way real data does;
+    with 0 every utterance is the same noise process and the segment-level batch norms amplify rounding noise)."""
     rng = np.random.default_rng(seed)
     x = mfcc_like(rng, batch * frames, dim).reshape(batch, frames, dim)
     y = rng.integers(0, num_speakers, batch).astype(np.int32)
-    return x, y
+    if speaker_signal:
+        spk = np.random.default_rng(seed + 7919).standard_normal((num_speakers, dim)).astype(np.float32)
+        x = x + np.float32(speaker_signal) * spk[y][:, None, :] * x.std(axis=(0, 1), keepdims=True)
+    return x.astype(np.float32), y

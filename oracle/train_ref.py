@@ -60,11 +60,23 @@ def _act_bwd(dy, x, kind, alpha):
     return np.where(x > 0.0, dy, 0.0), None
 
 
+def bf16_round(x):
+    """fp64 -> fp32 -> bf16 (round to nearest even), returned as fp64: the operand rounding of the mixed-precision
+    training step (tcgen05 GEMMs with bf16 operands and fp32 accumulation)."""
+    x32 = np.ascontiguousarray(x, np.float32)
+    u = x32.view(np.uint32).astype(np.uint64)
+    u = (u + 0x7FFF + ((u >> 16) & 1)) & 0xFFFF0000
+    return u.astype(np.uint32).view(np.float32).reshape(x32.shape).astype(np.float64)
+
+
 class _Affine(object):
     """conv(1xk)/dense + BN(batch statistics) [+ activation] with a cached forward for the backward pass."""
 
-    def __init__(self, w, scope, name, kind, taps, has_bn=True, act=True, relu_kind=None, fused_bn=False):
+    def __init__(self, w, scope, name, kind, taps, has_bn=True, act=True, relu_kind=None, fused_bn=False, bf16_gemm=False):
         self.scope, self.name, self.kind, self.taps = scope, name, kind, taps
+        # bf16_gemm: the three GEMMs of this layer (forward, dgrad, wgrad) read bf16-rounded operands (activations,
+        # dZ and a per-step bf16 copy of the fp32 master kernel); everything else stays exact
+        self.rnd = bf16_round if bf16_gemm else (lambda v: v)
         self.has_bn, self.act, self.relu_kind, self.fused_bn = has_bn, act, relu_kind, fused_bn
         aff = "%s/%s_%s" % (scope, name, kind)
         self.kname, self.bname = aff + "/kernel", aff + "/bias"
@@ -80,14 +92,16 @@ class _Affine(object):
 
     def forward(self, a):
         """a [..., L, Cin] (rank 3) or [B, Cin] (rank 2)."""
+        a = self.rnd(a)
+        kq = self.rnd(self.k)
         self.a = a
         if a.ndim == 3:
             lo = a.shape[1] - self.taps + 1
             z = np.zeros((a.shape[0], lo, self.k.shape[2]))
             for j in range(self.taps):
-                z += a[:, j:j + lo, :] @ self.k[j]
+                z += a[:, j:j + lo, :] @ kq[j]
         else:
-            z = a @ self.k[0]
+            z = a @ kq[0]
         z = z + self.b
         self.z = z
         y = z
@@ -126,14 +140,15 @@ class _Affine(object):
         grads[self.bname] = dz.reshape(-1, dz.shape[-1]).sum(axis=0)
         dk = np.zeros_like(self.k)
         da = np.zeros_like(a)
+        dzq, kq = self.rnd(dz), self.rnd(self.k)
         if a.ndim == 3:
             lo = dz.shape[1]
             for j in range(self.taps):
-                dk[j] = np.einsum("blc,blo->co", a[:, j:j + lo, :], dz)
-                da[:, j:j + lo, :] += dz @ self.k[j].T
+                dk[j] = np.einsum("blc,blo->co", a[:, j:j + lo, :], dzq)
+                da[:, j:j + lo, :] += dzq @ kq[j].T
         else:
-            dk[0] = a.T @ dz
-            da = dz @ self.k[0].T
+            dk[0] = a.T @ dzq
+            da = dzq @ kq[0].T
         grads[self.kname] = dk
         return da
 
@@ -207,11 +222,11 @@ def loss_forward_backward(features, labels, w, params, global_step, want_grad=Tr
     return loss, df, grads
 
 
-def build_layers(w, params):
+def build_layers(w, params, bf16_gemm=False):
     kind = params.dict.get("network_relu_type", None) if "network_relu_type" in params.dict else None
     if kind not in ("prelu", "lrelu"):
         kind = None
-    frame = [_Affine(w, "tdnn", n, k, t, relu_kind=kind, fused_bn=(k == "conv")) for n, k, t in TDNN_LAYERS]
+    frame = [_Affine(w, "tdnn", n, k, t, relu_kind=kind, fused_bn=(k == "conv"), bf16_gemm=bf16_gemm) for n, k, t in TDNN_LAYERS]
     no_bn = bool(params.dict.get("last_layer_no_bn", False))
     linear = bool(params.dict.get("last_layer_linear", False))
     seg = [_Affine(w, "tdnn", "tdnn6", "dense", 1, relu_kind=kind),
@@ -219,12 +234,12 @@ def build_layers(w, params):
     return frame, seg
 
 
-def tower_forward_backward(features, labels, w, params, global_step=0, want_grad=True):
+def tower_forward_backward(features, labels, w, params, global_step=0, want_grad=True, bf16_gemm=False):
     """One tower: forward in training mode, loss, full backward.  Returns dict(loss, reg, total, grads, moving,
     endpoints).  grads include the L2-regularisation gradient wd * W of every kernel."""
     if params.network_type != "tdnn" or params.pooling_type != "statistics_pooling":
         raise NotImplementedError("training oracle: tdnn + statistics_pooling only")
-    frame, seg = build_layers(w, params)
+    frame, seg = build_layers(w, params, bf16_gemm)
     ep = OrderedDict()
     x = np.asarray(features, np.float64)
     for l in frame:
@@ -273,14 +288,15 @@ def tower_forward_backward(features, labels, w, params, global_step=0, want_grad
     return out
 
 
-def train_step(features, labels, w, params, learning_rate, global_step=0, num_towers=1, opt_state=None):
+def train_step(features, labels, w, params, learning_rate, global_step=0, num_towers=1, opt_state=None, bf16_gemm=False):
     """TrainerMGPU semantics (model/trainer.py:1133-1248) for `num_towers` towers (1 = Trainer): the batch is cut
     into equal slices, every tower uses its own BN batch statistics, gradients are averaged (add_n / N), moving
     averages come from tower 0, one optimizer step.  Returns (new_weights, info)."""
     n = features.shape[0]
     assert n % num_towers == 0
     per = n // num_towers
-    outs = [tower_forward_backward(features[i * per:(i + 1) * per], labels[i * per:(i + 1) * per], w, params, global_step)
+    outs = [tower_forward_backward(features[i * per:(i + 1) * per], labels[i * per:(i + 1) * per], w, params, global_step,
+                                   bf16_gemm=bf16_gemm)
             for i in range(num_towers)]
     grads = {k: sum(o["grads"][k] for o in outs) / num_towers for k in outs[0]["grads"]}
     if params.dict.get("clip_gradient", False):

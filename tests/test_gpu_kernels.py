@@ -44,11 +44,15 @@ def _run_gemm(eng, a, wt, taps, scale, shift, neg_slope, m_rows, dilation=1):
 
 
 def _ref_gemm(a, wt, taps, scale, shift, neg_slope, m_rows, dilation=1):
+    """out[m] = sum_j a[m + j*dilation] . wt[:, tap j]; rows outside [0, rows) read as zero (a negative dilation is the
+    data-gradient mode of the training step: taps reach backwards)."""
     rows, cin = a.shape
-    a64 = np.concatenate([a.astype(np.float64), np.zeros(((taps - 1) * dilation, cin))], axis=0)
+    pad = (taps - 1) * abs(dilation)
+    a64 = np.concatenate([np.zeros((pad, cin)), a.astype(np.float64), np.zeros((pad, cin))], axis=0)
     acc = np.zeros((m_rows, wt.shape[0]))
     for j in range(taps):
-        acc += a64[j * dilation:j * dilation + m_rows] @ wt[:, j * cin:(j + 1) * cin].astype(np.float64).T
+        lo = pad + j * dilation
+        acc += a64[lo:lo + m_rows] @ wt[:, j * cin:(j + 1) * cin].astype(np.float64).T
     y = acc * scale + shift
     return np.where(y >= 0, y, neg_slope * y)
 
@@ -62,6 +66,8 @@ def _ref_gemm(a, wt, taps, scale, shift, neg_slope, m_rows, dilation=1):
     (640, 192, 1, 512, 1),         # tdnn1 on pre-spliced rows (K = 150 -> 192)
     (20000, 512, 5, 512, 1),       # more tiles than SMs: persistent loop, both TMEM stages, ring wrap
     (900, 512, 3, 256, 2),         # dilation 2 (Kaldi-style context; the reference uses 1)
+    (1000, 512, 5, 512, -1),       # tap step -1: the data-gradient GEMM of the training step (negative TMA rows = 0)
+    (700, 1536, 1, 512, -1),       # tdnn5's data gradient: K = 1536
 ])
 def test_tcgen05_gemm_matches_fp64(eng, rows, cin, taps, n, dil):
     rng = np.random.default_rng(rows + cin + taps + n)

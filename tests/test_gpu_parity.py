@@ -81,8 +81,8 @@ def test_error_behaviour():
         eng.forward(x, np.array([40], np.int32), node="tdnn9_dense")
     assert eng.forward(np.zeros((0, 30), np.float32), np.zeros(0, np.int32)).shape == (0, 512)
     eng.close()
-    with pytest.raises(xvector_b200.XVectorError, match="Not implement resnet_18 network"):
-        xvector_b200.Engine(dict(cfg, network_type="resnet_18"), 30)
+    with pytest.raises(xvector_b200.XVectorError, match="Not implement ftdnn network"):
+        xvector_b200.Engine(dict(cfg, network_type="ftdnn"), 30)
     with pytest.raises(xvector_b200.XVectorError, match="Not implement lde pooling"):
         xvector_b200.Engine(dict(cfg, pooling_type="lde"), 30)
 

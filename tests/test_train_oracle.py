@@ -68,3 +68,18 @@ def test_tower_semantics_and_sgd_update():
     mv = np.asarray(w["tdnn/tdnn4_bn/moving_variance"], np.float64)
     assert np.all(np.abs(new1["tdnn/tdnn4_bn/moving_variance"] - mv) <= 0.0100001 * np.maximum(mv, 5.0))
     assert info2["loss"] == pytest.approx(np.mean(info2["tower_losses"]))
+
+
+def test_bf16_gemm_option_rounds_only_frame_layer_operands():
+    """train_ref's bf16_gemm restates the mixed-precision step: close to the exact step, not identical, same variables."""
+    from oracle import numpy_ref, synth, train_ref
+    cfg = dict(synth.TDNN_AMSOFTMAX_CONFIG)
+    w = synth.add_softmax_weights(synth.make_tdnn_weights(24, cfg, seed=5), 40, bias=False)
+    x, y = synth.config5_batch(8, 40, 24, 40, seed=6)
+    p = numpy_ref.OracleParams(**cfg)
+    _, exact = train_ref.train_step(x, y, w, p, 0.1, 0)
+    _, mixed = train_ref.train_step(x, y, w, p, 0.1, 0, bf16_gemm=True)
+    assert set(exact["grads"]) == set(mixed["grads"])
+    assert 0 < abs(exact["loss"] - mixed["loss"]) <= 1e-2 * abs(exact["loss"])
+    r = train_ref.bf16_round(np.array([1.0, 1.0 + 2.0 ** -8, 1.0 + 3 * 2.0 ** -9, -0.1]))
+    assert r[0] == 1.0 and r[1] == 1.0 and r[2] == 1.0 + 2.0 ** -7 and abs(r[3] + 0.1) < 2.0 ** -11

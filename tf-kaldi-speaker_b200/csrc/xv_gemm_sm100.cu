@@ -362,7 +362,8 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
         if (!kPool && p.out_f32 != nullptr && row_ok) {
           float4* dst = reinterpret_cast<float4*>(p.out_f32 + static_cast<size_t>(row) * p.ldo + n0 + c * 32);
 #pragma unroll
-          for (int g = 0; g < 8; ++g) dst[g] = make_float4(y[g * 4], y[g * 4 + 1], y[g * 4 + 2], y[g * 4 + 3]);
+          for (int g = 0; g < 8; ++g)
+            if (n0 + c * 32 + g * 4 < p.f32_cols) dst[g] = make_float4(y[g * 4], y[g * 4 + 1], y[g * 4 + 2], y[g * 4 + 3]);
         }
       }
       }

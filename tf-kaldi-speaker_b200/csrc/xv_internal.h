@@ -42,6 +42,7 @@ struct GemmParams {
   __nv_bfloat16* out_bf16;  // [m_rows, ldo] or null
   float* out_f32;           // [m_rows, ldo] or null
   int32_t ldo;
+  int32_t f32_cols = 0x7fffffff;   // fp32 stores are masked to columns < f32_cols (a multiple of 4); training: cout = 1500
   // fused statistics-pooling partial sums (tdnn5): acc[utt][0|1][pool_ld] += sum x | sum x^2
   double* pool_acc;    // fp64: atomics become order-independent at fp32 precision
   int32_t pool_ld;

@@ -188,7 +188,7 @@ int xv_gemm_bf16(xv_ctx* c, const void* a_dev, int64_t a_rows, int32_t cin, int3
                  void* out_dev, int32_t ldo, int64_t m_rows) {
   if (!c) return XV_EINVAL;
   if (!a_dev || !wt_dev || !scale_dev || !shift_dev || !out_dev) return fail(c, XV_EINVAL, "xv_gemm_bf16: null argument");
-  if (cin % kBK || n % kBN || ldo != n || taps < 1 || dilation < 1 || a_rows < kBM || m_rows > a_rows)
+  if (cin % kBK || n % kBN || ldo != n || taps < 1 || dilation == 0 || a_rows < kBM || m_rows > a_rows)
     return fail(c, XV_EINVAL,
                 "xv_gemm_bf16: needs cin %% 64 == 0, n %% 256 == 0, ldo == n, a_rows >= 128 (allocation), m_rows <= a_rows");
   cudaSetDevice(c->device);
@@ -235,7 +235,7 @@ int xv_gemm_bf16_async(xv_ctx* c, const void* a_dev, int64_t a_rows, int32_t cin
   if (!c) return XV_EINVAL;
   if (!a_dev || !wt_dev || !scale_dev || !shift_dev || !slope_dev || !out_dev)
     return fail(c, XV_EINVAL, "xv_gemm_bf16_async: null argument");
-  if (cin % kBK || n % kBN || taps < 1 || dilation < 1 || a_rows < kBM || m_rows > a_rows)
+  if (cin % kBK || n % kBN || taps < 1 || dilation == 0 || a_rows < kBM || m_rows > a_rows)
     return fail(c, XV_EINVAL, "xv_gemm_bf16_async: bad geometry");
   const int kpad = taps * cin;
   GemmPlan g;

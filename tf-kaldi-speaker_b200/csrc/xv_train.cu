@@ -148,7 +148,9 @@ namespace {
 // Per-column sums over the VALID rows of a [rows, C] matrix ((r mod T) < valid_len), NV fp64 sums per column.
 struct RowMask {
   int32_t t, valid_len;   // utterance length in rows and number of valid rows per utterance
-  __device__ __forceinline__ bool ok(int64_t r) const { return static_cast<int32_t>(r % t) < valid_len; }
+  __device__ __forceinline__ bool ok(int64_t r) const {     // rows of a step fit 32 bits (checked by xv_train_step)
+    return static_cast<int32_t>(static_cast<uint32_t>(r) % static_cast<uint32_t>(t)) < valid_len;
+  }
 };
 
 struct StatsF {            // v0 = sum z, v1 = sum z^2
@@ -191,9 +193,11 @@ __global__ void __launch_bounds__(256) col_reduce_kernel(const F f, const RowMas
   double v[F::NV];
 #pragma unroll
   for (int k = 0; k < F::NV; ++k) v[k] = 0.0;
-  if (c < c_total)
+  if (c < c_total) {
+#pragma unroll 4
     for (int64_t r = r0 + ry; r < r1; r += 8)
       if (mask.ok(r)) f(r, c, v);
+  }
 #pragma unroll
   for (int k = 0; k < F::NV; ++k) red[k][ry][cx] = v[k];
   __syncthreads();
@@ -236,74 +240,205 @@ __global__ void bn_finalize_kernel(const double* __restrict__ sums, int c_total,
 }
 
 // ------------------------------------------------------------------------------------------------ elementwise
-__global__ void bn_act_fwd_kernel(const float* __restrict__ z, int64_t rows, int c_total, RowMask mask,
-                                  const float* __restrict__ mean, const float* __restrict__ rstd,
-                                  const float* __restrict__ gamma, const float* __restrict__ beta,
-                                  const float* __restrict__ slope, float* __restrict__ y) {
-  const int64_t total = rows * c_total;
-  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-    const int c = static_cast<int>(i % c_total);
-    const int64_t r = i / c_total;
-    float v = 0.f;
-    if (mask.ok(r)) {
-      v = z[i];
-      if (mean != nullptr) v = fmaf(gamma[c], (v - mean[c]) * rstd[c], beta[c]);
-      v = v >= 0.f ? v : v * slope[c];
+// The three row-streaming kernels below give every thread FOUR consecutive channels (one 16-byte access per tensor) and
+// keep the per-channel constants in registers while the thread walks down the rows; widths that are not a multiple
+// of 4 take the scalar path (Q = 1).
+template <int Q> struct VecF;
+template <> struct VecF<4> {
+  static __device__ __forceinline__ void load(const float* p, float* v) { const float4 t = *reinterpret_cast<const float4*>(p); v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w; }
+  static __device__ __forceinline__ void store(float* p, const float* v) { *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]); }
+  static __device__ __forceinline__ void store_bf16(__nv_bfloat16* p, const float* v) {
+    const __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], v[3]);
+    uint2 u;
+    u.x = *reinterpret_cast<const uint32_t*>(&lo);
+    u.y = *reinterpret_cast<const uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(p) = u;
+  }
+};
+template <> struct VecF<1> {
+  static __device__ __forceinline__ void load(const float* p, float* v) { v[0] = *p; }
+  static __device__ __forceinline__ void store(float* p, const float* v) { *p = v[0]; }
+  static __device__ __forceinline__ void store_bf16(__nv_bfloat16* p, const float* v) { *p = __float2bfloat16(v[0]); }
+};
+
+// y = act(BN(z)) on valid rows, 0 elsewhere; optional fp32 output, optional bf16 operand copy (pad columns zeroed).
+template <int Q>
+__global__ void __launch_bounds__(256) bn_act_fwd_kernel(const float* __restrict__ z, int64_t rows, int c_total, RowMask mask,
+                                                         const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                         const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                         const float* __restrict__ slope, float* __restrict__ y,
+                                                         __nv_bfloat16* __restrict__ yb, int ldb) {
+  const int nq = c_total / Q;
+  const int64_t rstep = static_cast<int64_t>(gridDim.x) * blockDim.y;
+  for (int q = threadIdx.x; q < nq; q += blockDim.x) {
+    const int c0 = q * Q;
+    float mu[Q], rs[Q], ga[Q], be[Q], sl[Q];
+#pragma unroll
+    for (int k = 0; k < Q; ++k) {
+      mu[k] = 0.f; rs[k] = 1.f; ga[k] = 1.f; be[k] = 0.f;
+      if (mean != nullptr) { mu[k] = mean[c0 + k]; rs[k] = rstd[c0 + k]; ga[k] = gamma[c0 + k]; be[k] = beta[c0 + k]; }
+      sl[k] = slope[c0 + k];
     }
-    y[i] = v;
+    for (int64_t r = static_cast<int64_t>(blockIdx.x) * blockDim.y + threadIdx.y; r < rows; r += rstep) {
+      float v[Q];
+#pragma unroll
+      for (int k = 0; k < Q; ++k) v[k] = 0.f;
+      if (mask.ok(r)) {
+        VecF<Q>::load(z + r * c_total + c0, v);
+#pragma unroll
+        for (int k = 0; k < Q; ++k) {
+          float t = v[k];
+          if (mean != nullptr) t = fmaf(ga[k], (t - mu[k]) * rs[k], be[k]);      // same expression as BnBwdF / the apply kernel
+          v[k] = t >= 0.f ? t : t * sl[k];
+        }
+      }
+      if (y != nullptr) VecF<Q>::store(y + r * c_total + c0, v);
+      if (yb != nullptr) {
+        VecF<Q>::store_bf16(yb + r * ldb + c0, v);
+        if (q == nq - 1)
+          for (int k = c_total; k < ldb; ++k) yb[r * ldb + k] = __float2bfloat16(0.f);
+      }
+    }
   }
 }
 
-// dz = gamma*rstd*(g - sum_g/n - xhat*sum_gx/n) on valid rows, 0 elsewhere (in place over dy).
-__global__ void bn_bwd_apply_kernel(float* __restrict__ dy, const float* __restrict__ z, int64_t rows, int c_total,
-                                    RowMask mask, const float* __restrict__ mean, const float* __restrict__ rstd,
-                                    const float* __restrict__ gamma, const float* __restrict__ beta,
-                                    const float* __restrict__ slope, const double* __restrict__ sums, double n) {
-  const int64_t total = rows * c_total;
-  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-    const int c = static_cast<int>(i % c_total);
-    const int64_t r = i / c_total;
-    float out = 0.f;
-    if (mask.ok(r)) {
-      const float zz = z[i];
-      const float d = dy[i];
+// dz = gamma*rstd*(g - sum_g/n - xhat*sum_gx/n) on valid rows, 0 elsewhere (in place over dy); optional bf16 copy.
+template <int Q>
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(float* __restrict__ dy, const float* __restrict__ z, int64_t rows,
+                                                           int c_total, RowMask mask, const float* __restrict__ mean,
+                                                           const float* __restrict__ rstd, const float* __restrict__ gamma,
+                                                           const float* __restrict__ beta, const float* __restrict__ slope,
+                                                           const double* __restrict__ sums, double n,
+                                                           __nv_bfloat16* __restrict__ dzb, int ldb) {
+  const int nq = c_total / Q;
+  const int64_t rstep = static_cast<int64_t>(gridDim.x) * blockDim.y;
+  for (int q = threadIdx.x; q < nq; q += blockDim.x) {
+    const int c0 = q * Q;
+    float mu[Q], rs[Q], ga[Q], be[Q], sl[Q];
+    double k1[Q], k2[Q], gr[Q];
+#pragma unroll
+    for (int k = 0; k < Q; ++k) {
+      sl[k] = slope[c0 + k];
+      mu[k] = 0.f; rs[k] = 1.f; ga[k] = 1.f; be[k] = 0.f; k1[k] = 0.0; k2[k] = 0.0; gr[k] = 1.0;
       if (mean != nullptr) {
-        const float xh = (zz - mean[c]) * rstd[c];
-        const float pre = fmaf(gamma[c], xh, beta[c]);
-        const float g = pre > 0.f ? d : d * slope[c];
-        const double t = static_cast<double>(g) - sums[c] / n - static_cast<double>(xh) * (sums[c_total + c] / n);
-        out = static_cast<float>(static_cast<double>(gamma[c]) * rstd[c] * t);
-      } else {
-        out = zz > 0.f ? d : d * slope[c];
+        mu[k] = mean[c0 + k]; rs[k] = rstd[c0 + k]; ga[k] = gamma[c0 + k]; be[k] = beta[c0 + k];
+        k1[k] = sums[c0 + k] / n; k2[k] = sums[c_total + c0 + k] / n;
+        gr[k] = static_cast<double>(ga[k]) * rs[k];
       }
     }
-    dy[i] = out;
+    for (int64_t r = static_cast<int64_t>(blockIdx.x) * blockDim.y + threadIdx.y; r < rows; r += rstep) {
+      float out[Q];
+#pragma unroll
+      for (int k = 0; k < Q; ++k) out[k] = 0.f;
+      if (mask.ok(r)) {
+        float zz[Q], d[Q];
+        VecF<Q>::load(z + r * c_total + c0, zz);
+        VecF<Q>::load(dy + r * c_total + c0, d);
+#pragma unroll
+        for (int k = 0; k < Q; ++k) {
+          if (mean != nullptr) {
+            const float xh = (zz[k] - mu[k]) * rs[k];
+            const float pre = fmaf(ga[k], xh, be[k]);
+            const float g = pre > 0.f ? d[k] : d[k] * sl[k];
+            const double t = static_cast<double>(g) - k1[k] - static_cast<double>(xh) * k2[k];
+            out[k] = static_cast<float>(gr[k] * t);
+          } else {
+            out[k] = zz[k] > 0.f ? d[k] : d[k] * sl[k];
+          }
+        }
+      }
+      VecF<Q>::store(dy + r * c_total + c0, out);
+      if (dzb != nullptr) {
+        VecF<Q>::store_bf16(dzb + r * ldb + c0, out);
+        if (q == nq - 1)
+          for (int k = c_total; k < ldb; ++k) dzb[r * ldb + k] = __float2bfloat16(0.f);
+      }
+    }
   }
 }
 
 // Statistics-pooling backward (model/pooling.py:40-50): pooled = [mean | std]; dx = dmean/L + dstd*(x-mean)/(L*std).
-__global__ void pool_bwd_kernel(const float* __restrict__ x, int64_t rows, int c_total, RowMask mask,
-                                const float* __restrict__ pooled, const float* __restrict__ dpooled,
-                                float* __restrict__ dx) {
-  const int64_t total = rows * c_total;
+template <int Q>
+__global__ void __launch_bounds__(256) pool_bwd_kernel(const float* __restrict__ x, int64_t rows, int c_total, RowMask mask,
+                                                       const float* __restrict__ pooled, const float* __restrict__ dpooled,
+                                                       float* __restrict__ dx) {
+  const int nq = c_total / Q;
   const float inv_l = 1.f / static_cast<float>(mask.valid_len);
+  const int64_t rstep = static_cast<int64_t>(gridDim.x) * blockDim.y;
+  for (int q = threadIdx.x; q < nq; q += blockDim.x) {
+    const int c0 = q * Q;
+    for (int64_t r = static_cast<int64_t>(blockIdx.x) * blockDim.y + threadIdx.y; r < rows; r += rstep) {
+      float out[Q];
+#pragma unroll
+      for (int k = 0; k < Q; ++k) out[k] = 0.f;
+      if (mask.ok(r)) {
+        const int64_t u = r / mask.t;
+        float xv[Q], mu[Q], sd[Q], dm[Q], ds[Q];
+        VecF<Q>::load(x + r * c_total + c0, xv);
+        VecF<Q>::load(pooled + u * 2 * c_total + c0, mu);
+        VecF<Q>::load(pooled + u * 2 * c_total + c_total + c0, sd);
+        VecF<Q>::load(dpooled + u * 2 * c_total + c0, dm);
+        VecF<Q>::load(dpooled + u * 2 * c_total + c_total + c0, ds);
+#pragma unroll
+        for (int k = 0; k < Q; ++k) {
+          out[k] = dm[k] * inv_l;
+          if (sd[k] * sd[k] > 1.0000001e-12f) out[k] += ds[k] * (xv[k] - mu[k]) * inv_l / sd[k];   // variance floor: no gradient
+        }
+      }
+      VecF<Q>::store(dx + r * c_total + c0, out);
+    }
+  }
+}
+
+// Launch geometry of the row-streaming kernels: x covers the channel groups, y the rows.
+struct RowGrid { dim3 grid, block; };
+inline RowGrid row_grid(int groups, int sm_count) {
+  int bx = 32;
+  while (bx < groups && bx < 256) bx <<= 1;
+  RowGrid g;
+  g.block = dim3(bx, 256 / bx);
+  g.grid = dim3(sm_count * 8);
+  return g;
+}
+
+// ------------------------------------------------------------------------------------------------ bf16 operand copies
+// Master weights stay fp32 in the flat buffer; every step re-casts them into the two bf16 layouts the GEMMs read.
+// Forward operand: wt[n][k] (K-major), k = j*cstride + c  ->  W[j, c, n]; zero for n >= cout, c >= cin, j >= taps.
+__global__ void cast_w_fwd_kernel(const float* __restrict__ w, int taps, int cin, int cout, int cstride, int ktotal,
+                                  int n_alloc, __nv_bfloat16* __restrict__ wt) {
+  __shared__ float tile[32][33];
+  const int k0 = blockIdx.x * 32, n0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    const int k = k0 + i, n = n0 + threadIdx.x;
+    const int j = k / cstride, c = k - j * cstride;
+    float v = 0.f;
+    if (k < ktotal && j < taps && c < cin && n < cout) v = w[(static_cast<int64_t>(j) * cin + c) * cout + n];
+    tile[i][threadIdx.x] = v;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    const int n = n0 + i, k = k0 + threadIdx.x;
+    if (n < n_alloc && k < ktotal) wt[static_cast<int64_t>(n) * ktotal + k] = __float2bfloat16(tile[threadIdx.x][i]);
+  }
+}
+// Data-gradient operand: wd[c][j*ldz + n] = W[j, c, n]; zero for c >= cin, n >= cout.
+__global__ void cast_w_dgrad_kernel(const float* __restrict__ w, int taps, int cin, int cout, int ldz, int c_alloc,
+                                    __nv_bfloat16* __restrict__ wd) {
+  const int64_t total = static_cast<int64_t>(c_alloc) * taps * ldz;
   for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-    const int c = static_cast<int>(i % c_total);
-    const int64_t r = i / c_total;
-    float out = 0.f;
-    if (mask.ok(r)) {
-      const int64_t u = r / mask.t;
-      const float* p = pooled + u * 2 * c_total;
-      const float* dp = dpooled + u * 2 * c_total;
-      const float sd = p[c_total + c];
-      out = dp[c] * inv_l;
-      if (sd * sd > 1.0000001e-12f) out += dp[c_total + c] * (x[i] - p[c]) * inv_l / sd;   // variance floor: no gradient
-    }
-    dx[i] = out;
+    const int n = static_cast<int>(i % ldz);
+    const int64_t q = i / ldz;
+    const int j = static_cast<int>(q % taps);
+    const int c = static_cast<int>(q / taps);
+    float v = 0.f;
+    if (c < cin && n < cout) v = w[(static_cast<int64_t>(j) * cin + c) * cout + n];
+    wd[i] = __float2bfloat16(v);
   }
+}
+__global__ void pad_copy_kernel(const float* __restrict__ src, int n, float* __restrict__ dst, int n_alloc) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_alloc) dst[i] = i < n ? src[i] : 0.f;
 }
 
 __global__ void axpy_rows_kernel(float* __restrict__ y, const float* __restrict__ x, const float* __restrict__ coef,
@@ -316,15 +451,23 @@ __global__ void axpy_rows_kernel(float* __restrict__ y, const float* __restrict_
 
 // ------------------------------------------------------------------------------------------------ loss
 // r[s] = rsqrt(max(sum_e w[e,s]^2, 1e-12))  (tf.nn.l2_normalize(w, dim=0), model/loss.py:241)
-__global__ void col_rnorm_kernel(const float* __restrict__ w, int e_dim, int s_dim, float* __restrict__ r) {
-  const int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= s_dim) return;
+__global__ void __launch_bounds__(256) col_rnorm_kernel(const float* __restrict__ w, int e_dim, int s_dim, float* __restrict__ r) {
+  __shared__ double red[8][33];
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int s = blockIdx.x * 32 + cx;
   double ss = 0.0;
-  for (int e = 0; e < e_dim; ++e) {
-    const double v = w[static_cast<int64_t>(e) * s_dim + s];
-    ss += v * v;
+  if (s < s_dim)
+    for (int e = ry; e < e_dim; e += 8) {
+      const double v = w[static_cast<int64_t>(e) * s_dim + s];
+      ss += v * v;
+    }
+  red[ry][cx] = ss;
+  __syncthreads();
+  if (ry == 0 && s < s_dim) {
+    double t = 0.0;
+    for (int j = 0; j < 8; ++j) t += red[j][cx];
+    r[s] = static_cast<float>(1.0 / sqrt(fmax(t, 1e-12)));
   }
-  r[s] = static_cast<float>(1.0 / sqrt(fmax(ss, 1e-12)));
 }
 
 __device__ __forceinline__ double block_reduce(double v, double* sh, bool is_max) {
@@ -408,22 +551,125 @@ __global__ void __launch_bounds__(256) softmax_loss_kernel(float* __restrict__ l
 }
 
 // dW[e,s] = r_s * (dwn[e,s] - wn[e,s] * sum_e' dwn[e',s]*wn[e',s]),  wn = W * r_s   (in place over dwn)
-__global__ void amsoftmax_dw_kernel(float* __restrict__ dwn, const float* __restrict__ w, const float* __restrict__ r,
-                                    int e_dim, int s_dim) {
-  const int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= s_dim) return;
-  const double rs = r[s];
+__global__ void __launch_bounds__(256) amsoftmax_dw_kernel(float* __restrict__ dwn, const float* __restrict__ w,
+                                                           const float* __restrict__ r, int e_dim, int s_dim) {
+  __shared__ double red[8][33];
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int s = blockIdx.x * 32 + cx;
+  const double rs = s < s_dim ? r[s] : 0.0;
   double dot = 0.0;
-  for (int e = 0; e < e_dim; ++e) {
-    const int64_t i = static_cast<int64_t>(e) * s_dim + s;
-    dot += static_cast<double>(dwn[i]) * (static_cast<double>(w[i]) * rs);
-  }
+  if (s < s_dim)
+    for (int e = ry; e < e_dim; e += 8) {
+      const int64_t i = static_cast<int64_t>(e) * s_dim + s;
+      dot += static_cast<double>(dwn[i]) * (static_cast<double>(w[i]) * rs);
+    }
+  red[ry][cx] = dot;
+  __syncthreads();
+  dot = 0.0;
+  for (int j = 0; j < 8; ++j) dot += red[j][cx];
+  if (s >= s_dim) return;
   const bool floored = rs >= 0.999999e6;                         // sum w^2 <= 1e-12: l2_normalize's max() is flat
-  for (int e = 0; e < e_dim; ++e) {
+  for (int e = ry; e < e_dim; e += 8) {
     const int64_t i = static_cast<int64_t>(e) * s_dim + s;
     const double g = floored ? rs * dwn[i] : rs * (static_cast<double>(dwn[i]) - static_cast<double>(w[i]) * rs * dot);
     dwn[i] = static_cast<float>(g);
   }
+}
+
+// ------------------------------------------------------------------------------------------------ skinny GEMMs
+// The segment-level layers and the softmax layer multiply a [B, K] matrix with B = the utterances of a step (64): too
+// few rows for a 128-row tensor-core tile to pay, and fp32 keeps the loss head exact.  One block = 64 rows x 64 columns
+// x one K chunk; the K chunks of a tile are spread over blocks (split-K) and added with fp32 atomics into a zeroed
+// output, so that ~2 blocks per SM stream the weight matrix once at full bandwidth.
+//   TB = false: out[m, n] += cs[n] * sum_k a[m, k] * w[k, n]      (forward:  w = kernel [K, N])
+//   TB = true : out[m, n] += cs[n] * sum_k a[m, k] * w[n, k]      (backward: w = kernel [N, K], contraction over its columns)
+struct SkinnyArgs {
+  const float* a; int32_t lda;
+  const float* w; int32_t ldw;
+  float* out; int32_t ldo;
+  const float* col_scale;    // [n] or null
+  const float* bias;         // [n] or null, added by the first K chunk
+  int32_t m, n, k, ks;       // ks: K chunk per block (multiple of 64)
+};
+
+template <bool TB>
+__global__ void __launch_bounds__(256) skinny_gemm_kernel(const SkinnyArgs g) {
+  __shared__ float As[64][65];
+  __shared__ __align__(16) float Bs[64][68];
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;       // 16 x 16 threads, 4 x 4 outputs each
+  const int n0 = blockIdx.x * 64, m0 = blockIdx.z * 64;
+  const int kbeg = blockIdx.y * g.ks, kend = min(kbeg + g.ks, g.k);
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  for (int k0 = kbeg; k0 < kend; k0 += 64) {
+#pragma unroll 4
+    for (int i = 0; i < 16; ++i) {
+      const int idx = i * 256 + threadIdx.x;
+      const int mm = idx >> 6, kk = idx & 63;
+      const int m = m0 + mm, k = k0 + kk;
+      As[kk][mm] = (m < g.m && k < kend) ? g.a[static_cast<int64_t>(m) * g.lda + k] : 0.f;
+    }
+#pragma unroll 4
+    for (int i = 0; i < 16; ++i) {
+      const int idx = i * 256 + threadIdx.x;
+      if (TB) {
+        const int nn = idx >> 6, kk = idx & 63;
+        const int n = n0 + nn, k = k0 + kk;
+        Bs[kk][nn] = (n < g.n && k < kend) ? g.w[static_cast<int64_t>(n) * g.ldw + k] : 0.f;
+      } else {
+        const int kk = idx >> 6, nn = idx & 63;
+        const int n = n0 + nn, k = k0 + kk;
+        Bs[kk][nn] = (n < g.n && k < kend) ? g.w[static_cast<int64_t>(k) * g.ldw + n] : 0.f;
+      }
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int kk = 0; kk < 64; ++kk) {
+      const float4 b = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
+      float a[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = As[kk][ty + 16 * i];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        acc[i][0] = fmaf(a[i], b.x, acc[i][0]);
+        acc[i][1] = fmaf(a[i], b.y, acc[i][1]);
+        acc[i][2] = fmaf(a[i], b.z, acc[i][2]);
+        acc[i][3] = fmaf(a[i], b.w, acc[i][3]);
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int m = m0 + ty + 16 * i;
+    if (m >= g.m) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n0 + tx * 4 + j;
+      if (n >= g.n) continue;
+      float v = acc[i][j];
+      if (g.col_scale != nullptr) v *= g.col_scale[n];
+      if (g.bias != nullptr && blockIdx.y == 0) v += g.bias[n];
+      atomicAdd(g.out + static_cast<int64_t>(m) * g.ldo + n, v);
+    }
+  }
+}
+
+template <bool TB>
+cudaError_t launch_skinny_gemm(SkinnyArgs g, int sm_count, cudaStream_t s) {
+  cudaError_t e = cudaMemset2DAsync(g.out, sizeof(float) * g.ldo, 0, sizeof(float) * g.n, g.m, s);
+  if (e != cudaSuccess) return e;
+  const int nb = (g.n + 63) / 64, mb = (g.m + 63) / 64, kb = (g.k + 63) / 64;
+  int splits = (2 * sm_count + nb * mb - 1) / (nb * mb);
+  if (splits > kb) splits = kb;
+  if (splits < 1) splits = 1;
+  g.ks = (kb + splits - 1) / splits * 64;
+  splits = (g.k + g.ks - 1) / g.ks;
+  skinny_gemm_kernel<TB><<<dim3(nb, splits, mb), 256, 0, s>>>(g);
+  return cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------------------------ optimizer
@@ -488,6 +734,13 @@ struct TrLayer {
   int taps = 1, cin = 0, cout = 0, context = 0;
   int64_t off_kernel = -1, off_bias = -1, off_gamma = -1, off_beta = -1, off_alpha = -1, off_mm = -1, off_mv = -1;
   DevBuf z, y, mean, rstd;
+  // mixed precision (bf16 tensor-core GEMMs, fp32 master weights): frame layers only
+  int a_cin = 0, a_taps = 1;       // channels / taps of the bf16 A operand (layer 0 reads pre-spliced features)
+  int ktotal = 0;                  // a_taps * a_cin
+  int n_alloc = 0, c_alloc = 0;    // cout, a_cin rounded up to the 256-wide N tile
+  int ldb = 0;                     // row stride of this layer's bf16 y / dz copies (cout rounded up to 64)
+  DevBuf wt_fwd, wt_dgrad, bias_pad, yb;
+  CUtensorMap tm_wf, tm_wd;
 };
 
 struct UidBlob { char bytes[128]; };     // ncclUniqueId is a 128-byte POD passed by value
@@ -516,6 +769,8 @@ struct TrainState {
   std::string relu_type;
   DevBuf const_slope, zeros, feats, labels, d_cu, pooled, logits, gr, coef, rnorm, dbuf[2], sums, scalars, pool_ws, scratch;
   int cap_b = 0, cap_t = 0;
+  bool mixed = false;                    // context precision bf16: frame-layer GEMMs on tcgen05, everything else fp32
+  DevBuf xb0, dzb, ones_pad, zeros_pad;
   // data parallel
   NcclApi nccl;
   void* comm = nullptr;
@@ -600,11 +855,11 @@ void train_release(xv_ctx* c) {
 static int train_init(xv_ctx* c, int32_t num_speakers) {
   if (c->resnet || c->scope != "tdnn" || c->pooling_type != "statistics_pooling")
     return fail(c, XV_EUNSUPPORTED, "xv_train_init: the training step covers network_type tdnn with statistics_pooling");
-  if (c->bf16) return fail(c, XV_EUNSUPPORTED, "xv_train_init: create the context with \"precision\":\"fp32\" (the training step is the fp32 path)");
   if (c->feature_norm) return fail(c, XV_EUNSUPPORTED, "xv_train_init: feature_norm is not covered");
   train_release(c);
   TrainState* t = new TrainState();
   c->train = t;
+  t->mixed = c->bf16;
   const JValue& cfg = c->cfg;
   const JValue* lf = cfg.get("loss_func");
   const std::string loss = (lf && lf->type == JValue::Str) ? lf->str : "softmax";
@@ -704,6 +959,37 @@ static int train_init(xv_ctx* c, int32_t num_speakers) {
     if ((rc = ensure(c, &l.mean, sizeof(float) * l.cout)) != XV_OK) return rc;
     if ((rc = ensure(c, &l.rstd, sizeof(float) * l.cout)) != XV_OK) return rc;
   }
+  if (t->mixed) {
+    const char* we = wgrad_init();
+    if (we) return fail(c, XV_ECUDA, "%s", we);
+    int max_alloc = 256;
+    int prev_ldb = 0;
+    for (int i = 0; i < t->n_frame; ++i) {
+      TrLayer& l = t->layers[i];
+      if (l.cout % 4 != 0) return fail(c, XV_EUNSUPPORTED, "bf16 training needs layer widths that are multiples of 4 (%s has %d)", l.name.c_str(), l.cout);
+      if (i == 0) { l.a_taps = 1; l.a_cin = (l.taps * l.cin + kBK - 1) / kBK * kBK; }
+      else { l.a_taps = l.taps; l.a_cin = prev_ldb; }
+      l.ktotal = l.a_taps * l.a_cin;
+      l.n_alloc = (l.cout + kBN - 1) / kBN * kBN;
+      l.c_alloc = (l.a_cin + kBN - 1) / kBN * kBN;
+      l.ldb = (l.cout + kBK - 1) / kBK * kBK;
+      prev_ldb = l.ldb;
+      max_alloc = std::max(max_alloc, std::max(l.n_alloc, l.c_alloc));
+      if ((rc = ensure(c, &l.wt_fwd, sizeof(__nv_bfloat16) * static_cast<size_t>(l.n_alloc) * l.ktotal)) != XV_OK) return rc;
+      if ((rc = ensure(c, &l.bias_pad, sizeof(float) * l.n_alloc)) != XV_OK) return rc;
+      const char* e = make_tmap_bf16_2d(&l.tm_wf, l.wt_fwd.p, l.ktotal, l.n_alloc, static_cast<uint64_t>(l.ktotal) * 2, kBK, kBN);
+      if (!e && i > 0) {
+        const size_t kd = static_cast<size_t>(l.taps) * l.ldb;
+        if ((rc = ensure(c, &l.wt_dgrad, sizeof(__nv_bfloat16) * l.c_alloc * kd)) != XV_OK) return rc;
+        e = make_tmap_bf16_2d(&l.tm_wd, l.wt_dgrad.p, kd, l.c_alloc, kd * 2, kBK, kBN);
+      }
+      if (e) return fail(c, XV_ECUDA, "%s", e);
+    }
+    if ((rc = ensure(c, &t->ones_pad, sizeof(float) * max_alloc)) != XV_OK) return rc;
+    if ((rc = ensure(c, &t->zeros_pad, sizeof(float) * max_alloc)) != XV_OK) return rc;
+    fill_f32_kernel<<<64, 256, 0, c->stream>>>(static_cast<float*>(t->ones_pad.p), max_alloc, 1.f);
+    cudaMemsetAsync(t->zeros_pad.p, 0, sizeof(float) * max_alloc, c->stream);
+  }
   cudaError_t e = cudaStreamSynchronize(c->stream);
   if (e != cudaSuccess) return cuda_fail(c, e, "xv_train_init");
   return XV_OK;
@@ -728,11 +1014,20 @@ int tr_buffers(xv_ctx* c, TrainState* t, int b, int tt) {
   const int64_t rows = static_cast<int64_t>(b) * tt;
   int rc;
   int maxc = 0;
-  for (TrLayer& l : t->layers) {
+  int max_ldb = 0;
+  for (size_t i = 0; i < t->layers.size(); ++i) {
+    TrLayer& l = t->layers[i];
     const int64_t r = l.frame ? rows : b;
+    const bool bf16_only = t->mixed && static_cast<int>(i) < t->n_frame - 1;   // y feeds tensor-core GEMMs only
     if ((rc = ensure(c, &l.z, sizeof(float) * r * l.cout)) != XV_OK) return rc;
-    if ((rc = ensure(c, &l.y, sizeof(float) * r * l.cout)) != XV_OK) return rc;
+    if (!bf16_only && (rc = ensure(c, &l.y, sizeof(float) * r * l.cout)) != XV_OK) return rc;
+    if (bf16_only && (rc = ensure(c, &l.yb, sizeof(__nv_bfloat16) * r * l.ldb)) != XV_OK) return rc;
     maxc = std::max(maxc, l.frame ? l.cout : 0);
+    if (l.frame) max_ldb = std::max(max_ldb, l.ldb);
+  }
+  if (t->mixed) {
+    if ((rc = ensure(c, &t->xb0, sizeof(__nv_bfloat16) * rows * t->layers[0].a_cin)) != XV_OK) return rc;
+    if ((rc = ensure(c, &t->dzb, sizeof(__nv_bfloat16) * rows * max_ldb)) != XV_OK) return rc;
   }
   const int pool_c = t->layers[t->n_frame - 1].cout;
   if ((rc = ensure(c, &t->feats, sizeof(float) * rows * c->dim)) != XV_OK) return rc;
@@ -755,6 +1050,32 @@ int tr_buffers(xv_ctx* c, TrainState* t, int b, int tt) {
   return XV_OK;
 }
 
+// One frame-layer GEMM of the mixed-precision step on the tcgen05 kernel of the embedding path (xv_gemm_sm100.cu):
+// out[m, n] = sum_{j, k} a[m + j*dil, k] * wt[n][j*a_cin + k] + shift[n], fp32 stores masked to n < cols.
+int tr_gemm_tc(xv_ctx* c, TrainState* t, const CUtensorMap& tm_b, const void* a, int64_t rows, int a_cin, int taps, int dil,
+               int n_alloc, const float* shift, float* out, int ldo, int cols, const char* fam) {
+  GemmPlan g;
+  const char* err = make_tmap_bf16_2d(&g.tm_a, a, a_cin, rows, static_cast<uint64_t>(a_cin) * 2, kBK, kBM);
+  if (err) return fail(c, XV_ECUDA, "%s", err);
+  g.tm_b = tm_b;
+  g.tm_out = g.tm_a;     // never dereferenced (no bf16 output)
+  GemmParams& p = g.p;
+  p.m_rows = static_cast<int32_t>(rows);
+  p.m_tiles = static_cast<int32_t>((rows + kBM - 1) / kBM);
+  p.n_tiles = n_alloc / kBN;
+  p.taps = taps; p.dilation = dil; p.kb_per_tap = a_cin / kBK; p.cin = a_cin;
+  p.scale = static_cast<const float*>(t->ones_pad.p); p.shift = shift; p.slope = static_cast<const float*>(t->ones_pad.p);
+  p.act_tanh = 0; p.relu_only = 0;
+  p.out_bf16 = nullptr; p.out_f32 = out; p.ldo = ldo; p.f32_cols = cols;
+  p.pool_acc = nullptr; p.pool_ld = 0; p.tile_seg_ptr = nullptr; p.segs = nullptr; p.row_weight = nullptr;
+  p.heads = 1; p.head_width = n_alloc;
+  g.pool = false;
+  count_launch(c, fam);
+  cudaError_t e = launch_gemm(g, c->sm_count, c->stream);
+  if (e != cudaSuccess) return cuda_fail(c, e, "tcgen05 training GEMM launch");
+  return XV_OK;
+}
+
 }  // namespace
 
 static int train_step(xv_ctx* c, const float* feats, const int32_t* labels, int32_t b, int32_t tt, float lr,
@@ -762,6 +1083,7 @@ static int train_step(xv_ctx* c, const float* feats, const int32_t* labels, int3
   TrainState* t = c->train;
   if (!t) return fail(c, XV_ESTATE, "xv_train_step: call xv_train_init first");
   if (b < 1 || tt <= c->total_context) return fail(c, XV_EINVAL, "xv_train_step: need B >= 1 and T > %d", c->total_context);
+  if (static_cast<int64_t>(b) * tt >= (1LL << 31)) return fail(c, XV_EINVAL, "xv_train_step: B*T must stay below 2^31 rows");
   int rc = tr_buffers(c, t, b, tt);
   if (rc != XV_OK) return rc;
   cudaStream_t s = c->stream;
@@ -808,13 +1130,40 @@ static int train_step(xv_ctx* c, const float* feats, const int32_t* labels, int3
       in_c = 2 * pl.cout;
     }
     if (in_c != l.cin) return fail(c, XV_ESTATE, "training plan: layer %s expects %d inputs, got %d", l.name.c_str(), l.cin, in_c);
-    SimtGemmArgs ga;
-    ga.a = in; ga.a_rows = r; ga.cin = l.cin; ga.taps = l.taps; ga.dilation = 1;
-    ga.w = P + l.off_kernel; ga.n = l.cout; ga.bias = P + l.off_bias;
-    ga.bn_scale = nullptr; ga.bn_shift = nullptr; ga.slope = nullptr; ga.act_tanh = 0;
-    ga.out_dense = static_cast<float*>(l.z.p); ga.out_bn = nullptr; ga.out_act = nullptr; ga.m_rows = r;
-    count_launch(c, "train.gemm_fwd");
-    TR_CUDA(launch_simt_gemm(ga, s), "forward GEMM launch");
+    const bool tc = t->mixed && l.frame;
+    if (tc) {
+      const void* a_bf16;
+      if (i == 0) {
+        count_launch(c, "train.splice_cast");
+        TR_CUDA(launch_splice_cast(static_cast<const float*>(t->feats.p), rows, c->dim, l.taps, 1,
+                                   static_cast<__nv_bfloat16*>(t->xb0.p), l.a_cin, s), "splice launch");
+        a_bf16 = t->xb0.p;
+      } else {
+        a_bf16 = t->layers[i - 1].yb.p;
+      }
+      count_launch(c, "train.cast_w");
+      cast_w_fwd_kernel<<<dim3(l.ktotal / 32, l.n_alloc / 32), dim3(32, 8), 0, s>>>(
+          P + l.off_kernel, l.taps, l.cin, l.cout, i == 0 ? l.cin : l.a_cin, l.ktotal, l.n_alloc,
+          static_cast<__nv_bfloat16*>(l.wt_fwd.p));
+      pad_copy_kernel<<<(l.n_alloc + 255) / 256, 256, 0, s>>>(P + l.off_bias, l.cout, static_cast<float*>(l.bias_pad.p), l.n_alloc);
+      TR_CUDA(cudaGetLastError(), "weight cast launch");
+      if ((rc = tr_gemm_tc(c, t, l.tm_wf, a_bf16, rows, l.a_cin, l.a_taps, 1, l.n_alloc, static_cast<const float*>(l.bias_pad.p),
+                           static_cast<float*>(l.z.p), l.cout, l.cout, "train.tc_fwd")) != XV_OK) return rc;
+    } else if (!l.frame) {
+      SkinnyArgs sa;
+      sa.a = in; sa.lda = l.cin; sa.w = P + l.off_kernel; sa.ldw = l.cout; sa.out = static_cast<float*>(l.z.p); sa.ldo = l.cout;
+      sa.col_scale = nullptr; sa.bias = P + l.off_bias; sa.m = b; sa.n = l.cout; sa.k = l.cin; sa.ks = 0;
+      count_launch(c, "train.skinny_fwd");
+      TR_CUDA(launch_skinny_gemm<false>(sa, c->sm_count, s), "segment-level forward GEMM launch");
+    } else {
+      SimtGemmArgs ga;
+      ga.a = in; ga.a_rows = r; ga.cin = l.cin; ga.taps = l.taps; ga.dilation = 1;
+      ga.w = P + l.off_kernel; ga.n = l.cout; ga.bias = P + l.off_bias;
+      ga.bn_scale = nullptr; ga.bn_shift = nullptr; ga.slope = nullptr; ga.act_tanh = 0;
+      ga.out_dense = static_cast<float*>(l.z.p); ga.out_bn = nullptr; ga.out_act = nullptr; ga.m_rows = r;
+      count_launch(c, "train.gemm_fwd");
+      TR_CUDA(launch_simt_gemm(ga, s), "forward GEMM launch");
+    }
     const float *mean = nullptr, *rstd = nullptr, *gamma = nullptr, *beta = nullptr;
     if (l.has_bn) {
       count_launch(c, "train.bn_stats");
@@ -830,8 +1179,20 @@ static int train_step(xv_ctx* c, const float* feats, const int32_t* labels, int3
       gamma = P + l.off_gamma; beta = P + l.off_beta;
     }
     count_launch(c, "train.bn_act");
-    bn_act_fwd_kernel<<<ew_grid(c), 256, 0, s>>>(static_cast<const float*>(l.z.p), r, l.cout, mask, mean, rstd, gamma, beta,
-                                                 slope_of(l), static_cast<float*>(l.y.p));
+    const bool bf16_only = tc && static_cast<int>(i) < t->n_frame - 1;
+    {
+      float* y32 = bf16_only ? nullptr : static_cast<float*>(l.y.p);
+      __nv_bfloat16* y16 = bf16_only ? static_cast<__nv_bfloat16*>(l.yb.p) : nullptr;
+      if (l.cout % 4 == 0) {
+        const RowGrid rg = row_grid(l.cout / 4, c->sm_count);
+        bn_act_fwd_kernel<4><<<rg.grid, rg.block, 0, s>>>(static_cast<const float*>(l.z.p), r, l.cout, mask, mean, rstd, gamma, beta,
+                                                          slope_of(l), y32, y16, l.ldb);
+      } else {
+        const RowGrid rg = row_grid(l.cout, c->sm_count);
+        bn_act_fwd_kernel<1><<<rg.grid, rg.block, 0, s>>>(static_cast<const float*>(l.z.p), r, l.cout, mask, mean, rstd, gamma, beta,
+                                                          slope_of(l), y32, y16, l.ldb);
+      }
+    }
     TR_CUDA(cudaGetLastError(), "BN/activation launch");
     in = static_cast<const float*>(l.y.p);
     in_c = l.cout;
@@ -847,19 +1208,18 @@ static int train_step(xv_ctx* c, const float* feats, const int32_t* labels, int3
                                 static_cast<double>(t->lam_base) * pow(1.0 + static_cast<double>(t->lam_gamma) * static_cast<double>(global_step),
                                                                         -static_cast<double>(t->lam_power)));
     fa = static_cast<float>(1.0 / (1.0 + lam));
-    col_rnorm_kernel<<<(S + 127) / 128, 128, 0, s>>>(P + t->off_w, E, S, static_cast<float*>(t->rnorm.p));
+    col_rnorm_kernel<<<(S + 31) / 32, 256, 0, s>>>(P + t->off_w, E, S, static_cast<float*>(t->rnorm.p));
     TR_CUDA(cudaGetLastError(), "column norm launch");
   }
   {
-    SimtGemmArgs ga;
-    ga.a = fvec; ga.a_rows = b; ga.cin = E; ga.taps = 1; ga.dilation = 1; ga.w = P + t->off_w; ga.n = S;
-    ga.bias = t->amsoftmax ? nullptr : P + t->off_b;
-    ga.bn_scale = t->amsoftmax ? static_cast<const float*>(t->rnorm.p) : nullptr;
-    ga.bn_shift = static_cast<const float*>(t->zeros.p);
-    ga.slope = nullptr; ga.act_tanh = 0; ga.out_dense = nullptr; ga.out_bn = nullptr; ga.out_act = static_cast<float*>(t->logits.p);
-    ga.m_rows = b;
-    count_launch(c, "train.gemm_fwd");
-    TR_CUDA(launch_simt_gemm(ga, s), "logits GEMM launch");
+    // logits = f . W (softmax: + bias; AM-softmax: columns scaled by 1/|w_s|, model/loss.py:241-243)
+    SkinnyArgs sa;
+    sa.a = fvec; sa.lda = E; sa.w = P + t->off_w; sa.ldw = S; sa.out = static_cast<float*>(t->logits.p); sa.ldo = S;
+    sa.col_scale = t->amsoftmax ? static_cast<const float*>(t->rnorm.p) : nullptr;
+    sa.bias = t->amsoftmax ? nullptr : P + t->off_b;
+    sa.m = b; sa.n = S; sa.k = E; sa.ks = 0;
+    count_launch(c, "train.skinny_fwd");
+    TR_CUDA(launch_skinny_gemm<false>(sa, c->sm_count, s), "logits GEMM launch");
   }
   count_launch(c, "train.loss");
   softmax_loss_kernel<<<b, 256, 0, s>>>(static_cast<float*>(t->logits.p), S, fvec, E, static_cast<const int32_t*>(t->labels.p), b,
@@ -874,7 +1234,7 @@ static int train_step(xv_ctx* c, const float* feats, const int32_t* labels, int3
     count_launch(c, "train.gemm_wgrad");
     TR_CUDA(launch_tr_gemm<kWgrad>(wa, s), "softmax wgrad launch");
     if (t->amsoftmax) {
-      amsoftmax_dw_kernel<<<(S + 127) / 128, 128, 0, s>>>(G + t->off_w, P + t->off_w, static_cast<const float*>(t->rnorm.p), E, S);
+      amsoftmax_dw_kernel<<<(S + 31) / 32, 256, 0, s>>>(G + t->off_w, P + t->off_w, static_cast<const float*>(t->rnorm.p), E, S);
       TR_CUDA(cudaGetLastError(), "AM-softmax dW launch");
     } else {
       TR_CUDA(launch_col_reduce(SumF{static_cast<const float*>(t->logits.p), S}, RowMask{1, 1}, b, S, sums, s), "bias grad launch");
@@ -885,11 +1245,11 @@ static int train_step(xv_ctx* c, const float* feats, const int32_t* labels, int3
   int cur = 0;
   float* dy = static_cast<float*>(t->dbuf[cur].p);
   {
-    TrGemmArgs da;
-    da.a = nullptr; da.lda = 0; da.dz = static_cast<const float*>(t->gr.p); da.w = P + t->off_w; da.out = dy;
-    da.rows = b; da.cin = E; da.nz = S; da.taps = 1;
-    count_launch(c, "train.gemm_dgrad");
-    TR_CUDA(launch_tr_gemm<kDgrad>(da, s), "softmax dgrad launch");
+    SkinnyArgs sa;
+    sa.a = static_cast<const float*>(t->gr.p); sa.lda = S; sa.w = P + t->off_w; sa.ldw = S; sa.out = dy; sa.ldo = E;
+    sa.col_scale = nullptr; sa.bias = nullptr; sa.m = b; sa.n = E; sa.k = S; sa.ks = 0;
+    count_launch(c, "train.skinny_dgrad");
+    TR_CUDA(launch_skinny_gemm<true>(sa, c->sm_count, s), "softmax dgrad launch");
     if (t->amsoftmax) {
       axpy_rows_kernel<<<ew_grid(c), 256, 0, s>>>(dy, fvec, static_cast<const float*>(t->coef.p), b, E);
       TR_CUDA(cudaGetLastError(), "axpy launch");
@@ -906,12 +1266,20 @@ static int train_step(xv_ctx* c, const float* feats, const int32_t* labels, int3
       // dy currently holds d(pooled) [B, 2C]: statistics-pooling backward into [rows, C]
       float* dx = static_cast<float*>(t->dbuf[cur ^ 1].p);
       count_launch(c, "train.pool_bwd");
-      pool_bwd_kernel<<<ew_grid(c), 256, 0, s>>>(static_cast<const float*>(l.y.p), rows, l.cout, mask,
-                                                 static_cast<const float*>(t->pooled.p), dy, dx);
+      if (l.cout % 4 == 0) {
+        const RowGrid rg = row_grid(l.cout / 4, c->sm_count);
+        pool_bwd_kernel<4><<<rg.grid, rg.block, 0, s>>>(static_cast<const float*>(l.y.p), rows, l.cout, mask,
+                                                        static_cast<const float*>(t->pooled.p), dy, dx);
+      } else {
+        const RowGrid rg = row_grid(l.cout, c->sm_count);
+        pool_bwd_kernel<1><<<rg.grid, rg.block, 0, s>>>(static_cast<const float*>(l.y.p), rows, l.cout, mask,
+                                                        static_cast<const float*>(t->pooled.p), dy, dx);
+      }
       TR_CUDA(cudaGetLastError(), "pooling backward launch");
       cur ^= 1;
       dy = dx;
     }
+    const bool tc = t->mixed && l.frame;
     const float *mean = nullptr, *rstd = nullptr, *gamma = nullptr, *beta = nullptr;
     if (l.has_bn) {
       mean = static_cast<const float*>(l.mean.p); rstd = static_cast<const float*>(l.rstd.p);
@@ -926,33 +1294,83 @@ static int train_step(xv_ctx* c, const float* feats, const int32_t* labels, int3
     }
     if (l.off_alpha >= 0) d2f_kernel<<<(l.cout + 255) / 256, 256, 0, s>>>(sums + 2 * l.cout, G + l.off_alpha, l.cout);
     TR_CUDA(cudaGetLastError(), "d2f launch");
-    bn_bwd_apply_kernel<<<ew_grid(c), 256, 0, s>>>(dy, static_cast<const float*>(l.z.p), r, l.cout, mask, mean, rstd, gamma, beta,
-                                                   slope_of(l), sums, n);
+    {
+      __nv_bfloat16* dz16 = tc ? static_cast<__nv_bfloat16*>(t->dzb.p) : nullptr;
+      if (l.cout % 4 == 0) {
+        const RowGrid rg = row_grid(l.cout / 4, c->sm_count);
+        bn_bwd_apply_kernel<4><<<rg.grid, rg.block, 0, s>>>(dy, static_cast<const float*>(l.z.p), r, l.cout, mask, mean, rstd, gamma,
+                                                            beta, slope_of(l), sums, n, dz16, l.ldb);
+      } else {
+        const RowGrid rg = row_grid(l.cout, c->sm_count);
+        bn_bwd_apply_kernel<1><<<rg.grid, rg.block, 0, s>>>(dy, static_cast<const float*>(l.z.p), r, l.cout, mask, mean, rstd, gamma,
+                                                            beta, slope_of(l), sums, n, dz16, l.ldb);
+      }
+    }
     TR_CUDA(cudaGetLastError(), "BN backward apply launch");
     // now dy == dz of this layer
-    double* bsum = sums;     // reuse after the apply kernel has consumed the BN sums (same stream: ordered)
-    TR_CUDA(launch_col_reduce(SumF{dy, l.cout}, mask, r, l.cout, bsum, s), "bias grad launch");
-    d2f_kernel<<<(l.cout + 255) / 256, 256, 0, s>>>(bsum, G + l.off_bias, l.cout);
-    TR_CUDA(cudaGetLastError(), "d2f launch");
+    if (l.has_bn) {
+      // a bias in front of a batch norm: sum_rows dz = -gamma*rstd*(sum xhat)*(sum g*xhat)/n with sum xhat == 0, i.e. the
+      // gradient is identically zero (TF evaluates the same sum and gets rounding residue of the order 1e-9)
+      TR_CUDA(cudaMemsetAsync(G + l.off_bias, 0, sizeof(float) * l.cout, s), "memset bias grad");
+    } else {
+      double* bsum = sums;     // reuse after the apply kernel has consumed the BN sums (same stream: ordered)
+      TR_CUDA(launch_col_reduce(SumF{dy, l.cout}, mask, r, l.cout, bsum, s), "bias grad launch");
+      d2f_kernel<<<(l.cout + 255) / 256, 256, 0, s>>>(bsum, G + l.off_bias, l.cout);
+      TR_CUDA(cudaGetLastError(), "d2f launch");
+    }
     const float* a_in;
     int lda;
     if (i == 0) { a_in = static_cast<const float*>(t->feats.p); lda = c->dim; }
     else if (i == t->n_frame) { a_in = static_cast<const float*>(t->pooled.p); lda = l.cin; }
     else { a_in = static_cast<const float*>(t->layers[i - 1].y.p); lda = l.cin; }
-    TrGemmArgs wa;
-    wa.a = a_in; wa.lda = lda; wa.dz = dy; wa.w = nullptr; wa.out = G + l.off_kernel; wa.rows = r; wa.cin = l.cin; wa.nz = l.cout;
-    wa.taps = l.taps;
-    count_launch(c, "train.gemm_wgrad");
-    TR_CUDA(launch_tr_gemm<kWgrad>(wa, s), "wgrad launch");
-    if (i > 0) {
-      float* dx = static_cast<float*>(t->dbuf[cur ^ 1].p);
-      TrGemmArgs da;
-      da.a = nullptr; da.lda = 0; da.dz = dy; da.w = P + l.off_kernel; da.out = dx; da.rows = r; da.cin = l.cin; da.nz = l.cout;
-      da.taps = l.taps;
-      count_launch(c, "train.gemm_dgrad");
-      TR_CUDA(launch_tr_gemm<kDgrad>(da, s), "dgrad launch");
-      cur ^= 1;
-      dy = dx;
+    if (tc) {
+      // dW on the MN-major tcgen05 kernel (xv_wgrad_sm100.cu): layer 0 contracts the pre-spliced features (one tap of width
+      // taps*dim), the others shift the previous layer's bf16 activations by the tap index
+      const void* a_bf16 = i == 0 ? t->xb0.p : t->layers[i - 1].yb.p;
+      TR_CUDA(cudaMemsetAsync(G + l.off_kernel, 0, sizeof(float) * static_cast<size_t>(l.taps) * l.cin * l.cout, s), "memset dW");
+      cudaError_t ce;
+      count_launch(c, "train.tc_wgrad");
+      const char* we = launch_wgrad(a_bf16, rows, l.a_cin, t->dzb.p, l.ldb, rows, i == 0 ? 1 : l.taps, i == 0 ? l.taps * l.cin : l.cin,
+                                    l.cout, G + l.off_kernel, l.cout, c->sm_count, s, &ce);
+      if (we) return fail(c, XV_ECUDA, "%s", we);
+      TR_CUDA(ce, "tcgen05 wgrad launch");
+      if (i > 0) {
+        float* dx = static_cast<float*>(t->dbuf[cur ^ 1].p);
+        count_launch(c, "train.cast_w");
+        cast_w_dgrad_kernel<<<ew_grid(c), 256, 0, s>>>(P + l.off_kernel, l.taps, l.cin, l.cout, l.ldb, l.c_alloc,
+                                                       static_cast<__nv_bfloat16*>(l.wt_dgrad.p));
+        TR_CUDA(cudaGetLastError(), "dgrad weight cast launch");
+        // dX[m, c] = sum_j sum_n dZ[m - j, n] W[j, c, n]: the forward kernel with tap step -1 (rows < 0 are TMA zero fill)
+        if ((rc = tr_gemm_tc(c, t, l.tm_wd, t->dzb.p, rows, l.ldb, l.taps, -1, l.c_alloc, static_cast<const float*>(t->zeros_pad.p),
+                             dx, l.cin, l.cin, "train.tc_dgrad")) != XV_OK) return rc;
+        cur ^= 1;
+        dy = dx;
+      }
+    } else {
+      TrGemmArgs wa;
+      wa.a = a_in; wa.lda = lda; wa.dz = dy; wa.w = nullptr; wa.out = G + l.off_kernel; wa.rows = r; wa.cin = l.cin; wa.nz = l.cout;
+      wa.taps = l.taps;
+      count_launch(c, "train.gemm_wgrad");
+      TR_CUDA(launch_tr_gemm<kWgrad>(wa, s), "wgrad launch");
+      if (i > 0 && !l.frame) {
+        float* dx = static_cast<float*>(t->dbuf[cur ^ 1].p);
+        SkinnyArgs sa;
+        sa.a = dy; sa.lda = l.cout; sa.w = P + l.off_kernel; sa.ldw = l.cout; sa.out = dx; sa.ldo = l.cin;
+        sa.col_scale = nullptr; sa.bias = nullptr; sa.m = b; sa.n = l.cin; sa.k = l.cout; sa.ks = 0;
+        count_launch(c, "train.skinny_dgrad");
+        TR_CUDA(launch_skinny_gemm<true>(sa, c->sm_count, s), "segment-level dgrad launch");
+        cur ^= 1;
+        dy = dx;
+      } else if (i > 0) {
+        float* dx = static_cast<float*>(t->dbuf[cur ^ 1].p);
+        TrGemmArgs da;
+        da.a = nullptr; da.lda = 0; da.dz = dy; da.w = P + l.off_kernel; da.out = dx; da.rows = r; da.cin = l.cin; da.nz = l.cout;
+        da.taps = l.taps;
+        count_launch(c, "train.gemm_dgrad");
+        TR_CUDA(launch_tr_gemm<kDgrad>(da, s), "dgrad launch");
+        cur ^= 1;
+        dy = dx;
+      }
     }
   }
 
