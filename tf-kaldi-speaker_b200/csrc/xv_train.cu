@@ -222,6 +222,91 @@ cudaError_t launch_col_reduce(const F& f, RowMask mask, int64_t rows, int c_tota
   return cudaGetLastError();
 }
 
+// Four-channel variants of the two hot reductions (widths that are multiples of 4): one 16-byte load per tensor and row,
+// per-channel constants in registers, fp64 accumulators.  KIND 0: v0 = sum z, v1 = sum z^2.  KIND 1: the BnBwdF sums.
+template <int KIND>
+__global__ void __launch_bounds__(256) col_reduce4_kernel(const float* __restrict__ dy, const float* __restrict__ z,
+                                                          const RowMask mask, int64_t rows, int c_total, int64_t rows_per_block,
+                                                          const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                          const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                          const float* __restrict__ slope, double* __restrict__ out) {
+  constexpr int NV = KIND == 0 ? 2 : 3;
+  __shared__ double red[NV][8][129];
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int c0 = (blockIdx.x * 32 + cx) * 4;
+  const int64_t r0 = static_cast<int64_t>(blockIdx.y) * rows_per_block;
+  const int64_t r1 = min(r0 + rows_per_block, rows);
+  double v[NV][4];
+#pragma unroll
+  for (int k = 0; k < NV; ++k)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[k][j] = 0.0;
+  if (c0 < c_total) {
+    float mu[4], rs[4], ga[4], be[4], sl[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      mu[j] = 0.f; rs[j] = 1.f; ga[j] = 1.f; be[j] = 0.f; sl[j] = 0.f;
+      if (KIND == 1) {
+        sl[j] = slope[c0 + j];
+        if (mean != nullptr) { mu[j] = mean[c0 + j]; rs[j] = rstd[c0 + j]; ga[j] = gamma[c0 + j]; be[j] = beta[c0 + j]; }
+      }
+    }
+#pragma unroll 2
+    for (int64_t r = r0 + ry; r < r1; r += 8) {
+      if (!mask.ok(r)) continue;
+      const float4 z4 = *reinterpret_cast<const float4*>(z + r * c_total + c0);
+      const float zz[4] = {z4.x, z4.y, z4.z, z4.w};
+      if (KIND == 0) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const double x = zz[j];
+          v[0][j] += x; v[1][j] += x * x;
+        }
+      } else {
+        const float4 d4 = *reinterpret_cast<const float4*>(dy + r * c_total + c0);
+        const float dd[4] = {d4.x, d4.y, d4.z, d4.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float xh = 0.f, pre = zz[j];
+          if (mean != nullptr) { xh = (zz[j] - mu[j]) * rs[j]; pre = fmaf(ga[j], xh, be[j]); }
+          const float g = pre > 0.f ? dd[j] : dd[j] * sl[j];
+          v[0][j] += g; v[1][j] += static_cast<double>(g) * xh;
+          if (pre < 0.f) v[2][j] += static_cast<double>(dd[j]) * pre;
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < NV; ++k)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) red[k][ry][cx * 4 + j] = v[k][j];
+  __syncthreads();
+  for (int i = threadIdx.x; i < NV * 128; i += 256) {
+    const int k = i >> 7, cc = i & 127;
+    const int c = blockIdx.x * 128 + cc;
+    if (c >= c_total) continue;
+    double sum = 0.0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sum += red[k][j][cc];
+    atomicAdd(out + static_cast<int64_t>(k) * c_total + c, sum);
+  }
+}
+
+template <int KIND>
+cudaError_t launch_col_reduce4(const float* dy, const float* z, RowMask mask, int64_t rows, int c_total, const float* mean,
+                               const float* rstd, const float* gamma, const float* beta, const float* slope, double* out,
+                               int sm_count, cudaStream_t s) {
+  cudaError_t e = cudaMemsetAsync(out, 0, sizeof(double) * (KIND == 0 ? 2 : 3) * c_total, s);
+  if (e != cudaSuccess) return e;
+  const int bx = (c_total + 127) / 128;
+  int64_t chunks = (4 * sm_count + bx - 1) / bx;
+  int64_t rpb = (rows + chunks - 1) / chunks;
+  if (rpb < 64) rpb = 64;
+  dim3 grid(bx, static_cast<unsigned>((rows + rpb - 1) / rpb));
+  col_reduce4_kernel<KIND><<<grid, 256, 0, s>>>(dy, z, mask, rows, c_total, rpb, mean, rstd, gamma, beta, slope, out);
+  return cudaGetLastError();
+}
+
 // mean / biased variance / rstd from the fp64 sums; moving-average targets for the flat-buffer tail.
 __global__ void bn_finalize_kernel(const double* __restrict__ sums, int c_total, double n, float eps, int unbiased_moving,
                                    float* __restrict__ mean, float* __restrict__ rstd, const float* __restrict__ mov_mean,
@@ -1167,7 +1252,11 @@ static int train_step(xv_ctx* c, const float* feats, const int32_t* labels, int3
     const float *mean = nullptr, *rstd = nullptr, *gamma = nullptr, *beta = nullptr;
     if (l.has_bn) {
       count_launch(c, "train.bn_stats");
-      TR_CUDA(launch_col_reduce(StatsF{static_cast<const float*>(l.z.p), l.cout}, mask, r, l.cout, sums, s), "BN statistics launch");
+      if (l.cout % 4 == 0)
+        TR_CUDA(launch_col_reduce4<0>(nullptr, static_cast<const float*>(l.z.p), mask, r, l.cout, nullptr, nullptr, nullptr, nullptr,
+                                      nullptr, sums, c->sm_count, s), "BN statistics launch");
+      else
+        TR_CUDA(launch_col_reduce(StatsF{static_cast<const float*>(l.z.p), l.cout}, mask, r, l.cout, sums, s), "BN statistics launch");
       // new moving statistics go to the tail of the gradient buffer on rank 0 (tower 0), zeros elsewhere
       float* nm = t->rank == 0 ? G + l.off_mm : static_cast<float*>(t->dbuf[0].p);
       float* nv = t->rank == 0 ? G + l.off_mv : static_cast<float*>(t->dbuf[0].p) + l.cout;
@@ -1286,7 +1375,11 @@ static int train_step(xv_ctx* c, const float* feats, const int32_t* labels, int3
       gamma = P + l.off_gamma; beta = P + l.off_beta;
     }
     count_launch(c, "train.bn_bwd");
-    TR_CUDA(launch_col_reduce(BnBwdF{dy, static_cast<const float*>(l.z.p), l.cout, mean, rstd, gamma, beta, slope_of(l)}, mask, r,
+    if (l.cout % 4 == 0)
+      TR_CUDA(launch_col_reduce4<1>(dy, static_cast<const float*>(l.z.p), mask, r, l.cout, mean, rstd, gamma, beta, slope_of(l), sums,
+                                    c->sm_count, s), "BN backward reduce launch");
+    else
+      TR_CUDA(launch_col_reduce(BnBwdF{dy, static_cast<const float*>(l.z.p), l.cout, mean, rstd, gamma, beta, slope_of(l)}, mask, r,
                               l.cout, sums, s), "BN backward reduce launch");
     if (l.has_bn) {
       d2f_kernel<<<(l.cout + 255) / 256, 256, 0, s>>>(sums, G + l.off_beta, l.cout);
@@ -1375,7 +1468,7 @@ static int train_step(xv_ctx* c, const float* feats, const int32_t* labels, int3
   }
 
   // ------------------------------------------------------------------ regularisation, exchange, update
-  reg_loss_kernel<<<dim3(32, static_cast<unsigned>(t->segs.size())), 256, 0, s>>>(P, static_cast<const ParamSeg*>(t->d_segs.p),
+  reg_loss_kernel<<<dim3(128, static_cast<unsigned>(t->segs.size())), 256, 0, s>>>(P, static_cast<const ParamSeg*>(t->d_segs.p),
                                                                                  static_cast<int>(t->segs.size()), scalars + 1);
   TR_CUDA(cudaGetLastError(), "regularisation launch");
   loss_to_tail_kernel<<<1, 1, 0, s>>>(scalars, G + t->n_total);
