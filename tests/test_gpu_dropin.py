@@ -143,3 +143,46 @@ def test_trainer_predict_and_extractor(tmp_path, precision):
     with pytest.raises(SystemExit):
         t2.predict(x)                                            # "Cannot find model in ..." (trainer.py:891-895)
     t2.close()
+
+
+def test_extract_cli_ark_to_ark(tmp_path):
+    """extract.py's command line (egs/voxceleb/v1/nnet/lib/extract.py:11-93) end to end: compressed-matrix ark in through
+    an input pipe, native batch reader -> xv_forward -> native vector writer, embeddings ark out; against the oracle's
+    restatement of the extraction loop on the features the reference reader decodes."""
+    import json
+    from oracle import kaldi_io_ref, numpy_ref, synth
+    from xvector_b200 import kaldi_io
+    from xvector_b200.extract import main
+    cfg = dict(synth.TDNN_STAT_CONFIG)
+    w = synth.make_tdnn_weights(30, cfg, seed=16)
+    nnet = tmp_path / "nnet"
+    nnet.mkdir()
+    (nnet / "config.json").write_text(json.dumps(cfg))
+    (nnet / "feature_dim").write_text("30\n")
+    np.savez(str(nnet / "weights.npz"), **w)
+    (nnet / "checkpoint").write_text('model_checkpoint_path: "model-10"\n')
+    lens = [20, 120, 530, 260, 77]
+    feats = [synth.packed_features(np.array([n]), 30, seed=140 + n) for n in lens]
+    keys = ["spk%d-utt%d" % (i % 2, i) for i in range(len(lens))]
+    ark = str(tmp_path / "feats.ark")
+    with open(ark, "wb") as f:
+        for i, (k, m) in enumerate(zip(keys, feats)):
+            f.write(kaldi_io_ref.write_cm_bytes(m, k) if i % 2 else kaldi_io_ref.write_mat_bytes(m, k))
+    decoded = dict(kaldi_io_ref.parse_ark(open(ark, "rb").read()))          # what the reference reader would hand over
+    out = str(tmp_path / "xvector.ark")
+    oparams = numpy_ref.OracleParams(**cfg)
+    pred = lambda a: numpy_ref.predict(a, oparams, w, 30)
+    for norm, spec in ((False, "ark:" + out), (True, "ark:| cat > " + out)):
+        argv = ["--precision", "fp32", "-s", "200", "-m", "25"] + (["-n"] if norm else []) + [str(tmp_path), "ark:cat %s |" % ark, spec]
+        main(argv)
+        got = dict(kaldi_io.read_vec_flt_ark(out))
+        assert list(got) == keys[1:]                                         # the 20-frame utterance is skipped
+        for k in keys[1:]:
+            want = numpy_ref.extract_embedding(decoded[k], pred, chunk_size=200, min_chunk_size=25, normalize=norm)
+            assert got[k].dtype == np.float32 and max_rel(got[k][None], want[None]) <= TOL["fp32"], k
+    # the zero-copy branch: every utterance within [min, chunk] -> one packed xv_forward per batch
+    main(["--precision", "bf16", str(tmp_path), ark, out, "-m", "10"])
+    got = dict(kaldi_io.read_vec_flt_ark(out))
+    assert list(got) == keys
+    for k in keys:
+        assert max_rel(got[k][None], pred(decoded[k])[None]) <= TOL["bf16"], k

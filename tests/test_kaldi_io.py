@@ -1,0 +1,209 @@
+"""Kaldi ark/scp I/O, CPU: the native library (lib/libxvkaldi.so through its C-ABI and the
+reference-named Python mirror) and the numpy restatement against golden vectors produced by the reference's own
+dataset/kaldi_io.py (tests/golden/make_kaldi_io_golden.py).  Bit-exact everywhere."""
+import ctypes as C
+import gzip
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+@pytest.fixture(scope="module")
+def K():
+    import xvector_b200.kaldi_io as kaldi_io
+    return kaldi_io
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return dict(np.load(os.path.join(GOLDEN, "kaldi_io_golden.npz")))
+
+
+def _same(a, b):
+    a, b = np.asarray(a), np.asarray(b)
+    return a.dtype == b.dtype and a.shape == b.shape and np.array_equal(a.view(np.uint8), b.view(np.uint8))
+
+
+def test_library_exports_every_declared_symbol(K):
+    header = open(os.path.join(ROOT, "include", "xvkaldi.h")).read()
+    declared = set(re.findall(r"\b(xvk_[a-z0-9_]+)\s*\(", header))
+    assert declared == set(K.PROTOTYPES), declared ^ set(K.PROTOTYPES)
+    lib = K.load()
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert b"xvkaldi" in lib.xvk_version()
+
+
+@pytest.mark.parametrize("ark,prefix", [("kaldi_io_mats.ark", "mats/"), ("kaldi_io_cm.ark", "cm/"), ("kaldi_io_text.ark", "text/")])
+def test_read_mat_ark_matches_reference(K, gold, ark, prefix):
+    got = list(K.read_mat_ark(os.path.join(GOLDEN, ark)))
+    want = [(k[len(prefix):], v) for k, v in gold.items() if k.startswith(prefix)]
+    assert [k for k, _ in got] == [k for k, _ in want]
+    for (k, m), (_, ref) in zip(got, want):
+        assert _same(m, ref), k
+
+
+def test_read_vec_flt_ark_matches_reference(K, gold):
+    got = list(K.read_vec_flt_ark("ark:" + os.path.join(GOLDEN, "kaldi_io_vecs.ark")))
+    want = [(k[5:], v) for k, v in gold.items() if k.startswith("vecs/")]
+    assert [k for k, _ in got] == [k for k, _ in want]
+    for (k, v), (_, ref) in zip(got, want):
+        assert _same(v, ref), k
+
+
+def test_oracle_restatement_matches_reference(gold):
+    from oracle import kaldi_io_ref as O
+    for ark, prefix in (("kaldi_io_mats.ark", "mats/"), ("kaldi_io_cm.ark", "cm/"), ("kaldi_io_vecs.ark", "vecs/")):
+        parsed = O.parse_ark(open(os.path.join(GOLDEN, ark), "rb").read())
+        want = [(k[len(prefix):], v) for k, v in gold.items() if k.startswith(prefix)]
+        assert [k for k, _ in parsed] == [k for k, _ in want]
+        for (k, m), (_, ref) in zip(parsed, want):
+            assert _same(np.ascontiguousarray(m), ref), k
+
+
+def test_writers_reproduce_the_reference_bytes(K, gold, tmp_path):
+    """write_mat / write_vec_flt: the bytes the reference's writers produced for the same arrays."""
+    for ark, prefix, write in (("kaldi_io_mats.ark", "mats/", K.write_mat), ("kaldi_io_vecs.ark", "vecs/", K.write_vec_flt)):
+        out = str(tmp_path / ark)
+        with K.open_or_fd(out, "wb") as f:
+            for k, v in gold.items():
+                if k.startswith(prefix):
+                    write(f, v, key=k[len(prefix):])
+        assert open(out, "rb").read() == open(os.path.join(GOLDEN, ark), "rb").read()
+    from oracle import kaldi_io_ref as O
+    blob = b"".join(O.write_mat_bytes(v, k[5:]) for k, v in gold.items() if k.startswith("mats/"))
+    assert blob == open(os.path.join(GOLDEN, "kaldi_io_mats.ark"), "rb").read()
+    with pytest.raises(K.UnsupportedDataType):
+        K.write_mat(str(tmp_path / "bad.ark"), np.zeros((2, 2), np.int32), key="x")
+
+
+def test_submatrix_reads_match_reference(K, gold):
+    for name, ref in gold.items():
+        if not name.startswith("sub/"):
+            continue
+        _, key, start, length = name.split("/")
+        ark = "kaldi_io_cm.ark" if key.startswith("cm") else "kaldi_io_mats.ark"
+        fd = K.open_or_fd(os.path.join(GOLDEN, ark))
+        k = K.read_key(fd)
+        while k != key:
+            k = K.read_key(fd)                 # an unread body is skipped
+        _, kind, rows, cols = fd._head
+        got = fd.read_rows(int(start), int(length), cols)
+        fd._head = None
+        assert _same(got, ref), name
+        nxt = K.read_key(fd)                   # the stream is positioned on the next object
+        assert nxt is None or isinstance(nxt, str)
+        fd.close()
+    fd = K.open_or_fd(os.path.join(GOLDEN, "kaldi_io_mats.ark"))
+    K.read_key(fd)
+    with pytest.raises(K.KaldiIOError, match="not enough for length"):
+        fd.read_rows(0, 5, 30)                 # fm_0 has one row (dataset/kaldi_io.py:1046)
+    fd.close()
+
+
+def test_cm_decode_every_byte_value(K, tmp_path):
+    """All 256 byte values in every column, extreme percentiles: native table == restated float32 evaluation."""
+    from oracle import kaldi_io_ref as O
+    import struct
+    rng = np.random.default_rng(3)
+    cols, rows = 7, 256
+    heads = np.sort(rng.integers(0, 65536, (cols, 4)).astype(np.uint16), axis=1)
+    heads[0] = (0, 1, 65534, 65535)
+    data = np.stack([rng.permutation(256).astype(np.uint8) for _ in range(cols)])
+    body = struct.pack("<ffii", -13.25, 77.125, rows, cols) + heads.tobytes() + data.tobytes()
+    path = str(tmp_path / "cm.ark")
+    open(path, "wb").write(b"k \0BCM " + body)
+    (key, got), = list(K.read_mat_ark(path))
+    ref, used = O.decode_cm(body)
+    assert key == "k" and used == len(body) and _same(got, np.ascontiguousarray(ref))
+
+
+def test_specifiers_pipes_gzip_offsets_and_scp(K, gold, tmp_path):
+    mats = os.path.join(GOLDEN, "kaldi_io_mats.ark")
+    want = [(k[5:], v) for k, v in gold.items() if k.startswith("mats/")]
+    # input pipe and the ark: prefix with options
+    got = list(K.read_mat_ark("ark,s,cs:cat %s |" % mats))
+    assert [k for k, _ in got] == [k for k, _ in want] and all(_same(a, b) for (_, a), (_, b) in zip(got, want))
+    # gzip in, gzip out
+    gz = str(tmp_path / "m.ark.gz")
+    with K.open_or_fd(gz, "wb") as f:
+        for k, v in want:
+            K.write_mat(f, v, key=k)
+    assert gzip.open(gz, "rb").read() == open(mats, "rb").read()
+    assert all(_same(a, b) for (_, a), (_, b) in zip(K.read_mat_ark(gz), want))
+    # output pipe
+    piped = str(tmp_path / "piped.ark")
+    with K.open_or_fd("ark:| cat > %s" % piped, "wb") as f:
+        for k, v in want:
+            K.write_mat(f, v, key=k)
+    assert open(piped, "rb").read() == open(mats, "rb").read()
+    # ark,scp writer -> scp random access (single, threaded, header-only)
+    ark, scp = str(tmp_path / "x.ark"), str(tmp_path / "x.scp")
+    with K.open_or_fd("ark,scp:%s,%s" % (ark, scp), "wb") as f:
+        for k, v in want:
+            K.write_mat(f, v, key=k)
+    assert open(ark, "rb").read() == open(mats, "rb").read()
+    got = list(K.read_mat_scp(scp))
+    assert [k for k, _ in got] == [k for k, _ in want] and all(_same(a, b) for (_, a), (_, b) in zip(got, want))
+    table = K.ScpTable("scp:" + scp)
+    f32 = [i for i, (k, v) in enumerate(want) if v.dtype == np.float32 and v.shape[1] == 30]
+    rows, cols = table.dims(f32, threads=3)
+    assert list(rows) == [want[i][1].shape[0] for i in f32] and set(cols) == {30}
+    packed, lens = table.read_many(f32, threads=4)
+    assert _same(packed, np.concatenate([want[i][1] for i in f32]))
+    one = K.read_mat(table.rxfile(2))          # "path:offset"
+    assert _same(one, want[2][1])
+    table.close()
+
+
+def test_batch_reader_refuses_a_dimension_change(K):
+    br = K.BatchReader(os.path.join(GOLDEN, "kaldi_io_cm.ark"), 30, max_rows=400)
+    with pytest.raises(K.KaldiIOError, match="feature dimension 24, expected 30"):
+        list(br)
+    with pytest.raises(K.KaldiIOError, match="expected a feature matrix, found a vector"):
+        list(K.BatchReader(os.path.join(GOLDEN, "kaldi_io_vecs.ark"), 512))
+
+
+def test_batch_reader_shapes(K, gold, tmp_path):
+    mats = [(k[5:], v) for k, v in gold.items() if k.startswith("mats/") and v.shape[1] == 30 and v.dtype == np.float32]
+    path = str(tmp_path / "b.ark")
+    with K.open_or_fd(path, "wb") as f:
+        for rep in range(3):
+            for k, v in mats:
+                K.write_mat(f, v, key="%s_%d" % (k, rep))
+    allk, allf, alll = [], [], []
+    for keys, feats, lens in K.BatchReader(path, 30, max_rows=230, max_utts=3):
+        assert len(keys) <= 3 and feats.shape[0] == lens.sum() <= 230
+        allk += keys
+        allf.append(feats.copy())
+        alll += list(lens)
+    assert allk == ["%s_%d" % (k, rep) for rep in range(3) for k, _ in mats]
+    assert _same(np.concatenate(allf), np.concatenate([v for _ in range(3) for _, v in mats]))
+    assert alll == [v.shape[0] for _ in range(3) for _, v in mats]
+    with pytest.raises(K.KaldiIOError, match="does not fit an empty batch"):
+        list(K.BatchReader(path, 30, max_rows=100))
+
+
+def test_error_behaviour(K, tmp_path):
+    bad = str(tmp_path / "bad.ark")
+    open(bad, "wb").write(b"k \0BXM \4\1\0\0\0\4\1\0\0\0")
+    with pytest.raises(K.UnknownMatrixHeader, match="The header contained 'XM '"):
+        list(K.read_mat_ark(bad))
+    open(bad, "wb").write(b"k \0BCM2 ")
+    with pytest.raises(K.KaldiIOError, match="CM2, CM3 are not supported"):
+        list(K.read_mat_ark(bad))
+    open(bad, "wb").write(b"k \0BFM \4\5\0\0\0\4\3\0\0\0abc")
+    with pytest.raises(K.KaldiIOError, match="unexpected end of stream"):
+        list(K.read_mat_ark(bad))
+    with pytest.raises(K.KaldiIOError, match="cannot open"):
+        K.open_or_fd(str(tmp_path / "missing.ark"))
+    with pytest.raises(K.SubprocessFailed):
+        list(K.read_mat_ark("ark:exit 3 |"))
+    assert list(K.read_mat_ark("ark:true |")) == []
+    with pytest.raises(ValueError):
+        K.open_or_fd(bad, "x")

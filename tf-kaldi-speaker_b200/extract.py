@@ -75,6 +75,44 @@ def extract_many(trainer, features_list, chunk_size=10000, min_chunk_size=25, no
     return out
 
 
+def extract_stream(trainer, rspecifier, wspecifier, dim, chunk_size=10000, min_chunk_size=25, normalize=False,
+                   max_rows=1 << 20, max_utts=4096, pinned=True):
+    """The reference's extraction loop (extract.py:63-93) as a stream of packed batches: the native ark reader
+    (kaldi_io.BatchReader, lib/libxvkaldi.so) decodes whole batches into one pinned buffer, xv_forward embeds the
+    batch, the native writer emits the vectors.  Batches whose utterances all lie in [min_chunk_size, chunk_size]
+    go down without any host-side copy; others take extract_many's chunk plan.  Returns (written, skipped)."""
+    from . import kaldi_io
+    pin = None
+    buffer = None
+    if pinned:
+        from .engine import PinnedArray
+        pin = PinnedArray((max_rows, dim))
+        buffer = pin.array
+    written = skipped = 0
+    try:
+        with kaldi_io.open_or_fd(wspecifier, "wb") as fp_out:
+            for keys, feats, lengths in kaldi_io.BatchReader(rspecifier, dim, max_rows=max_rows, max_utts=max_utts, buffer=buffer):
+                if lengths.min() >= min_chunk_size and lengths.max() <= chunk_size:
+                    emb = np.asarray(trainer.predict_packed(feats, lengths), np.float32)
+                    if normalize:
+                        emb = emb / np.sqrt(np.sum(np.square(emb), axis=1, keepdims=True))
+                    kaldi_io.write_vecs_flt(fp_out, keys, emb)
+                    written += len(keys)
+                    continue
+                offs = np.concatenate([[0], np.cumsum(lengths)])
+                embs = extract_many(trainer, [feats[offs[i]:offs[i + 1]] for i in range(len(keys))], chunk_size,
+                                    min_chunk_size, normalize)
+                keep = [i for i, e in enumerate(embs) if e is not None]
+                skipped += len(keys) - len(keep)
+                if keep:
+                    kaldi_io.write_vecs_flt(fp_out, [keys[i] for i in keep], np.stack([embs[i] for i in keep]).astype(np.float32))
+                    written += len(keep)
+    finally:
+        if pin is not None:
+            pin.close()
+    return written, skipped
+
+
 def main(argv=None):
     """CLI with the reference's flags (extract.py:11-22)."""
     parser = argparse.ArgumentParser()
@@ -91,8 +129,6 @@ def main(argv=None):
 
     from .misc.utils import Params
     from .model.trainer import Trainer
-    from . import kaldi_io
-
     config_json = os.path.join(args.model_dir, "nnet/config.json")
     if not os.path.isfile(config_json):
         sys.exit("Cannot find params.json in %s" % config_json)
@@ -105,15 +141,9 @@ def main(argv=None):
     trainer.build("predict")
     if args.rspecifier.rsplit(".", 1)[-1] == "scp":
         sys.exit("The rspecifier must be ark or input pipe")
-    keys, feats = [], []
-    for key, feature in kaldi_io.read_mat_ark(args.rspecifier):
-        keys.append(key)
-        feats.append(feature)
-    embs = extract_many(trainer, feats, args.chunk_size, args.min_chunk_size, args.normalize)
-    with kaldi_io.open_or_fd(args.wspecifier, "wb") as fp_out:
-        for key, e in zip(keys, embs):
-            if e is not None:
-                kaldi_io.write_vec_flt(fp_out, e, key=key)
+    written, skipped = extract_stream(trainer, args.rspecifier, args.wspecifier, dim, args.chunk_size, args.min_chunk_size,
+                                      args.normalize)
+    print("[INFO] wrote %d embeddings, skipped %d short utterances" % (written, skipped))
     trainer.close()
 
 

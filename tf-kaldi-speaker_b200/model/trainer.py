@@ -141,6 +141,16 @@ class Trainer(object):
             return np.stack(self.engine.forward_frames(packed, lengths, node), axis=0)
         return self.engine.forward(packed, lengths, node)
 
+    def predict_packed(self, packed, lengths):
+        """Utterances already packed back to back ([sum T_u, D] float32, e.g. a pinned buffer filled by
+        kaldi_io.BatchReader) + their lengths: the layout xv_forward takes, no host-side copy."""
+        if not self.is_loaded:
+            if os.path.isfile(os.path.join(self.model, "weights.npz")):
+                self.load()
+            else:
+                sys.exit("Cannot find model in %s" % self.model)
+        return self.engine.forward(packed, np.ascontiguousarray(lengths, np.int32), self.params.embedding_node)
+
     def predict_ragged(self, features_list):
         """Extension of predict(): a list of [T_u, D] utterances of different lengths in ONE packed call.
         Row u of the result equals predict(features_list[u]) (each utterance is computed as a batch of one)."""
