@@ -76,6 +76,9 @@ int xvk_read_rows_f32(xvk_reader* r, int32_t start, int32_t length, float* dst, 
  * 1 = more objects may follow, 0 = end of stream reached; an object that does not fit stays pending. */
 int xvk_read_batch_f32(xvk_reader* r, float* dst, int64_t cap_rows, int32_t dim, int32_t max_utts, int32_t* lengths,
                        char* keys, size_t keys_cap, int32_t* n_utts, int64_t* n_rows);
+/* Regular (seekable, uncompressed) files only: xvk_read_batch_f32 scans the headers of a batch, then decodes the
+ * bodies with `threads` workers through per-thread descriptors.  Streams and gzip stay sequential. */
+int xvk_reader_set_threads(xvk_reader* r, int32_t threads);
 const char* xvk_reader_error(const xvk_reader* r);
 /* Closes the stream; for a command, waits for it: XVK_EIO if it returned a status > 0 (SubprocessFailed). */
 int xvk_reader_close(xvk_reader* r);

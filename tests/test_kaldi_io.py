@@ -169,7 +169,8 @@ def test_batch_reader_refuses_a_dimension_change(K):
         list(K.BatchReader(os.path.join(GOLDEN, "kaldi_io_vecs.ark"), 512))
 
 
-def test_batch_reader_shapes(K, gold, tmp_path):
+@pytest.mark.parametrize("threads", [1, 4])
+def test_batch_reader_shapes(K, gold, tmp_path, threads):
     mats = [(k[5:], v) for k, v in gold.items() if k.startswith("mats/") and v.shape[1] == 30 and v.dtype == np.float32]
     path = str(tmp_path / "b.ark")
     with K.open_or_fd(path, "wb") as f:
@@ -177,7 +178,7 @@ def test_batch_reader_shapes(K, gold, tmp_path):
             for k, v in mats:
                 K.write_mat(f, v, key="%s_%d" % (k, rep))
     allk, allf, alll = [], [], []
-    for keys, feats, lens in K.BatchReader(path, 30, max_rows=230, max_utts=3):
+    for keys, feats, lens in K.BatchReader(path, 30, max_rows=230, max_utts=3, threads=threads):
         assert len(keys) <= 3 and feats.shape[0] == lens.sum() <= 230
         allk += keys
         allf.append(feats.copy())
@@ -186,7 +187,20 @@ def test_batch_reader_shapes(K, gold, tmp_path):
     assert _same(np.concatenate(allf), np.concatenate([v for _ in range(3) for _, v in mats]))
     assert alll == [v.shape[0] for _ in range(3) for _, v in mats]
     with pytest.raises(K.KaldiIOError, match="does not fit an empty batch"):
-        list(K.BatchReader(path, 30, max_rows=100))
+        list(K.BatchReader(path, 30, max_rows=100, threads=threads))
+    # compressed and text objects through the same batch path
+    mixed = str(tmp_path / "mixed.ark")
+    from oracle import kaldi_io_ref as O
+    with open(mixed, "wb") as f:
+        for i, (k, v) in enumerate(mats):
+            f.write(O.write_cm_bytes(v, k) if i % 2 == 0 and v.shape[0] > 1 else O.write_mat_bytes(v, k))
+    want = dict(O.parse_ark(open(mixed, "rb").read()))
+    got = {}
+    for keys, feats, lens in K.BatchReader(mixed, 30, max_rows=300, threads=threads):
+        offs = np.concatenate([[0], np.cumsum(lens)])
+        for i, k in enumerate(keys):
+            got[k] = feats[offs[i]:offs[i + 1]].copy()
+    assert list(got) == list(want) and all(_same(got[k], np.ascontiguousarray(want[k])) for k in want)
 
 
 def test_error_behaviour(K, tmp_path):

@@ -116,6 +116,8 @@ struct Source {
   pid_t child = -1;
   std::string cmd;
   bool seekable = false;
+  std::string path;            // regular files: the name, for the per-thread descriptors of the indexed batch reader
+  size_t fill_limit = 0;       // > 0: refill at most this many bytes (header scans that seek over the bodies)
   std::vector<uint8_t> buf;
   size_t pos = 0, end = 0;
   bool eof = false;
@@ -142,6 +144,7 @@ struct Source {
       if (fd < 0) { set_err(&err, "cannot open %s: %s", file.c_str(), strerror(errno)); return XVK_EOPEN; }
       struct stat st;
       seekable = fstat(fd, &st) == 0 && S_ISREG(st.st_mode);
+      if (seekable) path = file;
       if (offset >= 0 && lseek(fd, offset, SEEK_SET) < 0) { set_err(&err, "cannot seek %s to %lld", file.c_str(), (long long)offset); return XVK_EOPEN; }
 #ifdef POSIX_FADV_SEQUENTIAL
       if (seekable && offset < 0) posix_fadvise(fd, 0, 0, POSIX_FADV_SEQUENTIAL);
@@ -169,7 +172,7 @@ struct Source {
     if (eof) return false;
     pos = 0;
     end = 0;
-    const ssize_t got = raw_read(buf.data(), buf.size());
+    const ssize_t got = raw_read(buf.data(), fill_limit ? std::min(fill_limit, buf.size()) : buf.size());
     if (got <= 0) { eof = true; return false; }
     end = static_cast<size_t>(got);
     return true;
@@ -470,6 +473,8 @@ int decode_body(Source& s, const ObjHeader& h, int32_t start, int32_t length, T*
 // ================================================================================================ ark reader
 struct xvk_reader {
   Source src;
+  int threads = 1;
+  std::vector<int> worker_fds;
   bool keyless = false, first = true, pending = false;
   std::string key, err;
   ObjHeader h;
@@ -511,6 +516,81 @@ int skip_pending(xvk_reader* r) {
   r->pending = false;
   if (!r->src.skip(body_bytes(r->h))) { r->err = r->src.err; return XVK_EIO; }
   return XVK_OK;
+}
+
+template <class Fn>
+int parallel_for(int64_t n, int threads, Fn fn, std::string* err);
+
+// Regular files: scan the headers of a batch (one short read + one seek per object), then decode the bodies with
+// `threads` workers, each through its own descriptor positioned on the body.
+int read_batch_indexed(xvk_reader* r, float* dst, int64_t cap_rows, int32_t dim, int32_t max_utts, int32_t* lengths,
+                       char* keys, size_t keys_cap, int32_t* n_utts, int64_t* n_rows) {
+  struct Item { int64_t off, row0; ObjHeader h; };
+  std::vector<Item> items;
+  int64_t rows = 0;
+  size_t kpos = 0;
+  int more = 1;
+  *n_utts = 0;
+  *n_rows = 0;
+  Source& s = r->src;
+  s.fill_limit = 4096;
+  for (;;) {
+    if (!r->pending) {
+      const int rc = xvk_next(r, nullptr, nullptr, nullptr, nullptr);
+      if (rc < 0) { s.fill_limit = 0; return rc; }
+      if (rc == 0) { more = 0; break; }
+    }
+    const ObjHeader& h = r->h;
+    int bad = XVK_OK;
+    if (h.kind == XVK_VEC_F32 || h.kind == XVK_VEC_F64 || h.kind == XVK_VEC_TEXT) {
+      set_err(&r->err, "key %s: expected a feature matrix, found a vector", r->key.c_str());
+      bad = XVK_EFORMAT;
+    } else if (h.cols != dim && h.rows > 0) {
+      set_err(&r->err, "key %s: feature dimension %d, expected %d", r->key.c_str(), h.cols, dim);
+      bad = XVK_EFORMAT;
+    } else if (static_cast<int32_t>(items.size()) == max_utts || rows + h.rows > cap_rows || kpos + r->key.size() + 1 > keys_cap) {
+      if (items.empty()) {
+        set_err(&r->err, "key %s (%d rows) does not fit an empty batch of %lld rows", r->key.c_str(), h.rows, (long long)cap_rows);
+        bad = XVK_ECAPACITY;
+      } else {
+        break;
+      }
+    }
+    if (bad != XVK_OK) { s.fill_limit = 0; return bad; }
+    Item it;
+    it.off = static_cast<int64_t>(lseek(s.fd, 0, SEEK_CUR)) - static_cast<int64_t>(s.end - s.pos);
+    it.row0 = rows;
+    it.h = h;
+    items.push_back(it);
+    memcpy(keys + kpos, r->key.c_str(), r->key.size() + 1);
+    kpos += r->key.size() + 1;
+    lengths[items.size() - 1] = h.rows;
+    rows += h.rows;
+    r->pending = false;
+    if (!s.skip(body_bytes(h))) { r->err = s.err; s.fill_limit = 0; return XVK_EIO; }
+  }
+  s.fill_limit = 0;
+  const int threads = std::min<int64_t>(r->threads, std::max<int64_t>(1, static_cast<int64_t>(items.size())));
+  while (static_cast<int>(r->worker_fds.size()) < threads) {
+    const int fd = ::open(s.path.c_str(), O_RDONLY | O_CLOEXEC);
+    if (fd < 0) { set_err(&r->err, "cannot open %s: %s", s.path.c_str(), strerror(errno)); return XVK_EOPEN; }
+    r->worker_fds.push_back(fd);
+  }
+  const int rc = parallel_for(static_cast<int64_t>(items.size()), threads, [&](int64_t i, int tid, std::vector<uint8_t>* scratch, std::string* err) {
+    const Item& it = items[i];
+    Source w;
+    w.fd = r->worker_fds[tid];
+    w.seekable = true;
+    w.buf.resize(1 << 12);
+    if (lseek(w.fd, it.off, SEEK_SET) < 0) { set_err(err, "lseek(): %s", strerror(errno)); w.fd = -1; return static_cast<int>(XVK_EIO); }
+    const int drc = decode_body(w, it.h, 0, it.h.rows, dst + it.row0 * dim, static_cast<int64_t>(dim), scratch, err);
+    w.fd = -1;                                  // the descriptor belongs to the reader
+    return drc;
+  }, &r->err);
+  if (rc != XVK_OK) return rc;
+  *n_utts = static_cast<int32_t>(items.size());
+  *n_rows = rows;
+  return more;
 }
 
 template <class T>
@@ -569,9 +649,17 @@ int xvk_read_rows_f32(xvk_reader* r, int32_t start, int32_t length, float* dst, 
   return reader_decode(r, start, length, dst, ld);
 }
 
+int xvk_reader_set_threads(xvk_reader* r, int32_t threads) {
+  if (!r || threads < 1) return XVK_EINVAL;
+  r->threads = threads;
+  return XVK_OK;
+}
+
 int xvk_read_batch_f32(xvk_reader* r, float* dst, int64_t cap_rows, int32_t dim, int32_t max_utts, int32_t* lengths,
                        char* keys, size_t keys_cap, int32_t* n_utts, int64_t* n_rows) {
   if (!r || !dst || !lengths || !keys || !n_utts || !n_rows || dim <= 0 || max_utts <= 0) return XVK_EINVAL;
+  if (r->threads > 1 && r->src.seekable && !r->src.gz && !r->src.path.empty())
+    return read_batch_indexed(r, dst, cap_rows, dim, max_utts, lengths, keys, keys_cap, n_utts, n_rows);
   int32_t n = 0;
   int64_t rows = 0;
   size_t kpos = 0;
@@ -614,6 +702,7 @@ const char* xvk_reader_error(const xvk_reader* r) { return r ? r->err.c_str() : 
 
 int xvk_reader_close(xvk_reader* r) {
   if (!r) return XVK_OK;
+  for (const int fd : r->worker_fds) ::close(fd);
   const int rc = r->src.close_all();
   delete r;
   return rc;
@@ -666,7 +755,7 @@ int parallel_for(int64_t n, int threads, Fn fn, std::string* err) {
     for (;;) {
       const int64_t i = next.fetch_add(1);
       if (i >= n || status.load() != XVK_OK) return;
-      const int rc = fn(i, &scratch, &errs[tid]);
+      const int rc = fn(i, tid, &scratch, &errs[tid]);
       if (rc != XVK_OK) { int expect = XVK_OK; status.compare_exchange_strong(expect, rc); return; }
     }
   };
@@ -748,7 +837,7 @@ int xvk_scp_read_many_f32(xvk_scp* s, const int64_t* idx, int64_t n, float* dst,
   const int64_t count = static_cast<int64_t>(s->entries.size());
   for (int64_t k = 0; k < n; ++k)
     if (idx[k] < 0 || idx[k] >= count || row_off[k] < 0 || row_off[k] > cap_rows) { s->err = "index or row offset out of range"; return XVK_EINVAL; }
-  return parallel_for(n, threads, [&](int64_t k, std::vector<uint8_t>* scratch, std::string* err) {
+  return parallel_for(n, threads, [&](int64_t k, int, std::vector<uint8_t>* scratch, std::string* err) {
     ObjHeader h;
     const int rc = scp_fetch(s->entries[idx[k]], &h, dst + row_off[k] * ld, ld, cap_rows - row_off[k], scratch, err);
     if (rc == XVK_OK && rows_out) rows_out[k] = h.rows;
@@ -761,7 +850,7 @@ int xvk_scp_dims_many(xvk_scp* s, const int64_t* idx, int64_t n, int32_t* rows_o
   const int64_t count = static_cast<int64_t>(s->entries.size());
   for (int64_t k = 0; k < n; ++k)
     if (idx[k] < 0 || idx[k] >= count) { s->err = "index out of range"; return XVK_EINVAL; }
-  return parallel_for(n, threads, [&](int64_t k, std::vector<uint8_t>* scratch, std::string* err) {
+  return parallel_for(n, threads, [&](int64_t k, int, std::vector<uint8_t>* scratch, std::string* err) {
     ObjHeader h;
     const int rc = scp_fetch(s->entries[idx[k]], &h, nullptr, 0, 0, scratch, err);
     if (rc == XVK_OK) {

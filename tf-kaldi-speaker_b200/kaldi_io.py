@@ -62,6 +62,7 @@ PROTOTYPES = {
     "xvk_read_f64": (C.c_int, [_p, _p, C.c_int64]),
     "xvk_read_rows_f32": (C.c_int, [_p, C.c_int32, C.c_int32, _p, C.c_int64]),
     "xvk_read_batch_f32": (C.c_int, [_p, _p, C.c_int64, C.c_int32, C.c_int32, _i32p, _p, C.c_size_t, _i32p, _i64p]),
+    "xvk_reader_set_threads": (C.c_int, [_p, C.c_int32]),
     "xvk_reader_error": (C.c_char_p, [_p]),
     "xvk_reader_close": (C.c_int, [_p]),
     "xvk_scp_open": (_p, [C.c_char_p, C.c_char_p, C.c_size_t]),
@@ -464,8 +465,9 @@ class BatchReader(object):
     `max_rows` rows / `max_utts` utterances each, decoded natively into `buffer` (pass a pinned array to make the
     H2D copy of xv_forward asynchronous).  The arrays of a batch are views: consume them before the next one."""
 
-    def __init__(self, rspecifier, dim, max_rows=1 << 20, max_utts=4096, buffer=None):
+    def __init__(self, rspecifier, dim, max_rows=1 << 20, max_utts=4096, buffer=None, threads=8):
         self.fd = open_or_fd(rspecifier)
+        self.fd._check(self.fd._lib.xvk_reader_set_threads(self.fd._h, max(int(threads), 1)))   # regular files: parallel decode
         self.dim = int(dim)
         self.max_utts = int(max_utts)
         self.buffer = np.empty((max_rows, dim), np.float32) if buffer is None else buffer
