@@ -186,3 +186,49 @@ def test_extract_cli_ark_to_ark(tmp_path):
     assert list(got) == keys
     for k in keys:
         assert max_rel(got[k][None], pred(decoded[k])[None]) <= TOL["bf16"], k
+
+
+def test_extract_frame_and_attention_cli(tmp_path):
+    """extract_frame.py (edge-replication padding, consecutive chunks) and extract_attention.py (first chunk only)."""
+    import json
+    from oracle import kaldi_io_ref, numpy_ref, synth
+    from xvector_b200 import kaldi_io
+    from xvector_b200.extract_frame import main, main_attention
+    cfg = dict(synth.TDNN_ATT_CONFIG)
+    w = synth.make_tdnn_weights(30, cfg, seed=26)
+    nnet = tmp_path / "nnet"
+    nnet.mkdir()
+    (nnet / "config.json").write_text(json.dumps(cfg))
+    (nnet / "feature_dim").write_text("30\n")
+    np.savez(str(nnet / "weights.npz"), **w)
+    (nnet / "checkpoint").write_text('model_checkpoint_path: "model-10"\n')
+    lens = [20, 90, 230]
+    feats = [synth.packed_features(np.array([n]), 30, seed=240 + n) for n in lens]
+    keys = ["u%d" % i for i in range(len(lens))]
+    ark = str(tmp_path / "feats.ark")
+    with open(ark, "wb") as f:
+        for k, m in zip(keys, feats):
+            f.write(kaldi_io_ref.write_mat_bytes(m, k))
+    oparams = numpy_ref.OracleParams(**cfg)
+    out = str(tmp_path / "frames.ark")
+    main(["--precision", "fp32", "--node", "tdnn4_relu", "-s", "100", str(tmp_path), ark, out])
+    got = dict(kaldi_io.read_mat_ark(out))
+    assert list(got) == keys[1:]
+
+    def want_frames(x):
+        pieces = [x[s:s + 100] for s in range(0, x.shape[0], 100)]
+        outs = []
+        for p in pieces:
+            y = numpy_ref.predict(p, oparams, w, 30, node="tdnn4_relu")
+            pad = (p.shape[0] - y.shape[0]) // 2
+            outs.append(np.concatenate([np.repeat(y[:1], pad, 0), y, np.repeat(y[-1:], pad, 0)]))
+        return np.concatenate(outs)
+    for k, x in zip(keys[1:], feats[1:]):
+        ref = want_frames(x)
+        assert got[k].shape == (x.shape[0], 512) and tensor_rel(got[k], ref) <= TOL["fp32"], k
+    main_attention(["--precision", "fp32", "-s", "100", str(tmp_path), ark, out])
+    got = dict(kaldi_io.read_mat_ark(out))
+    assert list(got) == keys[1:]
+    for k, x in zip(keys[1:], feats[1:]):
+        ref = numpy_ref.predict(x[:100], oparams, w, 30, node="attention_weights")
+        assert got[k].shape == ref.shape and tensor_rel(got[k], ref) <= TOL["fp32"] * 2, k
