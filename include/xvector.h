@@ -200,6 +200,22 @@ int   xv_conv2d_bf16_async(xv_ctx* ctx, const void* x_dev, int32_t nb, int32_t t
 int   xv_wgrad_bf16_async(xv_ctx* ctx, const void* a_dev, int64_t a_rows, int32_t lda, const void* dz_dev, int32_t ldz,
                           int64_t rows, int32_t taps, int32_t cin, int32_t n_valid, float* out_dev, int32_t ldo);
 
+/* ---- post-extraction vector operations -------------------------------------------------
+ * What egs/voxceleb/v1/nnet/run_extract_embeddings.sh:80-103 runs on the x-vectors through Kaldi binaries, and the
+ * cosine trial scores of misc/utils.py:307-346.  Host pointers in and out; synchronous.
+ *
+ * ivector-normalize-length: out_i = x_i / |x_i| (scaleup = 0, the recipe's --scaleup=false) or x_i * sqrt(dim) / |x_i|
+ * (scaleup = 1); a zero vector is copied unchanged. */
+int   xv_vec_normalize_length(xv_ctx* ctx, const float* x, int64_t n, int32_t dim, int scaleup, float* out);
+/* ivector-mean over spk2utt: out[g] = mean of the vectors with group[i] == g (group[i] < 0: not used), summed in input
+ * order; counts[g] (may be NULL) = number of members (num_utts.ark); an empty group gives a zero vector. */
+int   xv_vec_group_mean(xv_ctx* ctx, const float* x, int64_t n, int32_t dim, const int32_t* group, int32_t n_groups,
+                        float* out, int32_t* counts);
+/* out[i, j] = a_i . b_j / (sqrt(|a_i|^2 + eps) * sqrt(|b_j|^2 + eps)); compute_cos_pairwise_eer uses eps = 1e-12 and
+ * a == b (misc/utils.py:318,326). */
+int   xv_cosine_scores(xv_ctx* ctx, const float* a, int64_t na, const float* b, int64_t nb, int32_t dim, float eps,
+                       float* out);
+
 const char* xv_version(void);
 
 #ifdef __cplusplus

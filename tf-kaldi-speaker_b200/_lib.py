@@ -75,6 +75,9 @@ PROTOTYPES = {
     "xv_train_get_grad": (C.c_int, [_p, C.c_char_p, _p, C.c_int64]),
     "xv_comm_unique_id": (C.c_int, [_p, _p]),
     "xv_comm_init": (C.c_int, [_p, _p, C.c_int, C.c_int]),
+    "xv_vec_normalize_length": (C.c_int, [_p, _f32p, C.c_int64, C.c_int32, C.c_int, _f32p]),
+    "xv_vec_group_mean": (C.c_int, [_p, _f32p, C.c_int64, C.c_int32, _i32p, C.c_int32, _f32p, _i32p]),
+    "xv_cosine_scores": (C.c_int, [_p, _f32p, C.c_int64, _f32p, C.c_int64, C.c_int32, C.c_float, _f32p]),
     "xv_version": (C.c_char_p, []),
 }
 

@@ -305,6 +305,32 @@ class Engine(object):
         self._check(self.lib.xv_profile_query(self._ctx, family.encode(), C.byref(ms), C.byref(cnt)))
         return float(ms.value), int(cnt.value)
 
+    # -- post-extraction vector operations
+    def normalize_length(self, x, scaleup=False):
+        """ivector-normalize-length [--scaleup=false]: rows of x [n, dim] scaled to unit length (or to sqrt(dim))."""
+        x = _f32(x)
+        out = np.empty_like(x)
+        self._check(self.lib.xv_vec_normalize_length(self._ctx, _fptr(x), x.shape[0], x.shape[1], int(bool(scaleup)), _fptr(out)))
+        return out
+
+    def group_mean(self, x, group, n_groups):
+        """ivector-mean: -> (means [n_groups, dim], counts [n_groups]); group[i] < 0 leaves vector i out."""
+        x = _f32(x)
+        group = np.ascontiguousarray(group, np.int32)
+        out = np.empty((n_groups, x.shape[1]), np.float32)
+        counts = np.zeros(n_groups, np.int32)
+        self._check(self.lib.xv_vec_group_mean(self._ctx, _fptr(x), x.shape[0], x.shape[1], group.ctypes.data_as(C.POINTER(C.c_int32)),
+                                               n_groups, _fptr(out), counts.ctypes.data_as(C.POINTER(C.c_int32))))
+        return out, counts
+
+    def cosine_scores(self, a, b=None, eps=1e-12):
+        """[na, nb] cosine similarities (misc/utils.py:318,326)."""
+        a = _f32(a)
+        b = a if b is None else _f32(b)
+        out = np.empty((a.shape[0], b.shape[0]), np.float32)
+        self._check(self.lib.xv_cosine_scores(self._ctx, _fptr(a), a.shape[0], _fptr(b), b.shape[0], a.shape[1], C.c_float(eps), _fptr(out)))
+        return out
+
     def flush_l2(self):
         self._check(self.lib.xv_flush_l2(self._ctx))
 
