@@ -117,6 +117,10 @@ int xvk_writer_flush(xvk_writer* w);
 const char* xvk_writer_error(const xvk_writer* w);
 int xvk_writer_close(xvk_writer* w);
 
+/* CRC-32C (Castagnoli) of n bytes continuing from `crc` (0 to start): the checksum TensorFlow's tensor-bundle files
+ * carry (tf_checkpoint.py). */
+uint32_t xvk_crc32c(const void* data, size_t n, uint32_t crc);
+
 const char* xvk_version(void);
 
 #ifdef __cplusplus

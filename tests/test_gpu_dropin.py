@@ -232,3 +232,27 @@ def test_extract_frame_and_attention_cli(tmp_path):
     for k, x in zip(keys[1:], feats[1:]):
         ref = numpy_ref.predict(x[:100], oparams, w, 30, node="attention_weights")
         assert got[k].shape == ref.shape and tensor_rel(got[k], ref) <= TOL["fp32"] * 2, k
+
+
+def test_trainer_loads_a_tf_checkpoint_directly(tmp_path):
+    """Trainer.load (model/trainer.py:277-294) on the reference's own storage format: a tf.train.Saver tensor bundle +
+    `checkpoint` state file, no weights.npz."""
+    import json
+    from oracle import numpy_ref, synth, tf_bundle_ref
+    from xvector_b200.misc.utils import Params
+    from xvector_b200.model.trainer import Trainer
+    cfg = dict(synth.TDNN_STAT_CONFIG)
+    w = synth.make_tdnn_weights(30, cfg, seed=36)
+    nnet = tmp_path / "nnet"
+    nnet.mkdir()
+    (nnet / "config.json").write_text(json.dumps(cfg))
+    saved = dict(w, global_step=np.array(820000, np.int64))
+    saved["tdnn/tdnn4_dense/kernel/Momentum"] = np.ones_like(w["tdnn/tdnn4_dense/kernel"])
+    tf_bundle_ref.write_checkpoint(str(nnet), 820000, saved)
+    trainer = Trainer(Params(str(nnet / "config.json")), str(tmp_path), 30, single_cpu=True, precision="fp32")
+    trainer.build("predict")
+    x = synth.config1_features(2, 70, 30, seed=3)
+    e = trainer.predict(x)                                        # loads lazily like the reference's predict
+    assert trainer.load() == 820000
+    assert max_rel(e, numpy_ref.predict(x, numpy_ref.OracleParams(**cfg), w, 30)) <= TOL["fp32"]
+    trainer.close()

@@ -1062,6 +1062,38 @@ int xvk_writer_close(xvk_writer* w) {
   return rc;
 }
 
+// CRC-32C (Castagnoli), slicing-by-8: the checksum of TensorFlow's tensor-bundle blocks and tensors (tf_checkpoint.py).
+uint32_t xvk_crc32c(const void* data, size_t n, uint32_t crc) {
+  static uint32_t table[8][256];
+  static std::atomic<bool> ready(false);
+  if (!ready.load(std::memory_order_acquire)) {
+    uint32_t t[8][256];
+    for (uint32_t i = 0; i < 256; ++i) {
+      uint32_t c = i;
+      for (int k = 0; k < 8; ++k) c = (c & 1) ? (c >> 1) ^ 0x82F63B78u : c >> 1;
+      t[0][i] = c;
+    }
+    for (uint32_t i = 0; i < 256; ++i)
+      for (int k = 1; k < 8; ++k) t[k][i] = (t[k - 1][i] >> 8) ^ t[0][t[k - 1][i] & 0xFF];
+    memcpy(table, t, sizeof(t));                 // identical contents from every thread: benign race
+    ready.store(true, std::memory_order_release);
+  }
+  const uint8_t* p = static_cast<const uint8_t*>(data);
+  uint32_t c = ~crc;
+  while (n >= 8) {
+    uint32_t lo, hi;
+    memcpy(&lo, p, 4);
+    memcpy(&hi, p + 4, 4);
+    lo ^= c;
+    c = table[7][lo & 0xFF] ^ table[6][(lo >> 8) & 0xFF] ^ table[5][(lo >> 16) & 0xFF] ^ table[4][lo >> 24] ^
+        table[3][hi & 0xFF] ^ table[2][(hi >> 8) & 0xFF] ^ table[1][(hi >> 16) & 0xFF] ^ table[0][hi >> 24];
+    p += 8;
+    n -= 8;
+  }
+  while (n--) c = table[0][(c ^ *p++) & 0xFF] ^ (c >> 8);
+  return ~c;
+}
+
 const char* xvk_version(void) { return "xvkaldi 0.1 (ark/scp FM DM CM FV DV text; gzip; pipes)"; }
 
 }  // extern "C"

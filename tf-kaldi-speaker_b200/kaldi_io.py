@@ -84,6 +84,7 @@ PROTOTYPES = {
     "xvk_writer_flush": (C.c_int, [_p]),
     "xvk_writer_error": (C.c_char_p, [_p]),
     "xvk_writer_close": (C.c_int, [_p]),
+    "xvk_crc32c": (C.c_uint32, [C.c_char_p, C.c_size_t, C.c_uint32]),
     "xvk_version": (C.c_char_p, []),
 }
 

@@ -6,6 +6,7 @@ import sys
 
 import numpy as np
 
+from .. import tf_checkpoint
 from ..engine import Engine
 from .tdnn import tdnn, etdnn  # noqa: F401  (kept importable from here like the reference)
 from .resnet import resnet_18  # noqa: F401
@@ -92,28 +93,37 @@ class Trainer(object):
         if not self.is_built:
             sys.exit("The graph has not been build. Cannot load the models.")
         path = os.path.join(self.model, "weights.npz")
-        if not os.path.isfile(path):
-            sys.exit("Failed to find a checkpoint in {}".format(self.model))
-        with np.load(path) as z:
-            weights = {k: z[k] for k in z.files}
-        self.set_weights(weights)
         step = 0
-        ckpt = os.path.join(self.model, "checkpoint")
-        if os.path.isfile(ckpt):
-            with open(ckpt) as f:
-                m = re.search(r'model_checkpoint_path:\s*"([^"]+)"', f.read())
-            if m:
-                digits = list(re.finditer(r"(\d+)(?!.*\d)", os.path.basename(m.group(1))))
-                if digits:
-                    step = int(digits[0].group(0))
+        if os.path.isfile(path):
+            with np.load(path) as z:
+                weights = {k: z[k] for k in z.files}
+            state = tf_checkpoint.get_checkpoint_state(self.model)
+            if state:
+                try:
+                    step = tf_checkpoint.checkpoint_step(state[0])
+                except StopIteration:
+                    step = 0
+        elif self._has_tf_checkpoint():
+            # the reference's own format: tf.train.Saver tensor bundle named by the `checkpoint` state file
+            weights, step = tf_checkpoint.load_weights(self.model)
+        else:
+            sys.exit("Failed to find a checkpoint in {}".format(self.model))
+        self.set_weights(weights)
         self.is_loaded = True
         return step
+
+    def _has_model(self):
+        return os.path.isfile(os.path.join(self.model, "weights.npz")) or self._has_tf_checkpoint()
+
+    def _has_tf_checkpoint(self):
+        state = tf_checkpoint.get_checkpoint_state(self.model)
+        return bool(state) and os.path.isfile(os.path.join(self.model, os.path.basename(state[0])) + ".index")
 
     def predict(self, features):
         """Output the embeddings (model/trainer.py:886-913): rank-2 [T, D] -> [E]; rank-3 [B, T, D] -> [B, E];
         frame-level nodes give [T', N] / [B, T', N].  Features wider than `dim` are sliced."""
         if not self.is_loaded:
-            if os.path.isfile(os.path.join(self.model, "weights.npz")):
+            if self._has_model():
                 self.load()
             else:
                 sys.exit("Cannot find model in %s" % self.model)
@@ -145,7 +155,7 @@ class Trainer(object):
         """Utterances already packed back to back ([sum T_u, D] float32, e.g. a pinned buffer filled by
         kaldi_io.BatchReader) + their lengths: the layout xv_forward takes, no host-side copy."""
         if not self.is_loaded:
-            if os.path.isfile(os.path.join(self.model, "weights.npz")):
+            if self._has_model():
                 self.load()
             else:
                 sys.exit("Cannot find model in %s" % self.model)
@@ -155,7 +165,7 @@ class Trainer(object):
         """Extension of predict(): a list of [T_u, D] utterances of different lengths in ONE packed call.
         Row u of the result equals predict(features_list[u]) (each utterance is computed as a batch of one)."""
         if not self.is_loaded:
-            if os.path.isfile(os.path.join(self.model, "weights.npz")):
+            if self._has_model():
                 self.load()
             else:
                 sys.exit("Cannot find model in %s" % self.model)
