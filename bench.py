@@ -137,6 +137,24 @@ class Workload(object):
             self.tensor_prefixes = ("gemm",)
             self.kernel = "xv_tdnn_gemm_kernel (tcgen05 spliced GEMM + fused epilogue), all 6 layer launches of a step"
             self.workload = Workload.describe(args)
+        elif self.name == "attention":
+            # configs[2]: TDNN + multi-head self-attention pooling (egs/voxceleb/v1/nnet_conf/tdnn_softmax_1e-2_tdnn4_att_pretrain.json
+            # with att_num_heads = 4: keys from tdnn4_relu through a 1500-1500 network, values = tdnn5_relu, both split by head)
+            self.dim = args.dim or 64
+            self.cfg = dict(synth.TDNN_ATT_CONFIG, att_num_heads=4)
+            self.weights = synth.make_tdnn_weights(self.dim, self.cfg, seed=1234)
+            self.utts = args.utts or 2500
+            self.lengths = make_shard(rank, world, self.utts)
+            self.batch_frames = args.batch_frames or 262144
+            self.scale = np.ones(self.dim, np.float32)
+            t = self.lengths.astype(np.float64)
+            key = 2.0 * (512 * 1500 + 1500 * 1500) * (t - 14)
+            self.layer_flops = {}
+            self.flops = float((scheduler.utterance_flops(self.lengths, self.dim) + key).sum())
+            self.tensor_prefixes = ("gemm",)
+            self.kernel = ("xv_tdnn_gemm_kernel: 5 frame layers + the 2 attention-key layers + tdnn6 (att_scores / att_softmax / "
+                           "weighted pooling are separate HBM-bound kernels, listed in kernel_families_ms_per_step)")
+            self.workload = Workload.describe(args)
         else:
             self.dim = args.dim or 64
             self.cfg = dict(synth.RESNET_CONFIG)
@@ -160,6 +178,9 @@ class Workload(object):
         if getattr(args, "workload", "tdnn") == "resnet18":
             return ("configs[3]: ResNet-18 + statistics pooling (egs/voxceleb/v3) embedding extraction, "
                     "%d-dim fbank x 400 frames" % (args.dim or 64))
+        if getattr(args, "workload", "tdnn") == "attention":
+            return ("configs[2]: x-vector TDNN with 4-head self-attention pooling (keys: tdnn4_relu -> 1500 -> 1500, values: "
+                    "tdnn5_relu) on %d-dim fbank utterances of log-uniform length 200-6000 frames" % (args.dim or 64))
         return ("configs[1]: standard x-vector TDNN (5x512 frame layers, 1500 pre-pool, stats pooling, "
                 "tdnn6_dense 512-d) on 30-dim MFCC utterances of log-uniform length 200-6000 frames")
 
@@ -493,6 +514,15 @@ def cpu_baseline(seconds, args=None):
         cfg = dict(synth.RESNET_CONFIG)
         w = synth.make_resnet_weights(dim, cfg, seed=1234)
         what = "%d-dim fbank x 400-frame utterances of configs[3]" % dim
+    elif workload == "attention":
+        dim = (args.dim or 64)
+        lengths = synth.config2_lengths(UTTS_PER_GPU, seed=202)
+        take = np.random.default_rng(0).permutation(len(lengths))[:max(4 * cores, 64)]
+        sub = lengths[take].astype(np.int32)
+        feats = synth.fbank_like(int(sub.sum()), dim, seed=202)
+        cfg = dict(synth.TDNN_ATT_CONFIG, att_num_heads=4)
+        w = synth.make_tdnn_weights(dim, cfg, seed=1234)
+        what = "%d-dim utterances drawn from the configs[2] length distribution (4-head attention pooling)" % dim
     else:
         lengths = synth.config2_lengths(UTTS_PER_GPU, seed=202)
         take = np.random.default_rng(0).permutation(len(lengths))[:max(4 * cores, 64)]
@@ -541,7 +571,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="tdnn", choices=["tdnn", "resnet18", "train"],
+    ap.add_argument("--workload", default="tdnn", choices=["tdnn", "attention", "resnet18", "train"],
                     help="tdnn = BASELINE.json configs[1] (the headline metric); resnet18 = configs[3] (secondary)")
     ap.add_argument("--dim", type=int, default=0, help="feature dim of the resnet18 workload (default 64; 40 = reference-legal)")
     ap.add_argument("--batch-frames", type=int, default=0)

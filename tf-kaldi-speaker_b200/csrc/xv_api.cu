@@ -574,7 +574,7 @@ void xv_destroy(xv_ctx* c) {
   resnet_release(c);
   for (DevBuf& b : c->frame_out) release(&b);
   DevBuf* bufs[] = {&c->att_query, &c->att_post_scale, &c->att_post_shift, &c->att_post_slope, &c->d_feats,
-                    &c->d_feat_ring[0], &c->d_feat_ring[1], &c->a1, &c->scores, &c->pool_acc, &c->pool_ws,
+                    &c->d_feat_ring[0], &c->d_feat_ring[1], &c->a1, &c->scores, &c->scores_acc, &c->att_query_pad, &c->pool_acc, &c->pool_ws,
                     &c->pooled_f32, &c->pooled_bf16, &c->pooled_pre_f32, &c->seg_out[0], &c->seg_out[1],
                     &c->seg_out_bf16, &c->d_cu, &c->d_segs, &c->d_tile_seg_ptr, &c->d_gather_meta, &c->d_gather_out,
                     &c->flush_buf};

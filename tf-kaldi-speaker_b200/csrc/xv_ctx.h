@@ -169,6 +169,8 @@ struct xv_ctx {
   xv::DevBuf a1;                           // spliced bf16 [batch rows, k1pad]
   std::vector<xv::DevBuf> frame_out;       // per frame layer output (bf16 or fp32) [batch rows, n_alloc | cout]
   xv::DevBuf scores;                       // attention scores/weights fp32 [H][batch rows]
+  xv::DevBuf scores_acc;                   // fused key-layer epilogue: fp64 score accumulators [H][batch rows]
+  xv::DevBuf att_query_pad;                // query flattened + zero padded to the key layer's n_alloc
   xv::DevBuf pool_acc;                     // fused pooling accumulators
   xv::DevBuf pool_ws;                      // launch_pool workspace
   xv::DevBuf pooled_f32, pooled_bf16, pooled_pre_f32;

@@ -95,10 +95,20 @@ int plan_job(xv_ctx* c, const int32_t* lengths, int32_t n_utts) {
   return XV_OK;
 }
 
+// Attention fusions of a layer launch: softmax-weighted pooled sums (value layer) or score accumulation (last key layer).
+struct GemmExtras {
+  const float* row_weight = nullptr;
+  int heads = 1, head_width = 0, weight_ld = 0;
+  const float* dot_q = nullptr;
+  double* dot_out = nullptr;
+  int dot_ld = 0;
+  float dot_scale = 1.f;
+};
+
 // ---- one tcgen05 layer launch -------------------------------------------------------------------
 static int gemm_layer(xv_ctx* c, const Layer& l, const void* a_base, int64_t a_rows_alloc, int stage,
                       __nv_bfloat16* out_bf16, float* out_f32, int64_t m_rows, bool pool, double* pool_acc,
-                      const int32_t* tile_seg, const PoolSeg* segs) {
+                      const int32_t* tile_seg, const PoolSeg* segs, const GemmExtras* ex = nullptr) {
   if (m_rows <= 0) return XV_OK;
   GemmPlan g;
   const char* err = make_tmap_bf16_2d(&g.tm_a, a_base, l.a_cin, a_rows_alloc, static_cast<uint64_t>(l.a_cin) * 2, kBK, kBM);
@@ -130,6 +140,10 @@ static int gemm_layer(xv_ctx* c, const Layer& l, const void* a_base, int64_t a_r
   p.row_weight = nullptr;
   p.heads = 1;
   p.head_width = l.n_alloc;
+  if (ex != nullptr) {
+    p.row_weight = ex->row_weight; p.heads = ex->heads; p.head_width = ex->head_width; p.weight_ld = ex->weight_ld;
+    p.dot_q = ex->dot_q; p.dot_out = ex->dot_out; p.dot_ld = ex->dot_ld; p.dot_scale = ex->dot_scale;
+  }
   g.pool = pool;
   const std::string fam = std::string(pool ? "gemm_pool." : "gemm.") + l.name;
   ProfScope ps(c, fam.c_str());
@@ -214,8 +228,26 @@ int run_job(xv_ctx* c, const char* node_name, bool pipelined_h2d, float* frames_
   }
   // A layer that feeds another layer must be at its final stage; the target layer is a leaf unless it also
   // feeds something (only possible for frame-level requests, where it is the last of its chain).
-  const bool fuse_pool = c->bf16 && !attention && utt_level;    // tdnn5 never stored
   const int pool_layer = c->n_main_frame - 1;
+  // Attention pooling fuses into the value layer's epilogue when the values are the last main layer itself (no value
+  // network), every head owns a slice of its columns (or there is one head), and the keys do not read that layer:
+  // tdnn1-4 -> key layers -> scores -> softmax -> tdnn5 with softmax-weighted sums in the epilogue, never stored.
+  bool att_fusable = attention && c->value_layers.empty() && c->att_value_buf == pool_layer &&
+                     (c->att_split_value || c->att_heads == 1) && c->att_value_dim / c->att_heads >= 32;
+  if (att_fusable) {
+    static const bool no_fuse = getenv("XV_ATT_POOL_IMPL") != nullptr && getenv("XV_ATT_POOL_IMPL")[0] == 's';   // 's'tandalone
+    int l = c->key_layers.front();
+    while (l >= 0 && l != pool_layer) l = c->frame_layers[l].in_buf;
+    if (l == pool_layer || no_fuse) att_fusable = false;
+  }
+  const bool fuse_pool = c->bf16 && utt_level && (!attention || att_fusable);    // tdnn5 never stored
+  const bool fuse_att = fuse_pool && attention;
+  // ... and the scores fuse into the last key layer's epilogue (its output is then never stored) when every head owns a
+  // slice of the key columns (or there is one head) that is at least half a tile wide.
+  const int key_last = attention ? c->key_layers.back() : -1;
+  const bool fuse_scores = fuse_att && (c->att_split_key || c->att_heads == 1) && c->att_dk >= 128 &&
+                           c->att_heads * c->att_dk <= c->frame_layers[key_last].n_alloc &&
+                           !(getenv("XV_ATT_SCORES_IMPL") != nullptr && getenv("XV_ATT_SCORES_IMPL")[0] == 's');
 
   // ---- buffers ----
   int64_t max_rows = 0, max_in_rows = 0;
@@ -228,6 +260,7 @@ int run_job(xv_ctx* c, const char* node_name, bool pipelined_h2d, float* frames_
   for (int l = 0; l < nl; ++l) {
     if (stage_of[l] < 0) continue;
     if (fuse_pool && l == pool_layer) continue;
+    if (fuse_scores && l == key_last) continue;
     const int w = c->bf16 ? c->frame_layers[l].n_alloc : c->frame_layers[l].cout;
     if ((rc = ensure(c, &c->frame_out[l], static_cast<size_t>(rows_alloc) * w * esz, true)) != XV_OK) return rc;
   }
@@ -262,6 +295,16 @@ int run_job(xv_ctx* c, const char* node_name, bool pipelined_h2d, float* frames_
   if (attention && (utt_level || ni.level == 2))
     if ((rc = ensure(c, &c->scores, static_cast<size_t>(c->att_heads) * rows_alloc * 4)) != XV_OK) return rc;
 
+  if (fuse_scores) {
+    const int kn = c->frame_layers[key_last].n_alloc;
+    if ((rc = ensure(c, &c->scores_acc, static_cast<size_t>(c->att_heads) * rows_alloc * sizeof(double))) != XV_OK) return rc;
+    if ((rc = ensure(c, &c->att_query_pad, sizeof(float) * kn)) != XV_OK) return rc;
+    cudaError_t qe = cudaMemsetAsync(c->att_query_pad.p, 0, sizeof(float) * kn, c->stream);   // refreshed per call: weights may change
+    if (qe == cudaSuccess)
+      qe = cudaMemcpyAsync(c->att_query_pad.p, c->att_query.p, sizeof(float) * c->att_heads * c->att_dk, cudaMemcpyDeviceToDevice,
+                           c->stream);
+    if (qe != cudaSuccess) return cuda_fail(c, qe, "query copy");
+  }
   const int32_t* d_cu_global = static_cast<const int32_t*>(c->d_cu.p);
   const int32_t* d_cu_local = d_cu_global + (n + 1);
   size_t cu_local_off = 0;
@@ -317,9 +360,20 @@ int run_job(xv_ctx* c, const char* node_name, bool pipelined_h2d, float* frames_
     }
     for (int l = 0; l < nl; ++l) {
       if (stage_of[l] < 0) continue;
+      if (fuse_att && l == pool_layer) continue;             // runs after the attention weights exist (below)
       const Layer& L = c->frame_layers[l];
       const bool pool_here = fuse_pool && l == pool_layer;
-      if (c->bf16) {
+      if (fuse_scores && l == key_last) {
+        GemmExtras ex;
+        ex.heads = c->att_heads; ex.head_width = c->att_dk;
+        ex.dot_q = static_cast<const float*>(c->att_query_pad.p); ex.dot_out = static_cast<double*>(c->scores_acc.p);
+        ex.dot_ld = static_cast<int>(b.rows);
+        ex.dot_scale = c->att_use_scale ? 1.0f / sqrtf(static_cast<float>(c->att_dk)) : 1.0f;
+        if ((e = cudaMemsetAsync(c->scores_acc.p, 0, sizeof(double) * c->att_heads * b.rows, c->stream)) != cudaSuccess)
+          return cuda_fail(c, e, "cudaMemsetAsync(scores)");
+        rc = gemm_layer(c, L, c->frame_out[L.in_buf].p, rows_alloc, stage_of[l], nullptr, nullptr, b.rows, false, nullptr, nullptr,
+                        nullptr, &ex);
+      } else if (c->bf16) {
         const void* a = L.in_buf < 0 ? a_first : c->frame_out[L.in_buf].p;
         const int64_t a_rows = (L.in_buf < 0 && c->resnet) ? b.rows : rows_alloc;
         rc = gemm_layer(c, L, a, a_rows, stage_of[l], pool_here ? nullptr : static_cast<__nv_bfloat16*>(c->frame_out[l].p),
@@ -333,6 +387,34 @@ int run_job(xv_ctx* c, const char* node_name, bool pipelined_h2d, float* frames_
     }
     // ---- pooling of this batch ----
     const bool need_pool = utt_level || ni.level == 2;
+    if (fuse_att) {
+      const int kl = c->key_layers.back();
+      const Layer& KL = c->frame_layers[kl];
+      const Layer& VL = c->frame_layers[pool_layer];
+      const float scale = c->att_use_scale ? 1.0f / sqrtf(static_cast<float>(c->att_dk)) : 1.0f;
+      if (!fuse_scores) {
+        ProfScope ps(c, "att_scores");
+        e = launch_att_scores(c->frame_out[kl].p, XV_DTYPE_BF16, KL.n_alloc, b.rows, static_cast<const float*>(c->att_query.p),
+                              c->att_heads, c->att_dk, c->att_split_key ? 1 : 0, scale, static_cast<float*>(c->scores.p), c->stream);
+        if (e != cudaSuccess) return cuda_fail(c, e, "att_scores launch");
+      }
+      {
+        ProfScope ps(c, "att_softmax");
+        if (fuse_scores)
+          e = launch_att_softmax_f64(static_cast<const double*>(c->scores_acc.p), static_cast<float*>(c->scores.p), b.rows, cu_b,
+                                     c->total_context, nb, c->att_heads, c->stream);
+        else
+          e = launch_att_softmax(static_cast<float*>(c->scores.p), b.rows, cu_b, c->total_context, nb, c->att_heads, c->stream);
+        if (e != cudaSuccess) return cuda_fail(c, e, "att_softmax launch");
+      }
+      const void* a = VL.in_buf < 0 ? a_first : c->frame_out[VL.in_buf].p;
+      GemmExtras ex;
+      ex.row_weight = static_cast<const float*>(c->scores.p); ex.heads = c->att_heads;
+      ex.head_width = c->att_value_dim / c->att_heads; ex.weight_ld = static_cast<int>(b.rows);
+      rc = gemm_layer(c, VL, a, rows_alloc, stage_of[pool_layer], nullptr, nullptr, b.rows, true, static_cast<double*>(c->pool_acc.p),
+                      static_cast<const int32_t*>(c->d_tile_seg_ptr.p) + 2 * b.tile0, static_cast<const PoolSeg*>(c->d_segs.p), &ex);
+      if (rc != XV_OK) return rc;
+    }
     if (need_pool && !fuse_pool) {
       const int dtype = c->bf16 ? XV_DTYPE_BF16 : XV_DTYPE_F32;
       PoolArgs pa;
@@ -437,8 +519,9 @@ int run_job(xv_ctx* c, const char* node_name, bool pipelined_h2d, float* frames_
     const Layer& P = c->frame_layers[pool_layer];
     count_launch(c, "pool_finalize");
     e = launch_pool_finalize(static_cast<const double*>(c->pool_acc.p), P.n_alloc, d_cu_global, c->total_context, n, P.cout,
-                             static_cast<float*>(c->pooled_f32.p), c->pooled_dim, static_cast<__nv_bfloat16*>(c->pooled_bf16.p),
-                             l6.kpad, 0, c->stream);
+                             static_cast<float*>(c->has_att_post ? c->pooled_pre_f32.p : c->pooled_f32.p), c->pooled_dim,
+                             c->has_att_post ? nullptr : static_cast<__nv_bfloat16*>(c->pooled_bf16.p), l6.kpad, fuse_att ? 1 : 0,
+                             c->stream);
     if (e != cudaSuccess) return cuda_fail(c, e, "pool finalize launch");
   }
   if (c->has_att_post && ni.kind != 2 && ni.kind != 3) {

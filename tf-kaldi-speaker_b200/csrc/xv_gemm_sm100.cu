@@ -37,7 +37,7 @@ constexpr uint32_t kABytes = kBM * kBK * 2;                  // 16384
 constexpr uint32_t kBBytes = kBN * kBK * 2;                  // 32768
 constexpr uint32_t kStageBytes = kABytes + kBBytes;          // 49152
 constexpr uint32_t kRingBytes = kStages * kStageBytes;       // 196608
-constexpr uint32_t kEpiParamBytes = kAccStages * kBN * 12;   // (scale,shift) float2 + slope float = 6144
+constexpr uint32_t kEpiParamBytes = kAccStages * kBN * 16;   // (scale,shift) float2 + slope float + query float = 8192
 constexpr uint32_t kStoreStageBytes = 32 * 64;               // per warp: 32 rows x 32 bf16, SWIZZLE_64B
 constexpr uint32_t kEpiScratchBytes = kEpiWarps * kStoreStageBytes;
 constexpr uint32_t kBarrierBytes = 256;
@@ -63,6 +63,7 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   uint8_t* ring = smem;
   float2* ep_ss = reinterpret_cast<float2*>(smem + kRingBytes);                       // [2][256] scale,shift
   float* ep_sl = reinterpret_cast<float*>(smem + kRingBytes + kAccStages * kBN * 8);  // [2][256] slope
+  float* ep_sq = reinterpret_cast<float*>(smem + kRingBytes + kAccStages * kBN * 12); // [2][256] attention query (fused scores)
   uint8_t* scratch = smem + kRingBytes + kEpiParamBytes;                              // per-warp staging / transpose
   uint64_t* bars = reinterpret_cast<uint64_t*>(scratch + kEpiScratchBytes);
   uint64_t* full_bar = bars;                       // [kStages]   TMA -> MMA
@@ -167,6 +168,8 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       float* sl = ep_sl + as * kBN;
       ss[etid] = make_float2(__ldg(p.scale + n0 + etid), __ldg(p.shift + n0 + etid));
       sl[etid] = __ldg(p.slope + n0 + etid);
+      float* sq = ep_sq + as * kBN;
+      if (!kPool && p.dot_out != nullptr) sq[etid] = __ldg(p.dot_q + n0 + etid);
       asm volatile("bar.sync 1, 256;" ::: "memory");
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after();
@@ -188,7 +191,26 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
             w_last = s;
           }
         }
-        w_full = w_first == w_last && w_sg.r0 <= mw && w_sg.r1 >= mw + 32;
+        w_full = w_first == w_last && w_sg.r0 <= mw && w_sg.r1 >= mw + 32 && p.row_weight == nullptr;
+      }
+      // attention pooling, common case (one utterance under this warp's 32 rows, heads at least a tile wide): the masked
+      // softmax weights of the thread's four rows for the (at most two) heads of this tile, loaded once per tile
+      float tw_a[4] = {0.f, 0.f, 0.f, 0.f}, tw_b[4] = {0.f, 0.f, 0.f, 0.f};
+      int tile_bound = 0;
+      const bool tile_weights = kPool && p.row_weight != nullptr && w_first == w_last && p.head_width >= kBN;
+      if (tile_weights) {
+        const int ha = n0 / p.head_width;
+        tile_bound = (ha + 1) * p.head_width - n0;
+        const int lo = max(w_sg.r0, mw) - mw, hi = min(w_sg.r1, mw + 32) - mw;
+        const int rq0 = lane >> 2;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int rr = rq0 + 8 * k;
+          const bool in = rr >= lo && rr < hi;
+          const int r = min(mw + rr, p.m_rows - 1);
+          tw_a[k] = (in && ha < p.heads) ? __ldg(p.row_weight + static_cast<size_t>(ha) * p.weight_ld + r) : 0.f;
+          tw_b[k] = (in && tile_bound < kBN && ha + 1 < p.heads) ? __ldg(p.row_weight + static_cast<size_t>(ha + 1) * p.weight_ld + r) : 0.f;
+        }
       }
       if (kPool) {
         // ---- pooled layer: nothing is stored; per-utterance column sums of y and y^2 ----
@@ -250,12 +272,39 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
               float m[4];
 #pragma unroll
               for (int k = 0; k < 4; ++k) m[k] = (rq + 8 * k >= lo && rq + 8 * k < hi) ? 1.f : 0.f;
+              // attention pooling: the row mask becomes the softmax weight of (head of the column, row); a 32-column
+              // chunk touches at most two heads (head_width >= 32), the second one from column `bound` on
+              float mb[4] = {0.f, 0.f, 0.f, 0.f};
+              int bound = 32;
+              if (tile_weights) {
+                bound = tile_bound - c * 32;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) { m[k] = tw_a[k]; mb[k] = tw_b[k]; }
+                if (bound <= 0) {                       // the whole chunk belongs to the second head
+#pragma unroll
+                  for (int k = 0; k < 4; ++k) m[k] = tw_b[k];
+                  bound = 32;
+                }
+              } else if (p.row_weight != nullptr) {
+                const int nbase = n0 + c * 32;
+                const int ha = nbase / p.head_width;
+                bound = (ha + 1) * p.head_width - nbase;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  const int r = min(mw + rq + 8 * k, p.m_rows - 1);
+                  const float wa = ha < p.heads ? __ldg(p.row_weight + static_cast<size_t>(ha) * p.weight_ld + r) : 0.f;
+                  const float wb = (bound < 32 && ha + 1 < p.heads) ? __ldg(p.row_weight + static_cast<size_t>(ha + 1) * p.weight_ld + r) : 0.f;
+                  mb[k] = m[k] * wb;
+                  m[k] *= wa;
+                }
+              }
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
+                const bool second = 8 * (j >> 1) + cq + (j & 1) >= bound;
                 float a1 = 0.f, a2 = 0.f;
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                  const float t = m[k] * y[k][j];
+                  const float t = (second ? mb[k] : m[k]) * y[k][j];
                   a1 += t;
                   a2 = fmaf(t, y[k][j], a2);
                 }
@@ -299,6 +348,15 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
           }
         }
       } else {
+      // fused attention scores: this warp's 128 columns lie in at most two heads (head_width >= 128)
+      float dot_a = 0.f, dot_b = 0.f;
+      int dot_ha = 0, dot_bound = 0;
+      const bool dots = p.dot_out != nullptr;
+      if (dots) {
+        const int half_base = n0 + half * 128;
+        dot_ha = half_base / p.head_width;
+        dot_bound = (dot_ha + 1) * p.head_width - half_base;
+      }
 #pragma unroll 1
       for (int ci = 0; ci < 4; ++ci) {
         const int c = half * 4 + ci;             // 32-column chunk of the tile
@@ -336,6 +394,26 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
             for (int j = 0; j < 32; ++j) y[j] = tanhf(y[j]);
           }
         }
+        if (dots) {
+          const float4* q4 = reinterpret_cast<const float4*>(sq + c * 32);
+          const int bnd = dot_bound - ci * 32;            // columns of this chunk from `bnd` on belong to the next head
+          float acc_lo = 0.f, acc_hi = 0.f;
+#pragma unroll
+          for (int g = 0; g < 8; ++g) {
+            const float4 qv = q4[g];
+            const float t0 = y[4 * g] * qv.x, t1 = y[4 * g + 1] * qv.y, t2 = y[4 * g + 2] * qv.z, t3 = y[4 * g + 3] * qv.w;
+            if (4 * g + 3 < bnd) {
+              acc_lo += (t0 + t1) + (t2 + t3);
+            } else if (4 * g >= bnd) {
+              acc_hi += (t0 + t1) + (t2 + t3);
+            } else {
+              acc_lo += (4 * g < bnd ? t0 : 0.f) + (4 * g + 1 < bnd ? t1 : 0.f) + (4 * g + 2 < bnd ? t2 : 0.f);
+              acc_hi += (4 * g < bnd ? 0.f : t0) + (4 * g + 1 < bnd ? 0.f : t1) + (4 * g + 2 < bnd ? 0.f : t2) + t3;
+            }
+          }
+          dot_a += acc_lo;
+          dot_b += acc_hi;
+        }
         if (store_bf16) {
           // stage this warp's 32 rows x 32 bf16 in the TMA SWIZZLE_64B layout (16-byte chunk index XOR
           // ((row >> 1) & 3)): conflict-free 16-byte shared stores, then one TMA store writes full lines.
@@ -365,6 +443,11 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
           for (int g = 0; g < 8; ++g)
             if (n0 + c * 32 + g * 4 < p.f32_cols) dst[g] = make_float4(y[g * 4], y[g * 4 + 1], y[g * 4 + 2], y[g * 4 + 3]);
         }
+      }
+      if (dots && row_ok) {
+        if (dot_ha < p.heads) atomicAdd(p.dot_out + static_cast<size_t>(dot_ha) * p.dot_ld + row, static_cast<double>(dot_a * p.dot_scale));
+        if (dot_bound < 128 && dot_ha + 1 < p.heads)
+          atomicAdd(p.dot_out + static_cast<size_t>(dot_ha + 1) * p.dot_ld + row, static_cast<double>(dot_b * p.dot_scale));
       }
       }
       if (++as == kAccStages) { as = 0; aphase ^= 1; }

@@ -49,9 +49,16 @@ struct GemmParams {
   const int32_t* tile_seg_ptr;  // [2 * m_tiles]: (lo, hi) index range into segs per tile
   const PoolSeg* segs;
   // optional per-row weights (attention pooling): weighted sums  sum w x | sum w x^2 ; [heads, m_rows]
-  const float* row_weight;
+  const float* row_weight;   // [heads, weight_ld] softmax weights of the rows (null: plain sums)
   int32_t heads;        // number of heads; column n belongs to head n / head_width
   int32_t head_width;
+  int32_t weight_ld = 0;
+  // fused attention scores (last key layer): dot_out[h][row] += dot_scale * sum_{n in head h} y[row, n] * dot_q[n]
+  // (fp64 atomics: order-independent at fp32 precision); heads / head_width above give the column -> head map
+  const float* dot_q = nullptr;   // [N_alloc], zero beyond the key width
+  double* dot_out = nullptr;      // [heads][dot_ld], zeroed by the caller
+  int32_t dot_ld = 0;
+  float dot_scale = 1.f;
 };
 
 struct GemmPlan {
@@ -173,6 +180,9 @@ cudaError_t launch_att_scores(const void* key, int dtype, int ldk, int64_t rows,
 // Per (utt, head): softmax over the valid rows, in place -> weights.
 cudaError_t launch_att_softmax(float* scores, int64_t rows, const int32_t* cu, int context, int n, int heads,
                                cudaStream_t stream);
+// Same from fp64 score accumulators (fused key-layer epilogue) into the fp32 weight buffer.
+cudaError_t launch_att_softmax_f64(const double* acc, float* weights, int64_t rows, const int32_t* cu, int context, int n,
+                                   int heads, cudaStream_t stream);
 cudaError_t launch_gather_att_weights(const float* w, int64_t rows, const int32_t* cu, int context, int heads, int n,
                                       const int64_t* dst_off, float* dst, cudaStream_t stream);
 

@@ -441,17 +441,20 @@ __global__ void att_scores_kernel(const T* __restrict__ key, int ldk, int64_t ro
   }
 }
 
-// In-place softmax over the valid rows of each (utterance, head) (model/pooling.py:197).
-__global__ void att_softmax_kernel(float* __restrict__ scores, int64_t rows, const int32_t* __restrict__ cu,
-                                   int context) {
+// Softmax over the valid rows of each (utterance, head) (model/pooling.py:197): fp32 in place, or from the fp64 score
+// accumulators of the fused key-layer epilogue (src != null) into the fp32 weight buffer.
+template <typename S>
+__global__ void att_softmax_kernel(const S* __restrict__ src, float* __restrict__ scores, int64_t rows,
+                                   const int32_t* __restrict__ cu, int context) {
   __shared__ float sh[32];
   const int u = blockIdx.x, h = blockIdx.y;
   const int32_t cs = cu[u];
   const int32_t len = cu[u + 1] - cs - context;
+  const S* in = src + static_cast<int64_t>(h) * rows + cs;
   float* s = scores + static_cast<int64_t>(h) * rows + cs;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
   float m = -FLT_MAX;
-  for (int i = threadIdx.x; i < len; i += blockDim.x) m = fmaxf(m, s[i]);
+  for (int i = threadIdx.x; i < len; i += blockDim.x) m = fmaxf(m, static_cast<float>(in[i]));
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
   if (lane == 0) sh[wid] = m;
@@ -461,7 +464,7 @@ __global__ void att_softmax_kernel(float* __restrict__ scores, int64_t rows, con
   __syncthreads();
   float z = 0.f;
   for (int i = threadIdx.x; i < len; i += blockDim.x) {
-    const float e = expf(s[i] - m);
+    const float e = expf(static_cast<float>(in[i]) - m);
     s[i] = e;
     z += e;
   }
@@ -649,7 +652,14 @@ cudaError_t launch_att_scores(const void* key, int dtype, int ldk, int64_t rows,
 cudaError_t launch_att_softmax(float* scores, int64_t rows, const int32_t* cu, int context, int n, int heads,
                                cudaStream_t stream) {
   if (n <= 0) return cudaSuccess;
-  att_softmax_kernel<<<dim3(n, heads), 256, 0, stream>>>(scores, rows, cu, context);
+  att_softmax_kernel<float><<<dim3(n, heads), 256, 0, stream>>>(scores, scores, rows, cu, context);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_att_softmax_f64(const double* acc, float* weights, int64_t rows, const int32_t* cu, int context, int n,
+                                   int heads, cudaStream_t stream) {
+  if (n <= 0) return cudaSuccess;
+  att_softmax_kernel<double><<<dim3(n, heads), 256, 0, stream>>>(acc, weights, rows, cu, context);
   return cudaGetLastError();
 }
 
