@@ -341,7 +341,14 @@ static int build_plan(xv_ctx* c) {
   for (size_t i = 0; i < c->frame_layers.size(); ++i) {
     Layer& l = c->frame_layers[i];
     l.n_alloc = round_up(l.cout, kBN);
-    if (l.in_buf < 0) {               // reads the pre-spliced feature rows
+    if (l.in_buf < 0 && !c->resnet && l.taps > 1) {
+      // first TDNN layer: the features are cast to bf16 rows padded to a multiple of 64 channels and the context is
+      // spliced by the TMA row coordinate like every other layer (K = taps * 64 for the 23..64-dim front ends); the
+      // im2col rows are never materialised
+      l.a_cin = round_up(l.cin, kBK);
+      l.a_taps = l.taps;
+      l.kpad = l.a_taps * l.a_cin;
+    } else if (l.in_buf < 0) {        // reads rows prepared by the caller (ResNet tail: conv5 over flattened F' x C)
       l.kpad = round_up(l.taps * l.cin, kBK);
       l.a_cin = l.kpad;
       l.a_taps = 1;

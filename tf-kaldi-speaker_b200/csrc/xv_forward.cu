@@ -265,7 +265,7 @@ int run_job(xv_ctx* c, const char* node_name, bool pipelined_h2d, float* frames_
     if ((rc = ensure(c, &c->frame_out[l], static_cast<size_t>(rows_alloc) * w * esz, true)) != XV_OK) return rc;
   }
   const Layer& l0 = c->frame_layers[0];
-  if (c->bf16 && !c->resnet && (rc = ensure(c, &c->a1, static_cast<size_t>(rows_alloc) * l0.kpad * 2, true)) != XV_OK) return rc;
+  if (c->bf16 && !c->resnet && (rc = ensure(c, &c->a1, static_cast<size_t>(rows_alloc) * l0.a_cin * 2, true)) != XV_OK) return rc;
   if (pipelined_h2d)
     for (int s = 0; s < 2; ++s)
       if ((rc = ensure(c, &c->d_feat_ring[s], static_cast<size_t>(max_in_rows) * c->dim * 4)) != XV_OK) return rc;
@@ -352,7 +352,11 @@ int run_job(xv_ctx* c, const char* node_name, bool pipelined_h2d, float* frames_
       if ((rc = resnet_run_batch(c, feats_b, nb, b.t_in, &a_first)) != XV_OK) return rc;
     } else if (c->bf16) {
       ProfScope ps(c, "splice_cast");
-      e = launch_splice_cast(feats_b, b.rows, c->dim, l0.taps, l0.dil, static_cast<__nv_bfloat16*>(c->a1.p), l0.kpad, c->stream);
+      // fp32 -> bf16 rows padded to a_cin channels (taps > 1: the context splice happens in tdnn1's TMA loads)
+      if (l0.a_taps > 1)
+        e = launch_splice_cast(feats_b, b.rows, c->dim, 1, 1, static_cast<__nv_bfloat16*>(c->a1.p), l0.a_cin, c->stream);
+      else
+        e = launch_splice_cast(feats_b, b.rows, c->dim, l0.taps, l0.dil, static_cast<__nv_bfloat16*>(c->a1.p), l0.kpad, c->stream);
       if (e != cudaSuccess) return cuda_fail(c, e, "splice_cast launch");
       a_first = c->a1.p;
     } else {
