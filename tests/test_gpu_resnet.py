@@ -61,6 +61,10 @@ def _run_conv(eng, x, kernel, st, sf, scale, shift, slope, residual):
     (1, 400, 5, 512, 512, 3, 1, 1, True),      # stage-4 shape (tile = 5 bins x 25 steps = 125 rows)
     (5, 33, 8, 128, 256, 3, 1, 1, True),       # F = 8 (64-dim fbank, stage 4 of F=64)
     (40, 64, 20, 128, 128, 3, 1, 1, False),    # more tiles than SMs
+    (2, 30, 64, 64, 64, 3, 1, 1, True),        # halo tile 16 bins x 7 steps (F = 64 stage 1), ragged last time tile
+    (3, 23, 32, 128, 128, 3, 1, 1, True),      # halo tile, two channel blocks per tap (F = 64 stage 2)
+    (1, 5, 16, 64, 128, 3, 1, 1, False),       # halo tile taller than the utterance
+    (150, 21, 40, 64, 64, 3, 1, 1, True),      # halo tile 40 bins x 3 steps, several tiles per CTA (ring wrap-around)
 ])
 def test_conv2d_implicit_gemm_matches_fp64(eng, nb, t, f, cin, cout, k, st, sf, res):
     from oracle import numpy_ref

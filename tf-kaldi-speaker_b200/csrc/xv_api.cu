@@ -545,6 +545,7 @@ int xv_create(int device, const char* config_json, xv_ctx** out) {
   if (c->resnet && !c->cfg.has("batch_frames")) c->batch_frames = 16384;   // keeps a stage's activations L2-sized
   const char* ge = gemm_init();
   if (!ge && c->resnet) ge = conv_gemm_init();
+  if (!ge && c->resnet) ge = conv_halo_init();
   if (ge) {
     fail(nullptr, XV_ECUDA, "%s", ge);
     delete c;

@@ -95,13 +95,23 @@ struct ConvGemmParams {
   const __nv_bfloat16* residual;   // [n_utts][t_alloc_res][f_out][cout] added before the activation, or null
   int32_t t_alloc_res;
   int32_t cout;
+  // halo mode (xv_conv_halo_sm100.cu; 3x3 stride-1 layers with 64 / 128 input channels): the tile is tb time steps x
+  // fbh = fb + 2 columns INCLUDING the frequency halo, so that every tap is the same shared-memory box shifted by a
+  // constant number of rows; columns fb, fb+1 of a tile row are junk and are dropped by the epilogue
+  int32_t fbh = 0;
+  int32_t debug = 0;          // XV_CONV_HALO_DEBUG (timing experiments only): 1 no activation loads, 2 no epilogue stores, 4 no shortcut
+  int32_t a_stages = 0, a_stage_bytes = 0;   // halo ring: stages (2..8) of round_up((tb+2)*fbh*128, 1024) bytes
 };
 struct ConvGemmPlan {
   CUtensorMap tm_a, tm_b, tm_out;
   ConvGemmParams p;
   int bn;                    // 64 | 128 | 256
+  uint32_t halo_smem = 0;    // dynamic shared memory of the halo kernel (conv_halo_plan)
 };
 const char* conv_gemm_init();
+const char* conv_halo_init();
+bool conv_halo_plan(ConvGemmParams* p, uint32_t* smem_bytes);   // needs fb, tb, fbh, kb_per_tap
+cudaError_t launch_conv_halo(const ConvGemmPlan& plan, int sm_count, cudaStream_t stream);   // plan.tm_a = halo box map
 cudaError_t launch_conv_gemm(const ConvGemmPlan& plan, int sm_count, cudaStream_t stream);
 // rank-N bf16 tensor map (dims/strides innermost first; strides[0] is implied = 2 bytes).
 const char* make_tmap_bf16_nd(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,

@@ -4,6 +4,7 @@
 // fp32 convolution (validation mode).  conv5 / dense1 / dense2 / pooling / tdnn6 / tdnn7 are ordinary frame and
 // segment layers and live in xv_api.cu / xv_forward.cu.
 #include <math.h>
+#include <stdlib.h>
 
 #include <algorithm>
 
@@ -398,6 +399,25 @@ void pick_tile(int t_out, int f_out, int* fb_out, int* tb_out) {
   *fb_out = best_fb;
   *tb_out = best_tb;
 }
+
+// Halo-tile geometry (xv_conv_halo_sm100.cu): tile rows live on a (fb + 2)-wide grid, tb = 128 / (fb + 2) time steps;
+// the pair with the most useful rows per 128-row MMA wins (ties: wider fb = fewer junk columns re-read).
+bool pick_halo_tile(int t_out, int f_out, int* fb_out, int* tb_out) {
+  int best = 0;
+  for (int fb = 1; fb <= f_out && fb + 2 <= 128; ++fb) {
+    if (f_out % fb) continue;
+    const int tb = 128 / (fb + 2);
+    if (tb < 1) continue;
+    if (fb * tb > best || (fb * tb == best && fb > *fb_out)) { best = fb * tb; *fb_out = fb; *tb_out = tb; }
+  }
+  (void)t_out;
+  return best >= 64;        // below half-filled MMAs the generic kernel is the better one
+}
+
+int halo_env(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v && *v ? atoi(v) : dflt;
+}
 }  // namespace
 
 // One implicit-GEMM convolution launch: builds the 5-D input map, the 4-D output map and the tap table.
@@ -405,6 +425,7 @@ struct ConvBf16Args {
   const void* in; int nb, t_in, ta_in, f_in, cin;
   int kh, kw, st, sf, cout, bn_tile;
   const CUtensorMap* tm_b;
+  const void* wt;             // the weights tm_b describes ([cout][kh*kw*cin] bf16): the halo kernel maps them in 64-row slabs
   const float *scale, *shift, *slope; bool plain_relu;
   const void* res; int ta_res;
   void* out; int ta_out;
@@ -421,12 +442,27 @@ static int conv_bf16_launch(xv_ctx* c, const ConvBf16Args& a, const char* name) 
   plan.bn = a.bn_tile;
   ConvGemmParams& p = plan.p;
   p.n_utts = a.nb; p.t_out = t_out; p.f_out = f_out;
-  pick_tile(t_out, f_out, &p.fb, &p.tb);
+  // 3x3 stride-1 layers with <= 128-wide output tiles: activation tile + halo loaded once per channel block
+  // (Cin = 128 fits as well, but with 64-column MMAs it only ties the generic kernel: XV_CONV_HALO=2 forces it)
+  const int halo_mode = halo_env("XV_CONV_HALO", 1);
+  bool halo = a.kh == 3 && a.kw == 3 && a.st == 1 && a.sf == 1 && a.cout % 64 == 0 &&
+              ((halo_mode == 1 && a.cin == 64) || (halo_mode == 2 && a.cin <= 128));
+  if (halo) halo = pick_halo_tile(t_out, f_out, &p.fb, &p.tb);
+  if (halo) {
+    p.fbh = p.fb + 2;
+    p.kb_per_tap = a.cin / kBK;
+    halo = conv_halo_plan(&p, &plan.halo_smem);
+    p.debug = halo_env("XV_CONV_HALO_DEBUG", 0);
+  }
+  if (!halo) {
+    p.fbh = 0;
+    pick_tile(t_out, f_out, &p.fb, &p.tb);
+  }
   p.tiles_f = f_out / p.fb;
   p.tiles_t = (t_out + p.tb - 1) / p.tb;
   p.tile_rows = p.fb * p.tb;
   p.m_tiles = a.nb * p.tiles_t * p.tiles_f;
-  p.n_tiles = a.cout / a.bn_tile;
+  p.n_tiles = a.cout / (halo ? 64 : a.bn_tile);
   p.taps = a.kh * a.kw;
   p.kb_per_tap = a.cin / kBK;
   p.cin = a.cin;
@@ -449,7 +485,8 @@ static int conv_bf16_launch(xv_ctx* c, const ConvBf16Args& a, const char* name) 
                               static_cast<uint64_t>(a.st), static_cast<uint64_t>(a.st == 2 ? a.ta_in / 2 : a.t_in),
                               static_cast<uint64_t>(a.nb)};
   const uint64_t str_a[5] = {2, a.sf * cb, a.f_in * cb, a.st * a.f_in * cb, static_cast<uint64_t>(a.ta_in) * a.f_in * cb};
-  const uint32_t box_a[5] = {static_cast<uint32_t>(kBK), static_cast<uint32_t>(p.fb), 1, static_cast<uint32_t>(p.tb), 1};
+  const uint32_t box_a[5] = {static_cast<uint32_t>(kBK), static_cast<uint32_t>(halo ? p.fbh : p.fb), 1,
+                             static_cast<uint32_t>(halo ? p.tb + 2 : p.tb), 1};
   const char* err = make_tmap_bf16_nd(&plan.tm_a, a.in, 5, dims_a, str_a, box_a, 128);
   const uint64_t co = static_cast<uint64_t>(a.cout) * 2;
   const uint64_t dims_o[4] = {static_cast<uint64_t>(a.cout), static_cast<uint64_t>(f_out), static_cast<uint64_t>(t_out),
@@ -458,8 +495,14 @@ static int conv_bf16_launch(xv_ctx* c, const ConvBf16Args& a, const char* name) 
   const uint32_t box_o[4] = {32, static_cast<uint32_t>(p.fb), static_cast<uint32_t>(p.tb), 1};
   if (!err) err = make_tmap_bf16_nd(&plan.tm_out, a.out, 4, dims_o, str_o, box_o, 64);
   if (err) return fail(c, XV_ECUDA, "%s (layer %s)", err, name);
-  plan.tm_b = *a.tm_b;
-  cudaError_t e = launch_conv_gemm(plan, c->sm_count, c->stream);
+  if (halo) {
+    const int K = a.kh * a.kw * a.cin;
+    const char* be = make_tmap_bf16_2d(&plan.tm_b, a.wt, K, a.cout, static_cast<uint64_t>(K) * 2, kBK, 64);
+    if (be) return fail(c, XV_ECUDA, "%s (layer %s)", be, name);
+  } else {
+    plan.tm_b = *a.tm_b;
+  }
+  cudaError_t e = halo ? launch_conv_halo(plan, c->sm_count, c->stream) : launch_conv_gemm(plan, c->sm_count, c->stream);
   if (e != cudaSuccess) return cuda_fail(c, e, "conv GEMM launch");
   return XV_OK;
 }
@@ -535,7 +578,7 @@ int resnet_run_batch(xv_ctx* c, const float* feats, int nb, int t, const void** 
     if (c->bf16) {
       ConvBf16Args ca;
       ca.in = slot_ptr(l.in_slot); ca.nb = nb; ca.t_in = t_in; ca.ta_in = g[l.in_slot].t_alloc; ca.f_in = f_in; ca.cin = l.cin;
-      ca.kh = l.kh; ca.kw = l.kw; ca.st = l.st; ca.sf = l.sf; ca.cout = l.cout; ca.bn_tile = l.bn_tile; ca.tm_b = &l.tm_b;
+      ca.kh = l.kh; ca.kw = l.kw; ca.st = l.st; ca.sf = l.sf; ca.cout = l.cout; ca.bn_tile = l.bn_tile; ca.tm_b = &l.tm_b; ca.wt = l.wt.p;
       ca.scale = static_cast<const float*>(l.scale.p); ca.shift = static_cast<const float*>(l.shift.p);
       ca.slope = static_cast<const float*>(l.slope.p); ca.plain_relu = l.plain_relu;
       ca.res = l.res_slot >= 0 ? slot_ptr(l.res_slot) : nullptr;
@@ -580,6 +623,7 @@ extern "C" int xv_conv2d_bf16_async(xv_ctx* c, const void* x_dev, int32_t nb, in
     return fail(c, XV_EINVAL, "xv_conv2d_bf16_async: strides must be 1 or 2 (time stride 2 needs an even T)");
   cudaSetDevice(c->device);
   const char* ge = conv_gemm_init();
+  if (!ge) ge = conv_halo_init();
   if (ge) return fail(c, XV_ECUDA, "%s", ge);
   const int bn_tile = cout % 256 == 0 ? 256 : (cout % 128 == 0 ? 128 : 64);
   const int K = kh * kw * cin;
@@ -588,7 +632,7 @@ extern "C" int xv_conv2d_bf16_async(xv_ctx* c, const void* x_dev, int32_t nb, in
   if (e) return fail(c, XV_ECUDA, "%s", e);
   ConvBf16Args a;
   a.in = x_dev; a.nb = nb; a.t_in = t; a.ta_in = t; a.f_in = f; a.cin = cin;
-  a.kh = kh; a.kw = kw; a.st = st; a.sf = sf; a.cout = cout; a.bn_tile = bn_tile; a.tm_b = &tm_b;
+  a.kh = kh; a.kw = kw; a.st = st; a.sf = sf; a.cout = cout; a.bn_tile = bn_tile; a.tm_b = &tm_b; a.wt = wt_dev;
   a.scale = scale_dev; a.shift = shift_dev; a.slope = slope_dev; a.plain_relu = false;
   const int t_out = (t + st - 1) / st;
   a.res = residual_dev; a.ta_res = t_out; a.out = out_dev; a.ta_out = t_out;
