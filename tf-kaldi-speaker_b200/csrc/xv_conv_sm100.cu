@@ -125,28 +125,32 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = ptx::make_idesc_bf16(kBM, BN);
-      uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
+    // warp-uniform loop, one elected lane issues (see xv_gemm_sm100.cu: a lone lane spends ~450 clk per round in
+    // its own instruction stream, more than the 270 clk four 128-column MMAs execute in)
+    constexpr uint32_t idesc = ptx::make_idesc_bf16(kBM, BN);
+    const uint32_t ring_lo = ptx::sw128_desc_lo(ptx::smem_u32(ring));
+    uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
+      ptx::tc_fence_after();
+      const uint32_t tmem_d = tmem_base + as * BN;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        ptx::mbar_wait(&full_bar[stage], phase);
         ptx::tc_fence_after();
-        const uint32_t tmem_d = tmem_base + as * BN;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          ptx::mbar_wait(&full_bar[stage], phase);
-          ptx::tc_fence_after();
-          const uint32_t a_addr = ptx::smem_u32(ring + stage * S::kStage);
-          const uint64_t adesc = ptx::make_kmajor_sw128_desc(a_addr);
-          const uint64_t bdesc = ptx::make_kmajor_sw128_desc(a_addr + kConvABytes);
+        if (ptx::elect_one()) {
+          const uint32_t a_lo = ring_lo + stage * (S::kStage >> 4);
+          const uint32_t b_lo = a_lo + (kConvABytes >> 4);
 #pragma unroll
           for (int k = 0; k < kBK / kUK; ++k)
-            ptx::umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            ptx::umma_bf16_lo(tmem_d, a_lo + 2 * k, b_lo + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
           ptx::umma_commit(&empty_bar[stage]);
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        ptx::umma_commit(&tfull_bar[as]);
-        if (++as == kAccStages) { as = 0; aphase ^= 1; }
+        __syncwarp();
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
+      if (ptx::elect_one()) ptx::umma_commit(&tfull_bar[as]);
+      __syncwarp();
+      if (++as == kAccStages) { as = 0; aphase ^= 1; }
     }
   } else {
     // ===================== epilogue (warps 2..9) =====================

@@ -32,14 +32,28 @@ namespace xv {
 
 namespace {
 
-constexpr int kEpiWarps = 8;
+// Epilogue warps: 4 TMEM lane quarters x kParts column parts.  The storing kernel runs 8 (each needs a 2 KB TMA store
+// staging buffer and shared memory is full).  The pooled kernel stores nothing and could run 16 (-DXV_POOL_EPI_WARPS=16);
+// measured, that is SLOWER (tdnn5: 11.6 -> 14.3 ms): the register cap drops to 96 and every warp repeats the per-tile
+// segment search for half as many columns.
+#ifndef XV_POOL_EPI_WARPS
+#define XV_POOL_EPI_WARPS 8
+#endif
+constexpr int kEpiWarpsStore = 8;
+template <bool kPool>
+struct EpiCfg {
+  static constexpr int kEpiWarps = kPool ? XV_POOL_EPI_WARPS : kEpiWarpsStore;
+  static constexpr int kParts = kEpiWarps / 4;
+  static constexpr int kChunksPerWarp = 8 / kParts;            // 32-column chunks of the 256-column tile per warp
+  static constexpr int kThreads = 64 + kEpiWarps * 32;
+};
 constexpr uint32_t kABytes = kBM * kBK * 2;                  // 16384
 constexpr uint32_t kBBytes = kBN * kBK * 2;                  // 32768
 constexpr uint32_t kStageBytes = kABytes + kBBytes;          // 49152
 constexpr uint32_t kRingBytes = kStages * kStageBytes;       // 196608
 constexpr uint32_t kEpiParamBytes = kAccStages * kBN * 16;   // (scale,shift) float2 + slope float + query float = 8192
 constexpr uint32_t kStoreStageBytes = 32 * 64;               // per warp: 32 rows x 32 bf16, SWIZZLE_64B
-constexpr uint32_t kEpiScratchBytes = kEpiWarps * kStoreStageBytes;
+constexpr uint32_t kEpiScratchBytes = kEpiWarpsStore * kStoreStageBytes;
 constexpr uint32_t kBarrierBytes = 256;
 constexpr uint32_t kTmemCols = 512;
 constexpr uint32_t kSmemBytes = 1024 /*alignment slack (normally unused: the array is declared __align__(1024))*/ + kRingBytes + kEpiParamBytes + kEpiScratchBytes + kBarrierBytes;
@@ -52,12 +66,15 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 }
 
 template <bool kPool>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __launch_bounds__(EpiCfg<kPool>::kThreads, 1)
 xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                     const __grid_constant__ CUtensorMap tm_out, const GemmParams p) {
   // 128-byte swizzle atoms need 1024-byte aligned stage buffers.  The pad is added as an OFFSET to the
   // __shared__ symbol (not via an integer round trip) so the compiler keeps the shared address space and emits
   // LDS/STS rather than generic loads in the epilogue.
+  constexpr int kEpiWarps = EpiCfg<kPool>::kEpiWarps;
+  constexpr int kParts = EpiCfg<kPool>::kParts;
+  constexpr int kChunksPerWarp = EpiCfg<kPool>::kChunksPerWarp;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* ring = smem;
@@ -124,38 +141,44 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = ptx::make_idesc_bf16(kBM, kBN);
-      uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);   // epilogue has drained this accumulator
+    // The whole warp walks the loop (barrier waits included) so that every operand is warp-uniform and the compiler
+    // issues UTCHMMA straight from uniform registers; one elected lane issues.  A lone lane under `if (lane == 0)`
+    // costs ~450 clk per (wait, 4 MMAs, commit) round in its own instruction stream -- 88% of the 512 clk the four
+    // MMAs execute in (tools/debug/umma_issue.cu) -- which leaves no slack to absorb a late TMA arrival.
+    constexpr uint32_t idesc = ptx::make_idesc_bf16(kBM, kBN);
+    const uint32_t ring_lo = ptx::sw128_desc_lo(ptx::smem_u32(ring));
+    uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);   // epilogue has drained this accumulator
+      ptx::tc_fence_after();
+      const uint32_t tmem_d = tmem_base + as * kBN;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        ptx::mbar_wait(&full_bar[stage], phase);     // TMA bytes have landed
         ptx::tc_fence_after();
-        const uint32_t tmem_d = tmem_base + as * kBN;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          ptx::mbar_wait(&full_bar[stage], phase);     // TMA bytes have landed
-          ptx::tc_fence_after();
-          const uint32_t a_addr = ptx::smem_u32(ring + stage * kStageBytes);
-          const uint64_t adesc = ptx::make_kmajor_sw128_desc(a_addr);
-          const uint64_t bdesc = ptx::make_kmajor_sw128_desc(a_addr + kABytes);
+        if (ptx::elect_one()) {
+          const uint32_t a_lo = ring_lo + stage * (kStageBytes >> 4);
+          const uint32_t b_lo = a_lo + (kABytes >> 4);
 #pragma unroll
           for (int k = 0; k < kBK / kUK; ++k) {
             // advance 16 elements (32 bytes) along K inside the 128-byte swizzle atom: +2 in the address field
-            ptx::umma_bf16(tmem_d, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            ptx::umma_bf16_lo(tmem_d, a_lo + 2 * k, b_lo + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
           }
           ptx::umma_commit(&empty_bar[stage]);          // frees the smem slot when these MMAs retire
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        ptx::umma_commit(&tfull_bar[as]);               // accumulator complete -> epilogue
-        if (++as == kAccStages) { as = 0; aphase ^= 1; }
+        __syncwarp();
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
+      if (ptx::elect_one()) ptx::umma_commit(&tfull_bar[as]);   // accumulator complete -> epilogue
+      __syncwarp();
+      if (++as == kAccStages) { as = 0; aphase ^= 1; }
     }
   } else {
     // ===================== epilogue (warps 2..9) =====================
     const uint32_t e = warp - 2;                 // 0..7
     const uint32_t q = warp & 3;                 // TMEM lane quarter this warp may access
-    const uint32_t half = e >> 2;                // which 128 of the tile's 256 columns
+    const uint32_t half = e >> 2;                // which column part of the tile's 256 columns
     const uint32_t etid = threadIdx.x - 64;      // 0..255
-    uint8_t* stage_buf = scratch + e * kStoreStageBytes;                       // bf16 store staging (non-pool)
+    uint8_t* stage_buf = scratch + (kPool ? 0 : e) * kStoreStageBytes;         // bf16 store staging (non-pool)
     const bool relu_only = p.relu_only != 0;
     const bool store_bf16 = !kPool && p.out_bf16 != nullptr;
     uint32_t as = 0, aphase = 0;
@@ -166,11 +189,13 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       // per-tile epilogue parameters -> smem (double buffered by accumulator stage)
       float2* ss = ep_ss + as * kBN;
       float* sl = ep_sl + as * kBN;
-      ss[etid] = make_float2(__ldg(p.scale + n0 + etid), __ldg(p.shift + n0 + etid));
-      sl[etid] = __ldg(p.slope + n0 + etid);
       float* sq = ep_sq + as * kBN;
-      if (!kPool && p.dot_out != nullptr) sq[etid] = __ldg(p.dot_q + n0 + etid);
-      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (etid < kBN) {
+        ss[etid] = make_float2(__ldg(p.scale + n0 + etid), __ldg(p.shift + n0 + etid));
+        sl[etid] = __ldg(p.slope + n0 + etid);
+        if (!kPool && p.dot_out != nullptr) sq[etid] = __ldg(p.dot_q + n0 + etid);
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after();
 
@@ -222,14 +247,14 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
         // atomics (order-independent at fp32 precision; no cancellation noise in E[x^2] - mean^2).
         const int rq = lane >> 2, cq = (lane & 3) * 2;
 #pragma unroll 1
-        for (int ci = 0; ci < 4; ++ci) {
-          const int c = half * 4 + ci;
+        for (int ci = 0; ci < kChunksPerWarp; ++ci) {
+          const int c = half * kChunksPerWarp + ci;
           uint32_t ra[16], rb[16];
           const uint32_t tcol = as * kBN + c * 32;
           ptx::tmem_ld_16x256b_x4(tmem_base + ((q * 32) << 16) + tcol, ra);
           ptx::tmem_ld_16x256b_x4(tmem_base + ((q * 32 + 16) << 16) + tcol, rb);
           ptx::tmem_ld_wait();
-          if (ci == 3) {
+          if (ci == kChunksPerWarp - 1) {
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
@@ -353,17 +378,17 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       int dot_ha = 0, dot_bound = 0;
       const bool dots = p.dot_out != nullptr;
       if (dots) {
-        const int half_base = n0 + half * 128;
+        const int half_base = n0 + half * (kBN / kParts);
         dot_ha = half_base / p.head_width;
         dot_bound = (dot_ha + 1) * p.head_width - half_base;
       }
 #pragma unroll 1
-      for (int ci = 0; ci < 4; ++ci) {
-        const int c = half * 4 + ci;             // 32-column chunk of the tile
+      for (int ci = 0; ci < kChunksPerWarp; ++ci) {
+        const int c = half * kChunksPerWarp + ci;   // 32-column chunk of the tile
         uint32_t r[32];
         ptx::tmem_ld_32x32(tmem_base + ((q * 32) << 16) + as * kBN + c * 32, r);
         ptx::tmem_ld_wait();
-        if (ci == 3) {
+        if (ci == kChunksPerWarp - 1) {
           // last TMEM read of this tile by this warp: hand the accumulator back to the MMA warp now
           ptx::tc_fence_before();
           __syncwarp();
@@ -446,7 +471,7 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       }
       if (dots && row_ok) {
         if (dot_ha < p.heads) atomicAdd(p.dot_out + static_cast<size_t>(dot_ha) * p.dot_ld + row, static_cast<double>(dot_a * p.dot_scale));
-        if (dot_bound < 128 && dot_ha + 1 < p.heads)
+        if (dot_bound < kBN / kParts && dot_ha + 1 < p.heads)
           atomicAdd(p.dot_out + static_cast<size_t>(dot_ha + 1) * p.dot_ld + row, static_cast<double>(dot_b * p.dot_scale));
       }
       }
@@ -540,9 +565,9 @@ cudaError_t launch_gemm(const GemmPlan& plan, int sm_count, cudaStream_t stream)
   if (tiles <= 0) return cudaSuccess;
   const int grid = tiles < sm_count ? tiles : sm_count;
   if (plan.pool) {
-    xv_tdnn_gemm_kernel<true><<<grid, kGemmThreads, kSmemBytes, stream>>>(plan.tm_a, plan.tm_b, plan.tm_out, plan.p);
+    xv_tdnn_gemm_kernel<true><<<grid, EpiCfg<true>::kThreads, kSmemBytes, stream>>>(plan.tm_a, plan.tm_b, plan.tm_out, plan.p);
   } else {
-    xv_tdnn_gemm_kernel<false><<<grid, kGemmThreads, kSmemBytes, stream>>>(plan.tm_a, plan.tm_b, plan.tm_out, plan.p);
+    xv_tdnn_gemm_kernel<false><<<grid, EpiCfg<false>::kThreads, kSmemBytes, stream>>>(plan.tm_a, plan.tm_b, plan.tm_out, plan.p);
   }
   return cudaGetLastError();
 }

@@ -107,20 +107,21 @@ xv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = ptx::make_idesc_bf16(128, 256) | (1u << 15) | (1u << 16);   // both operands MN-major
-      uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
-      for (int t = blockIdx.x; t < total; t += gridDim.x) {
-        const int split = t / mn_tiles;
-        const int64_t r_begin = static_cast<int64_t>(split) * p.rows_per_split;
-        const int64_t r_end = min(r_begin + p.rows_per_split, p.rows);
-        ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
+    // warp-uniform issue loop, one elected lane issues (see xv_gemm_sm100.cu)
+    constexpr uint32_t idesc = ptx::make_idesc_bf16(128, 256) | (1u << 15) | (1u << 16);   // both operands MN-major
+    uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
+    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+      const int split = t / mn_tiles;
+      const int64_t r_begin = static_cast<int64_t>(split) * p.rows_per_split;
+      const int64_t r_end = min(r_begin + p.rows_per_split, p.rows);
+      ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
+      ptx::tc_fence_after();
+      const uint32_t tmem_d = tmem_base + as * 256;
+      uint32_t first = 1;
+      for (int64_t r = r_begin; r < r_end; r += 64) {
+        ptx::mbar_wait(&full_bar[stage], phase);
         ptx::tc_fence_after();
-        const uint32_t tmem_d = tmem_base + as * 256;
-        uint32_t first = 1;
-        for (int64_t r = r_begin; r < r_end; r += 64) {
-          ptx::mbar_wait(&full_bar[stage], phase);
-          ptx::tc_fence_after();
+        if (ptx::elect_one()) {
           const uint32_t a_addr = ptx::smem_u32(ring + stage * kWgStage);
           const uint32_t b_addr = a_addr + kWgABytes;
 #pragma unroll
@@ -130,13 +131,15 @@ xv_wgrad_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant_
             const uint64_t bdesc = make_mnmajor_sw128_desc(b_addr + k * 2048, 8192, 1024);
             ptx::umma_bf16(tmem_d, adesc, bdesc, idesc, (first && k == 0) ? 0u : 1u);
           }
-          first = 0;
           ptx::umma_commit(&empty_bar[stage]);
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        ptx::umma_commit(&tfull_bar[as]);
-        if (++as == kAccStages) { as = 0; aphase ^= 1; }
+        __syncwarp();
+        first = 0;
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
+      if (ptx::elect_one()) ptx::umma_commit(&tfull_bar[as]);
+      __syncwarp();
+      if (++as == kAccStages) { as = 0; aphase ^= 1; }
     }
   } else {
     const uint32_t q = warp & 3;                     // TMEM lane quarter of this warp
