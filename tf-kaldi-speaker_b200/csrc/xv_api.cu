@@ -480,7 +480,7 @@ static int finalize_layer(xv_ctx* c, Layer& l) {
         for (int n = 0; n < l.cout; ++n) wt[static_cast<size_t>(n) * l.kpad + kk] = f32_to_bf16_rne(src[n]);
       }
     if ((rc = upload(c, &l.wt, wt.data(), wt.size() * 2)) != XV_OK) return rc;
-    const char* e = make_tmap_bf16_2d(&l.tm_b, l.wt.p, l.kpad, l.n_alloc, static_cast<uint64_t>(l.kpad) * 2, kBK, kBN);
+    const char* e = make_tmap_bf16_2d(&l.tm_b, l.wt.p, l.kpad, l.n_alloc, static_cast<uint64_t>(l.kpad) * 2, kBK, kBLoadRows);
     if (e) return fail(c, XV_ECUDA, "%s", e);
   }
   return XV_OK;

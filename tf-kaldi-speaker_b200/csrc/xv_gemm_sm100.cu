@@ -24,6 +24,7 @@
 // TMEM holds two 128x256 fp32 accumulators so the epilogue of tile i overlaps the MMAs of tile i+1; the
 // accumulator is handed back to the MMA warp as soon as the last tcgen05.ld of the tile has completed.
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "xv_internal.h"
 #include "xv_ptx.cuh"
@@ -49,6 +50,7 @@ struct EpiCfg {
 };
 constexpr uint32_t kABytes = kBM * kBK * 2;                  // 16384
 constexpr uint32_t kBBytes = kBN * kBK * 2;                  // 32768
+constexpr uint32_t kBHalfBytes = kBLoadRows * kBK * 2;       // 16384: one TMA box of the weight tile (xv_internal.h)
 constexpr uint32_t kStageBytes = kABytes + kBBytes;          // 49152
 constexpr uint32_t kRingBytes = kStages * kStageBytes;       // 196608
 constexpr uint32_t kEpiParamBytes = kAccStages * kBN * 16;   // (scale,shift) float2 + slope float + query float = 8192
@@ -91,6 +93,12 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
 
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = threadIdx.x & 31;
+  // Thread-block cluster of 1 (plain launch) or 2 CTAs.  A pair works on two row tiles of the SAME column tile: each
+  // CTA fetches one 128-row half of every weight tile and multicasts it into both shared memories, so the weights
+  // cross the L2 -> SM fabric once per pair (48 -> 32 KB per k-block and SM; the K = 512 layers are bound by that feed).
+  const uint32_t crank = ptx::cluster_ctarank();
+  const uint32_t csize = ptx::cluster_nctarank();
+  const uint16_t cmask = static_cast<uint16_t>((1u << csize) - 1u);
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&tm_a);
@@ -98,7 +106,7 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     if (!kPool && p.out_bf16 != nullptr) ptx::prefetch_tensormap(&tm_out);
     for (int s = 0; s < kStages; ++s) {
       ptx::mbar_init(&full_bar[s], 1);
-      ptx::mbar_init(&empty_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], csize);         // every CTA of the cluster retires its MMAs on this stage
     }
     for (int s = 0; s < kAccStages; ++s) {
       ptx::mbar_init(&tfull_bar[s], 1);
@@ -112,19 +120,25 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   }
   ptx::tc_fence_before();
   __syncthreads();
+  if (csize > 1) ptx::cluster_sync();               // the peer's barriers are initialised before anything targets them
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int total_tiles = p.m_tiles * p.n_tiles;
+  // work units: (group of csize consecutive row tiles, column tile); CTA `crank` takes row tile group*csize + crank.
+  // A row tile past the end (odd tile count) is a phantom: its loads are zero-filled, its epilogue only hands the
+  // accumulator back.
+  const int n_units = ((p.m_tiles + static_cast<int>(csize) - 1) / static_cast<int>(csize)) * p.n_tiles;
+  const int unit0 = blockIdx.x / csize;
+  const int unit_step = gridDim.x / csize;
   const int num_kb = p.taps * p.kb_per_tap;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const int m0 = (t / p.n_tiles) * kBM;
-        const int n0 = (t % p.n_tiles) * kBN;
+      for (int u = unit0; u < n_units; u += unit_step) {
+        const int m0 = ((u / p.n_tiles) * static_cast<int>(csize) + static_cast<int>(crank)) * kBM;
+        const int n0 = (u % p.n_tiles) * kBN;
         for (int tap = 0; tap < p.taps; ++tap) {
           const int row = m0 + tap * p.dilation;
           for (int cb = 0; cb < p.kb_per_tap; ++cb) {
@@ -133,7 +147,13 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
             uint8_t* sb = sa + kABytes;
             ptx::mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
             ptx::tma_load_2d(sa, &tm_a, &full_bar[stage], cb * kBK, row);
-            ptx::tma_load_2d(sb, &tm_b, &full_bar[stage], tap * p.cin + cb * kBK, n0);
+            const int kc = tap * p.cin + cb * kBK;
+            if (csize > 1) {
+              ptx::tma_load_2d_multicast(sb + crank * kBHalfBytes, &tm_b, &full_bar[stage], kc, n0 + static_cast<int>(crank) * kBLoadRows, cmask);
+            } else {
+              ptx::tma_load_2d(sb, &tm_b, &full_bar[stage], kc, n0);
+              ptx::tma_load_2d(sb + kBHalfBytes, &tm_b, &full_bar[stage], kc, n0 + kBLoadRows);
+            }
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         }
@@ -148,7 +168,7 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     constexpr uint32_t idesc = ptx::make_idesc_bf16(kBM, kBN);
     const uint32_t ring_lo = ptx::sw128_desc_lo(ptx::smem_u32(ring));
     uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+    for (int u = unit0; u < n_units; u += unit_step) {
       ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);   // epilogue has drained this accumulator
       ptx::tc_fence_after();
       const uint32_t tmem_d = tmem_base + as * kBN;
@@ -163,7 +183,9 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
             // advance 16 elements (32 bytes) along K inside the 128-byte swizzle atom: +2 in the address field
             ptx::umma_bf16_lo(tmem_d, a_lo + 2 * k, b_lo + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
           }
-          ptx::umma_commit(&empty_bar[stage]);          // frees the smem slot when these MMAs retire
+          // frees the smem slot (in every CTA of the cluster: the peer multicasts into it) when these MMAs retire
+          if (csize > 1) ptx::umma_commit_multicast(&empty_bar[stage], cmask);
+          else ptx::umma_commit(&empty_bar[stage]);
         }
         __syncwarp();
         if (++stage == kStages) { stage = 0; phase ^= 1; }
@@ -182,10 +204,19 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     const bool relu_only = p.relu_only != 0;
     const bool store_bf16 = !kPool && p.out_bf16 != nullptr;
     uint32_t as = 0, aphase = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-      const int mt = t / p.n_tiles;
+    for (int u = unit0; u < n_units; u += unit_step) {
+      const int mt = (u / p.n_tiles) * static_cast<int>(csize) + static_cast<int>(crank);
       const int m0 = mt * kBM;
-      const int n0 = (t % p.n_tiles) * kBN;
+      const int n0 = (u % p.n_tiles) * kBN;
+      if (mt >= p.m_tiles) {                       // phantom row tile of an odd pair: just recycle the accumulator
+        ptx::mbar_wait(&tfull_bar[as], aphase);
+        ptx::tc_fence_after();
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
+        if (++as == kAccStages) { as = 0; aphase ^= 1; }
+        continue;
+      }
       // per-tile epilogue parameters -> smem (double buffered by accumulator stage)
       float2* ss = ep_ss + as * kBN;
       float* sl = ep_sl + as * kBN;
@@ -482,6 +513,7 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
 
   ptx::tc_fence_before();
   __syncthreads();
+  if (csize > 1) ptx::cluster_sync();               // no CTA leaves while the peer may still signal its barriers
   if (warp == 1) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, kTmemCols);
@@ -560,16 +592,63 @@ const char* make_tmap_bf16_nd(CUtensorMap* out, const void* base, int rank, cons
   return nullptr;
 }
 
-cudaError_t launch_gemm(const GemmPlan& plan, int sm_count, cudaStream_t stream) {
-  const int tiles = plan.p.m_tiles * plan.p.n_tiles;
-  if (tiles <= 0) return cudaSuccess;
-  const int grid = tiles < sm_count ? tiles : sm_count;
-  if (plan.pool) {
-    xv_tdnn_gemm_kernel<true><<<grid, EpiCfg<true>::kThreads, kSmemBytes, stream>>>(plan.tm_a, plan.tm_b, plan.tm_out, plan.p);
-  } else {
-    xv_tdnn_gemm_kernel<false><<<grid, EpiCfg<false>::kThreads, kSmemBytes, stream>>>(plan.tm_a, plan.tm_b, plan.tm_out, plan.p);
+namespace {
+// Co-resident 2-CTA clusters of one kernel variant (one CTA per SM; a pair shares a TPC), -1 = not asked yet.
+template <bool kPool>
+int max_cluster_pairs() {
+  static int cached = -1;
+  if (cached >= 0) return cached;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2, 1, 1);
+  cfg.blockDim = dim3(EpiCfg<kPool>::kThreads, 1, 1);
+  cfg.dynamicSmemBytes = kSmemBytes;
+  cudaLaunchAttribute attr;
+  attr.id = cudaLaunchAttributeClusterDimension;
+  attr.val.clusterDim.x = 2; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+  cfg.attrs = &attr;
+  cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, xv_tdnn_gemm_kernel<kPool>, &cfg) != cudaSuccess) { cudaGetLastError(); n = 0; }
+  cached = n;
+  if (getenv("XV_GEMM_TRACE")) fprintf(stderr, "xv gemm: %d co-resident 2-CTA clusters (pool=%d)\n", n, int(kPool));
+  return cached;
+}
+
+template <bool kPool>
+cudaError_t launch_variant(const GemmPlan& plan, int sm_count, cudaStream_t stream) {
+  const GemmParams& p = plan.p;
+  // cluster pairs (weight tiles multicast) when the pairs cover (nearly) the whole chip; XV_GEMM_CLUSTER=0 disables
+  static const int want = getenv("XV_GEMM_CLUSTER") ? atoi(getenv("XV_GEMM_CLUSTER")) : 1;
+  int pairs = 0;
+  // (the pooled kernel is bound by its epilogue; pairing only couples the jitter of two of them: 880 vs 890 TFLOP/s)
+  if (want && p.m_tiles >= 2 && (!kPool || want > 1)) {
+    pairs = max_cluster_pairs<kPool>();
+    if (2 * pairs < sm_count - 4) pairs = 0;
   }
-  return cudaGetLastError();
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(EpiCfg<kPool>::kThreads, 1, 1);
+  cfg.dynamicSmemBytes = kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr;
+  if (pairs > 0) {
+    const int units = ((p.m_tiles + 1) / 2) * p.n_tiles;
+    const int n = units < pairs ? units : pairs;
+    cfg.gridDim = dim3(2 * n, 1, 1);
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = 2; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = 1;
+  } else {
+    const int tiles = p.m_tiles * p.n_tiles;
+    cfg.gridDim = dim3(tiles < sm_count ? tiles : sm_count, 1, 1);
+  }
+  return cudaLaunchKernelEx(&cfg, xv_tdnn_gemm_kernel<kPool>, plan.tm_a, plan.tm_b, plan.tm_out, p);
+}
+}  // namespace
+
+cudaError_t launch_gemm(const GemmPlan& plan, int sm_count, cudaStream_t stream) {
+  if (plan.p.m_tiles * plan.p.n_tiles <= 0) return cudaSuccess;
+  return plan.pool ? launch_variant<true>(plan, sm_count, stream) : launch_variant<false>(plan, sm_count, stream);
 }
 
 }  // namespace xv

@@ -11,6 +11,7 @@ namespace xv {
 constexpr int kBM = 128;        // rows (frames) per tile  = UMMA M
 constexpr int kBN = 256;        // output channels per tile = UMMA N
 constexpr int kBK = 64;         // K per pipeline stage = one 128-byte swizzle atom of bf16
+constexpr int kBLoadRows = 128; // rows of one weight TMA box: a 256-column tile is two boxes (one per CTA of a cluster pair)
 constexpr int kUK = 16;         // UMMA K for 16-bit inputs
 constexpr int kStages = 4;      // TMA->MMA smem ring depth
 constexpr int kAccStages = 2;   // TMEM accumulator double buffer (2 x 256 columns = all 512)

@@ -196,7 +196,7 @@ int xv_gemm_bf16(xv_ctx* c, const void* a_dev, int64_t a_rows, int32_t cin, int3
   GemmPlan g;
   if (m_rows <= 0) return XV_OK;
   const char* err = make_tmap_bf16_2d(&g.tm_a, a_dev, cin, a_rows, static_cast<uint64_t>(cin) * 2, kBK, kBM);
-  if (!err) err = make_tmap_bf16_2d(&g.tm_b, wt_dev, kpad, n, static_cast<uint64_t>(kpad) * 2, kBK, kBN);
+  if (!err) err = make_tmap_bf16_2d(&g.tm_b, wt_dev, kpad, n, static_cast<uint64_t>(kpad) * 2, kBK, kBLoadRows);
   if (!err) err = make_tmap_bf16_2d(&g.tm_out, out_dev, n, m_rows, static_cast<uint64_t>(n) * 2, 32, 32, 64);
   if (err) return fail(c, XV_ECUDA, "%s", err);
   DevBuf slope;
@@ -241,7 +241,7 @@ int xv_gemm_bf16_async(xv_ctx* c, const void* a_dev, int64_t a_rows, int32_t cin
   GemmPlan g;
   if (m_rows <= 0) return XV_OK;
   const char* err = make_tmap_bf16_2d(&g.tm_a, a_dev, cin, a_rows, static_cast<uint64_t>(cin) * 2, kBK, kBM);
-  if (!err) err = make_tmap_bf16_2d(&g.tm_b, wt_dev, kpad, n, static_cast<uint64_t>(kpad) * 2, kBK, kBN);
+  if (!err) err = make_tmap_bf16_2d(&g.tm_b, wt_dev, kpad, n, static_cast<uint64_t>(kpad) * 2, kBK, kBLoadRows);
   if (!err) err = make_tmap_bf16_2d(&g.tm_out, out_dev, n, m_rows, static_cast<uint64_t>(n) * 2, 32, 32, 64);
   if (err) return fail(c, XV_ECUDA, "%s", err);
   GemmParams& p = g.p;

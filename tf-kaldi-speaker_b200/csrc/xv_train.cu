@@ -1062,11 +1062,11 @@ static int train_init(xv_ctx* c, int32_t num_speakers) {
       max_alloc = std::max(max_alloc, std::max(l.n_alloc, l.c_alloc));
       if ((rc = ensure(c, &l.wt_fwd, sizeof(__nv_bfloat16) * static_cast<size_t>(l.n_alloc) * l.ktotal)) != XV_OK) return rc;
       if ((rc = ensure(c, &l.bias_pad, sizeof(float) * l.n_alloc)) != XV_OK) return rc;
-      const char* e = make_tmap_bf16_2d(&l.tm_wf, l.wt_fwd.p, l.ktotal, l.n_alloc, static_cast<uint64_t>(l.ktotal) * 2, kBK, kBN);
+      const char* e = make_tmap_bf16_2d(&l.tm_wf, l.wt_fwd.p, l.ktotal, l.n_alloc, static_cast<uint64_t>(l.ktotal) * 2, kBK, kBLoadRows);
       if (!e && i > 0) {
         const size_t kd = static_cast<size_t>(l.taps) * l.ldb;
         if ((rc = ensure(c, &l.wt_dgrad, sizeof(__nv_bfloat16) * l.c_alloc * kd)) != XV_OK) return rc;
-        e = make_tmap_bf16_2d(&l.tm_wd, l.wt_dgrad.p, kd, l.c_alloc, kd * 2, kBK, kBN);
+        e = make_tmap_bf16_2d(&l.tm_wd, l.wt_dgrad.p, kd, l.c_alloc, kd * 2, kBK, kBLoadRows);
       }
       if (e) return fail(c, XV_ECUDA, "%s", e);
     }
