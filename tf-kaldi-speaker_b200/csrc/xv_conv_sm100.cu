@@ -16,6 +16,7 @@
 // half stage their 128 rows x 32 columns in one SWIZZLE_64B buffer and ONE 4-D TMA store writes the
 // (32 ch, fb, tb) box; rows beyond the utterance end are clipped by the tensor map.
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "xv_internal.h"
 #include "xv_ptx.cuh"
@@ -68,6 +69,11 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = threadIdx.x & 31;
   constexpr uint32_t kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;
+  // cluster of 1 or 2 CTAs; a pair takes two row tiles of one column tile and multicasts the halves of every weight
+  // tile to each other (see xv_gemm_sm100.cu)
+  const uint32_t crank = ptx::cluster_ctarank();
+  const uint32_t csize = ptx::cluster_nctarank();
+  const uint16_t cmask = static_cast<uint16_t>((1u << csize) - 1u);
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&tm_a);
@@ -75,7 +81,7 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     ptx::prefetch_tensormap(&tm_out);
     for (int s = 0; s < kStages; ++s) {
       ptx::mbar_init(&full_bar[s], 1);
-      ptx::mbar_init(&empty_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], csize);
     }
     for (int s = 0; s < kAccStages; ++s) {
       ptx::mbar_init(&tfull_bar[s], 1);
@@ -89,10 +95,13 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   }
   ptx::tc_fence_before();
   __syncthreads();
+  if (csize > 1) ptx::cluster_sync();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int total_tiles = p.m_tiles * p.n_tiles;
+  const int n_units = ((p.m_tiles + static_cast<int>(csize) - 1) / static_cast<int>(csize)) * p.n_tiles;
+  const int unit0 = blockIdx.x / csize;
+  const int unit_step = gridDim.x / csize;
   const int num_kb = p.taps * p.kb_per_tap;
   const int tiles_per_utt = p.tiles_t * p.tiles_f;
   const uint32_t a_bytes = static_cast<uint32_t>(p.tile_rows) * kBK * 2;
@@ -101,9 +110,9 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     // ===================== TMA producer =====================
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const int mt = t / p.n_tiles;
-        const int n0 = (t - mt * p.n_tiles) * BN;
+      for (int u = unit0; u < n_units; u += unit_step) {
+        const int mt = (u / p.n_tiles) * static_cast<int>(csize) + static_cast<int>(crank);
+        const int n0 = (u % p.n_tiles) * BN;
         const int b = mt / tiles_per_utt;
         const int rem = mt - b * tiles_per_utt;
         const int tt = rem / p.tiles_f;
@@ -117,7 +126,13 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
             uint8_t* sb = sa + kConvABytes;
             ptx::mbar_arrive_expect_tx(&full_bar[stage], a_bytes + S::kBBytes);
             ptx::tma_load_5d(sa, &tm_a, &full_bar[stage], tp.c0 + cb * kBK, fo0 + tp.c1, tp.c2, to0 + tp.c3, b);
-            ptx::tma_load_2d(sb, &tm_b, &full_bar[stage], tap * p.cin + cb * kBK, n0);
+            const int kc = tap * p.cin + cb * kBK;
+            if (csize > 1) {
+              ptx::tma_load_2d_multicast(sb + crank * (S::kBBytes / 2), &tm_b, &full_bar[stage], kc, n0 + static_cast<int>(crank) * (BN / 2), cmask);
+            } else {
+              ptx::tma_load_2d(sb, &tm_b, &full_bar[stage], kc, n0);
+              ptx::tma_load_2d(sb + S::kBBytes / 2, &tm_b, &full_bar[stage], kc, n0 + BN / 2);
+            }
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         }
@@ -130,7 +145,7 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     constexpr uint32_t idesc = ptx::make_idesc_bf16(kBM, BN);
     const uint32_t ring_lo = ptx::sw128_desc_lo(ptx::smem_u32(ring));
     uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+    for (int u = unit0; u < n_units; u += unit_step) {
       ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
       ptx::tc_fence_after();
       const uint32_t tmem_d = tmem_base + as * BN;
@@ -143,7 +158,8 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
 #pragma unroll
           for (int k = 0; k < kBK / kUK; ++k)
             ptx::umma_bf16_lo(tmem_d, a_lo + 2 * k, b_lo + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-          ptx::umma_commit(&empty_bar[stage]);
+          if (csize > 1) ptx::umma_commit_multicast(&empty_bar[stage], cmask);
+          else ptx::umma_commit(&empty_bar[stage]);
         }
         __syncwarp();
         if (++stage == kStages) { stage = 0; phase ^= 1; }
@@ -166,9 +182,18 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     const int t_l = r / p.fb;
     const int f_l = r - t_l * p.fb;
     uint32_t as = 0, aphase = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-      const int mt = t / p.n_tiles;
-      const int n0 = (t - mt * p.n_tiles) * BN;
+    for (int u = unit0; u < n_units; u += unit_step) {
+      const int mt = (u / p.n_tiles) * static_cast<int>(csize) + static_cast<int>(crank);
+      const int n0 = (u % p.n_tiles) * BN;
+      if (mt >= p.m_tiles) {                       // phantom row tile of an odd pair: just recycle the accumulator
+        ptx::mbar_wait(&tfull_bar[as], aphase);
+        ptx::tc_fence_after();
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
+        if (++as == kAccStages) { as = 0; aphase ^= 1; }
+        continue;
+      }
       const int b = mt / tiles_per_utt;
       const int rem = mt - b * tiles_per_utt;
       const int tt = rem / p.tiles_f;
@@ -257,6 +282,7 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
 
   ptx::tc_fence_before();
   __syncthreads();
+  if (csize > 1) ptx::cluster_sync();
   if (warp == 1) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, kTmemCols);
@@ -279,17 +305,62 @@ const char* conv_gemm_init() {
   return nullptr;
 }
 
+namespace {
+template <int BN>
+int conv_cluster_pairs() {
+  static int cached = -1;
+  if (cached >= 0) return cached;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2, 1, 1);
+  cfg.blockDim = dim3(kGemmThreads, 1, 1);
+  cfg.dynamicSmemBytes = ConvSmem<BN>::kTotal;
+  cudaLaunchAttribute attr;
+  attr.id = cudaLaunchAttributeClusterDimension;
+  attr.val.clusterDim.x = 2; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+  cfg.attrs = &attr;
+  cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, xv_conv_gemm_kernel<BN>, &cfg) != cudaSuccess) { cudaGetLastError(); n = 0; }
+  cached = n;
+  return cached;
+}
+
+template <int BN>
+cudaError_t launch_conv_variant(const ConvGemmPlan& plan, int sm_count, cudaStream_t stream) {
+  const ConvGemmParams& p = plan.p;
+  static const int want = getenv("XV_CONV_CLUSTER") ? atoi(getenv("XV_CONV_CLUSTER")) : 1;
+  int pairs = 0;
+  if (want && p.m_tiles >= 2) {
+    pairs = conv_cluster_pairs<BN>();
+    if (2 * pairs < sm_count - 4) pairs = 0;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(kGemmThreads, 1, 1);
+  cfg.dynamicSmemBytes = ConvSmem<BN>::kTotal;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr;
+  if (pairs > 0) {
+    const int units = ((p.m_tiles + 1) / 2) * p.n_tiles;
+    const int n = units < pairs ? units : pairs;
+    cfg.gridDim = dim3(2 * n, 1, 1);
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = 2; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = 1;
+  } else {
+    const int tiles = p.m_tiles * p.n_tiles;
+    cfg.gridDim = dim3(tiles < sm_count ? tiles : sm_count, 1, 1);
+  }
+  return cudaLaunchKernelEx(&cfg, xv_conv_gemm_kernel<BN>, plan.tm_a, plan.tm_b, plan.tm_out, p);
+}
+}  // namespace
+
+// plan.tm_b must map the weights in boxes of bn / 2 rows (one per CTA of a cluster pair).
 cudaError_t launch_conv_gemm(const ConvGemmPlan& plan, int sm_count, cudaStream_t stream) {
-  const int tiles = plan.p.m_tiles * plan.p.n_tiles;
-  if (tiles <= 0) return cudaSuccess;
-  const int grid = tiles < sm_count ? tiles : sm_count;
-  if (plan.bn == 64)
-    xv_conv_gemm_kernel<64><<<grid, kGemmThreads, ConvSmem<64>::kTotal, stream>>>(plan.tm_a, plan.tm_b, plan.tm_out, plan.p);
-  else if (plan.bn == 128)
-    xv_conv_gemm_kernel<128><<<grid, kGemmThreads, ConvSmem<128>::kTotal, stream>>>(plan.tm_a, plan.tm_b, plan.tm_out, plan.p);
-  else
-    xv_conv_gemm_kernel<256><<<grid, kGemmThreads, ConvSmem<256>::kTotal, stream>>>(plan.tm_a, plan.tm_b, plan.tm_out, plan.p);
-  return cudaGetLastError();
+  if (plan.p.m_tiles * plan.p.n_tiles <= 0) return cudaSuccess;
+  if (plan.bn == 64) return launch_conv_variant<64>(plan, sm_count, stream);
+  if (plan.bn == 128) return launch_conv_variant<128>(plan, sm_count, stream);
+  return launch_conv_variant<256>(plan, sm_count, stream);
 }
 
 }  // namespace xv

@@ -360,7 +360,7 @@ int resnet_finalize(xv_ctx* c) {
         for (int n = 0; n < l.cout; ++n) wt[static_cast<size_t>(n) * K + kk] = f32_to_bf16_rne(src[n]);
       }
       if ((rc = upload(c, &l.wt, wt.data(), wt.size() * 2)) != XV_OK) return rc;
-      const char* e = make_tmap_bf16_2d(&l.tm_b, l.wt.p, K, l.cout, static_cast<uint64_t>(K) * 2, kBK, l.bn_tile);
+      const char* e = make_tmap_bf16_2d(&l.tm_b, l.wt.p, K, l.cout, static_cast<uint64_t>(K) * 2, kBK, l.bn_tile / 2);
       if (e) return fail(c, XV_ECUDA, "%s", e);
     } else {
       if ((rc = upload(c, &l.w32, k->data.data(), sizeof(float) * K * l.cout)) != XV_OK) return rc;
@@ -628,7 +628,7 @@ extern "C" int xv_conv2d_bf16_async(xv_ctx* c, const void* x_dev, int32_t nb, in
   const int bn_tile = cout % 256 == 0 ? 256 : (cout % 128 == 0 ? 128 : 64);
   const int K = kh * kw * cin;
   CUtensorMap tm_b;
-  const char* e = make_tmap_bf16_2d(&tm_b, wt_dev, K, cout, static_cast<uint64_t>(K) * 2, kBK, bn_tile);
+  const char* e = make_tmap_bf16_2d(&tm_b, wt_dev, K, cout, static_cast<uint64_t>(K) * 2, kBK, bn_tile / 2);
   if (e) return fail(c, XV_ECUDA, "%s", e);
   ConvBf16Args a;
   a.in = x_dev; a.nb = nb; a.t_in = t; a.ta_in = t; a.f_in = f; a.cin = cin;
