@@ -117,13 +117,9 @@ xv_conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
         const int fo0 = (rem - tt * p.tiles_f) * p.fb;
         for (int cb = 0; cb < p.kb_per_tap; ++cb) {
           ptx::mbar_wait(&a_empty[sa], pa ^ 1);
-          if (p.debug & 1) {
-            ptx::mbar_arrive(&a_full[sa]);
-          } else {
           ptx::mbar_arrive_expect_tx(&a_full[sa], a_bytes);
           // halo box: channels [cb*64, +64), bins [fo0-1, fo0+fb+1), steps [to0-1, to0+tb+1) of utterance b
           ptx::tma_load_5d(a_ring + sa * p.a_stage_bytes, &tm_a, &a_full[sa], cb * kBK, fo0 - 1, 0, to0 - 1, b);
-          }
           if (++sa == static_cast<uint32_t>(n_stages)) { sa = 0; pa ^= 1; }
         }
       }
@@ -199,7 +195,7 @@ xv_conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       const int tt = rem / p.tiles_f;
       const int to0 = tt * p.tb;
       const int fo0 = (rem - tt * p.tiles_f) * p.fb;
-      if (p.residual != nullptr && mt < p.m_tiles && col_ok && (to0 + t_l) < p.t_out && !(p.debug & 4)) {
+      if (p.residual != nullptr && mt < p.m_tiles && col_ok && (to0 + t_l) < p.t_out) {
         const uint4* rp = reinterpret_cast<const uint4*>(
             p.residual + ((static_cast<size_t>(b) * p.t_alloc_res + to0 + t_l) * p.f_out + fo0 + f_l) * p.cout + ncol);
 #pragma unroll
@@ -246,12 +242,6 @@ xv_conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
           v1 = v1 >= 0.f ? v1 : v1 * ng.y;
         }
         o[j] = hpack2(v0, v1);
-      }
-      if (p.debug & 2) {
-        if (o[3] == 0x12345678u && o[7] == 0x9abcdef0u) ep_sl[lane] = 1.f;   // keeps the math alive
-#pragma unroll
-        for (int g = 0; g < 4; ++g) rv[g] = rn[g];
-        continue;
       }
       // the previous tile's bulk store must have finished reading the staging buffer
       if (issuer) ptx::tma_store_wait_read<0>();

@@ -100,7 +100,6 @@ struct ConvGemmParams {
   // fbh = fb + 2 columns INCLUDING the frequency halo, so that every tap is the same shared-memory box shifted by a
   // constant number of rows; columns fb, fb+1 of a tile row are junk and are dropped by the epilogue
   int32_t fbh = 0;
-  int32_t debug = 0;          // XV_CONV_HALO_DEBUG (timing experiments only): 1 no activation loads, 2 no epilogue stores, 4 no shortcut
   int32_t a_stages = 0, a_stage_bytes = 0;   // halo ring: stages (2..8) of round_up((tb+2)*fbh*128, 1024) bytes
 };
 struct ConvGemmPlan {

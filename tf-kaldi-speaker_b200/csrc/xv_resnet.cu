@@ -452,7 +452,6 @@ static int conv_bf16_launch(xv_ctx* c, const ConvBf16Args& a, const char* name) 
     p.fbh = p.fb + 2;
     p.kb_per_tap = a.cin / kBK;
     halo = conv_halo_plan(&p, &plan.halo_smem);
-    p.debug = halo_env("XV_CONV_HALO_DEBUG", 0);
   }
   if (!halo) {
     p.fbh = 0;

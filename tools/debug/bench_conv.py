@@ -37,8 +37,8 @@ def main():
     run(reps)
     ms, cnt = eng.profile_query("conv2d")
     flops = 2.0 * nb * t * f * 9 * cin * cout
-    print("shape nb=%d t=%d f=%d cin=%d cout=%d res=%d halo=%s dbg=%s: %.1f us/launch, %.0f TFLOP/s" % (
-        nb, t, f, cin, cout, res, os.environ.get("XV_CONV_HALO", "1"), os.environ.get("XV_CONV_HALO_DEBUG", "0"),
+    print("shape nb=%d t=%d f=%d cin=%d cout=%d res=%d halo=%s: %.1f us/launch, %.0f TFLOP/s" % (
+        nb, t, f, cin, cout, res, os.environ.get("XV_CONV_HALO", "1"),
         ms / cnt * 1e3, flops / (ms / cnt * 1e-3) / 1e12))
     eng.close()
 
