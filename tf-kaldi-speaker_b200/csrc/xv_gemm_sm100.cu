@@ -34,9 +34,10 @@ namespace xv {
 namespace {
 
 // Epilogue warps: 4 TMEM lane quarters x kParts column parts.  The storing kernel runs 8 (each needs a 2 KB TMA store
-// staging buffer and shared memory is full).  The pooled kernel stores nothing and could run 16 (-DXV_POOL_EPI_WARPS=16);
-// measured, that is SLOWER (tdnn5: 11.6 -> 14.3 ms): the register cap drops to 96 and every warp repeats the per-tile
-// segment search for half as many columns.
+// staging buffer and shared memory is full).  The pooled kernel stores nothing and can run 12 or 16
+// (-DXV_POOL_EPI_WARPS=...).  Measured on tdnn5: 12 warps = 8 warps (890 TFLOP/s either way), 16 warps slower
+// (11.6 -> 14.3 ms: the register cap drops to 96 and every warp repeats the per-tile segment search) -- the pooled
+// epilogue is bound by instruction throughput, not by the number of warps hiding latencies.
 #ifndef XV_POOL_EPI_WARPS
 #define XV_POOL_EPI_WARPS 8
 #endif
@@ -45,7 +46,7 @@ template <bool kPool>
 struct EpiCfg {
   static constexpr int kEpiWarps = kPool ? XV_POOL_EPI_WARPS : kEpiWarpsStore;
   static constexpr int kParts = kEpiWarps / 4;
-  static constexpr int kChunksPerWarp = 8 / kParts;            // 32-column chunks of the 256-column tile per warp
+  static constexpr int kChunksPerWarp = (8 + kParts - 1) / kParts;   // 32-column chunks of the 256-column tile per warp (the last part may get fewer)
   static constexpr int kThreads = 64 + kEpiWarps * 32;
 };
 constexpr uint32_t kABytes = kBM * kBK * 2;                  // 16384
@@ -277,15 +278,15 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
         // adjacent columns of either the sum (lane bit 4 = 0) or the sum of squares (bit 4 = 1) and issues two fp64
         // atomics (order-independent at fp32 precision; no cancellation noise in E[x^2] - mean^2).
         const int rq = lane >> 2, cq = (lane & 3) * 2;
+        const int c_end = min(8, static_cast<int>(half + 1) * kChunksPerWarp);
 #pragma unroll 1
-        for (int ci = 0; ci < kChunksPerWarp; ++ci) {
-          const int c = half * kChunksPerWarp + ci;
+        for (int c = half * kChunksPerWarp; c < c_end; ++c) {
           uint32_t ra[16], rb[16];
           const uint32_t tcol = as * kBN + c * 32;
           ptx::tmem_ld_16x256b_x4(tmem_base + ((q * 32) << 16) + tcol, ra);
           ptx::tmem_ld_16x256b_x4(tmem_base + ((q * 32 + 16) << 16) + tcol, rb);
           ptx::tmem_ld_wait();
-          if (ci == kChunksPerWarp - 1) {
+          if (c == c_end - 1) {
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
