@@ -26,6 +26,8 @@
 #include <stdio.h>
 #include <stdlib.h>
 
+#include <type_traits>
+
 #include "xv_internal.h"
 #include "xv_ptx.cuh"
 
@@ -66,6 +68,46 @@ static_assert((kRingBytes + kEpiParamBytes) % 1024 == 0, "store staging must sta
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// Pooled epilogue, last step: v[0..7] = this thread's partial column sums (column slot 2i + e = column 8i + 2(lane&3) + e
+// of a 32-column chunk), v[8..15] the partial sums of squares; the 8 lanes that share (lane & 3) hold different rows.
+// A 14-shuffle butterfly over lane bits 4, 3, 2 halves the live values each step; afterwards every lane owns two adjacent
+// columns of either the sum (lane bit 4 = 0) or the sum of squares (bit 4 = 1) and issues two fp64 atomics
+// (order-independent at fp32 precision; no cancellation noise in E[x^2] - mean^2).  acc_row = pool_acc + utt*2*pool_ld.
+__device__ __forceinline__ void pool_reduce_atomics(float (&v)[16], uint32_t lane, double* acc_row, int pool_ld, int col0) {
+  {
+    const bool up = (lane & 16) != 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float send = up ? v[j] : v[j + 8];
+      const float keep = up ? v[j + 8] : v[j];
+      v[j] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+  }
+  {
+    const bool up = (lane & 8) != 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float send = up ? v[j] : v[j + 4];
+      const float keep = up ? v[j + 4] : v[j];
+      v[j] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+  }
+  {
+    const bool up = (lane & 4) != 0;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const float send = up ? v[j] : v[j + 2];
+      const float keep = up ? v[j + 2] : v[j];
+      v[j] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    }
+  }
+  const int kind = (lane >> 4) & 1;                      // 0: sum, 1: sum of squares
+  const int ii = ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+  double* dst = acc_row + static_cast<size_t>(kind) * pool_ld + col0 + 8 * ii + (lane & 3) * 2;
+  atomicAdd(dst, static_cast<double>(v[0]));
+  atomicAdd(dst + 1, static_cast<double>(v[1]));
 }
 
 template <bool kPool>
@@ -128,9 +170,23 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   // work units: (group of csize consecutive row tiles, column tile); CTA `crank` takes row tile group*csize + crank.
   // A row tile past the end (odd tile count) is a phantom: its loads are zero-filled, its epilogue only hands the
   // accumulator back.
-  const int n_units = ((p.m_tiles + static_cast<int>(csize) - 1) / static_cast<int>(csize)) * p.n_tiles;
-  const int unit0 = blockIdx.x / csize;
-  const int unit_step = gridDim.x / csize;
+  // Column-stationary schedule (pooled layer, p.col_stationary): the grid is cpn x n_tiles CTAs, CTA b keeps column tile
+  // b % n_tiles for its whole life and walks a contiguous range of row tiles, so the pooling sums of an utterance stay in
+  // registers from tile to tile (see the epilogue); the n_tiles CTAs of one row range run in lock step and share every
+  // activation tile through the L2.
+  const bool col_stat = kPool && p.col_stationary != 0;
+  int unit0 = blockIdx.x / csize;
+  int unit_step = gridDim.x / csize;
+  int n_units = ((p.m_tiles + static_cast<int>(csize) - 1) / static_cast<int>(csize)) * p.n_tiles;
+  int nt_fixed = -1;
+  if (col_stat) {
+    const int cpn = gridDim.x / p.n_tiles;
+    const int j = blockIdx.x / p.n_tiles;
+    nt_fixed = blockIdx.x % p.n_tiles;
+    unit0 = static_cast<int>(static_cast<int64_t>(j) * p.m_tiles / cpn);
+    n_units = static_cast<int>(static_cast<int64_t>(j + 1) * p.m_tiles / cpn);
+    unit_step = 1;
+  }
   const int num_kb = p.taps * p.kb_per_tap;
 
   if (warp == 0) {
@@ -138,8 +194,8 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
       for (int u = unit0; u < n_units; u += unit_step) {
-        const int m0 = ((u / p.n_tiles) * static_cast<int>(csize) + static_cast<int>(crank)) * kBM;
-        const int n0 = (u % p.n_tiles) * kBN;
+        const int m0 = (col_stat ? u : (u / p.n_tiles) * static_cast<int>(csize) + static_cast<int>(crank)) * kBM;
+        const int n0 = (col_stat ? nt_fixed : u % p.n_tiles) * kBN;
         for (int tap = 0; tap < p.taps; ++tap) {
           const int row = m0 + tap * p.dilation;
           for (int cb = 0; cb < p.kb_per_tap; ++cb) {
@@ -205,10 +261,58 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     const bool relu_only = p.relu_only != 0;
     const bool store_bf16 = !kPool && p.out_bf16 != nullptr;
     uint32_t as = 0, aphase = 0;
+    // epilogue parameters of one column tile -> shared memory.  Pooled kernel: (scale, shift) are stored per COLUMN PAIR
+    // as (s0, s1, h0, h1) so that one LDS.128 yields the two packed-fp32 operands of an FFMA2.
+    auto fill_params = [&](float2* ss, float* sl, float* sq, int n0) {
+      if (etid < kBN) {
+        const float sc = __ldg(p.scale + n0 + etid), sh = __ldg(p.shift + n0 + etid);
+        if (kPool) {
+          float* ssf = reinterpret_cast<float*>(ss);
+          ssf[(etid >> 1) * 4 + (etid & 1)] = sc;
+          ssf[(etid >> 1) * 4 + 2 + (etid & 1)] = sh;
+        } else {
+          ss[etid] = make_float2(sc, sh);
+        }
+        sl[etid] = __ldg(p.slope + n0 + etid);
+        if (!kPool && p.dot_out != nullptr) sq[etid] = __ldg(p.dot_q + n0 + etid);
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");
+    };
+    if (col_stat) fill_params(ep_ss, ep_sl, ep_sq, nt_fixed * kBN);       // the column tile never changes
+    // pooling sums carried in registers from tile to tile (packed pairs: [chunk][i] = columns 8i + 2(lane&3) + {0,1})
+    uint64_t acc_s[kPool ? kChunksPerWarp : 1][4], acc_q[kPool ? kChunksPerWarp : 1][4];
+#pragma unroll
+    for (int ci = 0; ci < (kPool ? kChunksPerWarp : 1); ++ci)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { acc_s[ci][i] = 0ull; acc_q[ci][i] = 0ull; }
+    int held_utt = -1, held_n0 = 0, held_tiles = 0;
+    PoolSeg held_sg = {0, 0, 0, 0};                 // valid-row range of utterance held_utt
+    auto flush_held = [&]() {
+      if (kPool && held_utt >= 0) {
+        double* acc_row = p.pool_acc + static_cast<size_t>(held_utt) * 2 * p.pool_ld;
+#pragma unroll
+        for (int ci = 0; ci < kChunksPerWarp; ++ci) {
+          const int c = half * kChunksPerWarp + ci;
+          if (c < 8) {
+            float v[16];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              ptx::f2_unpack(acc_s[ci][i], v[2 * i], v[2 * i + 1]);
+              ptx::f2_unpack(acc_q[ci][i], v[8 + 2 * i], v[8 + 2 * i + 1]);
+              acc_s[ci][i] = 0ull;
+              acc_q[ci][i] = 0ull;
+            }
+            pool_reduce_atomics(v, lane, acc_row, p.pool_ld, held_n0 + c * 32);
+          }
+        }
+      }
+      held_utt = -1;
+      held_tiles = 0;
+    };
     for (int u = unit0; u < n_units; u += unit_step) {
-      const int mt = (u / p.n_tiles) * static_cast<int>(csize) + static_cast<int>(crank);
+      const int mt = col_stat ? u : (u / p.n_tiles) * static_cast<int>(csize) + static_cast<int>(crank);
       const int m0 = mt * kBM;
-      const int n0 = (u % p.n_tiles) * kBN;
+      const int n0 = (col_stat ? nt_fixed : u % p.n_tiles) * kBN;
       if (mt >= p.m_tiles) {                       // phantom row tile of an odd pair: just recycle the accumulator
         ptx::mbar_wait(&tfull_bar[as], aphase);
         ptx::tc_fence_after();
@@ -219,15 +323,10 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
         continue;
       }
       // per-tile epilogue parameters -> smem (double buffered by accumulator stage)
-      float2* ss = ep_ss + as * kBN;
-      float* sl = ep_sl + as * kBN;
-      float* sq = ep_sq + as * kBN;
-      if (etid < kBN) {
-        ss[etid] = make_float2(__ldg(p.scale + n0 + etid), __ldg(p.shift + n0 + etid));
-        sl[etid] = __ldg(p.slope + n0 + etid);
-        if (!kPool && p.dot_out != nullptr) sq[etid] = __ldg(p.dot_q + n0 + etid);
-      }
-      asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");
+      float2* ss = ep_ss + (col_stat ? 0 : as * kBN);
+      float* sl = ep_sl + (col_stat ? 0 : as * kBN);
+      float* sq = ep_sq + (col_stat ? 0 : as * kBN);
+      if (!col_stat) fill_params(ss, sl, sq, n0);
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after();
 
@@ -238,7 +337,12 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       int w_first = 0, w_last = -1;
       bool w_full = false;
       PoolSeg w_sg = {0, 0, 0, 0};
-      if (kPool) {
+      if (kPool && held_utt >= 0 && held_sg.r0 <= mw && held_sg.r1 >= mw + 32) {
+        // still inside the utterance whose sums this warp holds (segments are disjoint): no table lookups
+        w_first = w_last = 0;
+        w_sg = held_sg;
+        w_full = true;
+      } else if (kPool) {
         const int seg_lo = __ldg(p.tile_seg_ptr + 2 * mt);       // [lo, hi) utterance range intersecting this tile
         const int seg_hi = __ldg(p.tile_seg_ptr + 2 * mt + 1);
         for (int s = seg_lo; s < seg_hi; ++s) {
@@ -279,6 +383,93 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
         // atomics (order-independent at fp32 precision; no cancellation noise in E[x^2] - mean^2).
         const int rq = lane >> 2, cq = (lane & 3) * 2;
         const int c_end = min(8, static_cast<int>(half + 1) * kChunksPerWarp);
+        if (p.row_weight == nullptr) {
+          // ---- statistics pooling (unweighted).  The thread's 4 rows are added into register accumulators that live
+          // across tiles (same utterance, same columns); the butterfly and the atomics run once per utterance and warp
+          // instead of once per tile.  All math on packed fp32 pairs.  A warp whose 32 rows straddle an utterance edge
+          // makes one masked pass per utterance over the same accumulator tile (re-read from TMEM), flushing in between.
+          auto accumulate = [&](auto masked_c, int lo, int hi, bool release) {
+            constexpr bool kMasked = decltype(masked_c)::value;
+            uint64_t mk[4];
+            if (kMasked) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const float m = (rq + 8 * k >= lo && rq + 8 * k < hi) ? 1.f : 0.f;
+                mk[k] = ptx::f2_pack(m, m);
+              }
+            }
+            // 16-column half chunks, software-pipelined: the tcgen05.ld of half chunk h+1 is in flight while h is reduced
+            uint32_t r0[2][8], r1[2][8];               // [buffer]: rows q*32 + rq + {0, 8} | the same + 16
+            const uint32_t tbase = tmem_base + ((q * 32) << 16) + as * kBN + half * kChunksPerWarp * 32;
+            const int n_half = 2 * (c_end - static_cast<int>(half) * kChunksPerWarp);
+            ptx::tmem_ld_16x256b_x2(tbase, r0[0]);
+            ptx::tmem_ld_16x256b_x2(tbase + (16u << 16), r1[0]);
+#pragma unroll
+            for (int h = 0; h < 2 * kChunksPerWarp; ++h) {
+              if (h < n_half) {
+                ptx::tmem_ld_wait();
+                if (h + 1 < n_half) {
+                  ptx::tmem_ld_16x256b_x2(tbase + (h + 1) * 16, r0[(h + 1) & 1]);
+                  ptx::tmem_ld_16x256b_x2(tbase + (16u << 16) + (h + 1) * 16, r1[(h + 1) & 1]);
+                } else if (release) {
+                  ptx::tc_fence_before();              // last TMEM read of the tile: hand the accumulator back
+                  __syncwarp();
+                  if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
+                }
+                const int ci = h >> 1;
+                const int col = (half * kChunksPerWarp + ci) * 32 + (h & 1) * 16;
+#pragma unroll
+                for (int ii = 0; ii < 2; ++ii) {
+                  const int i = (h & 1) * 2 + ii;
+                  const ulonglong2 sh = *reinterpret_cast<const ulonglong2*>(ss + col + 8 * ii + cq);   // (s0,s1) | (h0,h1)
+                  float2 ng = make_float2(0.f, 0.f);
+                  if (!relu_only) ng = *reinterpret_cast<const float2*>(sl + col + 8 * ii + cq);
+#pragma unroll
+                  for (int k = 0; k < 4; ++k) {
+                    const uint32_t* src = k < 2 ? r0[h & 1] : r1[h & 1];
+                    uint64_t v = ptx::f2_fma(ptx::f2_pack_u32(src[4 * ii + 2 * (k & 1)], src[4 * ii + 2 * (k & 1) + 1]), sh.x, sh.y);
+                    float v0, v1;
+                    ptx::f2_unpack(v, v0, v1);
+                    if (relu_only) {
+                      v0 = fmaxf(v0, 0.f);
+                      v1 = fmaxf(v1, 0.f);
+                    } else {
+                      v0 = v0 >= 0.f ? v0 : v0 * ng.x;
+                      v1 = v1 >= 0.f ? v1 : v1 * ng.y;
+                      if (p.act_tanh) { v0 = tanhf(v0); v1 = tanhf(v1); }
+                    }
+                    v = ptx::f2_pack(v0, v1);
+                    if (kMasked) v = ptx::f2_mul(v, mk[k]);
+                    acc_s[ci][i] = ptx::f2_add(acc_s[ci][i], v);
+                    acc_q[ci][i] = ptx::f2_fma(v, v, acc_q[ci][i]);
+                  }
+                }
+              }
+            }
+          };
+          bool released = false;
+          for (int s = w_first; s <= w_last; ++s) {
+            const PoolSeg sg = s == w_first ? w_sg : p.segs[s];
+            const int lo = max(sg.r0, mw) - mw;
+            const int hi = min(sg.r1, mw + 32) - mw;
+            if (lo >= hi) continue;
+            if (held_utt != sg.utt || held_n0 != n0 || held_tiles >= 64) {
+              flush_held();
+              held_utt = sg.utt;
+              held_n0 = n0;
+              held_sg = sg;
+            }
+            ++held_tiles;
+            released = s == w_last;
+            if (lo == 0 && hi == 32) accumulate(std::false_type{}, lo, hi, released);
+            else accumulate(std::true_type{}, lo, hi, released);
+          }
+          if (!released) {                           // no valid row under this warp: just hand the accumulator back
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
+          }
+        } else {
 #pragma unroll 1
         for (int c = half * kChunksPerWarp; c < c_end; ++c) {
           uint32_t ra[16], rb[16];
@@ -299,8 +490,8 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               const uint32_t* src = k < 2 ? ra : rb;
-              float v0 = fmaf(__uint_as_float(src[4 * i + 2 * (k & 1)]), sh.x, sh.y);
-              float v1 = fmaf(__uint_as_float(src[4 * i + 2 * (k & 1) + 1]), sh.z, sh.w);
+              float v0 = fmaf(__uint_as_float(src[4 * i + 2 * (k & 1)]), sh.x, sh.z);       // pair layout (s0, s1, h0, h1)
+              float v1 = fmaf(__uint_as_float(src[4 * i + 2 * (k & 1) + 1]), sh.y, sh.w);
               if (relu_only) {
                 v0 = fmaxf(v0, 0.f);
                 v1 = fmaxf(v1, 0.f);
@@ -316,13 +507,7 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
           for (int s = w_first; s <= w_last; ++s) {
             const PoolSeg sg = s == w_first ? w_sg : p.segs[s];
             float v[16];
-            if (w_full) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                v[j] = (y[0][j] + y[1][j]) + (y[2][j] + y[3][j]);
-                v[8 + j] = fmaf(y[0][j], y[0][j], y[1][j] * y[1][j]) + fmaf(y[2][j], y[2][j], y[3][j] * y[3][j]);
-              }
-            } else {
+            {
               const int lo = max(sg.r0, mw) - mw;
               const int hi = min(sg.r1, mw + 32) - mw;
               if (lo >= hi) continue;
@@ -369,40 +554,9 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
                 v[8 + j] = a2;
               }
             }
-            // butterfly over lane bits 4, 3, 2: halves the live values each step
-            {
-              const bool up = (lane & 16) != 0;
-#pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                const float send = up ? v[j] : v[j + 8];
-                const float keep = up ? v[j + 8] : v[j];
-                v[j] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-              }
-            }
-            {
-              const bool up = (lane & 8) != 0;
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const float send = up ? v[j] : v[j + 4];
-                const float keep = up ? v[j + 4] : v[j];
-                v[j] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-              }
-            }
-            {
-              const bool up = (lane & 4) != 0;
-#pragma unroll
-              for (int j = 0; j < 2; ++j) {
-                const float send = up ? v[j] : v[j + 2];
-                const float keep = up ? v[j + 2] : v[j];
-                v[j] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-              }
-            }
-            const int kind = (lane >> 4) & 1;                      // 0: sum, 1: sum of squares
-            const int ii = ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
-            double* dst = p.pool_acc + (static_cast<size_t>(sg.utt) * 2 + kind) * p.pool_ld + n0 + c * 32 + 8 * ii + cq;
-            atomicAdd(dst, static_cast<double>(v[0]));
-            atomicAdd(dst + 1, static_cast<double>(v[1]));
+            pool_reduce_atomics(v, lane, p.pool_acc + static_cast<size_t>(sg.utt) * 2 * p.pool_ld, p.pool_ld, n0 + c * 32);
           }
+        }
         }
       } else {
       // fused attention scores: this warp's 128 columns lie in at most two heads (head_width >= 128)
@@ -509,6 +663,7 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       }
       if (++as == kAccStages) { as = 0; aphase ^= 1; }
     }
+    flush_held();
     if (store_bf16 && lane == 0) ptx::tma_store_wait<0>();      // all bulk stores of this warp have completed
   }
 
@@ -631,6 +786,17 @@ cudaError_t launch_variant(const GemmPlan& plan, int sm_count, cudaStream_t stre
   cfg.dynamicSmemBytes = kSmemBytes;
   cfg.stream = stream;
   cudaLaunchAttribute attr;
+  // pooled layer with plain (unweighted) sums: column-stationary schedule, floor(SMs / n_tiles) CTAs per column tile
+  // (144 of 148 SMs at 6 column tiles; the register-resident sums save more than the four idle SMs cost)
+  static const int want_cs = getenv("XV_POOL_COLSTAT") ? atoi(getenv("XV_POOL_COLSTAT")) : 1;
+  if (kPool && want_cs && pairs == 0 && p.row_weight == nullptr && p.n_tiles <= sm_count) {
+    GemmParams q = p;
+    int cpn = sm_count / p.n_tiles;
+    if (cpn > p.m_tiles) cpn = p.m_tiles;
+    q.col_stationary = 1;
+    cfg.gridDim = dim3(cpn * p.n_tiles, 1, 1);
+    return cudaLaunchKernelEx(&cfg, xv_tdnn_gemm_kernel<kPool>, plan.tm_a, plan.tm_b, plan.tm_out, q);
+  }
   if (pairs > 0) {
     const int units = ((p.m_tiles + 1) / 2) * p.n_tiles;
     const int n = units < pairs ? units : pairs;

@@ -47,6 +47,7 @@ struct GemmParams {
   // fused statistics-pooling partial sums (tdnn5): acc[utt][0|1][pool_ld] += sum x | sum x^2
   double* pool_acc;    // fp64: atomics become order-independent at fp32 precision
   int32_t pool_ld;
+  int32_t col_stationary = 0;   // set by launch_gemm: grid = cpn x n_tiles CTAs, each keeps one column tile (xv_gemm_sm100.cu)
   const int32_t* tile_seg_ptr;  // [2 * m_tiles]: (lo, hi) index range into segs per tile
   const PoolSeg* segs;
   // optional per-row weights (attention pooling): weighted sums  sum w x | sum w x^2 ; [heads, m_rows]
