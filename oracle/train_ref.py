@@ -1,6 +1,6 @@
 """fp64 numpy restatement of ONE training step of the reference (BASELINE.json config 5): TDNN in training mode
 (batch-statistics BN), additive-margin softmax or plain softmax, L2 regularisation, hand-derived backward pass,
-SGD / momentum update, BN moving-average update.  TEST INFRASTRUCTURE -- see oracle/__init__.py.
+SGD / momentum / Adam update, per-tensor gradient clipping, BN moving-average update.  TEST INFRASTRUCTURE -- see oracle/__init__.py.
 
 Follows, line by line:
   model/tdnn.py:36-181 with is_training=True            (network, BN -> activation order)
@@ -315,6 +315,17 @@ def train_step(features, labels, w, params, learning_rate, global_step=0, num_to
             acc = mom * state.get(k, 0.0) + g
             state[k] = acc
             new_w[k] = new_w[k] - learning_rate * ((g + mom * acc) if params.dict.get("use_nesterov", False) else acc)
+        elif opt == "adam":
+            # tf.train.AdamOptimizer(learning_rate) defaults (model/trainer.py:241-243): beta1 0.9, beta2 0.999, eps 1e-8;
+            # lr_t = lr * sqrt(1 - b2^t) / (1 - b1^t), m = b1 m + (1-b1) g, v = b2 v + (1-b2) g^2, w -= lr_t m / (sqrt(v) + eps)
+            t = state.get("__adam_t", 0) + (1 if k == next(iter(grads)) else 0)
+            state["__adam_t"] = t
+            m, v = state.get(k, (0.0, 0.0))
+            m = 0.9 * m + 0.1 * g
+            v = 0.999 * v + 0.001 * g * g
+            state[k] = (m, v)
+            lr_t = learning_rate * np.sqrt(1.0 - 0.999 ** t) / (1.0 - 0.9 ** t)
+            new_w[k] = new_w[k] - lr_t * m / (np.sqrt(v) + 1e-8)
         else:
             raise NotImplementedError("training oracle: optimizer %s" % opt)
     for k, v in outs[0]["moving"].items():

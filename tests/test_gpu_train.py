@@ -1,5 +1,5 @@
 """GPU: one training step (BASELINE.json config 5) through the C-ABI against the fp64 oracle: loss, every gradient,
-the SGD / momentum update and the BN moving averages."""
+the SGD / momentum / Adam update, gradient clipping and the BN moving averages."""
 import numpy as np
 import pytest
 
@@ -88,6 +88,45 @@ def test_train_step_matches_oracle(loss_func, relu, linear, no_bn, opt, step, se
         v2 = eng.train_weight(k, w[k].shape)
         assert np.linalg.norm(v2 - new_ref2[k].reshape(v2.shape)) <= 2 * FLIP_TOL * np.linalg.norm(new_ref2[k])
         assert eng.launch_count() > 0
+    finally:
+        eng.close()
+
+
+@pytest.mark.parametrize("opt,clip", [("adam", None), ("sgd", 0.02), ("adam", 0.02)], ids=["adam", "sgd_clip", "adam_clip"])
+def test_train_step_adam_and_clip(opt, clip):
+    """tf.train.AdamOptimizer defaults (model/trainer.py:241-243) and the per-variable tf.clip_by_norm of
+    clip_gradient (model/trainer.py:372-373, 529-533): two chained steps against the oracle.  Adam turns a gradient
+    into a step of size ~lr whatever its magnitude, so the update (not the weight) is compared, in L2."""
+    from oracle import numpy_ref, synth, train_ref
+    cfg = dict(synth.TDNN_AMSOFTMAX_CONFIG, optimizer=opt)
+    if clip:
+        cfg.update(clip_gradient=True, clip_gradient_norm=clip)
+    dim, speakers, batch, frames, lr = 24, 101, 8, 50, (1e-3 if opt == "adam" else 0.05)
+    eng, w, x, y = _setup(cfg, dim, speakers, batch, frames, seed=77)
+    try:
+        params = numpy_ref.OracleParams(**cfg)
+        loss, _ = eng.train_step(x, y, lr, 0)
+        ref1, info = train_ref.train_step(x, y, w, params, lr, 0)
+        assert abs(loss - info["loss"]) <= 1e-5 * abs(info["loss"])
+        if clip:
+            raw = train_ref.train_step(x, y, w, numpy_ref.OracleParams(**dict(cfg, clip_gradient=False)), lr, 0)[1]["grads"]
+            norms = {k: np.linalg.norm(g) for k, g in raw.items()}
+            assert any(n > clip for n in norms.values()) and any(n < clip for n in norms.values())   # both branches taken
+            for k, g_ref in info["grads"].items():
+                g = eng.train_grad(k, np.asarray(w[k]).shape)
+                assert np.linalg.norm(g - g_ref.reshape(g.shape)) <= FLIP_TOL * max(np.linalg.norm(g_ref), 1e-3 * clip), k
+                assert np.linalg.norm(g) <= clip * (1 + 1e-4), k
+        loss2, _ = eng.train_step(x, y, lr, 1)
+        ref2, info2 = train_ref.train_step(x, y, ref1, params, lr, 1, opt_state=info["opt_state"])
+        assert abs(loss2 - info2["loss"]) <= FLIP_TOL * abs(info2["loss"])
+        for k in info["grads"]:
+            w0 = np.asarray(w[k], np.float64)
+            v = eng.train_weight(k, w0.shape)
+            d, d_ref = v - w0, ref2[k].reshape(w0.shape) - w0
+            if k.endswith("/bias") and np.abs(info["grads"][k]).max() < 1e-12:
+                assert np.abs(d).max() <= 0.02 * lr, k     # exact-zero gradient in front of a BN: fp32 noise only
+                continue
+            assert np.linalg.norm(d - d_ref) <= 2e-2 * np.linalg.norm(d_ref), "%s: %.3e" % (k, np.linalg.norm(d - d_ref) / np.linalg.norm(d_ref))
     finally:
         eng.close()
 

@@ -83,3 +83,31 @@ def test_bf16_gemm_option_rounds_only_frame_layer_operands():
     assert 0 < abs(exact["loss"] - mixed["loss"]) <= 1e-2 * abs(exact["loss"])
     r = train_ref.bf16_round(np.array([1.0, 1.0 + 2.0 ** -8, 1.0 + 3 * 2.0 ** -9, -0.1]))
     assert r[0] == 1.0 and r[1] == 1.0 and r[2] == 1.0 + 2.0 ** -7 and abs(r[3] + 0.1) < 2.0 ** -11
+
+
+def test_adam_and_clip_updates_against_torch():
+    """The oracle's Adam / clip_by_norm branches against torch.optim.Adam and torch.nn.utils.clip_grad_norm_ driven by the
+    oracle's own gradients.  tf.train.AdamOptimizer's epsilon is the paper's "epsilon hat" (added to the UNcorrected
+    sqrt(v)); torch adds eps to the bias-corrected one, so torch is run with eps_t = 1e-8 / sqrt(1 - beta2^t)."""
+    import torch
+    cfg = dict(synth.TDNN_AMSOFTMAX_CONFIG, optimizer="adam", clip_gradient=True, clip_gradient_norm=0.5)
+    s = 23
+    w = synth.add_softmax_weights(synth.make_tdnn_weights(20, cfg, seed=5), s, bias=False)
+    x, y = synth.config5_batch(4, 40, 20, s, seed=2)
+    params = numpy_ref.OracleParams(**cfg)
+    lr = 1e-3
+    w1, i1 = train_ref.train_step(x, y, w, params, lr, 0)
+    raw1 = train_ref.train_step(x, y, w, numpy_ref.OracleParams(**dict(cfg, clip_gradient=False, optimizer="sgd")), lr, 0)[1]["grads"]
+    w2, i2 = train_ref.train_step(x, y, w1, params, lr, 1, opt_state=i1["opt_state"])
+    raw2 = train_ref.train_step(x, y, w1, numpy_ref.OracleParams(**dict(cfg, clip_gradient=False, optimizer="sgd")), lr, 1)[1]["grads"]
+    for k in ("tdnn/tdnn6_dense/kernel", "tdnn/tdnn2_conv/kernel", "softmax/output/kernel", "tdnn/tdnn5_bn/gamma"):
+        t = torch.tensor(np.asarray(w[k], np.float64), requires_grad=True)
+        opt = torch.optim.Adam([t], lr=lr, betas=(0.9, 0.999), eps=1e-8)
+        for step, (raw, ref) in enumerate(((raw1, w1), (raw2, w2)), start=1):
+            opt.param_groups[0]["eps"] = 1e-8 / np.sqrt(1.0 - 0.999 ** step)
+            t.grad = torch.tensor(raw[k].reshape(t.shape))
+            torch.nn.utils.clip_grad_norm_([t], 0.5)          # one tensor per call == tf.clip_by_norm per variable
+            opt.step()
+            d_ref = ref[k].reshape(t.shape) - np.asarray(w[k], np.float64)
+            d = t.detach().numpy() - np.asarray(w[k], np.float64)
+            assert np.linalg.norm(d - d_ref) <= 1e-5 * np.linalg.norm(d_ref), k   # clip_grad_norm_ adds 1e-6 to the norm

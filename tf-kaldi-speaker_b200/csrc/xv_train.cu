@@ -18,6 +18,7 @@
 // gradients match the fp64 oracle to <= 1e-4.
 #include <dlfcn.h>
 #include <math.h>
+#include <cmath>
 
 #include <algorithm>
 
@@ -779,10 +780,31 @@ __global__ void reg_loss_kernel(const float* __restrict__ p, const ParamSeg* __r
   if (threadIdx.x == 0 && s != 0.0) atomicAdd(out, 0.5 * sg.wd * s);
 }
 
-// g = gsum/world + wd*p (stored back for inspection); sgd: p -= lr*g; momentum: a = m*a + g; p -= lr*(nesterov ? g + m*a : a)
+// Per-variable squared L2 norm of the final gradient g = gsum/world + wd*p (tf.clip_by_norm works per tensor,
+// model/trainer.py:529-533 and :1245-1246): norms[seg] += sum g^2.  grid (x, n_segs).
+__global__ void grad_sqnorm_kernel(const float* __restrict__ p, const float* __restrict__ g, const ParamSeg* __restrict__ segs,
+                                   float inv_world, double* __restrict__ norms) {
+  __shared__ double sh[8];
+  const ParamSeg sg = segs[blockIdx.y];
+  double s = 0.0;
+  if (!sg.moving)
+    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < sg.size;
+         i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+      const double v = fmaf(sg.wd, p[sg.off + i], g[sg.off + i] * inv_world);
+      s += v * v;
+    }
+  s = block_reduce(s, sh, false);
+  if (threadIdx.x == 0 && s != 0.0) atomicAdd(norms + blockIdx.y, s);
+}
+
+// g = gsum/world + wd*p, optionally clipped per variable to clip_norm (g * clip / max(|g|, clip)); stored back for
+// inspection.  sgd: p -= lr*g; momentum: a = m*a + g; p -= lr*(nesterov ? g + m*a : a);
+// adam (tf.train.AdamOptimizer defaults b1 = 0.9, b2 = 0.999, eps = 1e-8; lr already holds lr*sqrt(1-b2^t)/(1-b1^t)):
+//   m = b1*m + (1-b1)*g; v = b2*v + (1-b2)*g^2; p -= lr*m/(sqrt(v)+eps), m = accum[0..total), v = accum[total..2 total)
 __global__ void apply_update_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ accum,
                                     const ParamSeg* __restrict__ segs, int n_segs, int64_t total, float inv_world, float lr,
-                                    int optimizer, float momentum, int nesterov) {
+                                    int optimizer, float momentum, int nesterov, const double* __restrict__ sqnorms,
+                                    float clip_norm) {
   for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
     int lo = 0, hi = n_segs - 1;
@@ -795,14 +817,21 @@ __global__ void apply_update_kernel(float* __restrict__ p, float* __restrict__ g
       p[i] = g[i];                       // rank 0's new moving statistic (other ranks contributed zeros)
       continue;
     }
-    const float grad = fmaf(sg.wd, p[i], g[i] * inv_world);
+    float grad = fmaf(sg.wd, p[i], g[i] * inv_world);
+    if (sqnorms != nullptr) grad *= clip_norm / fmaxf(static_cast<float>(sqrt(sqnorms[lo])), clip_norm);
     g[i] = grad;
     if (optimizer == 0) {
       p[i] -= lr * grad;
-    } else {
+    } else if (optimizer == 1) {
       const float a = fmaf(momentum, accum[i], grad);
       accum[i] = a;
       p[i] -= lr * (nesterov ? fmaf(momentum, a, grad) : a);
+    } else {
+      const float m = fmaf(0.9f, accum[i], 0.1f * grad);
+      const float v = fmaf(0.999f, accum[total + i], 0.001f * grad * grad);
+      accum[i] = m;
+      accum[total + i] = v;
+      p[i] -= lr * m / (sqrtf(v) + 1e-8f);
     }
   }
 }
@@ -850,7 +879,10 @@ struct TrainState {
   bool amsoftmax = true;
   float margin = 0.f, lam_min = 0.f, lam_base = 0.f, lam_gamma = 0.f, lam_power = 0.f;
   float wd = 0.f, wd_out = 0.f, bn_momentum = 0.99f, opt_momentum = 0.f;
-  int optimizer = 0, nesterov = 0;
+  int optimizer = 0, nesterov = 0;       // 0 sgd, 1 momentum, 2 adam
+  int64_t adam_t = 0;                    // Adam steps taken (beta powers; model/trainer.py:241-243)
+  float clip_norm = 0.f;                 // > 0: per-variable tf.clip_by_norm (clip_gradient / clip_gradient_norm)
+  DevBuf sqnorms;
   std::string relu_type;
   DevBuf const_slope, zeros, feats, labels, d_cu, pooled, logits, gr, coef, rnorm, dbuf[2], sums, scalars, pool_ws, scratch;
   int cap_b = 0, cap_t = 0;
@@ -931,7 +963,7 @@ void train_release(xv_ctx* c) {
   for (TrLayer& l : t->layers) { release(&l.z); release(&l.y); release(&l.mean); release(&l.rstd); }
   DevBuf* bufs[] = {&t->params, &t->grads, &t->accum, &t->d_segs, &t->const_slope, &t->zeros, &t->feats, &t->labels, &t->d_cu,
                     &t->pooled, &t->logits, &t->gr, &t->coef, &t->rnorm, &t->dbuf[0], &t->dbuf[1], &t->sums, &t->scalars,
-                    &t->pool_ws, &t->scratch};
+                    &t->pool_ws, &t->scratch, &t->sqnorms};
   for (DevBuf* b : bufs) release(b);
   delete t;
   c->train = nullptr;
@@ -976,11 +1008,17 @@ static int train_init(xv_ctx* c, int32_t num_speakers) {
     t->opt_momentum = static_cast<float>(jnum(cfg, "momentum", 0.9));
     const JValue* nv = cfg.get("use_nesterov");
     t->nesterov = (nv && nv->truthy()) ? 1 : 0;
+  } else if (opt == "adam") {
+    t->optimizer = 2;
   } else {
     return fail(c, XV_EUNSUPPORTED, "Optimizer %s is not supported.", opt.c_str());
   }
-  const JValue* cg = cfg.get("clip_gradient");
-  if (cg && cg->truthy()) return fail(c, XV_EUNSUPPORTED, "clip_gradient is not covered by this build");
+  const JValue* cg = cfg.get("clip_gradient");                                        // model/trainer.py:372-373, 529-533
+  if (cg && cg->truthy()) {
+    if (!cfg.has("clip_gradient_norm")) return fail(c, XV_EINVAL, "clip_gradient needs the config key 'clip_gradient_norm'");
+    t->clip_norm = static_cast<float>(jnum(cfg, "clip_gradient_norm", 0));
+    if (!(t->clip_norm > 0.f)) return fail(c, XV_EINVAL, "clip_gradient_norm must be positive");
+  }
   t->relu_type = c->relu_type;
   t->speakers = num_speakers;
   t->embed = c->last_nodes;
@@ -1024,10 +1062,12 @@ static int train_init(xv_ctx* c, int32_t num_speakers) {
   t->n_total = static_cast<int64_t>(host.size());
   if ((rc = upload(c, &t->params, host.data(), sizeof(float) * t->n_total)) != XV_OK) return rc;
   if ((rc = ensure(c, &t->grads, sizeof(float) * (t->n_total + 1), true)) != XV_OK) return rc;
-  if (t->optimizer == 1) {
-    if ((rc = ensure(c, &t->accum, sizeof(float) * t->n_total)) != XV_OK) return rc;
-    cudaMemsetAsync(t->accum.p, 0, sizeof(float) * t->n_total, c->stream);
+  if (t->optimizer != 0) {               // momentum accumulator | Adam first and second moments
+    const size_t nacc = static_cast<size_t>(t->n_total) * (t->optimizer == 2 ? 2 : 1);
+    if ((rc = ensure(c, &t->accum, sizeof(float) * nacc)) != XV_OK) return rc;
+    cudaMemsetAsync(t->accum.p, 0, sizeof(float) * nacc, c->stream);
   }
+  if (t->clip_norm > 0.f && (rc = ensure(c, &t->sqnorms, sizeof(double) * t->segs.size())) != XV_OK) return rc;
   if ((rc = upload(c, &t->d_segs, t->segs.data(), sizeof(ParamSeg) * t->segs.size())) != XV_OK) return rc;
   int maxc = std::max(num_speakers, 1);
   for (const TrLayer& l : t->layers) maxc = std::max(maxc, l.cout);
@@ -1479,10 +1519,27 @@ static int train_step(xv_ctx* c, const float* feats, const int32_t* labels, int3
     if (nrc != 0) return tr_fail_nccl(c, t, nrc, "ncclAllReduce");
     count_launch(c, "train.allreduce");
   }
+  const double* sqn = nullptr;
+  if (t->clip_norm > 0.f) {
+    // clipping acts on the AVERAGED gradient (model/trainer.py:1244-1246), per variable
+    double* d_sqn = static_cast<double*>(t->sqnorms.p);
+    TR_CUDA(cudaMemsetAsync(d_sqn, 0, sizeof(double) * t->segs.size(), s), "memset norms");
+    count_launch(c, "train.grad_norms");
+    grad_sqnorm_kernel<<<dim3(64, static_cast<unsigned>(t->segs.size())), 256, 0, s>>>(
+        P, G, static_cast<const ParamSeg*>(t->d_segs.p), 1.f / t->world, d_sqn);
+    TR_CUDA(cudaGetLastError(), "gradient norm launch");
+    sqn = d_sqn;
+  }
+  float lr_eff = lr;
+  if (t->optimizer == 2) {
+    ++t->adam_t;
+    lr_eff = static_cast<float>(lr * std::sqrt(1.0 - std::pow(0.999, static_cast<double>(t->adam_t))) /
+                                (1.0 - std::pow(0.9, static_cast<double>(t->adam_t))));
+  }
   count_launch(c, "train.update");
   apply_update_kernel<<<ew_grid(c), 256, 0, s>>>(P, G, static_cast<float*>(t->accum.p), static_cast<const ParamSeg*>(t->d_segs.p),
-                                                 static_cast<int>(t->segs.size()), t->n_total, 1.f / t->world, lr, t->optimizer,
-                                                 t->opt_momentum, t->nesterov);
+                                                 static_cast<int>(t->segs.size()), t->n_total, 1.f / t->world, lr_eff,
+                                                 t->optimizer, t->opt_momentum, t->nesterov, sqn, t->clip_norm);
   TR_CUDA(cudaGetLastError(), "update launch");
   if (loss_out) {
     float loss_sum = 0.f;
