@@ -56,6 +56,9 @@ constexpr uint32_t kBBytes = kBN * kBK * 2;                  // 32768
 constexpr uint32_t kBHalfBytes = kBLoadRows * kBK * 2;       // 16384: one TMA box of the weight tile (xv_internal.h)
 constexpr uint32_t kStageBytes = kABytes + kBBytes;          // 49152
 constexpr uint32_t kRingBytes = kStages * kStageBytes;       // 196608
+constexpr int kStages2Sm = 6;                                // 2-SM pairs: A 16 KB + this CTA's weight half 16 KB per stage
+constexpr uint32_t kStageBytes2Sm = kABytes + kBHalfBytes;   // 32768
+static_assert(kStages2Sm * kStageBytes2Sm == kRingBytes, "both ring layouts fill the same shared memory");
 constexpr uint32_t kEpiParamBytes = kAccStages * kBN * 16;   // (scale,shift) float2 + slope float + query float = 8192
 constexpr uint32_t kStoreStageBytes = 32 * 64;               // per warp: 32 rows x 32 bf16, SWIZZLE_64B
 constexpr uint32_t kEpiScratchBytes = kEpiWarpsStore * kStoreStageBytes;
@@ -110,7 +113,12 @@ __device__ __forceinline__ void pool_reduce_atomics(float (&v)[16], uint32_t lan
   atomicAdd(dst + 1, static_cast<double>(v[1]));
 }
 
-template <bool kPool>
+// k2Sm: the CTA pair of a 2-CTA cluster runs ONE 256 x 256 tcgen05.mma.cta_group::2 per K step.  Each CTA stages its own
+// 128 activation rows and its own 128-row half of the weight tile (32 KB per k-block and SM instead of 48 KB, six ring
+// stages instead of four), the leader (cluster rank 0) issues every MMA, commits multicast to both CTAs' barriers, both
+// epilogues read their own TMEM and hand the accumulator back on the LEADER's barrier.  Halves the shared-memory operand
+// reads and the L2 -> SM weight traffic per flop, which is what the power-capped tensor pipe is short of.
+template <bool kPool, bool k2Sm>
 __global__ void __launch_bounds__(EpiCfg<kPool>::kThreads, 1)
 xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                     const __grid_constant__ CUtensorMap tm_out, const GemmParams p) {
@@ -128,9 +136,11 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   float* ep_sq = reinterpret_cast<float*>(smem + kRingBytes + kAccStages * kBN * 12); // [2][256] attention query (fused scores)
   uint8_t* scratch = smem + kRingBytes + kEpiParamBytes;                              // per-warp staging / transpose
   uint64_t* bars = reinterpret_cast<uint64_t*>(scratch + kEpiScratchBytes);
-  uint64_t* full_bar = bars;                       // [kStages]   TMA -> MMA
-  uint64_t* empty_bar = bars + kStages;            // [kStages]   MMA -> TMA
-  uint64_t* tfull_bar = bars + 2 * kStages;        // [kAccStages] MMA -> epilogue
+  constexpr int kNumStages = k2Sm ? kStages2Sm : kStages;
+  constexpr uint32_t kStageB = k2Sm ? kStageBytes2Sm : kStageBytes;
+  uint64_t* full_bar = bars;                       // [kNumStages]   TMA -> MMA
+  uint64_t* empty_bar = bars + kNumStages;         // [kNumStages]   MMA -> TMA
+  uint64_t* tfull_bar = bars + 2 * kNumStages;     // [kAccStages] MMA -> epilogue
   uint64_t* tempty_bar = tfull_bar + kAccStages;   // [kAccStages] epilogue -> MMA
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + kAccStages);
 
@@ -147,19 +157,24 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     ptx::prefetch_tensormap(&tm_a);
     ptx::prefetch_tensormap(&tm_b);
     if (!kPool && p.out_bf16 != nullptr) ptx::prefetch_tensormap(&tm_out);
-    for (int s = 0; s < kStages; ++s) {
+    for (int s = 0; s < kNumStages; ++s) {
       ptx::mbar_init(&full_bar[s], 1);
-      ptx::mbar_init(&empty_bar[s], csize);         // every CTA of the cluster retires its MMAs on this stage
+      ptx::mbar_init(&empty_bar[s], k2Sm ? 1 : csize);   // multicast pairs: every CTA of the cluster retires its own MMAs on this stage
     }
     for (int s = 0; s < kAccStages; ++s) {
       ptx::mbar_init(&tfull_bar[s], 1);
-      ptx::mbar_init(&tempty_bar[s], kEpiWarps);   // one arrive per epilogue warp
+      ptx::mbar_init(&tempty_bar[s], k2Sm ? 2 * kEpiWarps : kEpiWarps);   // one arrive per epilogue warp (of both CTAs: 2-SM leader)
     }
     ptx::fence_mbar_init();
   }
   if (warp == 1) {
-    ptx::tmem_alloc(tmem_slot, kTmemCols);
-    ptx::tmem_relinquish();
+    if (k2Sm) {
+      ptx::tmem_alloc_2sm(tmem_slot, kTmemCols);
+      ptx::tmem_relinquish_2sm();
+    } else {
+      ptx::tmem_alloc(tmem_slot, kTmemCols);
+      ptx::tmem_relinquish();
+    }
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -179,14 +194,24 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   int unit_step = gridDim.x / csize;
   int n_units = ((p.m_tiles + static_cast<int>(csize) - 1) / static_cast<int>(csize)) * p.n_tiles;
   int nt_fixed = -1;
-  if (col_stat) {
-    const int cpn = gridDim.x / p.n_tiles;
-    const int j = blockIdx.x / p.n_tiles;
-    nt_fixed = blockIdx.x % p.n_tiles;
-    unit0 = static_cast<int>(static_cast<int64_t>(j) * p.m_tiles / cpn);
-    n_units = static_cast<int>(static_cast<int64_t>(j + 1) * p.m_tiles / cpn);
+  if (col_stat) {                                   // units = groups of csize consecutive row tiles of ONE column tile
+    const int cl = blockIdx.x / csize, n_cl = gridDim.x / csize;
+    const int cpn = n_cl / p.n_tiles;
+    const int j = cl / p.n_tiles;
+    const int groups = (p.m_tiles + static_cast<int>(csize) - 1) / static_cast<int>(csize);
+    nt_fixed = cl % p.n_tiles;
+    unit0 = static_cast<int>(static_cast<int64_t>(j) * groups / cpn);
+    n_units = static_cast<int>(static_cast<int64_t>(j + 1) * groups / cpn);
     unit_step = 1;
   }
+  // 2-SM pairs: the leader's barriers as shared::cluster addresses
+  const uint32_t lead_full0 = k2Sm ? ptx::mapa_u32(ptx::smem_u32(&full_bar[0]), 0) : 0u;
+  const uint32_t lead_tempty0 = k2Sm ? ptx::mapa_u32(ptx::smem_u32(&tempty_bar[0]), 0) : 0u;
+  // epilogue warp -> MMA warp: this accumulator stage is drained (lane 0 of the warp calls)
+  auto release_acc = [&](uint32_t as) {
+    if (k2Sm) ptx::mbar_arrive_cluster(lead_tempty0 + as * 8);
+    else ptx::mbar_arrive(&tempty_bar[as]);
+  };
   const int num_kb = p.taps * p.kb_per_tap;
 
   if (warp == 0) {
@@ -194,24 +219,32 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
       for (int u = unit0; u < n_units; u += unit_step) {
-        const int m0 = (col_stat ? u : (u / p.n_tiles) * static_cast<int>(csize) + static_cast<int>(crank)) * kBM;
+        const int m0 = ((col_stat ? u : u / p.n_tiles) * static_cast<int>(csize) + static_cast<int>(crank)) * kBM;
         const int n0 = (col_stat ? nt_fixed : u % p.n_tiles) * kBN;
         for (int tap = 0; tap < p.taps; ++tap) {
           const int row = m0 + tap * p.dilation;
           for (int cb = 0; cb < p.kb_per_tap; ++cb) {
             ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-            uint8_t* sa = ring + stage * kStageBytes;
+            uint8_t* sa = ring + stage * kStageB;
             uint8_t* sb = sa + kABytes;
+            const int kc = tap * p.cin + cb * kBK;
+            if (k2Sm) {
+              // both CTAs' boxes complete on the leader's barrier, which expects the bytes of the pair
+              if (crank == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * kStageBytes2Sm);
+              ptx::tma_load_2d_2sm(sa, &tm_a, lead_full0 + stage * 8, cb * kBK, row);
+              ptx::tma_load_2d_2sm(sb, &tm_b, lead_full0 + stage * 8, kc, n0 + static_cast<int>(crank) * kBLoadRows);
+              if (++stage == kNumStages) { stage = 0; phase ^= 1; }
+              continue;
+            }
             ptx::mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
             ptx::tma_load_2d(sa, &tm_a, &full_bar[stage], cb * kBK, row);
-            const int kc = tap * p.cin + cb * kBK;
             if (csize > 1) {
               ptx::tma_load_2d_multicast(sb + crank * kBHalfBytes, &tm_b, &full_bar[stage], kc, n0 + static_cast<int>(crank) * kBLoadRows, cmask);
             } else {
               ptx::tma_load_2d(sb, &tm_b, &full_bar[stage], kc, n0);
               ptx::tma_load_2d(sb + kBHalfBytes, &tm_b, &full_bar[stage], kc, n0 + kBLoadRows);
             }
-            if (++stage == kStages) { stage = 0; phase ^= 1; }
+            if (++stage == kNumStages) { stage = 0; phase ^= 1; }
           }
         }
       }
@@ -222,9 +255,10 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     // issues UTCHMMA straight from uniform registers; one elected lane issues.  A lone lane under `if (lane == 0)`
     // costs ~450 clk per (wait, 4 MMAs, commit) round in its own instruction stream -- 88% of the 512 clk the four
     // MMAs execute in (tools/debug/umma_issue.cu) -- which leaves no slack to absorb a late TMA arrival.
-    constexpr uint32_t idesc = ptx::make_idesc_bf16(kBM, kBN);
+    constexpr uint32_t idesc = ptx::make_idesc_bf16(k2Sm ? 2 * kBM : kBM, kBN);
     const uint32_t ring_lo = ptx::sw128_desc_lo(ptx::smem_u32(ring));
     uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
+    if (k2Sm && crank != 0) n_units = unit0;        // the peer's MMA warp only owns the TMEM allocation
     for (int u = unit0; u < n_units; u += unit_step) {
       ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);   // epilogue has drained this accumulator
       ptx::tc_fence_after();
@@ -233,21 +267,26 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
         ptx::mbar_wait(&full_bar[stage], phase);     // TMA bytes have landed
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
-          const uint32_t a_lo = ring_lo + stage * (kStageBytes >> 4);
+          const uint32_t a_lo = ring_lo + stage * (kStageB >> 4);
           const uint32_t b_lo = a_lo + (kABytes >> 4);
 #pragma unroll
           for (int k = 0; k < kBK / kUK; ++k) {
             // advance 16 elements (32 bytes) along K inside the 128-byte swizzle atom: +2 in the address field
-            ptx::umma_bf16_lo(tmem_d, a_lo + 2 * k, b_lo + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            if (k2Sm) ptx::umma_bf16_lo_2sm(tmem_d, a_lo + 2 * k, b_lo + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            else ptx::umma_bf16_lo(tmem_d, a_lo + 2 * k, b_lo + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
           }
           // frees the smem slot (in every CTA of the cluster: the peer multicasts into it) when these MMAs retire
-          if (csize > 1) ptx::umma_commit_multicast(&empty_bar[stage], cmask);
+          if (k2Sm) ptx::umma_commit_2sm(&empty_bar[stage], 3);
+          else if (csize > 1) ptx::umma_commit_multicast(&empty_bar[stage], cmask);
           else ptx::umma_commit(&empty_bar[stage]);
         }
         __syncwarp();
-        if (++stage == kStages) { stage = 0; phase ^= 1; }
+        if (++stage == kNumStages) { stage = 0; phase ^= 1; }
       }
-      if (ptx::elect_one()) ptx::umma_commit(&tfull_bar[as]);   // accumulator complete -> epilogue
+      if (ptx::elect_one()) {                                   // accumulator complete -> epilogue (of both CTAs)
+        if (k2Sm) ptx::umma_commit_2sm(&tfull_bar[as], 3);
+        else ptx::umma_commit(&tfull_bar[as]);
+      }
       __syncwarp();
       if (++as == kAccStages) { as = 0; aphase ^= 1; }
     }
@@ -310,7 +349,7 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       held_tiles = 0;
     };
     for (int u = unit0; u < n_units; u += unit_step) {
-      const int mt = col_stat ? u : (u / p.n_tiles) * static_cast<int>(csize) + static_cast<int>(crank);
+      const int mt = (col_stat ? u : u / p.n_tiles) * static_cast<int>(csize) + static_cast<int>(crank);
       const int m0 = mt * kBM;
       const int n0 = (col_stat ? nt_fixed : u % p.n_tiles) * kBN;
       if (mt >= p.m_tiles) {                       // phantom row tile of an odd pair: just recycle the accumulator
@@ -318,7 +357,7 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
         ptx::tc_fence_after();
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
+        if (lane == 0) release_acc(as);
         if (++as == kAccStages) { as = 0; aphase ^= 1; }
         continue;
       }
@@ -414,7 +453,7 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
                 } else if (release) {
                   ptx::tc_fence_before();              // last TMEM read of the tile: hand the accumulator back
                   __syncwarp();
-                  if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
+                  if (lane == 0) release_acc(as);
                 }
                 const int ci = h >> 1;
                 const int col = (half * kChunksPerWarp + ci) * 32 + (h & 1) * 16;
@@ -467,7 +506,7 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
           if (!released) {                           // no valid row under this warp: just hand the accumulator back
             ptx::tc_fence_before();
             __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
+            if (lane == 0) release_acc(as);
           }
         } else {
 #pragma unroll 1
@@ -480,7 +519,7 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
           if (c == c_end - 1) {
             ptx::tc_fence_before();
             __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
+            if (lane == 0) release_acc(as);
           }
           float y[4][8];                           // [row k: rq + 8k][column slot 2i + e]
 #pragma unroll
@@ -578,7 +617,7 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
           // last TMEM read of this tile by this warp: hand the accumulator back to the MMA warp now
           ptx::tc_fence_before();
           __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
+          if (lane == 0) release_acc(as);
         }
         float y[32];
         const float4* ss4 = reinterpret_cast<const float4*>(ss + c * 32);
@@ -672,7 +711,8 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   if (csize > 1) ptx::cluster_sync();               // no CTA leaves while the peer may still signal its barriers
   if (warp == 1) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, kTmemCols);
+    if (k2Sm) ptx::tmem_dealloc_2sm(tmem_base, kTmemCols);
+    else ptx::tmem_dealloc(tmem_base, kTmemCols);
   }
 }
 
@@ -696,10 +736,10 @@ const char* gemm_init() {
     }
     g_encode = reinterpret_cast<EncodeTiledFn>(fn);
   }
-  cudaError_t e = cudaFuncSetAttribute(xv_tdnn_gemm_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       kSmemBytes);
-  if (e == cudaSuccess)
-    e = cudaFuncSetAttribute(xv_tdnn_gemm_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  cudaError_t e = cudaFuncSetAttribute(xv_tdnn_gemm_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(xv_tdnn_gemm_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(xv_tdnn_gemm_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(xv_tdnn_gemm_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
   if (e != cudaSuccess) {
     snprintf(g_err, sizeof(g_err), "cudaFuncSetAttribute(max dynamic smem) failed: %s", cudaGetErrorString(e));
     return g_err;
@@ -750,7 +790,7 @@ const char* make_tmap_bf16_nd(CUtensorMap* out, const void* base, int rank, cons
 
 namespace {
 // Co-resident 2-CTA clusters of one kernel variant (one CTA per SM; a pair shares a TPC), -1 = not asked yet.
-template <bool kPool>
+template <bool kPool, bool k2Sm>
 int max_cluster_pairs() {
   static int cached = -1;
   if (cached >= 0) return cached;
@@ -764,52 +804,77 @@ int max_cluster_pairs() {
   cfg.attrs = &attr;
   cfg.numAttrs = 1;
   int n = 0;
-  if (cudaOccupancyMaxActiveClusters(&n, xv_tdnn_gemm_kernel<kPool>, &cfg) != cudaSuccess) { cudaGetLastError(); n = 0; }
+  if (cudaOccupancyMaxActiveClusters(&n, xv_tdnn_gemm_kernel<kPool, k2Sm>, &cfg) != cudaSuccess) { cudaGetLastError(); n = 0; }
   cached = n;
-  if (getenv("XV_GEMM_TRACE")) fprintf(stderr, "xv gemm: %d co-resident 2-CTA clusters (pool=%d)\n", n, int(kPool));
+  if (getenv("XV_GEMM_TRACE")) fprintf(stderr, "xv gemm: %d co-resident 2-CTA clusters (pool=%d, 2sm=%d)\n", n, int(kPool), int(k2Sm));
   return cached;
 }
 
 template <bool kPool>
 cudaError_t launch_variant(const GemmPlan& plan, int sm_count, cudaStream_t stream) {
-  const GemmParams& p = plan.p;
-  // cluster pairs (weight tiles multicast) when the pairs cover (nearly) the whole chip; XV_GEMM_CLUSTER=0 disables
+  GemmParams p = plan.p;
+  // XV_GEMM_2SM=0: no cta_group::2 pairs; XV_GEMM_CLUSTER=0: no multicast pairs either (A/B switches)
+  static const int want_2sm = getenv("XV_GEMM_2SM") ? atoi(getenv("XV_GEMM_2SM")) : 1;
   static const int want = getenv("XV_GEMM_CLUSTER") ? atoi(getenv("XV_GEMM_CLUSTER")) : 1;
-  int pairs = 0;
-  // (the pooled kernel is bound by its epilogue; pairing only couples the jitter of two of them: 880 vs 890 TFLOP/s)
-  if (want && p.m_tiles >= 2 && (!kPool || want > 1)) {
-    pairs = max_cluster_pairs<kPool>();
-    if (2 * pairs < sm_count - 4) pairs = 0;
-  }
+  static const int want_cs = getenv("XV_POOL_COLSTAT") ? atoi(getenv("XV_POOL_COLSTAT")) : 1;
   cudaLaunchConfig_t cfg = {};
   cfg.blockDim = dim3(EpiCfg<kPool>::kThreads, 1, 1);
   cfg.dynamicSmemBytes = kSmemBytes;
   cfg.stream = stream;
   cudaLaunchAttribute attr;
-  // pooled layer with plain (unweighted) sums: column-stationary schedule, floor(SMs / n_tiles) CTAs per column tile
-  // (144 of 148 SMs at 6 column tiles; the register-resident sums save more than the four idle SMs cost)
-  static const int want_cs = getenv("XV_POOL_COLSTAT") ? atoi(getenv("XV_POOL_COLSTAT")) : 1;
-  if (kPool && want_cs && pairs == 0 && p.row_weight == nullptr && p.n_tiles <= sm_count) {
-    GemmParams q = p;
+  attr.id = cudaLaunchAttributeClusterDimension;
+  attr.val.clusterDim.x = 2; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+  // pooled layer with plain (unweighted) sums: column-stationary schedule, floor(clusters / n_tiles) clusters per
+  // column tile (144 of 148 SMs at 6 column tiles; the register-resident sums save more than the four idle SMs cost)
+  const bool col_stat = kPool && want_cs && p.row_weight == nullptr;
+  const int groups2 = (p.m_tiles + 1) / 2;         // pairs of row tiles
+  // cta_group::2 pairs pay off where the main loop dominates the tile (measured on one box, 2-SM vs multicast pairs:
+  // tdnn2 K=2560 1341 -> 1465, tdnn3 K=3584 1393 -> 1508, pooled tdnn5 K=512 1074 -> 1104 TFLOP/s); the short-K storing
+  // layers, whose tile time is their epilogue, lose from the cross-SM accumulator handshake (tdnn4 K=512 959 -> 809,
+  // tdnn1 K=192 335 -> 276) and stay on multicast pairs.  XV_GEMM_2SM=2 forces pairs everywhere.
+  const int num_kb = p.taps * p.kb_per_tap;
+  // (the attention-weighted pooled epilogue is the long pole of its tile as well: 9.92 -> 10.53 ms with pairs)
+  if (want_2sm && p.m_tiles >= 2 && ((kPool && p.row_weight == nullptr) || num_kb >= 16 || want_2sm > 1)) {
+    const int pairs = max_cluster_pairs<kPool, true>();
+    if (2 * pairs >= sm_count - 4) {
+      int n = groups2 * p.n_tiles < pairs ? groups2 * p.n_tiles : pairs;
+      if (col_stat && p.n_tiles <= pairs) {
+        int cpn = pairs / p.n_tiles;
+        if (cpn > groups2) cpn = groups2;
+        n = cpn * p.n_tiles;
+        p.col_stationary = 1;
+      }
+      cfg.gridDim = dim3(2 * n, 1, 1);
+      cfg.attrs = &attr;
+      cfg.numAttrs = 1;
+      return cudaLaunchKernelEx(&cfg, xv_tdnn_gemm_kernel<kPool, true>, plan.tm_a, plan.tm_b, plan.tm_out, p);
+    }
+  }
+  if (col_stat && p.n_tiles <= sm_count) {
     int cpn = sm_count / p.n_tiles;
     if (cpn > p.m_tiles) cpn = p.m_tiles;
-    q.col_stationary = 1;
+    p.col_stationary = 1;
     cfg.gridDim = dim3(cpn * p.n_tiles, 1, 1);
-    return cudaLaunchKernelEx(&cfg, xv_tdnn_gemm_kernel<kPool>, plan.tm_a, plan.tm_b, plan.tm_out, q);
+    return cudaLaunchKernelEx(&cfg, xv_tdnn_gemm_kernel<kPool, false>, plan.tm_a, plan.tm_b, plan.tm_out, p);
+  }
+  // multicast pairs (1-SM MMAs, weight tile halves multicast) when the pairs cover (nearly) the whole chip
+  // (the pooled kernel gained nothing from them: 880 vs 890 TFLOP/s)
+  int pairs = 0;
+  if (want && p.m_tiles >= 2 && (!kPool || want > 1)) {
+    pairs = max_cluster_pairs<kPool, false>();
+    if (2 * pairs < sm_count - 4) pairs = 0;
   }
   if (pairs > 0) {
-    const int units = ((p.m_tiles + 1) / 2) * p.n_tiles;
+    const int units = groups2 * p.n_tiles;
     const int n = units < pairs ? units : pairs;
     cfg.gridDim = dim3(2 * n, 1, 1);
-    attr.id = cudaLaunchAttributeClusterDimension;
-    attr.val.clusterDim.x = 2; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
     cfg.attrs = &attr;
     cfg.numAttrs = 1;
   } else {
     const int tiles = p.m_tiles * p.n_tiles;
     cfg.gridDim = dim3(tiles < sm_count ? tiles : sm_count, 1, 1);
   }
-  return cudaLaunchKernelEx(&cfg, xv_tdnn_gemm_kernel<kPool>, plan.tm_a, plan.tm_b, plan.tm_out, p);
+  return cudaLaunchKernelEx(&cfg, xv_tdnn_gemm_kernel<kPool, false>, plan.tm_a, plan.tm_b, plan.tm_out, p);
 }
 }  // namespace
 
