@@ -35,8 +35,15 @@ struct ConvSmem {
   static constexpr uint32_t kRing = kStages * kStage;
   static constexpr uint32_t kParams = kAccStages * BN * 12;
   static constexpr uint32_t kStaging = 2 * 128 * 64;          // one 128-row x 32-column bf16 buffer per column half
-  static constexpr uint32_t kTotal = 1024 + kRing + kParams + kStaging + 256;
+  // cta_group::2 pairs: each CTA stages its 128 rows and ITS half of the weight tile, six stages
+  static constexpr int kStages2 = 6;
+  static constexpr uint32_t kStage2 = kConvABytes + kBBytes / 2;
+  static constexpr uint32_t kRing2 = kStages2 * kStage2;
+  static constexpr uint32_t kRingMax = kRing > kRing2 ? kRing : kRing2;
+  static constexpr uint32_t kTotal = 1024 + kRingMax + kParams + kStaging + 256;
 };
+static_assert(ConvSmem<64>::kStage2 % 1024 == 0 && ConvSmem<128>::kStage2 % 1024 == 0 && ConvSmem<256>::kStage2 % 1024 == 0,
+              "swizzled stage buffers stay 1024-byte aligned");
 static_assert(ConvSmem<256>::kTotal <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
 
 __device__ __forceinline__ uint32_t pack2(float a, float b) {
@@ -48,7 +55,8 @@ __device__ __forceinline__ void unpack2(uint32_t u, float& a, float& b) {
   b = __uint_as_float(u & 0xffff0000u);
 }
 
-template <int BN>
+// k2Sm: one 256 x BN tcgen05.mma.cta_group::2 per K step across the CTA pair (see xv_gemm_sm100.cu).
+template <int BN, bool k2Sm>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                     const __grid_constant__ CUtensorMap tm_out, const __grid_constant__ ConvGemmParams p) {
@@ -56,13 +64,15 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* ring = smem;
-  float2* ep_ss = reinterpret_cast<float2*>(smem + S::kRing);
-  float* ep_sl = reinterpret_cast<float*>(smem + S::kRing + kAccStages * BN * 8);
-  uint8_t* staging = smem + S::kRing + S::kParams;
+  float2* ep_ss = reinterpret_cast<float2*>(smem + S::kRingMax);
+  float* ep_sl = reinterpret_cast<float*>(smem + S::kRingMax + kAccStages * BN * 8);
+  uint8_t* staging = smem + S::kRingMax + S::kParams;
   uint64_t* bars = reinterpret_cast<uint64_t*>(staging + S::kStaging);
+  constexpr int kNumStages = k2Sm ? S::kStages2 : kStages;
+  constexpr uint32_t kStageB = k2Sm ? S::kStage2 : S::kStage;
   uint64_t* full_bar = bars;
-  uint64_t* empty_bar = bars + kStages;
-  uint64_t* tfull_bar = bars + 2 * kStages;
+  uint64_t* empty_bar = bars + kNumStages;
+  uint64_t* tfull_bar = bars + 2 * kNumStages;
   uint64_t* tempty_bar = tfull_bar + kAccStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + kAccStages);
 
@@ -79,19 +89,24 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     ptx::prefetch_tensormap(&tm_a);
     ptx::prefetch_tensormap(&tm_b);
     ptx::prefetch_tensormap(&tm_out);
-    for (int s = 0; s < kStages; ++s) {
+    for (int s = 0; s < kNumStages; ++s) {
       ptx::mbar_init(&full_bar[s], 1);
-      ptx::mbar_init(&empty_bar[s], csize);
+      ptx::mbar_init(&empty_bar[s], k2Sm ? 1 : csize);
     }
     for (int s = 0; s < kAccStages; ++s) {
       ptx::mbar_init(&tfull_bar[s], 1);
-      ptx::mbar_init(&tempty_bar[s], kConvEpiWarps);
+      ptx::mbar_init(&tempty_bar[s], k2Sm ? 2 * kConvEpiWarps : kConvEpiWarps);   // 2-SM: both CTAs' epilogues arrive on the leader's
     }
     ptx::fence_mbar_init();
   }
   if (warp == 1) {
-    ptx::tmem_alloc(tmem_slot, kTmemCols);
-    ptx::tmem_relinquish();
+    if (k2Sm) {
+      ptx::tmem_alloc_2sm(tmem_slot, kTmemCols);
+      ptx::tmem_relinquish_2sm();
+    } else {
+      ptx::tmem_alloc(tmem_slot, kTmemCols);
+      ptx::tmem_relinquish();
+    }
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -105,6 +120,12 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   const int num_kb = p.taps * p.kb_per_tap;
   const int tiles_per_utt = p.tiles_t * p.tiles_f;
   const uint32_t a_bytes = static_cast<uint32_t>(p.tile_rows) * kBK * 2;
+  const uint32_t lead_full0 = k2Sm ? ptx::mapa_u32(ptx::smem_u32(&full_bar[0]), 0) : 0u;
+  const uint32_t lead_tempty0 = k2Sm ? ptx::mapa_u32(ptx::smem_u32(&tempty_bar[0]), 0) : 0u;
+  auto release_acc = [&](uint32_t as) {              // epilogue warp (lane 0) -> MMA warp of the pair's leader
+    if (k2Sm) ptx::mbar_arrive_cluster(lead_tempty0 + as * 8);
+    else ptx::mbar_arrive(&tempty_bar[as]);
+  };
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -122,18 +143,25 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
           const ConvTap tp = p.tap[tap];
           for (int cb = 0; cb < p.kb_per_tap; ++cb) {
             ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-            uint8_t* sa = ring + stage * S::kStage;
+            uint8_t* sa = ring + stage * kStageB;
             uint8_t* sb = sa + kConvABytes;
+            const int kc = tap * p.cin + cb * kBK;
+            if (k2Sm) {
+              if (crank == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * (a_bytes + S::kBBytes / 2));
+              ptx::tma_load_5d_2sm(sa, &tm_a, lead_full0 + stage * 8, tp.c0 + cb * kBK, fo0 + tp.c1, tp.c2, to0 + tp.c3, b);
+              ptx::tma_load_2d_2sm(sb, &tm_b, lead_full0 + stage * 8, kc, n0 + static_cast<int>(crank) * (BN / 2));
+              if (++stage == kNumStages) { stage = 0; phase ^= 1; }
+              continue;
+            }
             ptx::mbar_arrive_expect_tx(&full_bar[stage], a_bytes + S::kBBytes);
             ptx::tma_load_5d(sa, &tm_a, &full_bar[stage], tp.c0 + cb * kBK, fo0 + tp.c1, tp.c2, to0 + tp.c3, b);
-            const int kc = tap * p.cin + cb * kBK;
             if (csize > 1) {
               ptx::tma_load_2d_multicast(sb + crank * (S::kBBytes / 2), &tm_b, &full_bar[stage], kc, n0 + static_cast<int>(crank) * (BN / 2), cmask);
             } else {
               ptx::tma_load_2d(sb, &tm_b, &full_bar[stage], kc, n0);
               ptx::tma_load_2d(sb + S::kBBytes / 2, &tm_b, &full_bar[stage], kc, n0 + BN / 2);
             }
-            if (++stage == kStages) { stage = 0; phase ^= 1; }
+            if (++stage == kNumStages) { stage = 0; phase ^= 1; }
           }
         }
       }
@@ -142,10 +170,11 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     // ===================== MMA issuer =====================
     // warp-uniform loop, one elected lane issues (see xv_gemm_sm100.cu: a lone lane spends ~450 clk per round in
     // its own instruction stream, more than the 270 clk four 128-column MMAs execute in)
-    constexpr uint32_t idesc = ptx::make_idesc_bf16(kBM, BN);
+    constexpr uint32_t idesc = ptx::make_idesc_bf16(k2Sm ? 2 * kBM : kBM, BN);
     const uint32_t ring_lo = ptx::sw128_desc_lo(ptx::smem_u32(ring));
     uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
-    for (int u = unit0; u < n_units; u += unit_step) {
+    const int mma_units = (k2Sm && crank != 0) ? unit0 : n_units;   // the peer's MMA warp only owns the TMEM allocation
+    for (int u = unit0; u < mma_units; u += unit_step) {
       ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
       ptx::tc_fence_after();
       const uint32_t tmem_d = tmem_base + as * BN;
@@ -153,18 +182,24 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
         ptx::mbar_wait(&full_bar[stage], phase);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
-          const uint32_t a_lo = ring_lo + stage * (S::kStage >> 4);
+          const uint32_t a_lo = ring_lo + stage * (kStageB >> 4);
           const uint32_t b_lo = a_lo + (kConvABytes >> 4);
 #pragma unroll
-          for (int k = 0; k < kBK / kUK; ++k)
-            ptx::umma_bf16_lo(tmem_d, a_lo + 2 * k, b_lo + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-          if (csize > 1) ptx::umma_commit_multicast(&empty_bar[stage], cmask);
+          for (int k = 0; k < kBK / kUK; ++k) {
+            if (k2Sm) ptx::umma_bf16_lo_2sm(tmem_d, a_lo + 2 * k, b_lo + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            else ptx::umma_bf16_lo(tmem_d, a_lo + 2 * k, b_lo + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          if (k2Sm) ptx::umma_commit_2sm(&empty_bar[stage], 3);
+          else if (csize > 1) ptx::umma_commit_multicast(&empty_bar[stage], cmask);
           else ptx::umma_commit(&empty_bar[stage]);
         }
         __syncwarp();
-        if (++stage == kStages) { stage = 0; phase ^= 1; }
+        if (++stage == kNumStages) { stage = 0; phase ^= 1; }
       }
-      if (ptx::elect_one()) ptx::umma_commit(&tfull_bar[as]);
+      if (ptx::elect_one()) {
+        if (k2Sm) ptx::umma_commit_2sm(&tfull_bar[as], 3);
+        else ptx::umma_commit(&tfull_bar[as]);
+      }
       __syncwarp();
       if (++as == kAccStages) { as = 0; aphase ^= 1; }
     }
@@ -190,7 +225,7 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
         ptx::tc_fence_after();
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
+        if (lane == 0) release_acc(as);
         if (++as == kAccStages) { as = 0; aphase ^= 1; }
         continue;
       }
@@ -230,7 +265,7 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
         if (ci == kChunks - 1) {
           ptx::tc_fence_before();
           __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
+          if (lane == 0) release_acc(as);
         }
         float y[32];
         const float4* ss4 = reinterpret_cast<const float4*>(ss + c * 32);
@@ -285,19 +320,26 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   if (csize > 1) ptx::cluster_sync();
   if (warp == 1) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, kTmemCols);
+    if (k2Sm) ptx::tmem_dealloc_2sm(tmem_base, kTmemCols);
+    else ptx::tmem_dealloc(tmem_base, kTmemCols);
   }
 }
 
 }  // namespace
 
+template <int BN, bool k2Sm>
+static cudaError_t conv_set_smem() {
+  return cudaFuncSetAttribute(xv_conv_gemm_kernel<BN, k2Sm>, cudaFuncAttributeMaxDynamicSharedMemorySize, ConvSmem<BN>::kTotal);
+}
+
 const char* conv_gemm_init() {
   static char err[160];
-  cudaError_t e = cudaFuncSetAttribute(xv_conv_gemm_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, ConvSmem<64>::kTotal);
-  if (e == cudaSuccess)
-    e = cudaFuncSetAttribute(xv_conv_gemm_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, ConvSmem<128>::kTotal);
-  if (e == cudaSuccess)
-    e = cudaFuncSetAttribute(xv_conv_gemm_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, ConvSmem<256>::kTotal);
+  cudaError_t e = conv_set_smem<64, false>();
+  if (e == cudaSuccess) e = conv_set_smem<128, false>();
+  if (e == cudaSuccess) e = conv_set_smem<256, false>();
+  if (e == cudaSuccess) e = conv_set_smem<64, true>();
+  if (e == cudaSuccess) e = conv_set_smem<128, true>();
+  if (e == cudaSuccess) e = conv_set_smem<256, true>();
   if (e != cudaSuccess) {
     snprintf(err, sizeof(err), "cudaFuncSetAttribute(conv max dynamic smem) failed: %s", cudaGetErrorString(e));
     return err;
@@ -306,7 +348,7 @@ const char* conv_gemm_init() {
 }
 
 namespace {
-template <int BN>
+template <int BN, bool k2Sm>
 int conv_cluster_pairs() {
   static int cached = -1;
   if (cached >= 0) return cached;
@@ -320,7 +362,7 @@ int conv_cluster_pairs() {
   cfg.attrs = &attr;
   cfg.numAttrs = 1;
   int n = 0;
-  if (cudaOccupancyMaxActiveClusters(&n, xv_conv_gemm_kernel<BN>, &cfg) != cudaSuccess) { cudaGetLastError(); n = 0; }
+  if (cudaOccupancyMaxActiveClusters(&n, xv_conv_gemm_kernel<BN, k2Sm>, &cfg) != cudaSuccess) { cudaGetLastError(); n = 0; }
   cached = n;
   return cached;
 }
@@ -329,29 +371,46 @@ template <int BN>
 cudaError_t launch_conv_variant(const ConvGemmPlan& plan, int sm_count, cudaStream_t stream) {
   const ConvGemmParams& p = plan.p;
   static const int want = getenv("XV_CONV_CLUSTER") ? atoi(getenv("XV_CONV_CLUSTER")) : 1;
-  int pairs = 0;
-  if (want && p.m_tiles >= 2) {
-    pairs = conv_cluster_pairs<BN>();
-    if (2 * pairs < sm_count - 4) pairs = 0;
-  }
+  // cta_group::2 pairs for the long-K convolutions (3x3 with >= 128 input channels: >= 18 k-blocks); the short ones keep
+  // multicast pairs (see launch_gemm in xv_gemm_sm100.cu for the measurements behind the rule).  XV_CONV_2SM=0|1|2.
+  // Measured on resnet18 (one box, 1650 MHz: not power-capped like the TDNN step): conv.c512 1460 -> 1465, conv.c256
+  // 1225 -> 1229 TFLOP/s -- within noise; these layers are not bound by weight traffic or operand reads.
+  static const int want_2sm = getenv("XV_CONV_2SM") ? atoi(getenv("XV_CONV_2SM")) : 1;
   cudaLaunchConfig_t cfg = {};
   cfg.blockDim = dim3(kGemmThreads, 1, 1);
   cfg.dynamicSmemBytes = ConvSmem<BN>::kTotal;
   cfg.stream = stream;
   cudaLaunchAttribute attr;
+  attr.id = cudaLaunchAttributeClusterDimension;
+  attr.val.clusterDim.x = 2; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+  const int units = ((p.m_tiles + 1) / 2) * p.n_tiles;
+  if (want_2sm && p.m_tiles >= 2 && (p.taps * p.kb_per_tap >= 16 || want_2sm > 1)) {
+    const int pairs = conv_cluster_pairs<BN, true>();
+    static bool traced = false;
+    if (!traced && getenv("XV_GEMM_TRACE")) { traced = true; fprintf(stderr, "xv conv<%d>: %d co-resident cta_group::2 pairs\n", BN, pairs); }
+    if (2 * pairs >= sm_count - 4) {
+      const int n = units < pairs ? units : pairs;
+      cfg.gridDim = dim3(2 * n, 1, 1);
+      cfg.attrs = &attr;
+      cfg.numAttrs = 1;
+      return cudaLaunchKernelEx(&cfg, xv_conv_gemm_kernel<BN, true>, plan.tm_a, plan.tm_b, plan.tm_out, p);
+    }
+  }
+  int pairs = 0;
+  if (want && p.m_tiles >= 2) {
+    pairs = conv_cluster_pairs<BN, false>();
+    if (2 * pairs < sm_count - 4) pairs = 0;
+  }
   if (pairs > 0) {
-    const int units = ((p.m_tiles + 1) / 2) * p.n_tiles;
     const int n = units < pairs ? units : pairs;
     cfg.gridDim = dim3(2 * n, 1, 1);
-    attr.id = cudaLaunchAttributeClusterDimension;
-    attr.val.clusterDim.x = 2; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
     cfg.attrs = &attr;
     cfg.numAttrs = 1;
   } else {
     const int tiles = p.m_tiles * p.n_tiles;
     cfg.gridDim = dim3(tiles < sm_count ? tiles : sm_count, 1, 1);
   }
-  return cudaLaunchKernelEx(&cfg, xv_conv_gemm_kernel<BN>, plan.tm_a, plan.tm_b, plan.tm_out, p);
+  return cudaLaunchKernelEx(&cfg, xv_conv_gemm_kernel<BN, false>, plan.tm_a, plan.tm_b, plan.tm_out, p);
 }
 }  // namespace
 

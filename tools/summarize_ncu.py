@@ -28,7 +28,7 @@ def launches(path):
             continue
         v = float(x["Metric Value"].replace(",", ""))
         v = {"ns": v / 1e3, "us": v, "ms": v * 1e3, "s": v * 1e6}[x["Metric Unit"]]
-        k = x["Kernel Name"].split("(")[0]
+        k = x["Kernel Name"].split("(")[0].replace(", ", ";")       # template arguments: keep the CSV columns aligned
         a = agg.setdefault(k, [0, 0.0])
         a[0] += 1
         a[1] += v
@@ -46,7 +46,7 @@ def full(path):
     print(",".join(hdr[i] for i in idx))
     print(",".join(units[i] for i in idx))
     for x in rows:
-        print(",".join(x[i].split("(")[0] if hdr[i] == "Kernel Name" else x[i] for i in idx))
+        print(",".join(x[i].split("(")[0].replace(", ", ";") if hdr[i] == "Kernel Name" else x[i].replace(",", "") for i in idx))
 
 
 if __name__ == "__main__":
