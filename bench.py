@@ -290,6 +290,12 @@ def run_ours(args):
         "gemm_share_of_step": gemm_ms / (ms_dev / args.steps) if world == 1 else None,
         "traffic": None,
     }
+    if wl.name == "tdnn":
+        # DRAM bytes per launch from the committed ncu --set full capture of the same kernels at the same batch size
+        # (profiles/rNN_gemm_full_summary.csv: one launch of every layer; never measured under this timed run)
+        tr = ncu_traffic("gemm_full_summary.csv", "xv_tdnn_gemm_kernel")
+        if tr:
+            roofline["traffic"], roofline["traffic_source"] = tr
 
     # ---------------- standalone statistics pooling (HBM roofline; rank 0 at N=1) ----------------
     pooling = None
@@ -348,6 +354,26 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def ncu_traffic(suffix, kernel_substr):
+    """(mean dram__bytes_read.sum + dram__bytes_write.sum per launch, source file) from the newest committed ncu summary
+    under profiles/ whose name ends with `suffix`, over the rows whose kernel name contains `kernel_substr`."""
+    import csv
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_" + suffix)))
+    for path in reversed(files):
+        try:
+            rows = [r for r in csv.reader(l for l in open(path) if not l.startswith("#"))]
+            hdr, units = rows[0], rows[1]
+            ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+            scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+            vals = [float(r[ir]) * scale[units[ir]] + float(r[iw]) * scale[units[iw]] for r in rows[2:] if kernel_substr in r[0]]
+            if vals:
+                return sum(vals) / len(vals), "%s (%d launches)" % (os.path.relpath(path, ROOT), len(vals))
+        except (OSError, ValueError, KeyError, IndexError):
+            continue
+    return None
+
+
 def pooling_roofline(eng, peaks, channels=1500, iters=10):
     """xv_stat_pooling_dev (the drop-in for direct statistics_pooling() callers, model/pooling.py:27-52) on a bf16
     [rows, 1500] matrix of 1.26 GB (10x the L2) cut into utterances with the configs[1] length distribution.
@@ -397,7 +423,7 @@ def pooling_roofline(eng, peaks, channels=1500, iters=10):
             "achieved": gbs, "peak": peaks["hbm"], "unit": "GB/s", "frac": gbs / peaks["hbm"],
             "peak_kind": "copy bandwidth, %s" % peaks["source"], "algorithmic_bytes_per_launch": nbytes,
             "rows": rows, "utterances": n, "channels": channels, "avg_launch_ms": ms / cnt, "launches": cnt,
-            "traffic": None}
+            "traffic": (ncu_traffic("pool_full_summary.csv", "pool_accum_bulk_kernel") or (None, None))[0]}
 
 
 def run_train(args):
