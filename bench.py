@@ -611,6 +611,9 @@ def main():
     ap.add_argument("--utts", type=int, default=0, help="utterances per GPU (default = the configs[1] set; "
                     "smaller values are for profiling runs only)")
     args = ap.parse_args()
+    # stdout carries ONE JSON line: NCCL's own "NCCL version ..." banner (NCCL_DEBUG=VERSION, set on some boxes) goes there too
+    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
     if args.impl == "reference":
