@@ -347,7 +347,7 @@ def run_ours(args):
             line["pooling_roofline"] = pooling
         if cpu is not None:
             line["cpu_baseline"] = cpu
-        print(json.dumps(line), flush=True)
+        emit(line)
     pin.close()
     eng.close()
     if dist is not None:
@@ -520,7 +520,7 @@ def run_train(args):
                          "note": "whole-step FLOPs / whole-step time" + ("" if mixed else "; this path runs on FFMA, not on the tensor cores")},
             "loss_first_last": [losses[0], losses[-1]],
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     pin.close()
     eng.close()
     if dist is not None:
@@ -588,7 +588,26 @@ def run_reference(args):
                        "sample": "bounded sample of that workload per step (see cpu_baseline.sample)"},
             "cpu_baseline": cpu,
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    """stdout carries exactly ONE JSON line: keep the real stdout aside and point fd 1 at stderr, so that anything a
+    library prints there (NCCL's version banner, a stray warning) cannot land beside it."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
 
 
 def main():
@@ -611,9 +630,7 @@ def main():
     ap.add_argument("--utts", type=int, default=0, help="utterances per GPU (default = the configs[1] set; "
                     "smaller values are for profiling runs only)")
     args = ap.parse_args()
-    # stdout carries ONE JSON line: NCCL's own "NCCL version ..." banner (NCCL_DEBUG=VERSION, set on some boxes) goes there too
-    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
-        os.environ["NCCL_DEBUG"] = "WARN"
+    claim_stdout()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
     if args.impl == "reference":
