@@ -338,6 +338,18 @@ __device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
   asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
   return d;
 }
+// relu(lo), relu(hi) of a packed fp32 pair -> one bf16x2 word (lo in the low half): conversion and ReLU in ONE instruction
+__device__ __forceinline__ uint32_t f2_relu_bf16x2(uint64_t v) {
+  uint32_t r;
+  asm("{\n\t"
+      ".reg .f32 lo, hi;\n\t"
+      "mov.b64 {lo, hi}, %1;\n\t"
+      "cvt.rn.relu.bf16x2.f32 %0, hi, lo;\n\t"
+      "}\n"
+      : "=r"(r)
+      : "l"(v));
+  return r;
+}
 __device__ __forceinline__ uint64_t f2_mul(uint64_t a, uint64_t b) {
   uint64_t d;
   asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
