@@ -842,7 +842,7 @@ int max_cluster_pairs() {
 template <bool kPool>
 cudaError_t launch_variant(const GemmPlan& plan, int sm_count, cudaStream_t stream) {
   GemmParams p = plan.p;
-  // XV_GEMM_2SM=0: no cta_group::2 pairs; XV_GEMM_CLUSTER=0: no multicast pairs either (A/B switches)
+  // XV_GEMM_2SM=0: no cta_group::2 pairs (multicast pairs instead); XV_GEMM_CLUSTER=0: no multicast pairs either (A/B switches)
   static const int want_2sm = getenv("XV_GEMM_2SM") ? atoi(getenv("XV_GEMM_2SM")) : 1;
   static const int want = getenv("XV_GEMM_CLUSTER") ? atoi(getenv("XV_GEMM_CLUSTER")) : 1;
   static const int want_cs = getenv("XV_POOL_COLSTAT") ? atoi(getenv("XV_POOL_COLSTAT")) : 1;
@@ -857,13 +857,12 @@ cudaError_t launch_variant(const GemmPlan& plan, int sm_count, cudaStream_t stre
   // column tile (144 of 148 SMs at 6 column tiles; the register-resident sums save more than the four idle SMs cost)
   const bool col_stat = kPool && want_cs && p.row_weight == nullptr;
   const int groups2 = (p.m_tiles + 1) / 2;         // pairs of row tiles
-  // cta_group::2 pairs pay off where the main loop dominates the tile (measured on one box, 2-SM vs multicast pairs:
-  // tdnn2 K=2560 1341 -> 1465, tdnn3 K=3584 1393 -> 1508, pooled tdnn5 K=512 1074 -> 1104 TFLOP/s); the short-K storing
-  // layers, whose tile time is their epilogue, lose from the cross-SM accumulator handshake (tdnn4 K=512 959 -> 809,
-  // tdnn1 K=192 335 -> 276) and stay on multicast pairs.  XV_GEMM_2SM=2 forces pairs everywhere.
-  const int num_kb = p.taps * p.kb_per_tap;
-  // (the attention-weighted pooled epilogue is the long pole of its tile as well: 9.92 -> 10.53 ms with pairs)
-  if (want_2sm && p.m_tiles >= 2 && ((kPool && p.row_weight == nullptr) || num_kb >= 16 || want_2sm > 1)) {
+  // cta_group::2 pairs for every layer with at least two row tiles.  Measured on one box, pairs vs multicast pairs:
+  // tdnn2 K=2560 1341 -> 1465, tdnn3 K=3584 1393 -> 1508, pooled tdnn5 K=512 1074 -> 1216, tdnn4 K=512 966 -> 1084,
+  // tdnn1 K=192 363 -> 381 TFLOP/s, attention key layer 0 5.82 -> 5.46 ms, weighted pooled layer 10.65 -> 9.67 ms.
+  // (The short-K layers LOST while the epilogues handed the accumulator back with a cluster-scope RELEASE arrive: its
+  // memory barrier sat on the MMA warp's critical path -- see ptx::mbar_arrive_cluster.)
+  if (want_2sm && p.m_tiles >= 2) {
     const int pairs = max_cluster_pairs<kPool, true>();
     if (2 * pairs >= sm_count - 4) {
       int n = groups2 * p.n_tiles < pairs ? groups2 * p.n_tiles : pairs;
