@@ -161,7 +161,8 @@ int   xv_gemm_bf16_async(xv_ctx* ctx, const void* a_dev, int64_t a_rows, int32_t
 /* ---- training step (BASELINE.json config 5) ------------------------------------------------------------
  * Replaces sess.run(train_op, {features, labels, is_training: True, global_step, learning_rate}) of
  * Trainer.train / TrainerMGPU (model/trainer.py:590-673, 1133-1248) for network_type tdnn + statistics_pooling with
- * loss_func softmax | additive_margin_softmax (model/loss.py:9-48, 201-286), optimizer sgd | momentum.
+ * loss_func softmax | additive_margin_softmax (model/loss.py:9-48, 201-286), optimizer sgd | momentum | adam
+ * (model/trainer.py:225-246), clip_gradient / clip_gradient_norm = per-variable tf.clip_by_norm (model/trainer.py:529-533).
  * The context must be created with "precision":"fp32"; every variable the reference's graph would hold
  * (tdnn/..., softmax/output/kernel [512, num_speakers] (+ /bias for softmax), BN moving statistics) is first given
  * with xv_set_weight; xv_train_init copies them into the flat parameter buffer that the step updates in place. */
