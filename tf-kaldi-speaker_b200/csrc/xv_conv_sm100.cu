@@ -217,6 +217,8 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
     const int t_l = r / p.fb;
     const int f_l = r - t_l * p.fb;
     uint32_t as = 0, aphase = 0;
+    int slot_n0_a = -1, slot_n0_b = -1;          // column tile whose parameters each accumulator stage's slot holds
+    bool bar_prev_tile = true;
     for (int u = unit0; u < n_units; u += unit_step) {
       const int mt = (u / p.n_tiles) * static_cast<int>(csize) + static_cast<int>(crank);
       const int n0 = (u % p.n_tiles) * BN;
@@ -227,6 +229,7 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
         __syncwarp();
         if (lane == 0) release_acc(as);
         if (++as == kAccStages) { as = 0; aphase ^= 1; }
+        bar_prev_tile = false;
         continue;
       }
       const int b = mt / tiles_per_utt;
@@ -236,11 +239,18 @@ xv_conv_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       const int fo0 = (rem - tt * p.tiles_f) * p.fb;
       float2* ss = ep_ss + as * BN;
       float* sl = ep_sl + as * BN;
-      if (etid < BN) {
-        ss[etid] = make_float2(__ldg(p.scale + n0 + etid), __ldg(p.shift + n0 + etid));
-        sl[etid] = __ldg(p.slope + n0 + etid);
+      if ((as ? slot_n0_b : slot_n0_a) != n0) {   // this stage's slot holds another column tile's parameters (see xv_gemm_sm100.cu)
+        if (!bar_prev_tile) asm volatile("bar.sync 1, 256;" ::: "memory");
+        bar_prev_tile = true;
+        if (etid < BN) {
+          ss[etid] = make_float2(__ldg(p.scale + n0 + etid), __ldg(p.shift + n0 + etid));
+          sl[etid] = __ldg(p.slope + n0 + etid);
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (as) slot_n0_b = n0; else slot_n0_a = n0;
+      } else {
+        bar_prev_tile = false;
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after();
       const bool row_ok = r < p.tile_rows && (to0 + t_l) < p.t_out;

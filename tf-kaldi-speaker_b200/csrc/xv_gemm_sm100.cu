@@ -324,6 +324,9 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");
     };
     if (col_stat) fill_params(ep_ss, ep_sl, ep_sq, nt_fixed * kBN);       // the column tile never changes
+    int slot_n0_a = -1, slot_n0_b = -1;          // column tile whose parameters each accumulator stage's slot holds
+    bool bar_prev_tile = true;                   // (nothing to protect before the first tile)
+    static_assert(kAccStages == 2, "one parameter slot per accumulator stage");
     // pooling sums carried in registers from tile to tile (packed pairs: [chunk][i] = columns 8i + 2(lane&3) + {0,1})
     uint64_t acc_s[kPool ? kChunksPerWarp : 1][4], acc_q[kPool ? kChunksPerWarp : 1][4];
 #pragma unroll
@@ -365,13 +368,25 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
         __syncwarp();
         if (lane == 0) release_acc(as);
         if (++as == kAccStages) { as = 0; aphase ^= 1; }
+        bar_prev_tile = false;
         continue;
       }
       // per-tile epilogue parameters -> smem (double buffered by accumulator stage)
       float2* ss = ep_ss + (col_stat ? 0 : as * kBN);
       float* sl = ep_sl + (col_stat ? 0 : as * kBN);
       float* sq = ep_sq + (col_stat ? 0 : as * kBN);
-      if (!col_stat) fill_params(ss, sl, sq, n0);
+      // The slot of this accumulator stage still holds the parameters of column tile slot_n0_{a,b}: a CTA whose units keep
+      // one column tile (n_tiles divides the unit stride, e.g. 2 column tiles over 74 pairs) fills each slot once and
+      // never meets the 256-thread barrier again (8 % of the storing epilogue's stall samples).  A slot is rewritten only
+      // after a barrier every epilogue warp has passed since its last use: the previous tile's, else one taken here.
+      if (!col_stat && (as ? slot_n0_b : slot_n0_a) != n0) {
+        if (!bar_prev_tile) asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");
+        bar_prev_tile = true;
+        fill_params(ss, sl, sq, n0);
+        if (as) slot_n0_b = n0; else slot_n0_a = n0;
+      } else {
+        bar_prev_tile = false;
+      }
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after();
 
