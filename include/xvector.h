@@ -163,8 +163,10 @@ int   xv_gemm_bf16_async(xv_ctx* ctx, const void* a_dev, int64_t a_rows, int32_t
  * Trainer.train / TrainerMGPU (model/trainer.py:590-673, 1133-1248) for network_type tdnn + statistics_pooling with
  * loss_func softmax | additive_margin_softmax (model/loss.py:9-48, 201-286), optimizer sgd | momentum | adam
  * (model/trainer.py:225-246), clip_gradient / clip_gradient_norm = per-variable tf.clip_by_norm (model/trainer.py:529-533).
- * The context must be created with "precision":"fp32"; every variable the reference's graph would hold
- * (tdnn/..., softmax/output/kernel [512, num_speakers] (+ /bias for softmax), BN moving statistics) is first given
+ * The context's "precision" picks the arithmetic: "bf16" (product path) runs the frame-layer GEMMs (forward, data and
+ * weight gradients) on tcgen05 with bf16 operands, fp32 accumulation and fp32 master weights; "fp32" is the
+ * validation-grade path (SIMT FFMA GEMMs).  Both share every other kernel.  Every variable the reference's graph would
+ * hold (tdnn/..., softmax/output/kernel [512, num_speakers] (+ /bias for softmax), BN moving statistics) is first given
  * with xv_set_weight; xv_train_init copies them into the flat parameter buffer that the step updates in place. */
 int  xv_train_init(xv_ctx* ctx, int32_t num_speakers);
 /* One step on this rank's slice of the batch: feats [batch, frames, D] fp32 (host or device), labels [batch]
@@ -177,11 +179,21 @@ int  xv_train_step(xv_ctx* ctx, const float* feats, const int32_t* labels, int32
 /* Current value / last averaged gradient (including the wd*W regularisation term) of a variable, by TF name. */
 int  xv_train_get_weight(xv_ctx* ctx, const char* tf_name, float* host, int64_t capacity);
 int  xv_train_get_grad(xv_ctx* ctx, const char* tf_name, float* host, int64_t capacity);
+/* The variables the training state holds (what tf.train.Saver would write, model/trainer.py:583): count (-1 without a
+ * training state), then name i (in name order) and its element count. */
+int  xv_train_num_variables(xv_ctx* ctx);
+int  xv_train_variable_name(xv_ctx* ctx, int32_t i, char* buf, size_t buf_size, int64_t* size);
 /* Data parallelism: rank 0 creates a 128-byte ncclUniqueId (xv_comm_unique_id), the launcher hands it to every
  * rank, each rank calls xv_comm_init(ctx, id, rank, world) after xv_train_init.  NCCL is loaded at run time
  * (libnccl.so.2, the copy already mapped by the process if there is one).  world == 1 needs no NCCL. */
 int  xv_comm_unique_id(xv_ctx* ctx, void* out128);
 int  xv_comm_init(xv_ctx* ctx, const void* nccl_unique_id, int rank, int world);
+/* The exchange step of xv_train_step as configured: this rank, the world size, the fp32 elements every step all-reduces
+ * (gradients + moving statistics + loss slot) and the number of buckets they travel in (3, launched on a side stream
+ * as the backward pass retires them; 1 when world == 1 or XV_TRAIN_OVERLAP=0).  A step that fails on one rank aborts
+ * the communicator (ncclCommAbort); the peers see an asynchronous NCCL error instead of a hang (ncclCommGetAsyncError is
+ * polled while a step is waited for) and every context of the job must be re-created. */
+int  xv_comm_info(xv_ctx* ctx, int32_t* rank, int32_t* world, int64_t* grad_elems, int32_t* buckets);
 
 /* One 2-D convolution of the ResNet-18 front end on the implicit-GEMM tcgen05 path (kernel-level tests and the
  * conv roofline bench): replaces tf.layers.conv2d(padding='same', use_bias=False) + batch_normalization

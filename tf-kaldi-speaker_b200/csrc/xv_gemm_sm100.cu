@@ -688,6 +688,35 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
             for (int j = 0; j < 32; ++j) y[j] = tanhf(y[j]);
           }
         }
+        if (p.stat_out != nullptr) {
+          // Batch-norm batch statistics of the training forward pass (tf.layers.batch_normalization(training=True),
+          // model/tdnn.py:49-52): column sums of y and y^2 over this warp's VALID rows.  x[0..31] = masked y, x[32..63] =
+          // its square; a halving butterfly over the five lane bits (62 shuffles) leaves every lane with two adjacent
+          // columns of either the sum (lane bit 4 = 0) or the sum of squares (bit 4 = 1): two fp64 atomics per lane
+          // (order-independent at fp32 precision).
+          const float mk = (row_ok && static_cast<int32_t>(static_cast<uint32_t>(row) % static_cast<uint32_t>(p.stat_t)) < p.stat_valid) ? 1.f : 0.f;
+          float x[64];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            x[j] = y[j] * mk;
+            x[32 + j] = x[j] * x[j];
+          }
+#pragma unroll
+          for (int h = 32; h >= 2; h >>= 1) {              // lane bit h/2 ... : masks 16, 8, 4, 2, 1
+            const bool up = (lane & (h >> 1)) != 0;
+#pragma unroll
+            for (int j = 0; j < h; ++j) {
+              const float send = up ? x[j] : x[j + h];
+              const float keep = up ? x[j + h] : x[j];
+              x[j] = keep + __shfl_xor_sync(0xffffffffu, send, h >> 1);
+            }
+          }
+          const int kind = (lane >> 4) & 1;
+          const int col = ((lane >> 3) & 1) * 16 + ((lane >> 2) & 1) * 8 + ((lane >> 1) & 1) * 4 + (lane & 1) * 2;
+          double* dst = p.stat_out + static_cast<size_t>(kind) * p.stat_ld + n0 + c * 32 + col;
+          atomicAdd(dst, static_cast<double>(x[0]));
+          atomicAdd(dst + 1, static_cast<double>(x[1]));
+        }
         if (dots) {
           const float4* q4 = reinterpret_cast<const float4*>(sq + c * 32);
           const int bnd = dot_bound - ci * 32;            // columns of this chunk from `bnd` on belong to the next head

@@ -61,6 +61,11 @@ struct GemmParams {
   double* dot_out = nullptr;      // [heads][dot_ld], zeroed by the caller
   int32_t dot_ld = 0;
   float dot_scale = 1.f;
+  // fused batch-norm batch statistics (training forward, storing kernel): stat_out[0][n] += sum_r y[r, n],
+  // stat_out[1][n] += sum_r y[r, n]^2 over the rows with (r mod stat_t) < stat_valid; [2][stat_ld] fp64, zeroed by the caller
+  double* stat_out = nullptr;
+  int32_t stat_ld = 0;
+  int32_t stat_t = 1, stat_valid = 1;
 };
 
 struct GemmPlan {
