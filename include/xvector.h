@@ -47,6 +47,10 @@ typedef struct xv_ctx xv_ctx;
  * Lazily-injected defaults (num_nodes_pooling_layer=1500 model/tdnn.py:114-116, ...) are applied. */
 int  xv_create(int device, const char* config_json, xv_ctx** out);
 void xv_destroy(xv_ctx* ctx);
+/* Parses config_json and builds the layer plan exactly as xv_create does, on the host only (no device needed): XV_OK
+ * and a one-line summary ("scope=tdnn;pooling=...;frame_layers=5;...") in buf, or the error xv_create would give
+ * (message through xv_last_error(NULL)).  Every reference nnet_conf JSON must get through (misc/utils.py:13-41). */
+int  xv_config_check(const char* config_json, char* buf, size_t buf_size);
 /* ctx may be NULL: returns the calling thread's last error from xv_create. */
 const char* xv_last_error(xv_ctx* ctx);
 

@@ -212,13 +212,15 @@ def tdnn(features, params, w):
     """model/tdnn.py:10-181, inference.  features [B,T,D] -> (last layer output, endpoints)."""
     ep = OrderedDict()
     x = np.asarray(features, np.float64)
+    # model/tdnn.py:38: features are expanded to [b, 1, l, d] for the three conv2d layers, so their endpoints are rank 4;
+    # only tdnn3_relu is overwritten with the squeezed rank-3 tensor (:94-96)
     for i in (1, 2, 3):
         x = conv_1xk(x, w["tdnn/tdnn%d_conv/kernel" % i], w["tdnn/tdnn%d_conv/bias" % i])
-        ep["tdnn%d_conv" % i] = x
+        ep["tdnn%d_conv" % i] = x[:, None]
         x = batch_norm_infer(x, w, "tdnn/tdnn%d_bn" % i)
-        ep["tdnn%d_bn" % i] = x
+        ep["tdnn%d_bn" % i] = x[:, None]
         x = activation(x, params, w, "tdnn/tdnn%d_relu" % i)
-        ep["tdnn%d_relu" % i] = x
+        ep["tdnn%d_relu" % i] = x[:, None] if i < 3 else x
     if "num_nodes_pooling_layer" not in params.dict:
         params.dict["num_nodes_pooling_layer"] = 1500
     for i in (4, 5):

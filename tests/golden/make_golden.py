@@ -132,6 +132,7 @@ def main():
         g[tag + "/x"] = x
         for node in ("tdnn1_relu", "tdnn3_relu", "tdnn5_relu", "pooling", "tdnn6_dense", "output"):
             v = ep[node]
+            v = v[:, 0] if v.ndim == 4 else v            # conv2d endpoints are [B, 1, T', 512]
             g[tag + "/" + node] = v if v.ndim < 3 else v[:, ::7, ::37]     # subsample frame-level nodes
     np.savez_compressed(os.path.join(HERE, "tdnn_small_golden.npz"), **g)
     print("wrote tdnn_small_golden.npz")

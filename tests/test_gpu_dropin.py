@@ -31,9 +31,12 @@ def test_tdnn_function_signature_and_endpoints(precision):
         assert list(endpoints.keys()) == list(ref_ep.keys())
         assert params.num_nodes_pooling_layer == 1500 and params.last_layer_no_bn is False
         assert out.shape == ref_out.shape and max_rel(out, ref_out) <= TOL[precision]
-        for node in ("tdnn1_conv", "tdnn3_relu", "tdnn5_bn", "pooling", "tdnn6_dense"):
+        for node in ("tdnn1_conv", "tdnn2_relu", "tdnn3_bn", "tdnn3_relu", "tdnn5_bn", "pooling", "tdnn6_dense"):
             assert endpoints[node].shape == ref_ep[node].shape
             assert tensor_rel(endpoints[node], ref_ep[node]) <= TOL[precision], node
+        # the reference's shapes (model/tdnn.py:38-96): conv2d endpoints keep the expanded axis, tdnn3_relu is squeezed
+        assert endpoints["tdnn1_conv"].shape == (3, 1, 56, 512) and endpoints["tdnn2_relu"].shape == (3, 1, 52, 512)
+        assert endpoints["tdnn3_bn"].shape == (3, 1, 46, 512) and endpoints["tdnn3_relu"].shape == (3, 46, 512)
     V.clear_engines()
 
 
@@ -124,6 +127,13 @@ def test_trainer_predict_and_extractor(tmp_path, precision):
     trainer.set_embedding("tdnn4_relu")
     f = trainer.predict(x[0])
     assert f.shape == (66, 512) and tensor_rel(f, numpy_ref.predict(x[0], oparams, w, 30, node="tdnn4_relu")) <= tol
+    # conv2d endpoints keep the reference's expanded axis (model/tdnn.py:38-91): [1, T', 512] for a rank-2 input
+    trainer.set_embedding("tdnn1_relu")
+    f = trainer.predict(x[0])
+    ref = numpy_ref.predict(x[0], oparams, w, 30, node="tdnn1_relu")
+    assert f.shape == ref.shape == (1, 76, 512) and tensor_rel(f, ref) <= tol
+    f = trainer.predict(x)
+    assert f.shape == (2, 1, 76, 512)
     trainer.set_embedding("tdnn6_dense")
     # extractor: skip / whole / chunked, with and without normalisation
     lens = [20, 120, 530, 260]

@@ -116,6 +116,25 @@ def test_stat_pooling_large_matches_oracle(eng):
         assert tensor_rel(out[u], ref) < 3e-5      # fp32 one-pass sums over 6000 rows; end-to-end budget is 1e-4
 
 
+def test_stat_pooling_matches_reference_golden(eng):
+    """Golden vectors = [np.mean | np.std] of the reference's compute_phone_pooling (model/test_utils.py:1110-1112);
+    channels whose variance is exactly 0 take the 1e-12 floor of model/pooling.py:46-47.  fp32 kernel: errors are judged
+    on the channel's scale max(|mean|, std) (one channel carries a 1e3 offset, i.e. fp32 inputs quantised at 6e-5)."""
+    g = np.load(os.path.join(GOLDEN, "statpool_golden.npz"))
+    for name in sorted({k.split("/")[0] for k in g.files}):
+        x, p1 = g[name + "/x"], g[name + "/p1"]
+        b, l, c = x.shape
+        cu = (np.arange(b + 1) * l).astype(np.int32)
+        out = eng.stat_pooling(x.reshape(b * l, c).astype(np.float32), cu, dtype="fp32").astype(np.float64)
+        scale = np.maximum(np.abs(p1[:, :c]), p1[:, c:])
+        scale = np.maximum(scale, 1e-3)
+        assert (np.abs(out[:, :c] - p1[:, :c]) / scale).max() < 2e-6, name
+        live = p1[:, c:] > 1e-5
+        assert (np.abs(out[:, c:] - p1[:, c:])[live] / scale[live]).max() < 2e-5, name
+        if (~live).any():
+            np.testing.assert_allclose(out[:, c:][~live], 1e-6, rtol=1e-3)
+
+
 def test_attention_pooling_matches_reference_golden(eng):
     """Golden vectors = outputs of the reference's compute_self_attention (model/test_utils.py:321-392)."""
     g = np.load(os.path.join(GOLDEN, "attention_golden.npz"))

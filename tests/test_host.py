@@ -30,6 +30,39 @@ def test_library_exports_every_declared_symbol():
     assert b"sm_100a" in lib.xv_version()
 
 
+NNET_CONF = sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "nnet_conf", "*.json")))
+
+
+def test_all_reference_nnet_conf_load_through_params_and_the_library_parser():
+    """all 42 egs/*/nnet_conf/*.json (fixtures copied by tests/golden/make_nnet_conf_fixtures.py) load
+    through Params AND through the library's own JSON reader + plan builder (xv_config_check = xv_create minus the
+    device).  The raw file text is used (comment-like "Note" keys, exponent floats, lists), with feature_dim spliced in."""
+    from xvector_b200.engine import config_json
+    assert len(NNET_CONF) == 42
+    lib = xvector_b200.load()
+    buf = C.create_string_buffer(512)
+    seen = set()
+    for path in NNET_CONF:
+        params = Params(path)
+        assert params.network_type in ("tdnn", "resnet_18") and "loss_func" in params.dict
+        dim = 40 if params.network_type == "resnet_18" else 30
+        raw = open(path).read()
+        raw = raw[:raw.index("{") + 1] + '"feature_dim": %d,' % dim + raw[raw.index("{") + 1:]
+        for text in (raw, config_json(params.dict, dim)):
+            rc = lib.xv_config_check(text.encode("utf-8"), buf, 512)
+            assert rc == 0, "%s: %s" % (os.path.basename(path), lib.xv_last_error(None))
+            summary = dict(kv.split("=") for kv in buf.value.decode().split(";"))
+            assert summary["embedding_node"] == params.dict.get("embedding_node", "tdnn6_dense")
+            assert summary["pooling"] == params.pooling_type
+            assert int(summary["pooled_dim"]) == 3000
+        seen.add((params.network_type, params.loss_func, params.pooling_type))
+    assert ("tdnn", "softmax", "self_attention") in seen and ("resnet_18", "softmax", "statistics_pooling") in seen
+    # what the reference rejects, the parser rejects with the reference's words (model/trainer.py:109-110)
+    rc = lib.xv_config_check(b'{"network_type": "ftdnn", "pooling_type": "statistics_pooling", "feature_dim": 30}', buf, 512)
+    assert rc == _lib.XV_EUNSUPPORTED and b"Not implement ftdnn network" in lib.xv_last_error(None)
+    assert lib.xv_config_check(b'{"network_type": "tdnn", "feature_dim": 30', buf, 512) == _lib.XV_EINVAL
+
+
 def test_create_fails_loudly_without_gpu_or_with_bad_config():
     lib = xvector_b200.load()
     ctx = C.c_void_p()

@@ -21,6 +21,26 @@ def test_attention_core_matches_reference_numpy_statement():
         np.testing.assert_allclose(w.sum(axis=2), 1.0, rtol=1e-12)
 
 
+def test_stat_pooling_matches_reference_numpy_statement():
+    """Pinned: p1 = [np.mean | np.std] of the reference's compute_phone_pooling (model/test_utils.py:1110-1112), and the
+    same statistic from its explicit loops (:1114-1128, +1e-16 under the root).  np.std has no variance floor; where the
+    variance is exactly 0 the oracle must give the floor of model/pooling.py:46-47 (sqrt(1e-12))."""
+    g = np.load(os.path.join(GOLDEN, "statpool_golden.npz"))
+    names = sorted({k.split("/")[0] for k in g.files})
+    assert names == ["offset", "relu_like", "small"]
+    for n in names:
+        x, p1, loops = g[n + "/x"], g[n + "/p1"], g[n + "/loops"]
+        c = x.shape[2]
+        out = numpy_ref.statistics_pooling(x)
+        np.testing.assert_allclose(out[:, :c], p1[:, :c], rtol=1e-12, atol=1e-12)
+        live = p1[:, c:] > 1e-5
+        assert (~live).any() == (n != "small")
+        np.testing.assert_allclose(out[:, c:][live], p1[:, c:][live], rtol=1e-9)
+        np.testing.assert_allclose(out[:, c:][~live], 1e-6, rtol=1e-9)          # VAR2STD_EPSILON floor
+        np.testing.assert_allclose(out[:, :c], loops[:, :c], rtol=1e-10, atol=1e-10)
+        np.testing.assert_allclose(out[:, c:][live], loops[:, c:][live], rtol=1e-6)
+
+
 def test_oracle_regression_fixtures():
     g = np.load(os.path.join(GOLDEN, "tdnn_small_golden.npz"))
     for tag, cfg in (("stat", synth.TDNN_STAT_CONFIG), ("att", dict(synth.TDNN_ATT_CONFIG, att_num_heads=3))):
@@ -29,6 +49,7 @@ def test_oracle_regression_fixtures():
         _, ep = numpy_ref.entire_network(g[tag + "/x"], numpy_ref.OracleParams(**cfg), w)
         for node in ("tdnn1_relu", "tdnn3_relu", "tdnn5_relu", "pooling", "tdnn6_dense", "output"):
             v = ep[node]
+            v = v[:, 0] if v.ndim == 4 else v            # conv2d endpoints: [B, 1, T', 512] (model/tdnn.py:38-91)
             v = v if v.ndim < 3 else v[:, ::7, ::37]
             np.testing.assert_allclose(v, g[tag + "/" + node], rtol=1e-10, atol=1e-12)
 
@@ -68,7 +89,8 @@ def test_tdnn_shapes_context_and_defaults():
     p = numpy_ref.OracleParams(**cfg)
     x = synth.config1_features(1, 40, 30)
     out, ep = numpy_ref.entire_network(x, p, w)
-    assert ep["tdnn1_relu"].shape == (1, 36, 512) and ep["tdnn2_relu"].shape == (1, 32, 512)
+    assert ep["tdnn1_relu"].shape == (1, 1, 36, 512) and ep["tdnn2_relu"].shape == (1, 1, 32, 512)    # model/tdnn.py:38-91
+    assert ep["tdnn3_bn"].shape == (1, 1, 26, 512)
     assert ep["tdnn3_relu"].shape == (1, 26, 512) and ep["tdnn5_relu"].shape == (1, 26, 1500)
     assert ep["pooling"].shape == (1, 3000) and ep["tdnn6_dense"].shape == (1, 512) and out.shape == (1, 512)
     # lazily injected defaults are visible on params afterwards (model/tdnn.py:114-116,152-154)

@@ -29,6 +29,7 @@ _f32p = C.POINTER(C.c_float)
 PROTOTYPES = {
     "xv_create": (C.c_int, [C.c_int, C.c_char_p, C.POINTER(_p)]),
     "xv_destroy": (None, [_p]),
+    "xv_config_check": (C.c_int, [C.c_char_p, C.c_char_p, C.c_size_t]),
     "xv_last_error": (C.c_char_p, [_p]),
     "xv_set_weight": (C.c_int, [_p, C.c_char_p, _f32p, _i64p, C.c_int]),
     "xv_finalize_weights": (C.c_int, [_p]),

@@ -566,6 +566,38 @@ int xv_create(int device, const char* config_json, xv_ctx** out) {
   return XV_OK;
 }
 
+// Parses a config exactly as xv_create does and builds the layer plan on the host only (no device is touched): the
+// check a caller can run anywhere (tests/test_host.py feeds it the reference's 42 nnet_conf JSONs).
+int xv_config_check(const char* config_json, char* buf, size_t buf_size) {
+  if (!config_json) return fail(nullptr, XV_EINVAL, "xv_config_check: null argument");
+  xv_ctx* c = new xv_ctx();
+  std::string perr;
+  JParser parser(config_json);
+  if (!parser.parse(&c->cfg, &perr) || c->cfg.type != JValue::Obj) {
+    fail(nullptr, XV_EINVAL, "config JSON: %s", perr.empty() ? "top level must be an object" : perr.c_str());
+    delete c;
+    return XV_EINVAL;
+  }
+  c->dim = jint(c->cfg, "feature_dim", 0);
+  if (c->dim <= 0) {
+    fail(nullptr, XV_EINVAL, "config needs a positive \"feature_dim\"");
+    delete c;
+    return XV_EINVAL;
+  }
+  const int rc = build_plan(c);
+  if (rc != XV_OK) {
+    g_create_err = c->err;
+    delete c;
+    return rc;
+  }
+  if (buf && buf_size > 0)
+    snprintf(buf, buf_size, "scope=%s;pooling=%s;frame_layers=%zu;seg_layers=%zu;convs=%zu;nodes=%zu;context=%d;pooled_dim=%d;embedding_node=%s",
+             c->scope.c_str(), c->pooling_type.c_str(), c->frame_layers.size(), c->seg_layers.size(), c->convs.size(),
+             c->nodes.size(), c->total_context, c->pooled_dim, c->embedding_node.c_str());
+  delete c;
+  return XV_OK;
+}
+
 void xv_destroy(xv_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);

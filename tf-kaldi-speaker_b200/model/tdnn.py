@@ -34,6 +34,11 @@ class Endpoints(OrderedDict):
         return [self[k] for k in self.keys()]
 
 
+# tdnn() runs its three conv2d layers on [b, 1, l, d] (model/tdnn.py:38), so these endpoints are rank 4 [B, 1, T', 512];
+# tdnn3_relu is overwritten with the squeezed tensor (:94-96).  etdnn() uses conv1d: rank 3 throughout.
+TDNN_RANK4_NODES = frozenset(("tdnn1_conv", "tdnn1_bn", "tdnn1_relu", "tdnn2_conv", "tdnn2_bn", "tdnn2_relu",
+                              "tdnn3_conv", "tdnn3_bn"))
+
 TDNN_FRAME_LAYERS = (("tdnn1", True), ("tdnn2", True), ("tdnn3", True), ("tdnn4", False), ("tdnn5", False))
 # etdnn: conv1d k=5,5,7,9 interleaved with dense layers (model/tdnn.py:376-518)
 ETDNN_FRAME_LAYERS = (("tdnn1", True), ("tdnn2", False), ("tdnn3", True), ("tdnn4", False), ("tdnn5", True),
@@ -102,7 +107,10 @@ def _run_network(features, params, network_type, names, last_prefix):
         _, frame_level, _ = eng.node_info(node)
         if not frame_level:
             return eng.forward(packed, lengths, node)
-        return np.stack(eng.forward_frames(packed, lengths, node), axis=0)
+        out = np.stack(eng.forward_frames(packed, lengths, node), axis=0)
+        if network_type == "tdnn" and node in TDNN_RANK4_NODES:
+            out = np.expand_dims(out, 1)
+        return out
 
     endpoints = Endpoints(names, compute)
     last = last_prefix + "_relu" if not params.last_layer_linear else (

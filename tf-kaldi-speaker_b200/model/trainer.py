@@ -8,7 +8,7 @@ import numpy as np
 
 from .. import tf_checkpoint
 from ..engine import Engine
-from .tdnn import tdnn, etdnn  # noqa: F401  (kept importable from here like the reference)
+from .tdnn import tdnn, etdnn, TDNN_RANK4_NODES  # noqa: F401  (kept importable from here like the reference)
 from .resnet import resnet_18  # noqa: F401
 
 _NETWORKS = ("tdnn", "extended_tdnn", "resnet_18")      # "tdnn-s" is dead code in the reference (quit() at model/tdnn.py:201)
@@ -121,7 +121,8 @@ class Trainer(object):
 
     def predict(self, features):
         """Output the embeddings (model/trainer.py:886-913): rank-2 [T, D] -> [E]; rank-3 [B, T, D] -> [B, E];
-        frame-level nodes give [T', N] / [B, T', N].  Features wider than `dim` are sliced."""
+        frame-level nodes give [T', N] / [B, T', N] -- [1, T', N] / [B, 1, T', N] for tdnn()'s conv2d endpoints, exactly the
+        reference's shapes (model/tdnn.py:38-96).  Features wider than `dim` are sliced."""
         if not self.is_loaded:
             if self._has_model():
                 self.load()
@@ -148,7 +149,10 @@ class Trainer(object):
         node = self.params.embedding_node
         _, frame_level, _ = self.engine.node_info(node)
         if frame_level:
-            return np.stack(self.engine.forward_frames(packed, lengths, node), axis=0)
+            out = np.stack(self.engine.forward_frames(packed, lengths, node), axis=0)
+            if self.network_type == "tdnn" and node in TDNN_RANK4_NODES:
+                out = np.expand_dims(out, 1)       # the reference's conv2d endpoints are [B, 1, T', 512] (model/tdnn.py:38-91)
+            return out
         return self.engine.forward(packed, lengths, node)
 
     def predict_packed(self, packed, lengths):
