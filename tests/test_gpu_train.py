@@ -225,9 +225,9 @@ def test_train_step_bf16_matches_oracle(loss_func, relu, opt, dim, batch, frames
             report[name] = (e_gpu, e_orc, d)
         bad = {k: v for k, v in report.items()
                if not (v[0] <= BF16_NOISE_FACTOR * v[1] + 3e-3 and v[2] <= BF16_TRACK_FACTOR * v[1] + 3e-3 and v[0] <= BF16_ABS_GRAD)}
-        assert not bad, "(err vs exact, oracle-bf16 vs exact, gpu vs oracle-bf16): %s" % bad
         print("bf16 gradient noise (max over variables): gpu-exact %.3e, oracle-exact %.3e, gpu-oracle %.3e" % tuple(
             max(v[i] for v in report.values()) for i in range(3)))
+        assert not bad, "(err vs exact, oracle-bf16 vs exact, gpu vs oracle-bf16): %s" % bad
         for name, v_ref in new_exact.items():
             if name not in exact["grads"] and "/moving_" not in name:
                 continue                                   # e.g. tdnn7_relu/alpha under last_layer_linear: not in the graph

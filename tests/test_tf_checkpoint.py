@@ -84,3 +84,42 @@ def test_get_checkpoint_selects_like_the_reference(tmp_path):
         T.get_checkpoint(str(model), "2500")
     with pytest.raises(SystemExit):
         T.get_checkpoint(str(tmp_path / "nowhere"))
+
+
+def test_product_writer_matches_the_independent_writer(tmp_path):
+    """tf_checkpoint.save_checkpoint (what Trainer.save writes, model/trainer.py:296-303) against the independent writer
+    of the same published format: identical data shard, identical index ENTRIES (the block split points are a free
+    choice of a table builder), optimizer slots named the reference's way ("/optimizer", model/trainer.py:234-243) are
+    left out by load_weights, max_to_keep prunes old bundles."""
+    from oracle import synth, tf_bundle_ref
+    from xvector_b200 import tf_checkpoint as T
+    cfg = dict(synth.TDNN_STAT_CONFIG, num_nodes_pooling_layer=96)
+    w = synth.make_tdnn_weights(24, cfg, seed=3, hidden=64)
+    saved = dict(w)
+    saved["tdnn/tdnn1_conv/kernel/optimizer"] = np.ones_like(w["tdnn/tdnn1_conv/kernel"])      # momentum slot
+    saved["tdnn/tdnn1_conv/kernel/optimizer_1"] = np.ones_like(w["tdnn/tdnn1_conv/kernel"])    # Adam second moment
+    saved["global_step"] = np.array(7, np.int64)
+    a, b = tmp_path / "a", tmp_path / "b"
+    a.mkdir()
+    b.mkdir()
+    pa = T.save_checkpoint(str(a), 90000, saved)
+    pb = tf_bundle_ref.write_checkpoint(str(b), 90000, saved)
+    assert open(pa + ".data-00000-of-00001", "rb").read() == open(pb + ".data-00000-of-00001", "rb").read()
+    assert T.read_table(pa + ".index") == T.read_table(pb + ".index")
+    got, step = T.load_weights(str(a))
+    assert step == 90000 and set(got) == set(w)
+    for k in w:
+        assert np.array_equal(got[k], w[k])
+    # a flipped byte in the data shard is caught by the per-tensor CRC
+    raw = bytearray(open(pa + ".data-00000-of-00001", "rb").read())
+    raw[1000] ^= 0x40
+    open(pa + ".data-00000-of-00001", "wb").write(bytes(raw))
+    with pytest.raises(IOError, match="checksum"):
+        T.load_weights(str(a))
+    # keep_checkpoint_max (model/trainer.py:382)
+    c = tmp_path / "c"
+    for step in (100, 200, 300):
+        T.save_checkpoint(str(c), step, {"v": np.arange(4, dtype=np.float32)}, max_to_keep=2)
+    cur, every = T.get_checkpoint_state(str(c))
+    assert cur == "model-300" and every == ["model-200", "model-300"]
+    assert not os.path.exists(str(c / "model-100.index")) and os.path.exists(str(c / "model-200.index"))

@@ -573,7 +573,11 @@ cudaError_t launch_pool(const PoolArgs& a, int sm_count, cudaStream_t stream) {
       p.threads_x = 0; p.rl = 1; p.rows_per_chunk = 0;
       dim3 grid(static_cast<unsigned>((a.rows + span - 1) / span), static_cast<unsigned>(hout));
       const int block = 32 + ((nv + 31) / 32) * 32;
-      static bool attr_done = false;
+      // function attributes are per device: one ctx per GPU may live in one process (multi-GPU extractor, TrainerMGPU)
+      static bool attr_done_dev[64] = {};
+      int cur_dev = 0;
+      cudaGetDevice(&cur_dev);
+      bool& attr_done = attr_done_dev[cur_dev & 63];
       if (!attr_done) {
         cudaFuncSetAttribute(pool_accum_bulk_kernel<__nv_bfloat16, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPoolBulkSmem);
         cudaFuncSetAttribute(pool_accum_bulk_kernel<__nv_bfloat16, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPoolBulkSmem);

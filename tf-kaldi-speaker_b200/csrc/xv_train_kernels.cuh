@@ -279,6 +279,7 @@ __global__ void __launch_bounds__(256) col_reduce4_kernel(const float* __restric
                                                           const float* __restrict__ slope, const PoolGrad pg,
                                                           double* __restrict__ out, int out_ld) {
   constexpr int NV = KIND == 0 ? 2 : 3;
+  constexpr int U = 4;                                 // rows in flight per thread: loads first, math after
   __shared__ double red[NV][8][129];
   const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
   const int c0 = (blockIdx.x * 32 + cx) * 4;
@@ -301,39 +302,50 @@ __global__ void __launch_bounds__(256) col_reduce4_kernel(const float* __restric
     }
     int64_t cur_u = -1;
     float pm[4] = {0.f, 0.f, 0.f, 0.f}, psd[4] = {1.f, 1.f, 1.f, 1.f}, pdm[4] = {0.f, 0.f, 0.f, 0.f}, pds[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 2
-    for (int64_t r = r0 + ry; r < r1; r += 8) {
-      if (!mask.ok(r)) continue;
-      const float4 z4 = *reinterpret_cast<const float4*>(z + r * c_total + c0);
-      const float zz[4] = {z4.x, z4.y, z4.z, z4.w};
-      if (KIND == 0) {
+    const bool read_dy = KIND == 1 && !pg.enabled;
+    for (int64_t rb = r0 + ry; rb < r1; rb += 8 * U) {
+      float zz[U][4], dd[U][4];
+      bool ok[U];
+      // invalid rows hold finite values (zeros / products of real data): loading them unconditionally keeps U loads in flight
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const double x = zz[j];
-          v[0][j] += x; v[1][j] += x * x;
+      for (int u = 0; u < U; ++u) {
+        const int64_t r = rb + 8 * u;
+        ok[u] = r < r1 && mask.ok(r);
+        if (r < r1) {
+          VecF<4>::load(z + r * c_total + c0, zz[u]);
+          if (read_dy) VecF<4>::load(dy + r * c_total + c0, dd[u]);
         }
-      } else {
-        float dd[4];
-        if (pg.enabled) {
-          const int64_t u = r / mask.t;
-          if (u != cur_u) {                         // per-utterance pooling vectors: reloaded when the row walk enters a new utterance
-            cur_u = u;
-            const float* pp = pg.pooled + u * 2 * c_total + c0;
-            const float* dp = pg.dpooled + u * 2 * c_total + c0;
-            VecF<4>::load(pp, pm); VecF<4>::load(pp + c_total, psd);
-            VecF<4>::load(dp, pdm); VecF<4>::load(dp + c_total, pds);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (!ok[u]) continue;
+        if (KIND == 0) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const double x = zz[u][j];
+            v[0][j] += x; v[1][j] += x * x;
           }
         } else {
-          VecF<4>::load(dy + r * c_total + c0, dd);
-        }
+          if (pg.enabled) {
+            const int64_t ut = (rb + 8 * u) / mask.t;
+            if (ut != cur_u) {                        // per-utterance pooling vectors: reloaded when the row walk enters a new utterance
+              cur_u = ut;
+              const float* pp = pg.pooled + ut * 2 * c_total + c0;
+              const float* dp = pg.dpooled + ut * 2 * c_total + c0;
+              VecF<4>::load(pp, pm); VecF<4>::load(pp + c_total, psd);
+              VecF<4>::load(dp, pdm); VecF<4>::load(dp + c_total, pds);
+            }
+          }
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          float xh = 0.f, pre = zz[j];
-          if (mean != nullptr) { xh = (zz[j] - mu[j]) * rs[j]; pre = fmaf(ga[j], xh, be[j]); }
-          if (pg.enabled) dd[j] = pool_grad(pre >= 0.f ? pre : pre * sl[j], pm[j], psd[j], pdm[j], pds[j], pg.inv_l);
-          const float g = pre > 0.f ? dd[j] : dd[j] * sl[j];
-          v[0][j] += g; v[1][j] += static_cast<double>(g) * xh;
-          if (pre < 0.f) v[2][j] += static_cast<double>(dd[j]) * pre;
+          for (int j = 0; j < 4; ++j) {
+            float xh = 0.f, pre = zz[u][j];
+            if (mean != nullptr) { xh = (zz[u][j] - mu[j]) * rs[j]; pre = fmaf(ga[j], xh, be[j]); }
+            float d = dd[u][j];
+            if (pg.enabled) d = pool_grad(pre >= 0.f ? pre : pre * sl[j], pm[j], psd[j], pdm[j], pds[j], pg.inv_l);
+            const float g = pre > 0.f ? d : d * sl[j];
+            v[0][j] += g; v[1][j] += static_cast<double>(g) * xh;
+            if (pre < 0.f) v[2][j] += static_cast<double>(d) * pre;
+          }
         }
       }
     }
@@ -359,9 +371,9 @@ cudaError_t launch_col_reduce4(const float* dy, const float* z, RowMask mask, in
                                const float* rstd, const float* gamma, const float* beta, const float* slope, const PoolGrad& pg,
                                double* out, int out_ld, int sm_count, cudaStream_t s) {
   const int bx = (c_total + 127) / 128;
-  int64_t chunks = (4 * sm_count + bx - 1) / bx;
+  int64_t chunks = (2 * sm_count + bx - 1) / bx;       // ~2 blocks per SM, each thread walks >= 16 rows in groups of 4
   int64_t rpb = (rows + chunks - 1) / chunks;
-  if (rpb < 64) rpb = 64;
+  if (rpb < 32) rpb = 32;
   dim3 grid(bx, static_cast<unsigned>((rows + rpb - 1) / rpb));
   col_reduce4_kernel<KIND><<<grid, 256, 0, s>>>(dy, z, mask, rows, c_total, rpb, mean, rstd, gamma, beta, slope, pg, out, out_ld);
   return cudaGetLastError();
@@ -378,8 +390,12 @@ struct BnFwdArgs {
   float* y; __nv_bfloat16* yb; int32_t ldb;
 };
 __global__ void __launch_bounds__(256) bn_act_fwd_kernel(const BnFwdArgs a) {
+  constexpr int U = 4;
   const int nq = a.c_total / 4;
-  const int64_t rstep = static_cast<int64_t>(gridDim.x) * blockDim.y;
+  // block b owns the rows [b*rpb, (b+1)*rpb): few blocks (2 per SM), many rows per thread -- the per-channel set-up (fp64
+  // divide + square root) is paid once per block, not once per handful of rows
+  const int64_t rpb = (a.rows + gridDim.x - 1) / gridDim.x;
+  const int64_t r0 = static_cast<int64_t>(blockIdx.x) * rpb, r1 = min(r0 + rpb, a.rows);
   for (int q = threadIdx.x; q < nq; q += blockDim.x) {
     const int c0 = q * 4;
     float mu[4], rs[4], ga[4], be[4], sl[4];
@@ -394,22 +410,30 @@ __global__ void __launch_bounds__(256) bn_act_fwd_kernel(const BnFwdArgs a) {
       }
       sl[k] = a.slope[c0 + k];
     }
-    for (int64_t r = static_cast<int64_t>(blockIdx.x) * blockDim.y + threadIdx.y; r < a.rows; r += rstep) {
-      float v[4] = {0.f, 0.f, 0.f, 0.f};
-      if (a.mask.ok(r)) {
-        VecF<4>::load(a.z + r * a.c_total + c0, v);
+    for (int64_t rb = r0 + threadIdx.y; rb < r1; rb += static_cast<int64_t>(blockDim.y) * U) {
+      float v[U][4];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t r = rb + static_cast<int64_t>(u) * blockDim.y;
+        if (r < r1) VecF<4>::load(a.z + r * a.c_total + c0, v[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t r = rb + static_cast<int64_t>(u) * blockDim.y;
+        if (r >= r1) continue;
+        const bool ok = a.mask.ok(r);
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-          float t = v[k];
+          float t = v[u][k];
           if (a.st.sums != nullptr) t = fmaf(ga[k], (t - mu[k]) * rs[k], be[k]);      // same expression in every backward kernel
-          v[k] = t >= 0.f ? t : t * sl[k];
+          v[u][k] = ok ? (t >= 0.f ? t : t * sl[k]) : 0.f;
         }
-      }
-      if (a.y != nullptr) VecF<4>::store(a.y + r * a.c_total + c0, v);
-      if (a.yb != nullptr) {
-        VecF<4>::store_bf16(a.yb + r * a.ldb + c0, v);
-        if (q == nq - 1)
-          for (int k = a.c_total; k < a.ldb; ++k) a.yb[r * a.ldb + k] = __float2bfloat16(0.f);
+        if (a.y != nullptr) VecF<4>::store(a.y + r * a.c_total + c0, v[u]);
+        if (a.yb != nullptr) {
+          VecF<4>::store_bf16(a.yb + r * a.ldb + c0, v[u]);
+          if (q == nq - 1)
+            for (int k = a.c_total; k < a.ldb; ++k) a.yb[r * a.ldb + k] = __float2bfloat16(0.f);
+        }
       }
     }
   }
@@ -490,8 +514,11 @@ struct BnBwdArgs {
   float* g_gamma; float* g_beta; float* g_alpha;     // may be null
 };
 __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnBwdArgs a) {
+  constexpr int U = 4;
   const int nq = a.c_total / 4;
-  const int64_t rstep = static_cast<int64_t>(gridDim.x) * blockDim.y;
+  const int64_t rpb = (a.rows + gridDim.x - 1) / gridDim.x;        // contiguous row range per block (see bn_act_fwd_kernel)
+  const int64_t r0 = static_cast<int64_t>(blockIdx.x) * rpb, r1 = min(r0 + rpb, a.rows);
+  const double inv_n = 1.0 / a.n;
   for (int q = threadIdx.x; q < nq; q += blockDim.x) {
     const int c0 = q * 4;
     float mu[4], rs[4], ga[4], be[4], sl[4];
@@ -502,7 +529,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnBwdArgs a) {
       mu[k] = 0.f; rs[k] = 1.f; ga[k] = 1.f; be[k] = 0.f; k1[k] = 0.0; k2[k] = 0.0; gr[k] = 1.0;
       if (a.mean != nullptr) {
         mu[k] = a.mean[c0 + k]; rs[k] = a.rstd[c0 + k]; ga[k] = a.gamma[c0 + k]; be[k] = a.beta[c0 + k];
-        k1[k] = a.sums[c0 + k] / a.n; k2[k] = a.sums[a.sums_ld + c0 + k] / a.n;
+        k1[k] = a.sums[c0 + k] * inv_n; k2[k] = a.sums[a.sums_ld + c0 + k] * inv_n;
         gr[k] = static_cast<double>(ga[k]) * rs[k];
       }
       if (blockIdx.x == 0 && threadIdx.y == 0) {
@@ -511,40 +538,55 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnBwdArgs a) {
         if (a.g_alpha != nullptr) a.g_alpha[c0 + k] = static_cast<float>(a.sums[2 * a.sums_ld + c0 + k]);
       }
     }
-    for (int64_t r = static_cast<int64_t>(blockIdx.x) * blockDim.y + threadIdx.y; r < a.rows; r += rstep) {
-      float out[4] = {0.f, 0.f, 0.f, 0.f};
-      if (a.mask.ok(r)) {
-        float zz[4], d[4];
-        VecF<4>::load(a.z + r * a.c_total + c0, zz);
-        float pm[4], psd[4], pdm[4], pds[4];
-        if (a.pg.enabled) {
-          const int64_t u = r / a.mask.t;
-          const float* pp = a.pg.pooled + u * 2 * a.c_total + c0;
-          const float* dp = a.pg.dpooled + u * 2 * a.c_total + c0;
-          VecF<4>::load(pp, pm); VecF<4>::load(pp + a.c_total, psd);
-          VecF<4>::load(dp, pdm); VecF<4>::load(dp + a.c_total, pds);
-        } else {
-          VecF<4>::load(a.dy + r * a.c_total + c0, d);
-        }
+    int64_t cur_u = -1;
+    float pm[4] = {0.f, 0.f, 0.f, 0.f}, psd[4] = {1.f, 1.f, 1.f, 1.f}, pdm[4] = {0.f, 0.f, 0.f, 0.f}, pds[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int64_t rb = r0 + threadIdx.y; rb < r1; rb += static_cast<int64_t>(blockDim.y) * U) {
+      float zz[U][4], d[U][4];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          float xh = 0.f, pre = zz[k];
-          if (a.mean != nullptr) { xh = (zz[k] - mu[k]) * rs[k]; pre = fmaf(ga[k], xh, be[k]); }
-          if (a.pg.enabled) d[k] = pool_grad(pre >= 0.f ? pre : pre * sl[k], pm[k], psd[k], pdm[k], pds[k], a.pg.inv_l);
-          const float g = pre > 0.f ? d[k] : d[k] * sl[k];
-          if (a.mean != nullptr) {
-            const double t = static_cast<double>(g) - k1[k] - static_cast<double>(xh) * k2[k];
-            out[k] = static_cast<float>(gr[k] * t);
-          } else {
-            out[k] = g;
-          }
+      for (int u = 0; u < U; ++u) {
+        const int64_t r = rb + static_cast<int64_t>(u) * blockDim.y;
+        if (r < r1) {
+          VecF<4>::load(a.z + r * a.c_total + c0, zz[u]);
+          if (!a.pg.enabled) VecF<4>::load(a.dy + r * a.c_total + c0, d[u]);
         }
       }
-      if (a.dz32 != nullptr) VecF<4>::store(a.dz32 + r * a.c_total + c0, out);
-      if (a.dzb != nullptr) {
-        VecF<4>::store_bf16(a.dzb + r * a.ldb + c0, out);
-        if (q == nq - 1)
-          for (int k = a.c_total; k < a.ldb; ++k) a.dzb[r * a.ldb + k] = __float2bfloat16(0.f);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t r = rb + static_cast<int64_t>(u) * blockDim.y;
+        if (r >= r1) continue;
+        float out[4] = {0.f, 0.f, 0.f, 0.f};
+        if (a.mask.ok(r)) {
+          if (a.pg.enabled) {
+            const int64_t ut = r / a.mask.t;
+            if (ut != cur_u) {
+              cur_u = ut;
+              const float* pp = a.pg.pooled + ut * 2 * a.c_total + c0;
+              const float* dp = a.pg.dpooled + ut * 2 * a.c_total + c0;
+              VecF<4>::load(pp, pm); VecF<4>::load(pp + a.c_total, psd);
+              VecF<4>::load(dp, pdm); VecF<4>::load(dp + a.c_total, pds);
+            }
+          }
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            float xh = 0.f, pre = zz[u][k];
+            if (a.mean != nullptr) { xh = (zz[u][k] - mu[k]) * rs[k]; pre = fmaf(ga[k], xh, be[k]); }
+            float dk = d[u][k];
+            if (a.pg.enabled) dk = pool_grad(pre >= 0.f ? pre : pre * sl[k], pm[k], psd[k], pdm[k], pds[k], a.pg.inv_l);
+            const float g = pre > 0.f ? dk : dk * sl[k];
+            if (a.mean != nullptr) {
+              const double t = static_cast<double>(g) - k1[k] - static_cast<double>(xh) * k2[k];
+              out[k] = static_cast<float>(gr[k] * t);
+            } else {
+              out[k] = g;
+            }
+          }
+        }
+        if (a.dz32 != nullptr) VecF<4>::store(a.dz32 + r * a.c_total + c0, out);
+        if (a.dzb != nullptr) {
+          VecF<4>::store_bf16(a.dzb + r * a.ldb + c0, out);
+          if (q == nq - 1)
+            for (int k = a.c_total; k < a.ldb; ++k) a.dzb[r * a.ldb + k] = __float2bfloat16(0.f);
+        }
       }
     }
   }
@@ -557,7 +599,7 @@ inline RowGrid row_grid(int groups, int sm_count) {
   while (bx < groups && bx < 256) bx <<= 1;
   RowGrid g;
   g.block = dim3(bx, 256 / bx);
-  g.grid = dim3(sm_count * 8);
+  g.grid = dim3(sm_count * 2);       // few fat blocks: see bn_act_fwd_kernel
   return g;
 }
 
@@ -857,9 +899,11 @@ __global__ void __launch_bounds__(256) head_wgrad_kernel(const float* __restrict
                                                          float* __restrict__ db, const double* __restrict__ loss_src,
                                                          float* __restrict__ loss_slot) {
   __shared__ __align__(16) float fs[16 * kHeadMaxE];
+  __shared__ float gs[16][32];
   __shared__ double red[8][33];
   const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
-  const int s = blockIdx.x * 32 + cx;
+  const int s0 = blockIdx.x * 32;
+  const int s = s0 + cx;
   const bool ok = s < s_dim;
   const int ept = e_dim >> 3;                       // rows per thread (multiple of 4, <= 64)
   const int e_base = ry * ept;
@@ -871,13 +915,16 @@ __global__ void __launch_bounds__(256) head_wgrad_kernel(const float* __restrict
   for (int b0 = 0; b0 < batch; b0 += 16) {
     const int nb = min(16, batch - b0);
     __syncthreads();
-    for (int i = threadIdx.x; i < nb * e_dim; i += 256) {
-      const int bb = i / e_dim, e = i - bb * e_dim;
-      fs[bb * kHeadMaxE + e] = f[static_cast<int64_t>(b0 + bb) * e_dim + e];
+    // stage 16 utterances of f and of this strip of G: the inner loop then touches shared memory only
+    for (int bb = 0; bb < nb; ++bb)
+      for (int e = threadIdx.x; e < e_dim; e += 256) fs[bb * kHeadMaxE + e] = f[static_cast<int64_t>(b0 + bb) * e_dim + e];
+    for (int i = threadIdx.x; i < nb * 32; i += 256) {
+      const int bb = i >> 5, c = i & 31;
+      gs[bb][c] = s0 + c < s_dim ? G[static_cast<int64_t>(b0 + bb) * s_dim + s0 + c] : 0.f;
     }
     __syncthreads();
     for (int bb = 0; bb < nb; ++bb) {
-      const float g = ok ? G[static_cast<int64_t>(b0 + bb) * s_dim + s] : 0.f;
+      const float g = gs[bb][cx];
       gsum += g;
       const float4* fp = reinterpret_cast<const float4*>(fs + bb * kHeadMaxE + e_base);
 #pragma unroll
@@ -902,11 +949,17 @@ __global__ void __launch_bounds__(256) head_wgrad_kernel(const float* __restrict
     return;
   }
   const double rs = ok ? static_cast<double>(r[s]) : 0.0;
+  const float* wcol = w + static_cast<int64_t>(e_base) * s_dim + s;
   double dot = 0.0;
   if (ok) {
 #pragma unroll
-    for (int k = 0; k < 64; ++k)
-      if (k < ept) dot += static_cast<double>(acc[k]) * (static_cast<double>(w[static_cast<int64_t>(e_base + k) * s_dim + s]) * rs);
+    for (int k0 = 0; k0 < 64; k0 += 16) {           // 16 independent loads in flight, then the fp64 chain
+      float wv[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) wv[j] = k0 + j < ept ? wcol[static_cast<int64_t>(k0 + j) * s_dim] : 0.f;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) dot += static_cast<double>(acc[k0 + j]) * (static_cast<double>(wv[j]) * rs);
+    }
   }
   red[ry][cx] = dot;
   __syncthreads();
@@ -915,12 +968,19 @@ __global__ void __launch_bounds__(256) head_wgrad_kernel(const float* __restrict
 #pragma unroll
   for (int j = 0; j < 8; ++j) dot += red[j][cx];
   const bool floored = rs >= 0.999999e6;                         // sum w^2 <= 1e-12: l2_normalize's max() is flat
+  float* dcol = dw + static_cast<int64_t>(e_base) * s_dim + s;
 #pragma unroll
-  for (int k = 0; k < 64; ++k) {
-    if (k < ept) {
-      const int64_t i = static_cast<int64_t>(e_base + k) * s_dim + s;
-      const double gval = floored ? rs * acc[k] : rs * (static_cast<double>(acc[k]) - static_cast<double>(w[i]) * rs * dot);
-      dw[i] = static_cast<float>(gval);
+  for (int k0 = 0; k0 < 64; k0 += 16) {
+    float wv[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) wv[j] = k0 + j < ept ? wcol[static_cast<int64_t>(k0 + j) * s_dim] : 0.f;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      if (k0 + j < ept) {
+        const double gval = floored ? rs * acc[k0 + j]
+                                    : rs * (static_cast<double>(acc[k0 + j]) - static_cast<double>(wv[j]) * rs * dot);
+        dcol[static_cast<int64_t>(k0 + j) * s_dim] = static_cast<float>(gval);
+      }
     }
   }
 }

@@ -100,8 +100,10 @@ class Engine(object):
     # -- weights
     def set_weights(self, weights):
         """weights: {tf variable name: ndarray}.  Copies everything, then folds/casts on the device."""
+        self._weight_shapes = {}
         for name, arr in weights.items():
             a = _f32(arr)
+            self._weight_shapes[name] = tuple(a.shape)
             if a.ndim == 0:
                 a = a.reshape(1)
             shape = np.asarray(a.shape, dtype=np.int64)
@@ -266,6 +268,36 @@ class Engine(object):
 
     def train_grad(self, name, shape):
         return self._train_read(self.lib.xv_train_get_grad, name, shape)
+
+    def train_variable_names(self):
+        """[(TF variable name, element count)] of everything the training state holds (what tf.train.Saver would save)."""
+        n = self.lib.xv_train_num_variables(self._ctx)
+        if n < 0:
+            raise XVectorError(_lib.XV_ESTATE, "no training state (call train_init)")
+        out = []
+        buf = C.create_string_buffer(512)
+        size = C.c_int64()
+        for i in range(n):
+            self._check(self.lib.xv_train_variable_name(self._ctx, i, buf, 512, C.byref(size)))
+            out.append((buf.value.decode("utf-8"), int(size.value)))
+        return out
+
+    def train_variables(self):
+        """{TF variable name: current value}, in the shapes the variables were given with set_weights."""
+        out = {}
+        shapes = getattr(self, "_weight_shapes", {})
+        for name, size in self.train_variable_names():
+            shape = shapes.get(name, (size,))
+            if int(np.prod(shape, dtype=np.int64)) != size:
+                shape = (size,)
+            out[name] = self.train_weight(name, shape)
+        return out
+
+    def comm_info(self):
+        rank, world, buckets = C.c_int32(), C.c_int32(), C.c_int32()
+        elems = C.c_int64()
+        self._check(self.lib.xv_comm_info(self._ctx, C.byref(rank), C.byref(world), C.byref(elems), C.byref(buckets)))
+        return {"rank": int(rank.value), "world": int(world.value), "grad_elems": int(elems.value), "buckets": int(buckets.value)}
 
     def comm_unique_id(self):
         buf = C.create_string_buffer(128)

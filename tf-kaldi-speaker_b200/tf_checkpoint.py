@@ -258,13 +258,181 @@ def load_weights(model_dir):
         raise IOError("Failed to find a checkpoint in %s" % model_dir)
     prefix = os.path.join(model_dir, os.path.basename(state[0]))
     reader = BundleReader(prefix)
-    skip = ("/Momentum", "/Adam", "/Adam_1", "/ExponentialMovingAverage")
+    # optimizer slot variables: the reference constructs every optimizer with name="optimizer" (model/trainer.py:234-243),
+    # so its slots are "<var>/optimizer" (momentum accumulator, Adam m) and "<var>/optimizer_1" (Adam v); the TF default
+    # slot names are skipped as well
+    skip = ("/optimizer", "/optimizer_1", "/Momentum", "/Adam", "/Adam_1", "/ExponentialMovingAverage")
     out = {}
     for name in reader.entries:
         if name.endswith(skip) or name in ("global_step", "beta1_power", "beta2_power"):
             continue
         out[name] = reader.get_tensor(name)
     return out, checkpoint_step(state[0])
+
+
+# ------------------------------------------------------------------------------------------------ writer
+def _put_varint(out, v):
+    v &= (1 << 64) - 1
+    while v >= 0x80:
+        out.append((v & 0x7F) | 0x80)
+        v >>= 7
+    out.append(v)
+
+
+def _pb_varint_field(out, field, v):
+    _put_varint(out, (field << 3) | 0)
+    _put_varint(out, v)
+
+
+def _pb_bytes_field(out, field, payload):
+    _put_varint(out, (field << 3) | 2)
+    _put_varint(out, len(payload))
+    out.extend(payload)
+
+
+class _BlockBuilder(object):
+    """One LevelDB-format block: prefix-compressed entries, a restart point every 16 keys, the restart array."""
+    RESTART_INTERVAL = 16
+
+    def __init__(self):
+        self.buf = bytearray()
+        self.restarts = [0]
+        self.count = 0
+        self.last_key = b""
+
+    def add(self, key, value):
+        shared = 0
+        if self.count % self.RESTART_INTERVAL == 0:
+            if self.count:
+                self.restarts.append(len(self.buf))
+        else:
+            n = min(len(key), len(self.last_key))
+            while shared < n and key[shared] == self.last_key[shared]:
+                shared += 1
+        _put_varint(self.buf, shared)
+        _put_varint(self.buf, len(key) - shared)
+        _put_varint(self.buf, len(value))
+        self.buf.extend(key[shared:])
+        self.buf.extend(value)
+        self.last_key = key
+        self.count += 1
+
+    def size_estimate(self):
+        return len(self.buf) + 4 * len(self.restarts) + 4
+
+    def finish(self):
+        out = bytearray(self.buf)
+        for r in self.restarts:
+            out.extend(struct.pack("<I", r))
+        out.extend(struct.pack("<I", len(self.restarts)))
+        return bytes(out)
+
+
+def _write_block(f, contents):
+    """Appends a block + its trailer (compression type 0, masked CRC32C of contents + type); returns its handle."""
+    offset = f.tell()
+    f.write(contents)
+    f.write(b"\x00")
+    f.write(struct.pack("<I", masked_crc32c(contents + b"\x00")))
+    handle = bytearray()
+    _put_varint(handle, offset)
+    _put_varint(handle, len(contents))
+    return bytes(handle)
+
+
+def write_table(path, items, block_size=4096):
+    """items: (key bytes, value bytes) in ascending key order -> a LevelDB-format table file (no compression, no filter)."""
+    with open(path, "wb") as f:
+        index = _BlockBuilder()
+        block = _BlockBuilder()
+        prev = None
+        for key, value in items:
+            if prev is not None and not key > prev:
+                raise ValueError("table keys must be strictly ascending (%r after %r)" % (key, prev))
+            block.add(key, value)
+            prev = key
+            if block.size_estimate() >= block_size:
+                index.add(block.last_key, _write_block(f, block.finish()))
+                block = _BlockBuilder()
+        if block.count:
+            index.add(block.last_key, _write_block(f, block.finish()))
+        meta = _write_block(f, _BlockBuilder().finish())
+        idx = _write_block(f, index.finish())
+        footer = bytearray(meta + idx)
+        footer.extend(b"\x00" * (40 - len(footer)))
+        footer.extend(struct.pack("<Q", TABLE_MAGIC))
+        f.write(footer)
+
+
+_DTYPE_ENUM = {np.dtype(v): k for k, v in _DTYPES.items()}
+
+
+def save_bundle(prefix, variables):
+    """Writes {name: array} as a single-shard tensor bundle <prefix>.index + <prefix>.data-00000-of-00001 -- what
+    tf.train.Saver.save produces (model/trainer.py:296-303): tensors laid out in name order, little endian, every tensor
+    and every index block carrying its masked CRC32C."""
+    names = sorted(variables, key=lambda n: n.encode("utf-8"))
+    header = bytearray()
+    _pb_varint_field(header, 1, 1)                       # num_shards
+    version = bytearray()
+    _pb_varint_field(version, 1, 1)                      # VersionDef.producer = kTensorBundleVersion
+    _pb_bytes_field(header, 3, version)
+    items = [(b"", bytes(header))]
+    offset = 0
+    with open(prefix + ".data-00000-of-00001", "wb") as f:
+        for name in names:
+            a = np.asarray(variables[name])
+            if a.ndim:                                   # (np.ascontiguousarray would turn a scalar into shape (1,))
+                a = np.ascontiguousarray(a)
+            if a.dtype not in _DTYPE_ENUM:
+                raise TypeError("%s: dtype %s cannot be stored in a tensor bundle" % (name, a.dtype))
+            raw = a.astype(a.dtype.newbyteorder("<"), copy=False).tobytes()
+            f.write(raw)
+            entry = bytearray()
+            _pb_varint_field(entry, 1, _DTYPE_ENUM[a.dtype])
+            shape = bytearray()
+            for d in a.shape:
+                dim = bytearray()
+                _pb_varint_field(dim, 1, int(d))
+                _pb_bytes_field(shape, 2, dim)
+            _pb_bytes_field(entry, 2, shape)
+            if offset:
+                _pb_varint_field(entry, 4, offset)
+            _pb_varint_field(entry, 5, len(raw))
+            _put_varint(entry, (6 << 3) | 5)
+            entry.extend(struct.pack("<I", masked_crc32c(raw)))
+            items.append((name.encode("utf-8"), bytes(entry)))
+            offset += len(raw)
+    write_table(prefix + ".index", items)
+
+
+def save_checkpoint(model_dir, step, variables, max_to_keep=None, basename="model"):
+    """saver.save(sess, <model_dir>/model, global_step=step) (model/trainer.py:296-303): the bundle plus the `checkpoint`
+    state file (model_checkpoint_path / all_model_checkpoint_paths, as rewritten by misc/utils.py:299-303); with
+    max_to_keep (= params.keep_checkpoint_max, model/trainer.py:382) the oldest bundles beyond it are deleted."""
+    os.makedirs(model_dir, exist_ok=True)
+    name = "%s-%d" % (basename, int(step))
+    save_bundle(os.path.join(model_dir, name), variables)
+    state = get_checkpoint_state(model_dir)
+    every = [os.path.basename(p) for p in state[1]] if state else []
+    if name in every:
+        every.remove(name)
+    every.append(name)
+    if max_to_keep and len(every) > max_to_keep:
+        for old in every[:-max_to_keep]:
+            for suffix in (".index", ".data-00000-of-00001"):
+                try:
+                    os.remove(os.path.join(model_dir, old + suffix))
+                except OSError:
+                    pass
+        every = every[-max_to_keep:]
+    tmp = os.path.join(model_dir, "checkpoint.tmp")
+    with open(tmp, "w") as f:
+        f.write('model_checkpoint_path: "%s"\n' % name)
+        for c in every:
+            f.write('all_model_checkpoint_paths: "%s"\n' % c)
+    os.replace(tmp, os.path.join(model_dir, "checkpoint"))
+    return os.path.join(model_dir, name)
 
 
 def main(argv=None):
