@@ -13,9 +13,21 @@ the N ranks; no collective on the data path).  A "step" = one pass of the hot pa
 
 Printed JSON line (rank 0): `value` = whole-job input frames/s with features resident in HBM, timed with CUDA
 events on the library's stream, max over ranks; `e2e` = same metric through the public C-ABI call xv_forward from
-pinned HOST memory (H2D of features and D2H of embeddings inside the timed region); `roofline` = the tcgen05 GEMM
-family (algorithmic FLOPs / summed GEMM launch durations, events around every launch) against the measured bf16
-peak; `cpu_baseline` = the fp32 torch-CPU restatement run the way the reference deploys extraction.
+pinned HOST memory (H2D of features and D2H of embeddings inside the timed region); `roofline` = the step's
+algorithmic GEMM FLOPs / the step's time against the measured bf16 peak (the summed GEMM launch
+durations are reported beside it); `cpu_baseline` = the fp32 torch-CPU restatement run the way the reference deploys
+extraction.
+
+The default run (workload tdnn) also takes short, bounded LEGS for the other BASELINE.json configs and attaches them
+under `legs` of the same JSON line, so that one driver run puts every config under its clock:
+  N = 1 : cfg0 (1000 x 300 frames: whole job + single-utterance Trainer.predict latency), cfg1_chunked
+          (chunk_size = 2000 through the extractor's chunk-and-average), attention (configs[2]), resnet18 (configs[3]),
+          train (configs[4], one GPU);
+  N > 1 : train_dp -- the library's own NCCL communicator (xv_comm_init): weak (64 utterances per GPU) and the
+          reference-faithful strong split (global 64, model/trainer.py:1133-1134) ms/step, the allreduce alone
+          (bus GB/s against 900 GB/s per direction), and a parity check of the N-tower step against a committed golden
+          (tests/golden/train_dp_golden.npz).
+A leg that fails reports {"error": ...} and never takes the headline down.  `--no-legs` skips them.
 """
 import argparse
 import json
@@ -149,7 +161,11 @@ class Workload(object):
             self.scale = np.ones(self.dim, np.float32)
             t = self.lengths.astype(np.float64)
             key = 2.0 * (512 * 1500 + 1500 * 1500) * (t - 14)
-            self.layer_flops = {}
+            lf = {"gemm.tdnn1": 2 * 512 * 5 * self.dim * (t - 4), "gemm.tdnn2": 2 * 512 * 2560 * (t - 8),
+                  "gemm.tdnn3": 2 * 512 * 3584 * (t - 14), "gemm.tdnn4": 2 * 512 * 512 * (t - 14),
+                  "gemm_pool.tdnn5": 2 * 512 * 1500 * (t - 14), "gemm.att_key0": 2.0 * 512 * 1500 * (t - 14),
+                  "gemm.att_key1": 2.0 * 1500 * 1500 * (t - 14), "gemm.tdnn6": 2 * 3000 * 512 + 0 * t}
+            self.layer_flops = {k: float(v.sum()) for k, v in lf.items()}
             self.flops = float((scheduler.utterance_flops(self.lengths, self.dim) + key).sum())
             self.tensor_prefixes = ("gemm",)
             self.kernel = ("xv_tdnn_gemm_kernel: 5 frame layers + the 2 attention-key layers + tdnn6 (att_scores / att_softmax / "
@@ -185,19 +201,71 @@ class Workload(object):
                 "tdnn6_dense 512-d) on 30-dim MFCC utterances of log-uniform length 200-6000 frames")
 
 
-def run_ours(args):
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    dist = None
-    if world > 1:
-        import torch
-        import torch.distributed as dist
-        torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    import xvector_b200
-    from oracle import synth
+class Dist(object):
+    """Rank bookkeeping + the torch.distributed plumbing the bench contract asks for (barrier, max / sum over ranks)."""
 
+    def __init__(self):
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        self.dist = None
+        if self.world > 1:
+            import torch
+            import torch.distributed as dist
+            torch.cuda.set_device(self.local)
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+            self.dist = dist
+
+    def barrier(self, eng=None):
+        if eng is not None:
+            eng.sync()
+        if self.dist is not None:
+            import torch
+            torch.cuda.synchronize()
+            self.dist.barrier()
+
+    def _reduce(self, v, op):
+        if self.dist is None:
+            return v
+        import torch
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    def max(self, v):
+        return self._reduce(v, self.dist.ReduceOp.MAX) if self.dist is not None else v
+
+    def sum(self, v):
+        return self._reduce(v, self.dist.ReduceOp.SUM) if self.dist is not None else v
+
+    def close(self):
+        if self.dist is not None:
+            self.dist.destroy_process_group()
+            self.dist = None
+
+
+class Solo(object):
+    """Dist stand-in for the single-GPU legs (no collective, rank 0 of 1)."""
+    rank, world, dist = 0, 1, None
+
+    def __init__(self, local=0):
+        self.local = local
+
+    def barrier(self, eng=None):
+        if eng is not None:
+            eng.sync()
+
+    def max(self, v):
+        return v
+
+    def sum(self, v):
+        return v
+
+
+def measure_extraction(args, dc, with_pool=True, with_cpu=True):
+    """One extraction workload at dc.world GPUs -> the JSON line (dict) of the bench contract."""
+    import xvector_b200
+    rank, world, local = dc.rank, dc.world, dc.local
     wl = Workload(args, rank, world)
     lengths, n_frames, cfg, weights, DIM = wl.lengths, wl.n_frames, wl.cfg, wl.weights, wl.dim
     eng = xvector_b200.Engine(cfg, DIM, precision="bf16", device=local, batch_frames=wl.batch_frames)
@@ -211,34 +279,11 @@ def run_ours(args):
         pin.array[s:e] = rng.standard_normal((e - s, DIM), dtype=np.float32) * scale
     feats = pin.array
 
-    def barrier():
-        eng.sync()
-        if dist is not None:
-            import torch
-            torch.cuda.synchronize()
-            dist.barrier()
-
-    def max_over_ranks(v):
-        if dist is None:
-            return v
-        import torch
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(v):
-        if dist is None:
-            return v
-        import torch
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
-
     # ---------------- device-resident timing (headline `value`) ----------------
     eng.stage(feats, lengths)
     for _ in range(args.warmup):
         eng.run()
-    barrier()
+    dc.barrier(eng)
     sampler = ClockSampler(local)
     sampler.start()
     launches0 = eng.launch_count()
@@ -249,13 +294,13 @@ def run_ours(args):
     eng.sync()
     ms_dev = eng.elapsed_ms(0, 1)
     launches = eng.launch_count() - launches0
-    barrier()
+    dc.barrier(eng)
     sampler.stop()
     emb = eng.fetch()
     assert np.isfinite(emb).all()
-    ms_dev = max_over_ranks(ms_dev)
-    total_frames = sum_over_ranks(float(n_frames))
-    total_launches = int(sum_over_ranks(float(launches)))
+    ms_dev = dc.max(ms_dev)
+    total_frames = dc.sum(float(n_frames))
+    total_launches = int(dc.sum(float(launches)))
     value = total_frames * args.steps / (ms_dev * 1e-3)
 
     # ---------------- per-kernel-family device time (roofline) ----------------
@@ -279,15 +324,19 @@ def run_ours(args):
             v["tflops"] = wl.layer_flops[k] / (v["ms_per_step"] * 1e-3) / 1e12
     flops = wl.flops
     peaks = read_peaks()
-    achieved = flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
+    step_ms = ms_dev / args.steps
+    # achieved = algorithmic FLOPs of the step / the step's time (every kernel of the step inside it)
+    achieved = flops / (step_ms * 1e-3) / 1e12
+    in_gemms = flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
     roofline = {
         "kernel": wl.kernel,
         "bound": "tensor", "achieved": achieved, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
         "frac": achieved / peaks["bf16_sustained"], "peak_kind": "sustained bf16, %s" % peaks["source"],
-        "frac_of_burst": achieved / peaks["bf16_burst"],
+        "frac_of_burst": achieved / peaks["bf16_burst"], "basis": "algorithmic FLOPs of the step / ms_per_step (rank 0 share at N > 1)",
         "algorithmic_flops_per_step": flops, "launches_per_step": gemm_launches,
         "avg_launch_ms": gemm_ms / gemm_launches if gemm_launches else None,
-        "gemm_share_of_step": gemm_ms / (ms_dev / args.steps) if world == 1 else None,
+        "achieved_inside_gemm_launches": in_gemms, "frac_inside_gemm_launches": in_gemms / peaks["bf16_sustained"],
+        "gemm_share_of_step": gemm_ms / step_ms,
         "traffic": None,
     }
     if wl.name == "tdnn":
@@ -299,7 +348,7 @@ def run_ours(args):
 
     # ---------------- standalone statistics pooling (HBM roofline; rank 0 at N=1) ----------------
     pooling = None
-    if rank == 0 and world == 1 and not args.no_pool_bench and wl.name == "tdnn":
+    if rank == 0 and world == 1 and with_pool and wl.name == "tdnn":
         pooling = pooling_roofline(eng, peaks)
 
     # ---------------- end to end through the public C-ABI call (host buffers) ----------------
@@ -307,51 +356,237 @@ def run_ours(args):
     out = None
     for _ in range(2):
         out = eng.forward(feats, lengths)
-    barrier()
+    dc.barrier(eng)
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
         out = eng.forward(feats, lengths)                        # H2D (pinned) + kernels + D2H + sync inside
     t1 = time.perf_counter()
-    barrier()
-    e2e_s = max_over_ranks(t1 - t0)
+    dc.barrier(eng)
+    e2e_s = dc.max(t1 - t0)
     e2e_value = total_frames * e2e_steps / e2e_s
     assert np.isfinite(out).all()
 
     # ---------------- CPU baseline (rank 0, N=1 only) ----------------
     cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and with_cpu:
         cpu = cpu_baseline(args.cpu_seconds, args)
 
-    if rank == 0:
-        clocks = sampler.summary()
-        line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16", "data": "synthetic",
-            "config": {
-                "workload": wl.workload,
-                "utts_per_gpu": wl.utts, "frames_rank0": n_frames, "feature_dim": DIM, "node": "tdnn6_dense",
-                "batch_frames": wl.batch_frames, "weights": "random init, seed 1234",
-                "parallelism": "utterance shards (LPT by FLOPs) over %d GPU(s), no collective" % world,
-                "l2_policy": "inputs larger than L2 (%.2f GB fp32 features per GPU vs 126 MB L2)" % (n_frames * DIM * 4 / 1e9),
-            },
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(n_frames * DIM * 4 + lengths.nbytes),
-                    "d2h_bytes_per_step": int(len(lengths) * 512 * 4), "steps": e2e_steps,
-                    "api": "xv_forward (pinned host features -> host embeddings)"},
-            "gpu_launches": total_launches,
-            "clocks": clocks,
-            "roofline": roofline,
-            "kernel_families_ms_per_step": fam,
-        }
-        if pooling is not None:
-            line["pooling_roofline"] = pooling
-        if cpu is not None:
-            line["cpu_baseline"] = cpu
-        emit(line)
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic",
+        "config": {
+            "workload": wl.workload,
+            "utts_per_gpu": wl.utts, "frames_rank0": n_frames, "feature_dim": DIM, "node": "tdnn6_dense",
+            "batch_frames": wl.batch_frames, "weights": "random init, seed 1234",
+            "parallelism": "utterance shards (LPT by FLOPs) over %d GPU(s), no collective" % world,
+            "l2_policy": "inputs larger than L2 (%.2f GB fp32 features per GPU vs 126 MB L2)" % (n_frames * DIM * 4 / 1e9),
+        },
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(n_frames * DIM * 4 + lengths.nbytes),
+                "d2h_bytes_per_step": int(len(lengths) * 512 * 4), "steps": e2e_steps,
+                "api": "xv_forward (pinned host features -> host embeddings)"},
+        "gpu_launches": total_launches,
+        "clocks": sampler.summary(),
+        "roofline": roofline,
+        "kernel_families_ms_per_step": fam,
+    }
+    if pooling is not None:
+        line["pooling_roofline"] = pooling
+    if cpu is not None:
+        line["cpu_baseline"] = cpu
     pin.close()
     eng.close()
-    if dist is not None:
-        dist.destroy_process_group()
+    return line
+
+
+def compact(line, keep_families=True):
+    """A leg's line cut down to what a reader of the combined JSON needs."""
+    keys = ["metric", "value", "unit", "ms_per_step", "steps", "warmup", "scaling", "dtype", "config", "e2e", "gpu_launches",
+            "clocks", "roofline", "loss_first_last"]
+    out = {k: line[k] for k in keys if k in line}
+    if keep_families and "kernel_families_ms_per_step" in line:
+        out["kernel_families_ms_per_step"] = {k: {kk: round(vv, 4) for kk, vv in v.items()}
+                                              for k, v in line["kernel_families_ms_per_step"].items()}
+    return out
+
+
+def leg_args(args, **kw):
+    a = argparse.Namespace(**vars(args))
+    for k, v in kw.items():
+        setattr(a, k, v)
+    return a
+
+
+def run_leg(name, fn, *a, **k):
+    t0 = time.time()
+    try:
+        out = fn(*a, **k)
+    except Exception as e:                                     # a leg never takes the headline down
+        import traceback
+        sys.stderr.write("leg %s failed:\n%s\n" % (name, traceback.format_exc()))
+        out = {"error": "%s: %s" % (type(e).__name__, str(e)[:300])}
+    if isinstance(out, dict):
+        out["leg_wall_s"] = round(time.time() - t0, 2)
+    return out
+
+
+class _P(object):
+    """Params stand-in (misc/utils.py:13-41 interface: attributes + .dict)."""
+
+    def __init__(self, **kw):
+        self.__dict__.update(kw)
+
+    @property
+    def dict(self):
+        return self.__dict__
+
+
+def leg_cfg0(args, local):
+    """BASELINE.json configs[0]: 1000 synthetic 30-dim MFCC utterances x 300 frames.  (a) the whole job in ONE packed call
+    (device-resident and through xv_forward from pinned host memory); (b) the reference's actual call pattern: one
+    Trainer.predict per utterance (model/trainer.py:886-913, extract.py:89), p50 / p99 wall latency."""
+    import xvector_b200
+    from oracle import synth
+    from xvector_b200.model.trainer import Trainer
+    from xvector_b200.scheduler import utterance_flops
+    n, t, dim = 1000, 300, DIM
+    cfg = dict(synth.TDNN_STAT_CONFIG)
+    w = synth.make_tdnn_weights(dim, cfg, seed=1234)
+    x = synth.config1_features(n, t, dim, seed=101)
+    lengths = np.full(n, t, np.int32)
+    flops = float(utterance_flops(lengths, dim).sum())
+    eng = xvector_b200.Engine(cfg, dim, precision="bf16", device=local)
+    eng.set_weights(w)
+    pin = xvector_b200.PinnedArray((n * t, dim))
+    pin.array[...] = x.reshape(n * t, dim)
+    out = {"workload": "configs[0]: standard x-vector TDNN, %d utterances x %d frames x %d dims, node tdnn6_dense" % (n, t, dim),
+           "frames": n * t, "algorithmic_flops": flops}
+    try:
+        eng.stage(pin.array, lengths)
+        for _ in range(5):
+            eng.run()
+        eng.sync()
+        steps = 50
+        eng.event_record(0)
+        for _ in range(steps):
+            eng.run()
+        eng.event_record(1)
+        eng.sync()
+        ms = eng.elapsed_ms(0, 1) / steps
+        peaks = read_peaks()
+        out["resident"] = {"ms_per_job": ms, "frames_per_s": n * t / (ms * 1e-3), "tflops": flops / (ms * 1e-3) / 1e12,
+                           "frac_of_sustained_bf16": flops / (ms * 1e-3) / 1e12 / peaks["bf16_sustained"], "steps": steps}
+        for _ in range(3):
+            emb = eng.forward(pin.array, lengths)
+        t0 = time.perf_counter()
+        for _ in range(20):
+            emb = eng.forward(pin.array, lengths)
+        wall = (time.perf_counter() - t0) / 20
+        assert np.isfinite(emb).all()
+        out["e2e"] = {"ms_per_job": wall * 1e3, "frames_per_s": n * t / wall, "h2d_bytes": int(n * t * dim * 4), "d2h_bytes": int(n * 512 * 4),
+                      "api": "xv_forward (pinned host features -> host embeddings), 20 calls"}
+    finally:
+        pin.close()
+        eng.close()
+    # (b) one predict per utterance, the way extract.py drives the reference
+    trainer = Trainer(_P(**cfg), "/nonexistent", dim, single_cpu=True, precision="bf16", device=local)
+    trainer.build("predict")
+    trainer.set_weights(w)
+    try:
+        for i in range(20):
+            trainer.predict(x[i])
+        lat = []
+        for i in range(300):
+            t0 = time.perf_counter()
+            e = trainer.predict(x[i % n])
+            lat.append(time.perf_counter() - t0)
+        assert e.shape == (512,)
+        lat = np.sort(np.array(lat)) * 1e3
+        out["predict_one_utterance"] = {"api": "Trainer.predict([300, 30]) (model/trainer.py:886-913), 300 calls", "p50_ms": float(lat[len(lat) // 2]),
+                                        "p99_ms": float(lat[int(len(lat) * 0.99)]), "mean_ms": float(lat.mean()),
+                                        "frames_per_s_serial": t / (float(lat.mean()) * 1e-3)}
+    finally:
+        trainer.close()
+    if not args.no_cpu_baseline:
+        # the CPU arm's per-utterance time on one core (the reference runs one single-thread process per core)
+        from oracle import torch_ref
+        import torch
+        torch.set_num_threads(1)
+        net = torch_ref.TorchTdnn(w, cfg)
+        net.embed(x[:1])
+        t0 = time.perf_counter()
+        reps = 8
+        for i in range(reps):
+            net.embed(x[i:i + 1])
+        out["cpu_one_utterance_ms"] = {"value": (time.perf_counter() - t0) / reps * 1e3, "kind": "port", "cores": 1,
+                                       "sample": "%d x one 300-frame utterance, torch fp32 CPU restatement, 1 thread" % reps}
+    return out
+
+
+def leg_cfg1_chunked(args, local):
+    """BASELINE.json configs[1] "chunked as in the extractor": utterances longer than chunk_size = 2000 are cut into
+    overlapping chunks (hop 1000), embedded, and averaged weighted by chunk length (extract.py:68-86), through the
+    drop-in extractor (xvector_b200.extract.extract_many -> ONE packed xv_forward call over every utterance and chunk)."""
+    import xvector_b200  # noqa: F401
+    from oracle import synth
+    from xvector_b200.extract import extract_many, plan_many
+    from xvector_b200.model.trainer import Trainer
+    dim, chunk = DIM, 2000
+    cfg = dict(synth.TDNN_STAT_CONFIG)
+    w = synth.make_tdnn_weights(dim, cfg, seed=1234)
+    lengths = synth.config2_lengths(UTTS_PER_GPU, seed=202)[:1024]
+    rng = np.random.default_rng(7)
+    scale = np.linspace(3.0, 0.5, dim).astype(np.float32)
+    feats = [rng.standard_normal((int(n), dim), dtype=np.float32) * scale for n in lengths]
+    work = plan_many(lengths, chunk, 25)
+    processed = int(sum(z for _, _, z in work))
+    trainer = Trainer(_P(**cfg), "/nonexistent", dim, single_cpu=True, precision="bf16", device=local)
+    trainer.build("predict")
+    trainer.set_weights(w)
+    try:
+        embs = extract_many(trainer, feats, chunk_size=chunk)
+        t0 = time.perf_counter()
+        reps = 3
+        for _ in range(reps):
+            embs = extract_many(trainer, feats, chunk_size=chunk)
+        wall = (time.perf_counter() - t0) / reps
+        assert all(e is not None and np.isfinite(e).all() for e in embs)
+        # the same list unchunked, for the cost of the overlap
+        t0 = time.perf_counter()
+        extract_many(trainer, feats, chunk_size=10000)
+        wall_plain = time.perf_counter() - t0
+    finally:
+        trainer.close()
+    n_in = int(lengths.sum())
+    return {"workload": "configs[1] lengths (first 1024 utterances), chunk_size %d, hop %d (extract.py:68-86)" % (chunk, chunk // 2),
+            "utterances": int(len(lengths)), "chunked_utterances": int((lengths > chunk).sum()), "pieces": len(work),
+            "input_frames": n_in, "processed_frames": processed, "ms_per_job": wall * 1e3,
+            "input_frames_per_s": n_in / wall, "processed_frames_per_s": processed / wall,
+            "unchunked_ms_per_job": wall_plain * 1e3,
+            "api": "extract_many (host list of utterances -> host embeddings; chunk slicing and packing on the host inside the timed region)"}
+
+
+def run_ours(args):
+    dc = Dist()
+    line = measure_extraction(args, dc, with_pool=not args.no_pool_bench, with_cpu=not args.no_cpu_baseline)
+    legs = {}
+    if args.workload == "tdnn" and not args.no_legs and not args.utts:
+        if dc.world == 1:
+            legs["cfg0"] = run_leg("cfg0", leg_cfg0, args, dc.local)
+            legs["cfg1_chunked"] = run_leg("cfg1_chunked", leg_cfg1_chunked, args, dc.local)
+            solo = Solo(dc.local)
+            for name in ("attention", "resnet18"):
+                la = leg_args(args, workload=name, steps=3, warmup=3, dim=0, batch_frames=0, utts=0)
+                legs[name] = run_leg(name, lambda la=la: compact(measure_extraction(la, solo, with_pool=False, with_cpu=False)))
+            la = leg_args(args, steps=200, warmup=20, train_global_batch=0)
+            legs["train"] = run_leg("train", lambda: compact(measure_train(la, Solo(dc.local))))
+        else:
+            legs["train_dp"] = run_leg("train_dp", leg_train_dp, args, dc)
+    if dc.rank == 0:
+        if legs:
+            line["legs"] = legs
+        emit(line)
+    dc.close()
 
 
 def ncu_traffic(suffix, kernel_substr):
@@ -426,29 +661,23 @@ def pooling_roofline(eng, peaks, channels=1500, iters=10):
             "traffic": (ncu_traffic("pool_full_summary.csv", "pool_accum_bulk_kernel") or (None, None))[0]}
 
 
-def run_train(args):
-    """--workload train: BASELINE.json configs[4] -- one TDNN + AM-softmax training step (fwd + bwd + update) per
-    step, data parallel with ONE ncclAllReduce over the flat gradient buffer.  Weak scaling: 64 utterances x 200
-    frames per GPU (the reference-faithful "global 64 split over N" is --train-global-batch 64)."""
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    dist = None
-    if world > 1:
-        import torch
-        import torch.distributed as dist
-        torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+def measure_train(args, dc, precision=None, comm_bench=False):
+    """BASELINE.json configs[4] -- one TDNN + AM-softmax training step (fwd + bwd + update) per step, data parallel with
+    the library's own NCCL communicator (xv_comm_init; bucketed ncclAllReduce overlapped with the backward pass).
+    Weak scaling: 64 utterances x 200 frames per GPU; --train-global-batch 64 = the reference-faithful split of a global
+    batch over the towers (model/trainer.py:1133-1134).  Returns the JSON line (dict) on every rank."""
     import xvector_b200
     from oracle import synth
     from xvector_b200 import train_dp
+    rank, world, local = dc.rank, dc.world, dc.local
     speakers, frames, dim = 5994, 200, DIM
     gbatch = args.train_global_batch or 64 * world
+    precision = precision or args.train_precision
     cfg = dict(synth.TDNN_AMSOFTMAX_CONFIG)
     w = synth.add_softmax_weights(synth.make_tdnn_weights(dim, cfg, seed=1234), speakers)
     x, y = synth.config5_batch(gbatch, frames, dim, speakers, seed=505)
-    mixed = args.train_precision == "bf16"
-    eng = xvector_b200.Engine(cfg, dim, precision=args.train_precision, device=local)
+    mixed = precision == "bf16"
+    eng = xvector_b200.Engine(cfg, dim, precision=precision, device=local)
     eng.set_weights(w)
     eng.train_init(speakers)
     uid = train_dp.exchange_unique_id_torch(eng, rank, world) if world > 1 else b"\0" * 128
@@ -456,26 +685,10 @@ def run_train(args):
     xs, ys = train_dp.slice_batch(x, y, rank, world)
     pin = xvector_b200.PinnedArray(xs.shape)
     pin.array[...] = xs
-
-    def barrier():
-        eng.sync()
-        if dist is not None:
-            import torch
-            torch.cuda.synchronize()
-            dist.barrier()
-
-    def max_over_ranks(v):
-        if dist is None:
-            return v
-        import torch
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
     losses = []
     for i in range(args.warmup):
         losses.append(eng.train_step(pin.array, ys, 0.01, i)[0])
-    barrier()
+    dc.barrier(eng)
     sampler = ClockSampler(local)
     sampler.start()
     launches0 = eng.launch_count()
@@ -487,44 +700,131 @@ def run_train(args):
     t1 = time.perf_counter()
     eng.event_record(1)
     eng.sync()
-    ms_dev = max_over_ranks(eng.elapsed_ms(0, 1))
-    wall = max_over_ranks(t1 - t0)
+    ms_dev = dc.max(eng.elapsed_ms(0, 1))
+    wall = dc.max(t1 - t0)
     launches = eng.launch_count() - launches0
-    barrier()
+    dc.barrier(eng)
     sampler.stop()
     assert np.isfinite(losses).all()
+    info = eng.comm_info()
+    comm = None
+    if comm_bench and world > 1:
+        comm = comm_roofline(eng, dc, info)
     total_frames = float(gbatch * frames)
     flops = train_dp.train_flops(gbatch, frames, dim, speakers)
     peaks = read_peaks()
-    if rank == 0:
-        achieved = flops * args.steps / (ms_dev * 1e-3) / 1e12
-        line = {
-            "metric": "tdnn_amsoftmax_train_frames_per_sec", "value": total_frames * args.steps / (ms_dev * 1e-3), "unit": UNIT,
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps,
-            "higher_is_better": True, "scaling": "weak" if not args.train_global_batch else "strong", "vs_baseline": None,
-            "dtype": "bf16 operands / f32 accumulate + f32 master weights" if mixed else "f32", "data": "synthetic",
-            "config": {"workload": "configs[4]: TDNN x-vector + AM-softmax training step fwd+bwd+update, %d x %d frames x %d dims, "
-                                   "%d speakers, SGD" % (gbatch, frames, dim, speakers), "global_batch": gbatch,
-                       "per_gpu_batch": gbatch // world, "weights": "random init, seed 1234",
-                       "parallelism": "dp%d: one ncclAllReduce(sum) of the flat gradient buffer (9.13 M fp32) per step" % world,
-                       "l2_policy": "activations + gradients of a step (0.4 GB) exceed the L2"},
-            "e2e": {"value": total_frames * args.steps / wall, "unit": UNIT, "h2d_bytes_per_step": int(xs.nbytes + ys.nbytes),
-                    "d2h_bytes_per_step": 16, "steps": args.steps, "api": "xv_train_step (pinned host batch -> loss on the host)"},
-            "gpu_launches": int(launches) * world, "clocks": sampler.summary(),
-            "roofline": {"kernel": ("tcgen05 GEMMs of the frame layers (forward + tap-step -1 dgrad on xv_tdnn_gemm_kernel, MN-major "
-                                    "xv_wgrad_kernel) inside the whole step" if mixed else
-                                    "fp32 SIMT GEMMs of the validation-grade training path (forward, dgrad, wgrad)"),
-                         "bound": "tensor", "achieved": achieved, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
-                         "frac": achieved / peaks["bf16_sustained"], "peak_kind": "sustained bf16, %s" % peaks["source"],
-                         "algorithmic_flops_per_step": flops, "traffic": None,
-                         "note": "whole-step FLOPs / whole-step time" + ("" if mixed else "; this path runs on FFMA, not on the tensor cores")},
-            "loss_first_last": [losses[0], losses[-1]],
-        }
-        emit(line)
+    achieved = flops * args.steps / (ms_dev * 1e-3) / 1e12 / world           # per GPU: the roofline is a per-device quantity
+    line = {
+        "metric": "tdnn_amsoftmax_train_frames_per_sec", "value": total_frames * args.steps / (ms_dev * 1e-3), "unit": UNIT,
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps,
+        "higher_is_better": True, "scaling": "weak" if not args.train_global_batch else "strong", "vs_baseline": None,
+        "dtype": "bf16 operands / f32 accumulate + f32 master weights" if mixed else "f32", "data": "synthetic",
+        "config": {"workload": "configs[4]: TDNN x-vector + AM-softmax training step fwd+bwd+update, %d x %d frames x %d dims, "
+                               "%d speakers, SGD" % (gbatch, frames, dim, speakers), "global_batch": gbatch,
+                   "per_gpu_batch": gbatch // world, "weights": "random init, seed 1234",
+                   "parallelism": "dp%d: ncclAllReduce(sum) of the flat gradient buffer (%d fp32) in %d bucket(s) on a side stream, "
+                                  "overlapped with the backward pass; library communicator (xv_comm_init)" % (
+                                      world, info["grad_elems"], info["buckets"]),
+                   "comm_nranks": info["world"],
+                   "l2_policy": "activations + gradients of a step (0.4 GB) exceed the L2"},
+        "e2e": {"value": total_frames * args.steps / wall, "unit": UNIT, "h2d_bytes_per_step": int(xs.nbytes + ys.nbytes),
+                "d2h_bytes_per_step": 16, "steps": args.steps, "api": "xv_train_step (pinned host batch -> loss on the host)"},
+        "gpu_launches": int(dc.sum(float(launches))), "clocks": sampler.summary(),
+        "roofline": {"kernel": ("tcgen05 GEMMs of the frame layers (forward + tap-step -1 dgrad on xv_tdnn_gemm_kernel, MN-major "
+                                "xv_wgrad_kernel) inside the whole step" if mixed else
+                                "fp32 SIMT GEMMs of the validation-grade training path (forward, dgrad, wgrad)"),
+                     "bound": "tensor", "achieved": achieved, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
+                     "frac": achieved / peaks["bf16_sustained"], "peak_kind": "sustained bf16, %s" % peaks["source"],
+                     "algorithmic_flops_per_step": flops, "traffic": None,
+                     "note": "whole-step FLOPs per GPU / whole-step time" + ("" if mixed else "; this path runs on FFMA, not on the tensor cores")},
+        "loss_first_last": [losses[0], losses[-1]],
+    }
+    if comm is not None:
+        line["allreduce"] = comm
     pin.close()
     eng.close()
-    if dist is not None:
-        dist.destroy_process_group()
+    return line
+
+
+def comm_roofline(eng, dc, info, iters=20):
+    """The exchange step alone: the step's gradient buckets all-reduced back to back through the library's communicator
+    (xv_comm_bench), CUDA events on the communication stream, max over ranks.  Bus bytes of a ring/tree allreduce =
+    2 (N-1)/N x payload; NVLink 5 gives 900 GB/s per direction per GPU."""
+    import ctypes as C
+    ms = C.c_float()
+    eng._check(eng.lib.xv_comm_bench(eng._ctx, 3, C.byref(ms)))       # warm-up
+    dc.barrier(eng)
+    eng._check(eng.lib.xv_comm_bench(eng._ctx, iters, C.byref(ms)))
+    per = dc.max(float(ms.value))
+    payload = info["grad_elems"] * 4
+    n = info["world"]
+    bus = 2.0 * (n - 1) / n * payload / (per * 1e-3) / 1e9
+    return {"ms_per_allreduce": per, "payload_bytes": payload, "buckets": info["buckets"], "nranks": n,
+            "bus_gbs": bus, "nvlink_peak_gbs_per_direction": 900.0, "frac_of_nvlink": bus / 900.0, "iters": iters}
+
+
+def train_dp_parity(dc):
+    """The N-tower step (fp32 validation path, small shapes) against the committed golden written from the fp64 oracle
+    (tests/golden/make_train_dp_golden.py): loss, three gradients and the tower-0 moving mean."""
+    import xvector_b200
+    from oracle import synth                                   # input / weight generators only
+    from xvector_b200 import train_dp
+    path = os.path.join(ROOT, "tests", "golden", "train_dp_golden.npz")
+    g = np.load(path)
+    n = dc.world
+    if "n%d/loss" % n not in g.files:
+        return {"skipped": "no golden for %d towers" % n}
+    cfg = dict(synth.TDNN_AMSOFTMAX_CONFIG)
+    dim, speakers, batch, frames = 24, 101, 16, 50
+    w = synth.add_softmax_weights(synth.make_tdnn_weights(dim, cfg, seed=31), speakers)
+    x, y = synth.config5_batch(batch, frames, dim, speakers, seed=32)
+    eng = xvector_b200.Engine(cfg, dim, precision="fp32", device=dc.local)
+    eng.set_weights(w)
+    eng.train_init(speakers)
+    eng.comm_init(train_dp.exchange_unique_id_torch(eng, dc.rank, n), dc.rank, n)
+    xs, ys = train_dp.slice_batch(x, y, dc.rank, n)
+    loss, _ = eng.train_step(xs, ys, 0.05, 0)
+    out = {"towers": n, "loss_rel": abs(loss - float(g["n%d/loss" % n])) / abs(float(g["n%d/loss" % n]))}
+    worst = 0.0
+    for key in g.files:
+        if not key.startswith("n%d/g:" % n):
+            continue
+        name = key.split(":", 1)[1]
+        ref = g[key]                                           # every 97th element of the flattened gradient
+        got = eng.train_grad(name, np.asarray(w[name]).shape).reshape(-1)[::97]
+        worst = max(worst, float(np.linalg.norm(got - ref) / max(np.linalg.norm(ref), 1e-30)))
+    mm = eng.train_weight("tdnn/tdnn1_bn/moving_mean", (512,))
+    out["grad_l2_rel_max"] = worst
+    out["moving_mean_abs_max"] = float(np.abs(mm - g["n%d/mm" % n]).max())
+    eng.close()
+    worst_all = dc.max(max(out["loss_rel"] / 1e-5, worst / 5e-3, out["moving_mean_abs_max"] / 1e-6))
+    out["ok"] = bool(worst_all <= 1.0)
+    out["tolerances"] = {"loss_rel": 1e-5, "grad_l2_rel": 5e-3, "moving_mean_abs": 1e-6}
+    return out
+
+
+def leg_train_dp(args, dc):
+    """N > 1: the data-parallel training step through the library's communicator -- weak (64 utterances per GPU), strong
+    (global 64 split over the towers, model/trainer.py:1133-1134), the allreduce alone, and the parity check."""
+    steps = 200
+    out = {}
+    la = leg_args(args, steps=steps, warmup=20, train_global_batch=0)
+    weak = measure_train(la, dc, comm_bench=True)
+    out["weak"] = compact(weak)
+    out["weak"]["allreduce"] = weak.get("allreduce")
+    if 64 % dc.world == 0:
+        ls = leg_args(args, steps=steps, warmup=20, train_global_batch=64)
+        out["strong_global64"] = compact(measure_train(ls, dc))
+    out["parity"] = train_dp_parity(dc)
+    return out
+
+
+def run_train(args):
+    dc = Dist()
+    line = measure_train(args, dc, comm_bench=True)
+    if dc.rank == 0:
+        emit(line)
+    dc.close()
 
 
 def cpu_baseline(seconds, args=None):
@@ -627,6 +927,8 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-pool-bench", action="store_true")
+    ap.add_argument("--no-legs", action="store_true", help="default workload only: skip the extra legs (cfg0, cfg1_chunked, "
+                    "attention, resnet18, train at N = 1; train_dp at N > 1)")
     ap.add_argument("--utts", type=int, default=0, help="utterances per GPU (default = the configs[1] set; "
                     "smaller values are for profiling runs only)")
     args = ap.parse_args()

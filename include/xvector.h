@@ -198,6 +198,10 @@ int  xv_comm_init(xv_ctx* ctx, const void* nccl_unique_id, int rank, int world);
  * the communicator (ncclCommAbort); the peers see an asynchronous NCCL error instead of a hang (ncclCommGetAsyncError is
  * polled while a step is waited for) and every context of the job must be re-created. */
 int  xv_comm_info(xv_ctx* ctx, int32_t* rank, int32_t* world, int64_t* grad_elems, int32_t* buckets);
+/* The exchange step alone (measurement): all-reduces the step's gradient buckets `iters` times back to back on the
+ * communication stream and reports the mean time of one full exchange (CUDA events on that stream).  Collective: every
+ * rank must call it with the same iters.  The gradient buffer is scratch between steps. */
+int  xv_comm_bench(xv_ctx* ctx, int32_t iters, float* ms_per_iter);
 
 /* One 2-D convolution of the ResNet-18 front end on the implicit-GEMM tcgen05 path (kernel-level tests and the
  * conv roofline bench): replaces tf.layers.conv2d(padding='same', use_bias=False) + batch_normalization

@@ -187,7 +187,10 @@ BF16_ABS_GRAD = 0.2
 @pytest.mark.parametrize("loss_func,relu,opt,dim,batch,frames", [
     ("additive_margin_softmax", None, "sgd", 24, 32, 40),
     ("additive_margin_softmax", "prelu", "momentum", 30, 16, 61),    # 5*30 = 150 spliced inputs padded to 192
-    ("softmax", "lrelu", "sgd", 24, 8, 50),
+    # 16 utterances: with 8 the segment-level batch norms (8 rows) amplify fp32-level perturbations to the size of the
+    # bf16 noise itself -- two GPU realisations of the SAME step that differ only in where the batch statistics are summed
+    # (GEMM epilogue vs a separate pass) were measured 4.5 % apart there, which makes a per-variable 1.6x bound a coin toss
+    ("softmax", "lrelu", "sgd", 24, 16, 50),
 ], ids=["amsoftmax_cfg5", "amsoftmax_prelu_momentum_dim30", "softmax_lrelu"])
 def test_train_step_bf16_matches_oracle(loss_func, relu, opt, dim, batch, frames):
     import xvector_b200

@@ -984,6 +984,45 @@ int xv_comm_init(xv_ctx* c, const void* nccl_unique_id, int rank, int world) {
   return XV_OK;
 }
 
+int xv_comm_bench(xv_ctx* c, int32_t iters, float* ms_per_iter) {
+  if (!c) return XV_EINVAL;
+  TrainState* t = c->train;
+  if (!t) return fail(c, XV_ESTATE, "xv_comm_bench: call xv_train_init first");
+  if (iters < 1 || !ms_per_iter) return fail(c, XV_EINVAL, "xv_comm_bench: bad argument");
+  if (t->world <= 1 || !t->comm) return fail(c, XV_ESTATE, "xv_comm_bench: no communicator (xv_comm_init with world > 1)");
+  cudaSetDevice(c->device);
+  // the gradient buffer is scratch between steps (every step rewrites it): reduce it in place, bucket by bucket
+  cudaError_t e = cudaStreamSynchronize(c->stream);
+  if (e != cudaSuccess) return cuda_fail(c, e, "stream synchronize");
+  cudaEvent_t a = nullptr, b = nullptr;
+  if ((e = cudaEventCreate(&a)) != cudaSuccess || (e = cudaEventCreate(&b)) != cudaSuccess) return cuda_fail(c, e, "cudaEventCreate");
+  float* G = static_cast<float*>(t->grads.p);
+  cudaMemsetAsync(G, 0, sizeof(float) * (t->n_total + 1), t->comm_stream);
+  cudaEventRecord(a, t->comm_stream);
+  int nrc = 0;
+  for (int it = 0; it < iters && nrc == 0; ++it) {
+    if (t->overlap) {
+      for (int k = 0; k < kNumBuckets && nrc == 0; ++k)
+        if (t->bucket_hi[k] > t->bucket_lo[k])
+          nrc = t->nccl.AllReduce(G + t->bucket_lo[k], G + t->bucket_lo[k], static_cast<size_t>(t->bucket_hi[k] - t->bucket_lo[k]), 7, 0,
+                                  t->comm, t->comm_stream);
+    } else {
+      nrc = t->nccl.AllReduce(G, G, static_cast<size_t>(t->n_total + 1), 7, 0, t->comm, t->comm_stream);
+    }
+  }
+  cudaEventRecord(b, t->comm_stream);
+  int rc = XV_OK;
+  if (nrc != 0) rc = tr_fail_nccl(c, t, nrc, "ncclAllReduce");
+  e = cudaStreamSynchronize(t->comm_stream);
+  if (rc == XV_OK && e != cudaSuccess) rc = cuda_fail(c, e, "stream synchronize");
+  float ms = 0.f;
+  if (rc == XV_OK && (e = cudaEventElapsedTime(&ms, a, b)) != cudaSuccess) rc = cuda_fail(c, e, "cudaEventElapsedTime");
+  cudaEventDestroy(a);
+  cudaEventDestroy(b);
+  *ms_per_iter = ms / iters;
+  return rc;
+}
+
 int xv_comm_info(xv_ctx* c, int32_t* rank, int32_t* world, int64_t* grad_elems, int32_t* buckets) {
   if (!c) return XV_EINVAL;
   TrainState* t = c->train;

@@ -265,6 +265,25 @@ __device__ __forceinline__ float pool_grad(float y, float mu, float sd, float dm
   if (sd * sd > 1.0000001e-12f) out += ds * (y - mu) * inv_l / sd;
   return out;
 }
+// The same per (utterance, channel) as two coefficients, so that the row loop pays one subtract and one FMA per element
+// instead of a divide: d x = ca + cb * (y - mean), ca = dmean / L, cb = dstd / (L * std) (0 under the variance floor).
+struct PoolCoef { float mu[4], ca[4], cb[4]; };
+__device__ __forceinline__ void pool_coef_load(const PoolGrad& pg, int64_t u, int c_total, int c0, PoolCoef* k) {
+  float sd[4], dm[4], ds[4];
+  const float* pp = pg.pooled + u * 2 * c_total + c0;
+  const float* dp = pg.dpooled + u * 2 * c_total + c0;
+  const float4 a = *reinterpret_cast<const float4*>(pp), b = *reinterpret_cast<const float4*>(pp + c_total);
+  const float4 c = *reinterpret_cast<const float4*>(dp), d = *reinterpret_cast<const float4*>(dp + c_total);
+  k->mu[0] = a.x; k->mu[1] = a.y; k->mu[2] = a.z; k->mu[3] = a.w;
+  sd[0] = b.x; sd[1] = b.y; sd[2] = b.z; sd[3] = b.w;
+  dm[0] = c.x; dm[1] = c.y; dm[2] = c.z; dm[3] = c.w;
+  ds[0] = d.x; ds[1] = d.y; ds[2] = d.z; ds[3] = d.w;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    k->ca[j] = dm[j] * pg.inv_l;
+    k->cb[j] = sd[j] * sd[j] > 1.0000001e-12f ? ds[j] * pg.inv_l / sd[j] : 0.f;
+  }
+}
 
 // ------------------------------------------------------------------------------------------------ frame-level reductions
 // Column sums over the valid rows of a [rows, C] matrix, four channels per thread (16-byte loads), fp64 accumulators.
@@ -301,7 +320,9 @@ __global__ void __launch_bounds__(256) col_reduce4_kernel(const float* __restric
       }
     }
     int64_t cur_u = -1;
-    float pm[4] = {0.f, 0.f, 0.f, 0.f}, psd[4] = {1.f, 1.f, 1.f, 1.f}, pdm[4] = {0.f, 0.f, 0.f, 0.f}, pds[4] = {0.f, 0.f, 0.f, 0.f};
+    PoolCoef pc;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { pc.mu[j] = 0.f; pc.ca[j] = 0.f; pc.cb[j] = 0.f; }
     const bool read_dy = KIND == 1 && !pg.enabled;
     for (int64_t rb = r0 + ry; rb < r1; rb += 8 * U) {
       float zz[U][4], dd[U][4];
@@ -316,24 +337,23 @@ __global__ void __launch_bounds__(256) col_reduce4_kernel(const float* __restric
           if (read_dy) VecF<4>::load(dy + r * c_total + c0, dd[u]);
         }
       }
+      // the U rows of a group are summed in fp32 (at most U terms), the running sums stay fp64
+      float p0[4] = {0.f, 0.f, 0.f, 0.f}, p1[4] = {0.f, 0.f, 0.f, 0.f}, p2[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         if (!ok[u]) continue;
         if (KIND == 0) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const double x = zz[u][j];
-            v[0][j] += x; v[1][j] += x * x;
+            p0[j] += zz[u][j];
+            p1[j] = fmaf(zz[u][j], zz[u][j], p1[j]);
           }
         } else {
           if (pg.enabled) {
             const int64_t ut = (rb + 8 * u) / mask.t;
-            if (ut != cur_u) {                        // per-utterance pooling vectors: reloaded when the row walk enters a new utterance
+            if (ut != cur_u) {                        // per-utterance pooling coefficients: reloaded when the row walk enters a new utterance
               cur_u = ut;
-              const float* pp = pg.pooled + ut * 2 * c_total + c0;
-              const float* dp = pg.dpooled + ut * 2 * c_total + c0;
-              VecF<4>::load(pp, pm); VecF<4>::load(pp + c_total, psd);
-              VecF<4>::load(dp, pdm); VecF<4>::load(dp + c_total, pds);
+              pool_coef_load(pg, ut, c_total, c0, &pc);
             }
           }
 #pragma unroll
@@ -341,12 +361,18 @@ __global__ void __launch_bounds__(256) col_reduce4_kernel(const float* __restric
             float xh = 0.f, pre = zz[u][j];
             if (mean != nullptr) { xh = (zz[u][j] - mu[j]) * rs[j]; pre = fmaf(ga[j], xh, be[j]); }
             float d = dd[u][j];
-            if (pg.enabled) d = pool_grad(pre >= 0.f ? pre : pre * sl[j], pm[j], psd[j], pdm[j], pds[j], pg.inv_l);
+            if (pg.enabled) d = fmaf(pc.cb[j], (pre >= 0.f ? pre : pre * sl[j]) - pc.mu[j], pc.ca[j]);
             const float g = pre > 0.f ? d : d * sl[j];
-            v[0][j] += g; v[1][j] += static_cast<double>(g) * xh;
-            if (pre < 0.f) v[2][j] += static_cast<double>(d) * pre;
+            p0[j] += g;
+            p1[j] = fmaf(g, xh, p1[j]);
+            if (pre < 0.f) p2[j] = fmaf(d, pre, p2[j]);
           }
         }
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        v[0][j] += p0[j]; v[1][j] += p1[j];
+        if (KIND == 1) v[2][j] += p2[j];
       }
     }
   }
@@ -539,7 +565,13 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnBwdArgs a) {
       }
     }
     int64_t cur_u = -1;
-    float pm[4] = {0.f, 0.f, 0.f, 0.f}, psd[4] = {1.f, 1.f, 1.f, 1.f}, pdm[4] = {0.f, 0.f, 0.f, 0.f}, pds[4] = {0.f, 0.f, 0.f, 0.f};
+    PoolCoef pc;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { pc.mu[k] = 0.f; pc.ca[k] = 0.f; pc.cb[k] = 0.f; }
+    // per-element arithmetic in fp32 (the fp64 sums only enter through k1, k2): dz = gr * (g - k1 - xhat * k2)
+    float k1f[4], k2f[4], grf[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { k1f[k] = static_cast<float>(k1[k]); k2f[k] = static_cast<float>(k2[k]); grf[k] = static_cast<float>(gr[k]); }
     for (int64_t rb = r0 + threadIdx.y; rb < r1; rb += static_cast<int64_t>(blockDim.y) * U) {
       float zz[U][4], d[U][4];
 #pragma unroll
@@ -560,10 +592,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnBwdArgs a) {
             const int64_t ut = r / a.mask.t;
             if (ut != cur_u) {
               cur_u = ut;
-              const float* pp = a.pg.pooled + ut * 2 * a.c_total + c0;
-              const float* dp = a.pg.dpooled + ut * 2 * a.c_total + c0;
-              VecF<4>::load(pp, pm); VecF<4>::load(pp + a.c_total, psd);
-              VecF<4>::load(dp, pdm); VecF<4>::load(dp + a.c_total, pds);
+              pool_coef_load(a.pg, ut, a.c_total, c0, &pc);
             }
           }
 #pragma unroll
@@ -571,14 +600,9 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnBwdArgs a) {
             float xh = 0.f, pre = zz[u][k];
             if (a.mean != nullptr) { xh = (zz[u][k] - mu[k]) * rs[k]; pre = fmaf(ga[k], xh, be[k]); }
             float dk = d[u][k];
-            if (a.pg.enabled) dk = pool_grad(pre >= 0.f ? pre : pre * sl[k], pm[k], psd[k], pdm[k], pds[k], a.pg.inv_l);
+            if (a.pg.enabled) dk = fmaf(pc.cb[k], (pre >= 0.f ? pre : pre * sl[k]) - pc.mu[k], pc.ca[k]);
             const float g = pre > 0.f ? dk : dk * sl[k];
-            if (a.mean != nullptr) {
-              const double t = static_cast<double>(g) - k1[k] - static_cast<double>(xh) * k2[k];
-              out[k] = static_cast<float>(gr[k] * t);
-            } else {
-              out[k] = g;
-            }
+            out[k] = a.mean != nullptr ? grf[k] * (g - k1f[k] - xh * k2f[k]) : g;
           }
         }
         if (a.dz32 != nullptr) VecF<4>::store(a.dz32 + r * a.c_total + c0, out);
@@ -916,8 +940,27 @@ __global__ void __launch_bounds__(256) head_wgrad_kernel(const float* __restrict
     const int nb = min(16, batch - b0);
     __syncthreads();
     // stage 16 utterances of f and of this strip of G: the inner loop then touches shared memory only
-    for (int bb = 0; bb < nb; ++bb)
-      for (int e = threadIdx.x; e < e_dim; e += 256) fs[bb * kHeadMaxE + e] = f[static_cast<int64_t>(b0 + bb) * e_dim + e];
+    {
+      // the nb rows of f are one contiguous run of nb*e_dim floats: every thread issues its (up to 8) 16-byte loads
+      // back to back, then stores -- a load -> store loop with run-time bounds exposes one L2 round trip per element
+      const float4* src = reinterpret_cast<const float4*>(f + static_cast<int64_t>(b0) * e_dim);
+      const int n4 = nb * e_dim / 4;
+      float4 tmp[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int i4 = threadIdx.x + 256 * j;
+        if (i4 < n4) tmp[j] = src[i4];
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int i4 = threadIdx.x + 256 * j;
+        if (i4 < n4) {
+          const int gi = i4 * 4;
+          const int bb = gi / e_dim, e = gi - bb * e_dim;
+          *reinterpret_cast<float4*>(fs + bb * kHeadMaxE + e) = tmp[j];
+        }
+      }
+    }
     for (int i = threadIdx.x; i < nb * 32; i += 256) {
       const int bb = i >> 5, c = i & 31;
       gs[bb][c] = s0 + c < s_dim ? G[static_cast<int64_t>(b0 + bb) * s_dim + s0 + c] : 0.f;
