@@ -121,7 +121,7 @@ def test_trainer_train_epoch_over_a_kaldi_directory(tmp_path):
         str(data), str(tmp_path / "spklist"), num_speakers=8, num_segments=1, min_len=40, max_len=60, seed=9).fetch(), 0.05)
     last = trainer.train(str(data), str(tmp_path / "spklist"), 0.05)
     assert trainer.curr_step == 12 and np.isfinite(last[0]) and last[0] < first[0]
-    assert abs(first[0] - np.log(n_spk)) < 1.0
+    assert abs(first[0] - np.log(n_spk)) < 1.5           # fresh variables: cross entropy in the neighbourhood of ln(S)
     state = __import__("xvector_b200.tf_checkpoint", fromlist=["x"]).get_checkpoint_state(str(tmp_path / "nnet"))
     assert state[0] == "model-12" and "model-5" in state[1] and "model-10" in state[1]
     trainer.close()

@@ -618,6 +618,66 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
           }
         }
         }
+      } else if (!store_bf16 && p.out_f32 != nullptr && p.dot_out == nullptr) {
+      // ---- fp32-only output (training forward / data gradient, segment layers): tcgen05.ld.16x256b gives each thread
+      // 4 rows x 2 adjacent columns per 8-column group, so a quad of lanes writes one full 32-byte sector of a row
+      // (st.global.v2: 8 sectors per instruction instead of 32 half-written ones with one row per lane), and the batch-norm
+      // column statistics need the 14-shuffle butterfly of the pooled epilogue instead of a 62-shuffle transpose.
+      const int rq = lane >> 2, cq = (lane & 3) * 2;
+      float mk[4];
+      bool rok[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int rr = mw + rq + 8 * k;
+        rok[k] = rr < p.m_rows;
+        mk[k] = (rok[k] && p.stat_out != nullptr &&
+                 static_cast<int32_t>(static_cast<uint32_t>(rr) % static_cast<uint32_t>(p.stat_t)) < p.stat_valid) ? 1.f : 0.f;
+      }
+#pragma unroll 1
+      for (int ci = 0; ci < kChunksPerWarp; ++ci) {
+        const int c = half * kChunksPerWarp + ci;
+        uint32_t ra[16], rb[16];
+        const uint32_t tcol = as * kBN + c * 32;
+        ptx::tmem_ld_16x256b_x4(tmem_base + ((q * 32) << 16) + tcol, ra);
+        ptx::tmem_ld_16x256b_x4(tmem_base + ((q * 32 + 16) << 16) + tcol, rb);
+        ptx::tmem_ld_wait();
+        if (ci == kChunksPerWarp - 1) {
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) release_acc(as);
+        }
+        float v[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = 0.f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int col = c * 32 + 8 * i + cq;                      // column inside the tile
+          const float4 sh = *reinterpret_cast<const float4*>(ss + col);      // (s0, h0, s1, h1)
+          const float2 ng = *reinterpret_cast<const float2*>(sl + col);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint32_t* src = k < 2 ? ra : rb;
+            float v0 = fmaf(__uint_as_float(src[4 * i + 2 * (k & 1)]), sh.x, sh.y);
+            float v1 = fmaf(__uint_as_float(src[4 * i + 2 * (k & 1) + 1]), sh.z, sh.w);
+            if (relu_only) {
+              v0 = fmaxf(v0, 0.f);
+              v1 = fmaxf(v1, 0.f);
+            } else {
+              v0 = v0 >= 0.f ? v0 : v0 * ng.x;
+              v1 = v1 >= 0.f ? v1 : v1 * ng.y;
+              if (p.act_tanh) { v0 = tanhf(v0); v1 = tanhf(v1); }
+            }
+            if (rok[k] && n0 + col < p.f32_cols)
+              *reinterpret_cast<float2*>(p.out_f32 + static_cast<size_t>(mw + rq + 8 * k) * p.ldo + n0 + col) = make_float2(v0, v1);
+            const float m0v = v0 * mk[k], m1v = v1 * mk[k];
+            v[2 * i] += m0v;
+            v[2 * i + 1] += m1v;
+            v[8 + 2 * i] = fmaf(m0v, m0v, v[8 + 2 * i]);
+            v[8 + 2 * i + 1] = fmaf(m1v, m1v, v[8 + 2 * i + 1]);
+          }
+        }
+        if (p.stat_out != nullptr) pool_reduce_atomics(v, lane, p.stat_out, p.stat_ld, n0 + c * 32);
+      }
       } else {
       // fused attention scores: this warp's 128 columns lie in at most two heads (head_width >= 128)
       float dot_a = 0.f, dot_b = 0.f;

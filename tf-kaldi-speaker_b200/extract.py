@@ -113,6 +113,118 @@ def extract_stream(trainer, rspecifier, wspecifier, dim, chunk_size=10000, min_c
     return written, skipped
 
 
+def extract_stream_mgpu(make_trainer, devices, rspecifier, wspecifier, dim, chunk_size=10000, min_chunk_size=25,
+                        normalize=False, max_rows=1 << 20, max_utts=4096, threads=8):
+    """extract_stream over several GPUs of one box: what `run.pl JOB=1:nj extract_wrapper.sh` does with nj processes
+    (egs/voxceleb/v1/nnet/run_extract_embeddings.sh:68-71), as ONE process -- one reader (native ark decoder into a ring of
+    pinned buffers), one host thread + one xv_ctx per GPU pulling batches from a queue (utterances are independent: no
+    collective), one writer that emits the vectors in input order.  Batches are cut exactly as the
+    single-GPU stream cuts them and each is embedded by one GPU, so the output file is byte-identical to the single-GPU
+    CLI's.  make_trainer(device) -> a built, loaded Trainer.  Returns (written, skipped)."""
+    import queue
+    import threading
+    from . import kaldi_io
+    from .engine import PinnedArray
+    n_dev = len(devices)
+    n_buf = 2 * n_dev + 1
+    pins = [PinnedArray((max_rows, dim)) for _ in range(n_buf)]
+    free_bufs = queue.Queue()
+    for i in range(n_buf):
+        free_bufs.put(i)
+    work = queue.Queue(maxsize=n_buf)
+    done = {}
+    done_cv = threading.Condition()
+    errors = []
+    n_batches = [None]
+
+    def embed(trainer, feats, lengths, keys):
+        if lengths.min() >= min_chunk_size and lengths.max() <= chunk_size:
+            emb = np.asarray(trainer.predict_packed(feats, lengths), np.float32)
+            if normalize:
+                emb = emb / np.sqrt(np.sum(np.square(emb), axis=1, keepdims=True))
+            return keys, emb, 0
+        offs = np.concatenate([[0], np.cumsum(lengths)])
+        embs = extract_many(trainer, [feats[offs[i]:offs[i + 1]] for i in range(len(keys))], chunk_size, min_chunk_size, normalize)
+        keep = [i for i, e in enumerate(embs) if e is not None]
+        out = np.stack([embs[i] for i in keep]).astype(np.float32) if keep else np.zeros((0, 0), np.float32)
+        return [keys[i] for i in keep], out, len(keys) - len(keep)
+
+    def worker(dev):
+        trainer = None
+        try:
+            trainer = make_trainer(dev)
+            while True:
+                item = work.get()
+                if item is None:
+                    break
+                seq, buf, keys, rows, lengths = item
+                res = embed(trainer, pins[buf].array[:rows], lengths, keys)
+                free_bufs.put(buf)
+                with done_cv:
+                    done[seq] = res
+                    done_cv.notify_all()
+        except BaseException as e:                  # surface in the main thread
+            with done_cv:
+                errors.append(e)
+                done_cv.notify_all()
+        finally:
+            if trainer is not None:
+                trainer.close()
+
+    def reader():
+        try:
+            buf = free_bufs.get()
+            rd = kaldi_io.BatchReader(rspecifier, dim, max_rows=max_rows, max_utts=max_utts, buffer=pins[buf].array, threads=threads)
+            seq = 0
+            for keys, feats, lengths in rd:
+                work.put((seq, buf, keys, int(feats.shape[0]), lengths))
+                seq += 1
+                buf = free_bufs.get()               # the generator reads self.buffer when it resumes
+                rd.buffer = pins[buf].array
+            n_batches[0] = seq
+        except BaseException as e:
+            with done_cv:
+                errors.append(e)
+        finally:
+            for _ in devices:
+                work.put(None)
+            with done_cv:
+                if n_batches[0] is None:
+                    n_batches[0] = -1
+                done_cv.notify_all()
+
+    workers = [threading.Thread(target=worker, args=(d,), daemon=True) for d in devices]
+    for t in workers:
+        t.start()
+    rt = threading.Thread(target=reader, daemon=True)
+    rt.start()
+    written = skipped = 0
+    try:
+        with kaldi_io.open_or_fd(wspecifier, "wb") as fp_out:
+            seq = 0
+            while True:
+                with done_cv:
+                    while seq not in done and not errors and not (n_batches[0] is not None and seq >= n_batches[0]):
+                        done_cv.wait(0.5)
+                    if errors:
+                        raise errors[0]
+                    if seq not in done:
+                        break
+                    keys, emb, sk = done.pop(seq)
+                if len(keys):
+                    kaldi_io.write_vecs_flt(fp_out, keys, emb)
+                written += len(keys)
+                skipped += sk
+                seq += 1
+    finally:
+        rt.join(timeout=30)
+        for t in workers:
+            t.join(timeout=30)
+        for p in pins:
+            p.close()
+    return written, skipped
+
+
 def main(argv=None):
     """CLI with the reference's flags (extract.py:11-22)."""
     parser = argparse.ArgumentParser()
@@ -122,6 +234,8 @@ def main(argv=None):
     parser.add_argument("-n", "--normalize", action="store_true")
     parser.add_argument("--node", type=str, default="")
     parser.add_argument("--precision", type=str, default="bf16", choices=["bf16", "fp32"])
+    parser.add_argument("--gpus", type=int, default=1, help="extract on this many GPUs of the box (devices gpu .. gpu+gpus-1): "
+                        "one reader, one host thread + context per GPU, one writer; replaces the run.pl JOB=1:nj fan-out")
     parser.add_argument("model_dir", type=str)
     parser.add_argument("rspecifier", type=str)
     parser.add_argument("wspecifier", type=str)
@@ -137,14 +251,30 @@ def main(argv=None):
         params.embedding_node = args.node
     with open(os.path.join(args.model_dir, "nnet", "feature_dim"), "r") as f:
         dim = int(f.readline().strip())
-    trainer = Trainer(params, args.model_dir, dim, single_cpu=True, precision=args.precision, device=max(args.gpu, 0))
-    trainer.build("predict")
     if args.rspecifier.rsplit(".", 1)[-1] == "scp":
         sys.exit("The rspecifier must be ark or input pipe")
-    written, skipped = extract_stream(trainer, args.rspecifier, args.wspecifier, dim, args.chunk_size, args.min_chunk_size,
-                                      args.normalize)
+
+    def make_trainer(device):
+        p = Params(config_json)
+        if len(args.node) != 0:
+            p.embedding_node = args.node
+        t = Trainer(p, args.model_dir, dim, single_cpu=True, precision=args.precision, device=device)
+        t.build("predict")
+        if not t._has_model():
+            sys.exit("Cannot find model in %s" % t.model)
+        t.load()
+        return t
+
+    first = max(args.gpu, 0)
+    if args.gpus > 1:
+        written, skipped = extract_stream_mgpu(make_trainer, list(range(first, first + args.gpus)), args.rspecifier, args.wspecifier,
+                                               dim, args.chunk_size, args.min_chunk_size, args.normalize)
+    else:
+        trainer = make_trainer(first)
+        written, skipped = extract_stream(trainer, args.rspecifier, args.wspecifier, dim, args.chunk_size, args.min_chunk_size,
+                                          args.normalize)
+        trainer.close()
     print("[INFO] wrote %d embeddings, skipped %d short utterances" % (written, skipped))
-    trainer.close()
 
 
 if __name__ == "__main__":
