@@ -339,7 +339,8 @@ static int train_init(xv_ctx* c, int32_t num_speakers) {
     int max_alloc = 256;
     int prev_ldb = 0;
     auto add_job = [&](RecastJob j, int fast, int64_t slow) {
-      j.tiles_x = (fast + 31) / 32;
+      const int tile_fast = j.kind == 0 ? 64 : 32;        // forward layout: 64 (k) x 32 (n) tiles, bf16 pairs along k
+      j.tiles_x = (fast + tile_fast - 1) / tile_fast;
       j.tile0 = t->recast.total_tiles;
       t->recast.total_tiles += j.tiles_x * static_cast<int32_t>((slow + 31) / 32);
       t->recast.j[t->recast.n++] = j;
@@ -618,7 +619,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     } else {
       if (tc) fa.yb = static_cast<__nv_bfloat16*>(l.yb.p); else fa.y = static_cast<float*>(l.y.p);
       count_launch(c, "train.bn_act");
-      const RowGrid rg = row_grid(l.cout / 4, c->sm_count);
+      const RowGrid rg = row_grid(l.cout / 4, c->sm_count, 4);       // light kernel (few registers): 4 blocks per SM keep more loads in flight
       bn_act_fwd_kernel<<<rg.grid, rg.block, 0, s>>>(fa);
       TR_CUDA(cudaGetLastError(), "BN/activation launch");
       in = static_cast<const float*>(l.y.p);
@@ -651,7 +652,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     TR_CUDA(launch_skinny_gemm<false>(sa, c->sm_count, s), "logits GEMM launch");
   }
   count_launch(c, "train.loss");
-  softmax_loss_kernel<<<b, 256, 0, s>>>(static_cast<float*>(t->logits.p), S, fvec, E, static_cast<const int32_t*>(t->labels.p), b,
+  softmax_loss_kernel<<<b, kLossThreads, 0, s>>>(static_cast<float*>(t->logits.p), S, fvec, E, static_cast<const int32_t*>(t->labels.p), b,
                                         t->amsoftmax ? static_cast<const float*>(t->rnorm.p) : nullptr, t->amsoftmax ? 1 : 0,
                                         t->margin, fa, static_cast<float*>(t->gr.p), static_cast<float*>(t->coef.p), scalars);
   TR_CUDA(cudaGetLastError(), "loss launch");

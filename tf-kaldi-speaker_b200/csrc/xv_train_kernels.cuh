@@ -499,13 +499,25 @@ __global__ void __launch_bounds__(256) bn_act_pool_fwd_kernel(const BnFwdArgs a,
       }
     };
     act_row(base, piv);
-    for (int i = ty; i < a.mask.valid_len; i += 8) {
-      float v[4];
-      act_row(base + i, v);
+    for (int i0 = ty; i0 < a.mask.valid_len; i0 += 8 * 4) {
+      float v[4][4];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const double d = static_cast<double>(v[k]) - static_cast<double>(piv[k]);
-        s1[k] += d; s2[k] += d * d;
+      for (int u = 0; u < 4; ++u)                       // four independent 16-byte loads, then the math
+        if (i0 + 8 * u < a.mask.valid_len) VecF<4>::load(a.z + (base + i0 + 8 * u) * a.c_total + c0, v[u]);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (i0 + 8 * u >= a.mask.valid_len) continue;
+        float p1[4], p2[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          float t = v[u][k];
+          if (a.st.sums != nullptr) t = fmaf(ga[k], (t - mu[k]) * rs[k], be[k]);
+          t = t >= 0.f ? t : t * sl[k];
+          const float d = t - piv[k];
+          p1[k] = d; p2[k] = d * d;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { s1[k] += p1[k]; s2[k] += p2[k]; }
       }
     }
   }
@@ -618,12 +630,12 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnBwdArgs a) {
 
 // Launch geometry of the row-streaming kernels: x covers the channel groups, y the rows.
 struct RowGrid { dim3 grid, block; };
-inline RowGrid row_grid(int groups, int sm_count) {
+inline RowGrid row_grid(int groups, int sm_count, int blocks_per_sm = 2) {
   int bx = 32;
   while (bx < groups && bx < 256) bx <<= 1;
   RowGrid g;
   g.block = dim3(bx, 256 / bx);
-  g.grid = dim3(sm_count * 2);       // few fat blocks: see bn_act_fwd_kernel
+  g.grid = dim3(sm_count * blocks_per_sm);       // few fat blocks: see bn_act_fwd_kernel
   return g;
 }
 
@@ -758,7 +770,7 @@ constexpr int kMaxRecastJobs = 16;
 struct RecastJobs { RecastJob j[kMaxRecastJobs]; int32_t n, total_tiles; };
 
 __global__ void __launch_bounds__(256) recast_weights_kernel(const RecastJobs jobs) {
-  __shared__ float tile[32][33];
+  __shared__ float tile[64][33];
   for (int t = blockIdx.x; t < jobs.total_tiles; t += gridDim.x) {
     int ji = 0;
     while (ji + 1 < jobs.n && jobs.j[ji + 1].tile0 <= t) ++ji;
@@ -766,18 +778,24 @@ __global__ void __launch_bounds__(256) recast_weights_kernel(const RecastJobs jo
     const int lt = t - J.tile0;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     if (J.kind == 0) {
-      const int k0 = (lt % J.tiles_x) * 32, n0 = (lt / J.tiles_x) * 32;
-      for (int i = ty; i < 32; i += 8) {
-        const int k = k0 + i, n = n0 + tx;
+      // 64 (k) x 32 (n) tile: 8 independent loads per thread along n (coalesced), bf16 PAIRS along k on the way out
+      const int k0 = (lt % J.tiles_x) * 64, n0 = (lt / J.tiles_x) * 32;
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int k = k0 + ty + 8 * u, n = n0 + tx;
         const int j = k / J.cstride, c = k - j * J.cstride;
-        float v = 0.f;
-        if (k < J.ktotal && j < J.taps && c < J.cin && n < J.cout) v = J.w[(static_cast<int64_t>(j) * J.cin + c) * J.cout + n];
-        tile[i][tx] = v;
+        v[u] = (k < J.ktotal && j < J.taps && c < J.cin && n < J.cout) ? J.w[(static_cast<int64_t>(j) * J.cin + c) * J.cout + n] : 0.f;
       }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) tile[ty + 8 * u][tx] = v[u];
       __syncthreads();
-      for (int i = ty; i < 32; i += 8) {
-        const int n = n0 + i, k = k0 + tx;
-        if (n < J.n_alloc && k < J.ktotal) J.dst[static_cast<int64_t>(n) * J.ktotal + k] = __float2bfloat16(tile[tx][i]);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int n = n0 + ty + 8 * u, k = k0 + 2 * tx;
+        if (n < J.n_alloc && k < J.ktotal)        // ktotal is a multiple of 64: the pair never straddles the end
+          *reinterpret_cast<__nv_bfloat162*>(J.dst + static_cast<int64_t>(n) * J.ktotal + k) =
+              __floats2bfloat162_rn(tile[2 * tx][ty + 8 * u], tile[2 * tx + 1][ty + 8 * u]);
       }
       __syncthreads();
     } else {
@@ -829,6 +847,7 @@ __global__ void __launch_bounds__(256) col_rnorm_kernel(const float* __restrict_
   }
 }
 
+// sh: one slot per warp of the block (<= 32)
 __device__ __forceinline__ double block_reduce(double v, double* sh, bool is_max) {
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 #pragma unroll
@@ -846,12 +865,13 @@ __device__ __forceinline__ double block_reduce(double v, double* sh, bool is_max
 
 // One block per utterance.  logits[b, :] = f.wn (AM-softmax) or f.W + bias (softmax) on entry; on exit it holds
 // G = d(loss)/d(base logits); gr = G * r[s] (AM-softmax) for the feature gradient; coef[b] = (dloss/d||f||)/||f||.
-__global__ void __launch_bounds__(256) softmax_loss_kernel(float* __restrict__ logits, int s_dim, const float* __restrict__ f,
+constexpr int kLossThreads = 1024;      // one block per utterance: the fp64 exp / log passes over S logits are spread over 32 warps
+__global__ void __launch_bounds__(kLossThreads) softmax_loss_kernel(float* __restrict__ logits, int s_dim, const float* __restrict__ f,
                                                            int e_dim, const int32_t* __restrict__ labels, int batch,
                                                            const float* __restrict__ r, int amsoftmax, float margin, float fa,
                                                            float* __restrict__ gr, float* __restrict__ coef,
                                                            double* __restrict__ loss_sum) {
-  __shared__ double sh[8];
+  __shared__ double sh[32];
   const int b = blockIdx.x;
   float* row = logits + static_cast<int64_t>(b) * s_dim;
   const int lab = labels[b];
@@ -1092,25 +1112,35 @@ __global__ void __launch_bounds__(256) skinny_gemm_kernel(const SkinnyArgs g) {
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
   for (int k0 = kbeg; k0 < kend; k0 += 64) {
-#pragma unroll 4
+    // every thread first issues its 32 loads of this K step, then stores: a load -> store loop pays one memory round trip
+    // per unrolled group, and these GEMMs are nothing but latency (64 rows against a weight matrix streamed once)
+    float av[16], bv[16];
+#pragma unroll
     for (int i = 0; i < 16; ++i) {
       const int idx = i * 256 + threadIdx.x;
       const int mm = idx >> 6, kk = idx & 63;
       const int m = m0 + mm, k = k0 + kk;
-      As[kk][mm] = (m < g.m && k < kend) ? g.a[static_cast<int64_t>(m) * g.lda + k] : 0.f;
+      av[i] = (m < g.m && k < kend) ? g.a[static_cast<int64_t>(m) * g.lda + k] : 0.f;
     }
-#pragma unroll 4
+#pragma unroll
     for (int i = 0; i < 16; ++i) {
       const int idx = i * 256 + threadIdx.x;
       if (TB) {
         const int nn = idx >> 6, kk = idx & 63;
         const int n = n0 + nn, k = k0 + kk;
-        Bs[kk][nn] = (n < g.n && k < kend) ? g.w[static_cast<int64_t>(n) * g.ldw + k] : 0.f;
+        bv[i] = (n < g.n && k < kend) ? g.w[static_cast<int64_t>(n) * g.ldw + k] : 0.f;
       } else {
         const int kk = idx >> 6, nn = idx & 63;
         const int n = n0 + nn, k = k0 + kk;
-        Bs[kk][nn] = (n < g.n && k < kend) ? g.w[static_cast<int64_t>(k) * g.ldw + n] : 0.f;
+        bv[i] = (n < g.n && k < kend) ? g.w[static_cast<int64_t>(k) * g.ldw + n] : 0.f;
       }
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int idx = i * 256 + threadIdx.x;
+      As[idx & 63][idx >> 6] = av[i];
+      if (TB) Bs[idx & 63][idx >> 6] = bv[i];
+      else Bs[idx >> 6][idx & 63] = bv[i];
     }
     __syncthreads();
 #pragma unroll 8
