@@ -82,11 +82,21 @@ int  xv_forward(xv_ctx* ctx, const float* feats, const int32_t* lengths, int32_t
 int  xv_forward_frames(xv_ctx* ctx, const float* feats, const int32_t* lengths, int32_t n_utts,
                        const char* node, float* out, const int64_t* out_offsets, int64_t out_capacity);
 
+/* As xv_forward, with the utterances given as VIEWS into one feature buffer: view i = rows
+ * [view_row0[i], view_row0[i] + lengths[i]) of feats [total_rows, D]; views may overlap and must come in ascending
+ * view_row0 order.  This is the extractor's chunk-and-average (egs/voxceleb/v1/nnet/lib/extract.py:68-86: chunks of
+ * chunk_size frames every chunk_size/2 frames) without materialising the overlapping copies on the host: the features
+ * cross the bus once, a gather pass packs each batch's views on the device.  out[n_views, width]. */
+int  xv_forward_views(xv_ctx* ctx, const float* feats, int64_t total_rows, const int64_t* view_row0,
+                      const int32_t* lengths, int32_t n_views, const char* node, float* out, int64_t out_capacity);
+
 /* Same path split in three so a caller (bench.py) can time device-resident work:
  * xv_stage  : H2D of features + length tables (kept on the device until the next xv_stage);
  * xv_run    : launches every kernel of the forward pass asynchronously on the ctx stream;
  * xv_fetch  : D2H of the utterance-level result of the last xv_run + stream sync. */
 int  xv_stage(xv_ctx* ctx, const float* feats, const int32_t* lengths, int32_t n_utts);
+int  xv_stage_views(xv_ctx* ctx, const float* feats, int64_t total_rows, const int64_t* view_row0,
+                    const int32_t* lengths, int32_t n_views);
 int  xv_run(xv_ctx* ctx, const char* node);
 int  xv_fetch(xv_ctx* ctx, float* out, int64_t out_capacity);
 int  xv_sync(xv_ctx* ctx);

@@ -198,6 +198,98 @@ def test_extract_cli_ark_to_ark(tmp_path):
         assert max_rel(got[k][None], pred(decoded[k])[None]) <= TOL["bf16"], k
 
 
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_extract_packed_views_match_oracle(precision):
+    """The chunk-and-average extractor over overlapping VIEWS of packed rows (xv_forward_views; extract.py:64-93): skip,
+    whole, chunked utterances, with and without normalisation, against the oracle's restatement of the loop -- and the
+    view path against the sliced-copy path (extract_many) it replaces."""
+    from oracle import numpy_ref, synth
+    from xvector_b200.extract import extract_many, extract_packed
+    from xvector_b200.model.trainer import Trainer
+    cfg = dict(synth.TDNN_STAT_CONFIG)
+    w = synth.make_tdnn_weights(30, cfg, seed=6)
+    trainer = Trainer(P(**cfg), "/nonexistent", 30, single_cpu=True, precision=precision, batch_frames=1024)   # several batches
+    trainer.build("predict")
+    trainer.set_weights(w)
+    lens = np.array([20, 120, 530, 260, 77, 1203, 200, 201], np.int32)
+    feats = synth.packed_features(lens, 30, seed=77)
+    offs = np.concatenate([[0], np.cumsum(lens)])
+    oparams = numpy_ref.OracleParams(**cfg)
+    pred = lambda a: numpy_ref.predict(a, oparams, w, 30)
+    for norm in (False, True):
+        got, kept = extract_packed(trainer, feats, lens, chunk_size=200, min_chunk_size=25, normalize=norm)
+        assert list(kept) == [1, 2, 3, 4, 5, 6, 7] and got.dtype == np.float32
+        ref_many = extract_many(trainer, [feats[offs[i]:offs[i + 1]] for i in range(len(lens))], chunk_size=200, min_chunk_size=25,
+                                normalize=norm)
+        for row, u in zip(got, kept):
+            want = numpy_ref.extract_embedding(feats[offs[u]:offs[u + 1]], pred, chunk_size=200, min_chunk_size=25, normalize=norm)
+            assert max_rel(row[None], want[None]) <= TOL[precision], (u, norm)
+            assert max_rel(row[None], ref_many[u][None]) <= 2e-6, (u, norm)            # same kernels, same rows
+    # views straight through the C-ABI wrapper: overlapping, gapped, ascending
+    row0 = np.array([0, 50, 50, 400, 1500], np.int64)
+    ln = np.array([100, 100, 300, 64, 700], np.int32)
+    e = trainer.predict_views(feats, row0, ln)
+    for i in range(len(ln)):
+        assert max_rel(e[i][None], pred(feats[row0[i]:row0[i] + ln[i]])[None]) <= TOL[precision], i
+    import xvector_b200
+    with pytest.raises(xvector_b200.XVectorError, match="ascending"):
+        trainer.predict_views(feats, row0[::-1].copy(), ln)
+    with pytest.raises(xvector_b200.XVectorError, match="outside"):
+        trainer.predict_views(feats, np.array([len(feats) - 10], np.int64), np.array([50], np.int32))
+    trainer.close()
+
+
+def test_extract_cli_multi_gpu_is_byte_identical(tmp_path):
+    """extract.py --gpus N (one reader, one host thread + context per GPU, ordered writer; replaces the run.pl JOB=1:nj
+    fan-out of run_extract_embeddings.sh:68-71): same bytes as the single-GPU CLI.  With one GPU in the box the two
+    contexts share it (the threading, queueing and ordering are what is under test)."""
+    import json
+    from oracle import synth
+    from xvector_b200 import kaldi_io
+    from xvector_b200.extract import extract_stream, extract_stream_mgpu, main
+    from xvector_b200.misc.utils import Params
+    from xvector_b200.model.trainer import Trainer
+    cfg = dict(synth.TDNN_STAT_CONFIG)
+    w = synth.make_tdnn_weights(30, cfg, seed=16)
+    nnet = tmp_path / "nnet"
+    nnet.mkdir()
+    (nnet / "config.json").write_text(json.dumps(cfg))
+    (nnet / "feature_dim").write_text("30\n")
+    np.savez(str(nnet / "weights.npz"), **w)
+    rng = np.random.default_rng(5)
+    lens = rng.integers(20, 700, 60)
+    ark = str(tmp_path / "feats.ark")
+    with kaldi_io.open_or_fd(ark, "wb") as fd:
+        for i, n in enumerate(lens):
+            kaldi_io.write_mat(fd, synth.packed_features(np.array([n]), 30, seed=300 + i), "utt%03d" % i)
+    one, two = str(tmp_path / "one.ark"), str(tmp_path / "two.ark")
+
+    def make_trainer(device):
+        t = Trainer(Params(str(nnet / "config.json")), str(tmp_path), 30, single_cpu=True, device=device)
+        t.build("predict")
+        t.load()
+        return t
+
+    # the same batch cuts on both sides (an utterance's pooling sums are grouped by the row tiles it falls on, so other cuts
+    # may move the last bit)
+    t1 = make_trainer(0)
+    w1, s1 = extract_stream(t1, ark, one, 30, chunk_size=300, min_chunk_size=25, max_rows=4096, max_utts=16)
+    t1.close()
+    n_dev = min(2, max(1, len([l for l in __import__("os").popen("nvidia-smi -L 2>/dev/null").read().splitlines() if l.startswith("GPU ")])))
+    devices = [0, 1] if n_dev == 2 else [0, 0]
+    written, skipped = extract_stream_mgpu(make_trainer, devices, ark, two, 30, chunk_size=300, min_chunk_size=25,
+                                           max_rows=4096, max_utts=16)            # small batches: many hand-offs
+    assert written == int((lens >= 25).sum()) and skipped == int((lens < 25).sum()) and (w1, s1) == (written, skipped)
+    assert open(one, "rb").read() == open(two, "rb").read()
+    main(["-s", "300", "-m", "25", "--gpus", str(len(devices)) if n_dev == 2 else "1", str(tmp_path), ark, str(tmp_path / "cli.ark")])
+    assert len(dict(kaldi_io.read_vec_flt_ark(str(tmp_path / "cli.ark")))) == written
+    a = dict(kaldi_io.read_vec_flt_ark(one))
+    b = dict(kaldi_io.read_vec_flt_ark(two))
+    assert list(a) == list(b)
+    for k in a:
+        np.testing.assert_array_equal(a[k], b[k])
+
+
 def test_extract_frame_and_attention_cli(tmp_path):
     """extract_frame.py (edge-replication padding, consecutive chunks) and extract_attention.py (first chunk only)."""
     import json

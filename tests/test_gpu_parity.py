@@ -201,3 +201,32 @@ def test_large_job_properties():
     ref = np.stack(oracle_embeddings(np.concatenate([feats[offs[i]:offs[i + 1]] for i in pick[:4]]), lengths[pick[:4]], cfg, w, 30))
     _check(sub[:4], ref, "bf16")
     eng.close()
+
+
+def test_storing_layers_are_bit_reproducible_over_200_runs():
+    """Stress of the hand-rolled cluster barrier protocol (cta_group::2 pairs: remote CTA-scope mbarrier arrives, multicast
+    commits, TMEM hand-back) on the layers that STORE their output: 200 runs of the same ragged batch must give the same
+    bits for tdnn1..tdnn4 (a lost or early barrier shows up as a stale or half-written tile sooner or later).  The batch
+    has an odd number of row tiles (phantom tile of the last pair) and several batches (ring wrap, both TMEM stages)."""
+    from oracle import synth
+    cfg = dict(synth.TDNN_STAT_CONFIG)
+    w = synth.make_tdnn_weights(30, cfg, seed=3)
+    lengths = np.array([700, 333, 1500, 61, 2222, 129], np.int32)          # 4945 rows: 39 row tiles at batch_frames 4096 -> 2 batches
+    feats = synth.packed_features(lengths, 30, seed=5)
+    eng = _engine(cfg, 30, "bf16", w, batch_frames=4096)
+    try:
+        first = {}
+        for it in range(200):
+            node = ("tdnn1_relu", "tdnn2_relu", "tdnn3_relu", "tdnn4_relu")[it % 4]
+            got = np.concatenate([g.reshape(-1) for g in eng.forward_frames(feats, lengths, node)])
+            if node not in first:
+                first[node] = got.copy()
+                assert np.isfinite(got).all()
+            else:
+                assert np.array_equal(got.view(np.uint32), first[node].view(np.uint32)), "run %d of %s differs" % (it, node)
+        # the pooled path (fp64 atomics: order-independent at fp32 precision) stays reproducible to the last bit as well
+        e0 = eng.forward(feats, lengths)
+        for _ in range(20):
+            assert np.array_equal(eng.forward(feats, lengths).view(np.uint32), e0.view(np.uint32))
+    finally:
+        eng.close()

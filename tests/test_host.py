@@ -149,3 +149,35 @@ def test_all_reference_style_configs_load(tmp_path):
         f = tmp_path / ("c%d.json" % i)
         f.write_text(json.dumps(cfg))
         assert Params(str(f)).network_type == "tdnn"
+
+
+def test_extract_packed_views_match_extract_many():
+    """Host logic of the view-based extractor (extract.py:64-93 semantics): with a stand-in trainer whose "embedding" is a
+    simple function of the rows, extract_packed (overlapping views of packed rows) == extract_many (sliced copies)."""
+    from xvector_b200.extract import extract_many, extract_packed
+
+    class Fake(object):
+        def _emb(self, a):
+            a = np.asarray(a, np.float64)
+            return np.concatenate([a.mean(axis=0), a.std(axis=0), [float(len(a))]]).astype(np.float32)
+
+        def predict_ragged(self, pieces):
+            return np.stack([self._emb(p) for p in pieces])
+
+        def predict_views(self, packed, row0, lengths):
+            assert (np.diff(row0) >= 0).all()                       # the C-ABI wants ascending source rows
+            return np.stack([self._emb(packed[r:r + n]) for r, n in zip(row0, lengths)])
+
+    rng = np.random.default_rng(3)
+    lengths = np.array([30, 410, 7, 200, 999, 201, 1000], np.int32)
+    feats = rng.standard_normal((int(lengths.sum()), 5)).astype(np.float32)
+    offs = np.concatenate([[0], np.cumsum(lengths)])
+    lst = [feats[offs[i]:offs[i + 1]] for i in range(len(lengths))]
+    for norm in (False, True):
+        ref = extract_many(Fake(), lst, chunk_size=200, min_chunk_size=25, normalize=norm)
+        got, kept = extract_packed(Fake(), feats, lengths, chunk_size=200, min_chunk_size=25, normalize=norm)
+        assert list(kept) == [i for i, e in enumerate(ref) if e is not None] == [0, 1, 3, 4, 5, 6]
+        for row, i in zip(got, kept):
+            np.testing.assert_allclose(row, ref[i], rtol=2e-6, atol=1e-7)
+    got, kept = extract_packed(Fake(), feats, lengths, chunk_size=10000, min_chunk_size=2000)
+    assert got.shape[0] == 0 and len(kept) == 0

@@ -36,7 +36,9 @@ PROTOTYPES = {
     "xv_node_info": (C.c_int, [_p, C.c_char_p, _i32p, _i32p, _i32p]),
     "xv_forward": (C.c_int, [_p, _p, _i32p, C.c_int32, C.c_char_p, _f32p, C.c_int64]),
     "xv_forward_frames": (C.c_int, [_p, _p, _i32p, C.c_int32, C.c_char_p, _f32p, _i64p, C.c_int64]),
+    "xv_forward_views": (C.c_int, [_p, _p, C.c_int64, _i64p, _i32p, C.c_int32, C.c_char_p, _f32p, C.c_int64]),
     "xv_stage": (C.c_int, [_p, _p, _i32p, C.c_int32]),
+    "xv_stage_views": (C.c_int, [_p, _p, C.c_int64, _i64p, _i32p, C.c_int32]),
     "xv_run": (C.c_int, [_p, C.c_char_p]),
     "xv_fetch": (C.c_int, [_p, _f32p, C.c_int64]),
     "xv_sync": (C.c_int, [_p]),

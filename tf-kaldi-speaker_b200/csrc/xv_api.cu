@@ -617,10 +617,12 @@ void xv_destroy(xv_ctx* c) {
                     &c->d_feat_ring[0], &c->d_feat_ring[1], &c->a1, &c->scores, &c->scores_acc, &c->att_query_pad, &c->pool_acc, &c->pool_ws,
                     &c->pooled_f32, &c->pooled_bf16, &c->pooled_pre_f32, &c->seg_out[0], &c->seg_out[1],
                     &c->seg_out_bf16, &c->d_cu, &c->d_segs, &c->d_tile_seg_ptr, &c->d_gather_meta, &c->d_gather_out,
-                    &c->flush_buf};
+                    &c->flush_buf, &c->d_view_src, &c->d_feat_gather};
   for (DevBuf* b : bufs) release(b);
   for (int i = 0; i < 2; ++i)
     if (c->h_pinned[i]) cudaFreeHost(c->h_pinned[i]);
+  if (c->h_tables) cudaFreeHost(c->h_tables);
+  if (c->tables_ev) cudaEventDestroy(c->tables_ev);
   for (auto& s : c->prof) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
   for (int i = 0; i < kNumEvents; ++i)
     if (c->events[i]) cudaEventDestroy(c->events[i]);

@@ -190,6 +190,16 @@ struct xv_ctx {
   std::vector<xv::Batch> batches;
   std::vector<xv::PoolSeg> segs;
   std::vector<int32_t> tile_seg_ptr;
+  // utterances given as VIEWS into the feature buffer (xv_forward_views: the extractor's overlapping chunks)
+  bool views = false;
+  bool pipeline_hint = false;              // the features of the job being planned will be streamed from the host
+  std::vector<int64_t> view_row0;          // [n] first source row of every view (ascending)
+  xv::DevBuf d_view_src;                   // int64 [n]: source row of a view relative to its batch's first source row
+  xv::DevBuf d_feat_gather;                // fp32 [batch rows, dim]: the views of a batch packed back to back
+  // pinned staging for the per-call tables (no stream synchronisation in plan_job)
+  void* h_tables = nullptr;
+  size_t h_tables_bytes = 0;
+  cudaEvent_t tables_ev = nullptr;
   const float* host_feats = nullptr;       // xv_forward pipelined path
   bool host_pinned = false;          // xv_forward source is pinned host memory
   // result of the last run
@@ -233,7 +243,7 @@ int upload(xv_ctx* c, DevBuf* b, const void* host, size_t bytes);
 int fold_bn(xv_ctx* c, const std::string& scope, int n, std::vector<double>* s, std::vector<double>* h);
 uint16_t f32_to_bf16_rne(float f);
 // forward pieces (xv_forward.cu)
-int plan_job(xv_ctx* c, const int32_t* lengths, int32_t n_utts);
+int plan_job(xv_ctx* c, const int32_t* lengths, int32_t n_utts, const int64_t* view_row0 = nullptr, int64_t view_total_rows = 0);
 int run_job(xv_ctx* c, const char* node, bool pipelined_h2d, float* frames_out, const int64_t* frames_off,
             int64_t frames_cap);
 }  // namespace xv

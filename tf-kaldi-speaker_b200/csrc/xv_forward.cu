@@ -14,11 +14,23 @@ namespace xv {
 
 static int64_t round_up64(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
 
-int plan_job(xv_ctx* c, const int32_t* lengths, int32_t n_utts) {
+int plan_job(xv_ctx* c, const int32_t* lengths, int32_t n_utts, const int64_t* view_row0, int64_t view_total_rows) {
   if (n_utts < 0) return fail(c, XV_EINVAL, "n_utts must be >= 0");
   c->staged = false;
   c->ran = false;
   c->n_utts = n_utts;
+  c->views = view_row0 != nullptr;
+  c->view_row0.clear();
+  if (c->views) {
+    if (c->resnet && c->resnet_time_stride) return fail(c, XV_EUNSUPPORTED, "views are not supported with resnet_time_stride");
+    for (int u = 0; u < n_utts; ++u) {
+      if (view_row0[u] < 0 || view_row0[u] + lengths[u] > view_total_rows)
+        return fail(c, XV_EINVAL, "view %d (rows %lld..%lld) lies outside the feature buffer of %lld rows", u, (long long)view_row0[u],
+                    (long long)(view_row0[u] + lengths[u]), (long long)view_total_rows);
+      if (u > 0 && view_row0[u] < view_row0[u - 1]) return fail(c, XV_EINVAL, "views must be given in ascending source-row order (view %d)", u);
+    }
+    c->view_row0.assign(view_row0, view_row0 + n_utts);
+  }
   c->lengths.assign(lengths, lengths + n_utts);
   c->cu.assign(n_utts + 1, 0);
   c->cu_in.assign(n_utts + 1, 0);
@@ -33,7 +45,12 @@ int plan_job(xv_ctx* c, const int32_t* lengths, int32_t n_utts) {
     c->cu_in[u + 1] = static_cast<int32_t>(rows);
     c->cu[u + 1] = static_cast<int32_t>(tail_rows);
   }
-  c->total_rows = rows;
+  c->total_rows = c->views ? view_total_rows : rows;      // rows of the caller's feature buffer
+  // Features that come from the host are copied batch by batch on a second stream while the previous batch computes: a
+  // job of only one or two full batches (BASELINE configs[0]: 300 k frames) is cut into four so that the copy hides
+  int64_t batch_frames = c->batch_frames;
+  if (c->pipeline_hint && !c->resnet && rows < 4 * batch_frames)
+    batch_frames = std::max<int64_t>(32768, round_up64((rows + 3) / 4, kBM));
   c->batches.clear();
   c->segs.assign(n_utts, PoolSeg{0, 0, 0, 0});
   c->tile_seg_ptr.clear();
@@ -46,9 +63,15 @@ int plan_job(xv_ctx* c, const int32_t* lengths, int32_t n_utts) {
     b.t_in = lengths[u];
     int64_t r = 0;
     // resnet_18: a batch is a run of EQUAL-length utterances (one 5-D tensor map describes [B,T,F,C])
-    while (u < n_utts && (r == 0 || (r + lengths[u] <= c->batch_frames && (!c->resnet || lengths[u] == b.t_in)))) r += lengths[u++];
+    while (u < n_utts && (r == 0 || (r + lengths[u] <= batch_frames && (!c->resnet || lengths[u] == b.t_in)))) r += lengths[u++];
     b.utt1 = u;
     b.in_rows = r;
+    if (c->views) {                      // source rows this batch's views cover: [first view's start, furthest end)
+      int64_t hi = 0;
+      for (int v = b.utt0; v < b.utt1; ++v) hi = std::max<int64_t>(hi, c->view_row0[v] + lengths[v]);
+      b.in_row0 = c->view_row0[b.utt0];
+      b.in_rows = hi - b.in_row0;
+    }
     b.rows = c->cu[u] - b.row0;
     b.m_tiles = static_cast<int32_t>((b.rows + kBM - 1) / kBM);
     b.tile0 = static_cast<int32_t>(c->tile_seg_ptr.size() / 2);
@@ -73,24 +96,50 @@ int plan_job(xv_ctx* c, const int32_t* lengths, int32_t n_utts) {
     }
     c->batches.push_back(b);
   }
-  // upload tables
+  // upload tables through a pinned staging area (no stream synchronisation: the previous call's copies are awaited
+  // only if they are still in flight when the staging area is about to be overwritten)
   int rc;
-  if ((rc = ensure(c, &c->d_cu, sizeof(int32_t) * (2 * (n_utts + 1) + c->batches.size() + 1))) != XV_OK) return rc;
-  if ((rc = ensure(c, &c->d_segs, sizeof(PoolSeg) * std::max(1, n_utts))) != XV_OK) return rc;
-  if ((rc = ensure(c, &c->d_tile_seg_ptr, sizeof(int32_t) * std::max<size_t>(2, c->tile_seg_ptr.size()))) != XV_OK)
-    return rc;
-  // d_cu = [global cu (n+1)] [batch-local cu, one (nb+1) run per batch]
-  std::vector<int32_t> cu_all(c->cu);
+  std::vector<int32_t> cu_all(c->cu);       // d_cu = [global cu (n+1)] [batch-local cu, one (nb+1) run per batch]
   for (const Batch& b : c->batches)
     for (int v = b.utt0; v <= b.utt1; ++v) cu_all.push_back(static_cast<int32_t>(c->cu[v] - b.row0));
-  cudaError_t e = cudaMemcpyAsync(c->d_cu.p, cu_all.data(), cu_all.size() * sizeof(int32_t), cudaMemcpyHostToDevice,
-                                  c->stream);
-  if (e == cudaSuccess && n_utts > 0)
-    e = cudaMemcpyAsync(c->d_segs.p, c->segs.data(), sizeof(PoolSeg) * n_utts, cudaMemcpyHostToDevice, c->stream);
-  if (e == cudaSuccess && !c->tile_seg_ptr.empty())
-    e = cudaMemcpyAsync(c->d_tile_seg_ptr.p, c->tile_seg_ptr.data(), sizeof(int32_t) * c->tile_seg_ptr.size(),
-                        cudaMemcpyHostToDevice, c->stream);
-  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);   // the host vectors above are not pinned
+  std::vector<int64_t> view_src;
+  if (c->views) {
+    view_src.resize(n_utts);
+    for (const Batch& b : c->batches)
+      for (int v = b.utt0; v < b.utt1; ++v) view_src[v] = c->view_row0[v] - b.in_row0;
+  }
+  const size_t cu_bytes = cu_all.size() * sizeof(int32_t);
+  const size_t seg_bytes = sizeof(PoolSeg) * static_cast<size_t>(n_utts);
+  const size_t tsp_bytes = sizeof(int32_t) * c->tile_seg_ptr.size();
+  const size_t vs_bytes = sizeof(int64_t) * view_src.size();
+  auto up16 = [](size_t v) { return (v + 15) / 16 * 16; };
+  const size_t off_seg = up16(cu_bytes), off_tsp = off_seg + up16(seg_bytes), off_vs = off_tsp + up16(tsp_bytes);
+  const size_t total = off_vs + up16(vs_bytes) + 16;
+  if ((rc = ensure(c, &c->d_cu, std::max<size_t>(cu_bytes, 16))) != XV_OK) return rc;
+  if ((rc = ensure(c, &c->d_segs, std::max<size_t>(seg_bytes, sizeof(PoolSeg)))) != XV_OK) return rc;
+  if ((rc = ensure(c, &c->d_tile_seg_ptr, std::max<size_t>(tsp_bytes, 8))) != XV_OK) return rc;
+  if (c->views && (rc = ensure(c, &c->d_view_src, std::max<size_t>(vs_bytes, 8))) != XV_OK) return rc;
+  cudaError_t e = cudaSuccess;
+  if (c->tables_ev == nullptr) e = cudaEventCreateWithFlags(&c->tables_ev, cudaEventDisableTiming);
+  else e = cudaEventSynchronize(c->tables_ev);
+  if (e != cudaSuccess) return cuda_fail(c, e, "table staging event");
+  if (c->h_tables_bytes < total) {
+    if (c->h_tables) cudaFreeHost(c->h_tables);
+    c->h_tables = nullptr;
+    c->h_tables_bytes = 0;
+    if ((e = cudaMallocHost(&c->h_tables, total * 2)) != cudaSuccess) return cuda_fail(c, e, "cudaMallocHost(tables)");
+    c->h_tables_bytes = total * 2;
+  }
+  char* h = static_cast<char*>(c->h_tables);
+  memcpy(h, cu_all.data(), cu_bytes);
+  if (seg_bytes) memcpy(h + off_seg, c->segs.data(), seg_bytes);
+  if (tsp_bytes) memcpy(h + off_tsp, c->tile_seg_ptr.data(), tsp_bytes);
+  if (vs_bytes) memcpy(h + off_vs, view_src.data(), vs_bytes);
+  e = cudaMemcpyAsync(c->d_cu.p, h, cu_bytes, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess && seg_bytes) e = cudaMemcpyAsync(c->d_segs.p, h + off_seg, seg_bytes, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess && tsp_bytes) e = cudaMemcpyAsync(c->d_tile_seg_ptr.p, h + off_tsp, tsp_bytes, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess && vs_bytes) e = cudaMemcpyAsync(c->d_view_src.p, h + off_vs, vs_bytes, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess) e = cudaEventRecord(c->tables_ev, c->stream);
   if (e != cudaSuccess) return cuda_fail(c, e, "upload of length tables");
   return XV_OK;
 }
@@ -344,6 +393,15 @@ int run_job(xv_ctx* c, const char* node_name, bool pipelined_h2d, float* frames_
       feats_b = static_cast<const float*>(c->d_feat_ring[slot].p);
     } else {
       feats_b = static_cast<const float*>(c->d_feats.p) + b.in_row0 * c->dim;
+    }
+    if (c->views) {
+      // the batch's views (possibly overlapping source rows) packed back to back: one gather pass over the features
+      if ((rc = ensure(c, &c->d_feat_gather, static_cast<size_t>(std::max<int64_t>(max_rows, 1)) * c->dim * 4)) != XV_OK) return rc;
+      count_launch(c, "gather_views");
+      e = launch_gather_views(feats_b, cu_b, static_cast<const int64_t*>(c->d_view_src.p) + b.utt0, nb, b.rows, c->dim,
+                              static_cast<float*>(c->d_feat_gather.p), c->stream);
+      if (e != cudaSuccess) return cuda_fail(c, e, "gather_views launch");
+      feats_b = static_cast<const float*>(c->d_feat_gather.p);
     }
     // ---- frame layers ----
     const void* a_first = nullptr;          // operand of the first frame layer
@@ -609,11 +667,12 @@ using namespace xv;
 
 extern "C" {
 
-int xv_stage(xv_ctx* c, const float* feats, const int32_t* lengths, int32_t n_utts) {
+static int stage_common(xv_ctx* c, const float* feats, const int32_t* lengths, int32_t n_utts, const int64_t* view_row0,
+                        int64_t total_rows) {
   if (!c) return XV_EINVAL;
   if (!feats || !lengths) return fail(c, XV_EINVAL, "xv_stage: null argument");
   cudaSetDevice(c->device);
-  int rc = plan_job(c, lengths, n_utts);
+  int rc = plan_job(c, lengths, n_utts, view_row0, total_rows);
   if (rc != XV_OK) return rc;
   const size_t bytes = static_cast<size_t>(c->total_rows) * c->dim * 4;
   if ((rc = ensure(c, &c->d_feats, bytes)) != XV_OK) return rc;
@@ -625,6 +684,16 @@ int xv_stage(xv_ctx* c, const float* feats, const int32_t* lengths, int32_t n_ut
   c->host_feats = nullptr;
   c->staged = true;
   return XV_OK;
+}
+
+int xv_stage(xv_ctx* c, const float* feats, const int32_t* lengths, int32_t n_utts) {
+  return stage_common(c, feats, lengths, n_utts, nullptr, 0);
+}
+
+int xv_stage_views(xv_ctx* c, const float* feats, int64_t total_rows, const int64_t* view_row0, const int32_t* lengths,
+                   int32_t n_views) {
+  if (c && !view_row0) return fail(c, XV_EINVAL, "xv_stage_views: null argument");
+  return stage_common(c, feats, lengths, n_views, view_row0, total_rows);
 }
 
 int xv_run(xv_ctx* c, const char* node) {
@@ -651,13 +720,16 @@ int xv_sync(xv_ctx* c) {
 }
 
 static int forward_common(xv_ctx* c, const float* feats, const int32_t* lengths, int32_t n_utts, const char* node,
-                          float* out, const int64_t* offs, int64_t cap, bool frames) {
+                          float* out, const int64_t* offs, int64_t cap, bool frames, const int64_t* view_row0 = nullptr,
+                          int64_t view_total_rows = 0) {
   if (!c) return XV_EINVAL;
   if (!feats || !lengths || !out || (frames && !offs)) return fail(c, XV_EINVAL, "xv_forward: null argument");
   cudaSetDevice(c->device);
-  int rc = plan_job(c, lengths, n_utts);
-  if (rc != XV_OK) return rc;
   const int kind = classify_pointer(feats);
+  c->pipeline_hint = kind != 2;
+  int rc = plan_job(c, lengths, n_utts, view_row0, view_total_rows);
+  c->pipeline_hint = false;
+  if (rc != XV_OK) return rc;
   if (kind == 2) {
     // device-resident features: no staging copy at all
     const size_t bytes = static_cast<size_t>(c->total_rows) * c->dim * 4;
@@ -686,6 +758,12 @@ static int forward_common(xv_ctx* c, const float* feats, const int32_t* lengths,
 int xv_forward(xv_ctx* c, const float* feats, const int32_t* lengths, int32_t n_utts, const char* node, float* out,
                int64_t out_capacity) {
   return forward_common(c, feats, lengths, n_utts, node, out, nullptr, out_capacity, false);
+}
+
+int xv_forward_views(xv_ctx* c, const float* feats, int64_t total_rows, const int64_t* view_row0, const int32_t* lengths,
+                     int32_t n_views, const char* node, float* out, int64_t out_capacity) {
+  if (c && !view_row0) return fail(c, XV_EINVAL, "xv_forward_views: null argument");
+  return forward_common(c, feats, lengths, n_views, node, out, nullptr, out_capacity, false, view_row0, total_rows);
 }
 
 int xv_forward_frames(xv_ctx* c, const float* feats, const int32_t* lengths, int32_t n_utts, const char* node,

@@ -143,6 +143,9 @@ const char* launch_wgrad(const void* a, int64_t a_rows, int lda, const void* dz,
 // features fp32 [rows, D] -> spliced bf16 [rows, kpad]: out[r, j*D + c] = in[r + j*dil, c] (0 beyond rows / kpad)
 cudaError_t launch_splice_cast(const float* feats, int64_t rows, int d, int taps, int dil, __nv_bfloat16* out,
                                int kpad, cudaStream_t stream);
+// views -> packed rows: dst[r, :] = src[src0[v] + (r - cu[v]), :] for the view v with cu[v] <= r < cu[v+1] (fp32, dim floats per row)
+cudaError_t launch_gather_views(const float* src, const int32_t* cu, const int64_t* src0, int32_t n_views, int64_t rows, int dim,
+                                float* dst, cudaStream_t stream);
 // fp32 validation GEMM with the same tap splice: out = act(scale*(A.W)+shift), optional 3 stage outputs.
 struct SimtGemmArgs {
   const float* a;       // [a_rows, cin]

@@ -183,6 +183,32 @@ __global__ void l2_scale_rows_kernel(float* __restrict__ x, int ld, int n_rows, 
 
 }  // namespace
 
+// One warp per packed row: find the view the row belongs to (binary search over the batch-local offsets) and copy its
+// `dim` floats from the source row.  Used by xv_forward_views (overlapping chunks of the extractor, extract.py:68-86).
+static __global__ void gather_views_kernel(const float* __restrict__ src, const int32_t* __restrict__ cu,
+                                           const int64_t* __restrict__ src0, int32_t n_views, int64_t rows, int dim,
+                                           float* __restrict__ dst) {
+  const int64_t r = static_cast<int64_t>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= rows) return;
+  const int lane = threadIdx.x & 31;
+  int lo = 0, hi = n_views - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (cu[mid] <= r) lo = mid; else hi = mid - 1;
+  }
+  const float* s = src + (src0[lo] + (r - cu[lo])) * dim;
+  float* d = dst + r * dim;
+  for (int k = lane; k < dim; k += 32) d[k] = __ldg(s + k);
+}
+
+cudaError_t launch_gather_views(const float* src, const int32_t* cu, const int64_t* src0, int32_t n_views, int64_t rows, int dim,
+                                float* dst, cudaStream_t stream) {
+  if (rows <= 0 || n_views <= 0) return cudaSuccess;
+  const int64_t blocks = (rows + 7) / 8;
+  gather_views_kernel<<<static_cast<unsigned>(blocks), 256, 0, stream>>>(src, cu, src0, n_views, rows, dim, dst);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_splice_cast(const float* feats, int64_t rows, int d, int taps, int dil, __nv_bfloat16* out,
                                int kpad, cudaStream_t stream) {
   if (rows <= 0) return cudaSuccess;

@@ -619,7 +619,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     } else {
       if (tc) fa.yb = static_cast<__nv_bfloat16*>(l.yb.p); else fa.y = static_cast<float*>(l.y.p);
       count_launch(c, "train.bn_act");
-      const RowGrid rg = row_grid(l.cout / 4, c->sm_count, 4);       // light kernel (few registers): 4 blocks per SM keep more loads in flight
+      const RowGrid rg = row_grid(l.cout / 4, c->sm_count);
       bn_act_fwd_kernel<<<rg.grid, rg.block, 0, s>>>(fa);
       TR_CUDA(cudaGetLastError(), "BN/activation launch");
       in = static_cast<const float*>(l.y.p);

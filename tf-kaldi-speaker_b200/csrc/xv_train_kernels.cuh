@@ -212,11 +212,12 @@ struct BnStat {
   double n;
 };
 __device__ __forceinline__ void bn_mean_rstd(const BnStat& b, int c, float eps, float* mean, float* rstd, double* var_out) {
-  const double m = b.sums[c] / b.n;
-  double var = b.sums[b.ld + c] / b.n - m * m;
+  const double inv_n = 1.0 / b.n;                   // uniform: one divide per thread, hoisted by the compiler
+  const double m = b.sums[c] * inv_n;
+  double var = b.sums[b.ld + c] * inv_n - m * m;    // fp64 where the cancellation is
   if (var < 0.0) var = 0.0;
   *mean = static_cast<float>(m);
-  *rstd = static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps)));
+  *rstd = rsqrtf(static_cast<float>(var) + eps);    // 1 ulp in fp32: every consumer of rstd is fp32 anyway
   *var_out = var;
 }
 // What the pass that first needs mean / rstd leaves behind for the backward pass and the optimizer:
@@ -1180,7 +1181,9 @@ cudaError_t launch_skinny_gemm(SkinnyArgs g, int sm_count, cudaStream_t s) {
   cudaError_t e = cudaMemset2DAsync(g.out, sizeof(float) * g.ldo, 0, sizeof(float) * g.n, g.m, s);
   if (e != cudaSuccess) return e;
   const int nb = (g.n + 63) / 64, mb = (g.m + 63) / 64, kb = (g.k + 63) / 64;
-  int splits = (2 * sm_count + nb * mb - 1) / (nb * mb);
+  // one 64-wide K step per block when the row count is a single tile (every product of the training step): one memory round
+  // trip per block and ~kb x nb blocks in flight; otherwise ~2 blocks per SM
+  int splits = mb == 1 ? kb : (2 * sm_count + nb * mb - 1) / (nb * mb);
   if (splits > kb) splits = kb;
   if (splits < 1) splits = 1;
   g.ks = (kb + splits - 1) / splits * 64;

@@ -141,6 +141,31 @@ class Engine(object):
                                         (node or "").encode("utf-8"), _fptr(out), out.size))
         return out
 
+    def forward_views(self, feats, view_row0, lengths, node=""):
+        """Utterances as views into one packed feature buffer (xv_forward_views): view i = rows
+        [view_row0[i], view_row0[i] + lengths[i]) of feats [rows, dim]; views may overlap (the extractor's chunks),
+        ascending view_row0.  -> [n_views, width] fp32."""
+        f = feats if (isinstance(feats, np.ndarray) and feats.dtype == np.float32 and feats.flags["C_CONTIGUOUS"]) else _f32(feats)
+        if f.ndim != 2 or f.shape[1] != self.dim:
+            raise ValueError("feats must be [rows, %d]; got %s" % (self.dim, f.shape))
+        row0 = np.ascontiguousarray(view_row0, dtype=np.int64)
+        lengths = np.ascontiguousarray(lengths, dtype=np.int32)
+        width, frame_level, _ = self.node_info(node)
+        if frame_level:
+            raise ValueError("node %r is frame level" % node)
+        out = np.empty((len(lengths), width), np.float32)
+        self._check(self.lib.xv_forward_views(self._ctx, f.ctypes.data_as(C.c_void_p), f.shape[0], _i64ptr(row0), _i32ptr(lengths),
+                                              len(lengths), (node or "").encode("utf-8"), _fptr(out), out.size))
+        return out
+
+    def stage_views(self, feats, view_row0, lengths):
+        f = feats if (isinstance(feats, np.ndarray) and feats.dtype == np.float32 and feats.flags["C_CONTIGUOUS"]) else _f32(feats)
+        row0 = np.ascontiguousarray(view_row0, dtype=np.int64)
+        lengths = np.ascontiguousarray(lengths, dtype=np.int32)
+        self._n_staged = len(lengths)
+        self._check(self.lib.xv_stage_views(self._ctx, f.ctypes.data_as(C.c_void_p), f.shape[0], _i64ptr(row0), _i32ptr(lengths),
+                                            len(lengths)))
+
     def forward_frames(self, feats, lengths, node):
         """Frame-level node -> list of per-utterance arrays [T_u - context, width] ([H, T_u - context] for
         attention_weights)."""

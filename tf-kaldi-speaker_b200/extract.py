@@ -2,9 +2,11 @@
 skip short utterances, split long ones into overlapping chunks (hop = chunk_size/2), embed, optionally
 L2-normalise, average the chunk embeddings weighted by chunk length.
 
-`extract_one` is the literal per-utterance loop body (two predict calls for a chunked utterance).
-`extract_many` is the B200 form: every utterance and every chunk of the whole list goes down in ONE packed
-xv_forward call (utterances stay independent, so results are identical to the per-utterance loop)."""
+`extract_one` is the per-utterance loop body (two predict calls for a chunked utterance).
+`extract_many` is the B200 form for a list of arrays: every utterance and every chunk of the whole list goes down in
+ONE packed xv_forward call (utterances stay independent, so results are identical to the per-utterance loop).
+`extract_packed` is the same for utterances already packed back to back: chunks become overlapping views of the packed
+rows (xv_forward_views), no host-side slicing or copying at all; the ark-to-ark stream uses it."""
 import argparse
 import os
 import sys
@@ -75,6 +77,43 @@ def extract_many(trainer, features_list, chunk_size=10000, min_chunk_size=25, no
     return out
 
 
+def extract_packed(trainer, feats, lengths, chunk_size=10000, min_chunk_size=25, normalize=False):
+    """extract_many for utterances that are already packed back to back (feats [sum(lengths), D] float32, e.g. the pinned
+    buffer the native ark reader fills): the chunks of a long utterance (extract.py:68-78: chunk_size frames every
+    chunk_size/2) are handed to the library as overlapping VIEWS of the packed rows (xv_forward_views), so nothing is
+    sliced, copied or concatenated on the host and the features cross the bus once; the chunk embeddings are averaged
+    weighted by chunk length (:86).  -> (embeddings [n_kept, E] float32, kept utterance indices); utterances shorter than
+    min_chunk_size are left out (:65-67)."""
+    lengths = np.asarray(lengths)
+    offs = np.concatenate([[0], np.cumsum(lengths, dtype=np.int64)])
+    work = plan_many(lengths, chunk_size, min_chunk_size)
+    if not work:
+        return np.zeros((0, 0), np.float32), np.zeros(0, np.int64)
+    owners = np.fromiter((u for u, _, _ in work), np.int64, len(work))
+    sizes = np.fromiter((z for _, _, z in work), np.int32, len(work))
+    row0 = offs[owners] + np.fromiter((s for _, s, _ in work), np.int64, len(work))
+    emb = trainer.predict_views(feats, row0, sizes)
+    first = np.concatenate([[0], np.nonzero(np.diff(owners))[0] + 1])             # pieces of an utterance are consecutive
+    kept = owners[first]
+    counts = np.diff(np.concatenate([first, [len(work)]]))
+    if counts.max() > 1:
+        e = emb.astype(np.float64)
+        if normalize:
+            multi = np.repeat(counts > 1, counts)
+            nrm = np.sqrt(np.sum(np.square(e), axis=1, keepdims=True))
+            e = np.where(multi[:, None], e / nrm, e)                              # per-chunk normalisation (:80-81) of chunked utterances only
+        w = sizes.astype(np.float64)[:, None]
+        out = np.add.reduceat(e * w, first, axis=0) / np.add.reduceat(w, first, axis=0)
+        single = counts == 1
+        out[single] = emb[first[single]]                                          # unchunked utterances: the embedding itself, bit for bit
+        out = out.astype(np.float32)
+    else:
+        out = emb
+    if normalize:
+        out = out / np.sqrt(np.sum(np.square(out), axis=1, keepdims=True))
+    return out.astype(np.float32), kept
+
+
 def extract_stream(trainer, rspecifier, wspecifier, dim, chunk_size=10000, min_chunk_size=25, normalize=False,
                    max_rows=1 << 20, max_utts=4096, pinned=True):
     """The reference's extraction loop (extract.py:63-93) as a stream of packed batches: the native ark reader
@@ -99,13 +138,10 @@ def extract_stream(trainer, rspecifier, wspecifier, dim, chunk_size=10000, min_c
                     kaldi_io.write_vecs_flt(fp_out, keys, emb)
                     written += len(keys)
                     continue
-                offs = np.concatenate([[0], np.cumsum(lengths)])
-                embs = extract_many(trainer, [feats[offs[i]:offs[i + 1]] for i in range(len(keys))], chunk_size,
-                                    min_chunk_size, normalize)
-                keep = [i for i, e in enumerate(embs) if e is not None]
+                emb, keep = extract_packed(trainer, feats, lengths, chunk_size, min_chunk_size, normalize)
                 skipped += len(keys) - len(keep)
-                if keep:
-                    kaldi_io.write_vecs_flt(fp_out, [keys[i] for i in keep], np.stack([embs[i] for i in keep]).astype(np.float32))
+                if len(keep):
+                    kaldi_io.write_vecs_flt(fp_out, [keys[i] for i in keep], emb)
                     written += len(keep)
     finally:
         if pin is not None:
@@ -143,11 +179,8 @@ def extract_stream_mgpu(make_trainer, devices, rspecifier, wspecifier, dim, chun
             if normalize:
                 emb = emb / np.sqrt(np.sum(np.square(emb), axis=1, keepdims=True))
             return keys, emb, 0
-        offs = np.concatenate([[0], np.cumsum(lengths)])
-        embs = extract_many(trainer, [feats[offs[i]:offs[i + 1]] for i in range(len(keys))], chunk_size, min_chunk_size, normalize)
-        keep = [i for i, e in enumerate(embs) if e is not None]
-        out = np.stack([embs[i] for i in keep]).astype(np.float32) if keep else np.zeros((0, 0), np.float32)
-        return [keys[i] for i in keep], out, len(keys) - len(keep)
+        emb, keep = extract_packed(trainer, feats, lengths, chunk_size, min_chunk_size, normalize)
+        return [keys[i] for i in keep], emb, len(keys) - len(keep)
 
     def worker(dev):
         trainer = None

@@ -326,6 +326,17 @@ class Trainer(object):
                 sys.exit("Cannot find model in %s" % self.model)
         return self.engine.forward(packed, np.ascontiguousarray(lengths, np.int32), self.params.embedding_node)
 
+    def predict_views(self, packed, view_row0, lengths):
+        """Utterances (or chunks) as views into packed features: view i = rows [view_row0[i], view_row0[i] + lengths[i]);
+        views may overlap (extract.py's chunk hop is chunk_size / 2).  One xv_forward_views call."""
+        if not self.is_loaded:
+            if self._has_model():
+                self.load()
+            else:
+                sys.exit("Cannot find model in %s" % self.model)
+        self._refresh_predict_weights()
+        return self.engine.forward_views(packed, view_row0, lengths, self.params.embedding_node)
+
     def predict_ragged(self, features_list):
         """Extension of predict(): a list of [T_u, D] utterances of different lengths in ONE packed call.
         Row u of the result equals predict(features_list[u]) (each utterance is computed as a batch of one)."""
