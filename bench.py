@@ -589,6 +589,74 @@ def leg_cfg1_chunked(args, local):
                          "processed_frames_per_s": processed / (ms_res * 1e-3)}}
 
 
+def leg_ark_e2e(args, devices):
+    """The real extraction job, ark file in -> x-vector ark out (egs/voxceleb/v1/nnet/lib/extract.py:63-93 as the
+    product runs it): native reader (mmap + decode threads) into a ring of pinned buffers, one host thread + context per
+    GPU (xvector_b200.extract.extract_stream_mgpu), ordered native writer.  The arks live on tmpfs so that the reader is
+    measured, not a disk.  FM = float matrices, CM = Kaldi compressed matrices (what the recipes store)."""
+    import shutil
+    import tempfile
+    from oracle import kaldi_io_ref, synth                     # generators / format writers for the INPUT files only
+    from xvector_b200 import kaldi_io
+    from xvector_b200.extract import extract_stream_mgpu
+    from xvector_b200.model.trainer import Trainer
+    dim = DIM
+    cfg = dict(synth.TDNN_STAT_CONFIG)
+    w = synth.make_tdnn_weights(dim, cfg, seed=1234)
+    base = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None
+    tmp = tempfile.mkdtemp(prefix="xv_ark_e2e_", dir=base)
+    out = {"devices": len(devices), "tmpfs": base is not None}
+    try:
+        rng = np.random.default_rng(11)
+        scale = np.linspace(3.0, 0.5, dim).astype(np.float32)
+        lengths = synth.config2_lengths(UTTS_PER_GPU, seed=202)
+        n_fm = 2048 * len(devices) if len(devices) <= 2 else 4096
+        n_fm = min(n_fm, len(lengths))
+        fm = os.path.join(tmp, "feats_fm.ark")
+        frames_fm = 0
+        with kaldi_io.open_or_fd(fm, "wb") as fd:
+            for i in range(n_fm):
+                m = rng.standard_normal((int(lengths[i]), dim), dtype=np.float32) * scale
+                kaldi_io.write_mat(fd, m, "utt%05d" % i)
+                frames_fm += m.shape[0]
+        n_cm = 256
+        cm = os.path.join(tmp, "feats_cm.ark")
+        frames_cm = 0
+        with open(cm, "wb") as f:
+            for i in range(n_cm):
+                m = rng.standard_normal((int(lengths[i]), dim), dtype=np.float32) * scale
+                f.write(kaldi_io_ref.write_cm_bytes(m, "utt%05d" % i))
+                frames_cm += m.shape[0]
+
+        def make_trainer(device):
+            t = Trainer(_P(**cfg), "/nonexistent", dim, single_cpu=True, precision="bf16", device=device)
+            t.build("predict")
+            t.set_weights(w)
+            return t
+
+        for name, path, frames, reps in (("fm", fm, frames_fm, 3), ("cm", cm, frames_cm, 2)):
+            best = None
+            for _ in range(reps):
+                t0 = time.perf_counter()
+                written, skipped = extract_stream_mgpu(make_trainer, devices, path, os.path.join(tmp, "xvector.ark"), dim,
+                                                       max_rows=1 << 19)
+                dt = time.perf_counter() - t0
+                best = dt if best is None else min(best, dt)
+            # the reader alone (decode into a pinned-size buffer, nothing else)
+            t0 = time.perf_counter()
+            rows = 0
+            for _, feats, _ in kaldi_io.BatchReader(path, dim, max_rows=1 << 19, max_utts=4096):
+                rows += feats.shape[0]
+            rd = time.perf_counter() - t0
+            out[name] = {"utterances": int(written), "frames": int(frames), "bytes": os.path.getsize(path),
+                         "seconds_best_of_%d" % reps: best, "frames_per_s": frames / best,
+                         "reader_alone_frames_per_s": rows / rd,
+                         "note": "wall clock incl. context creation + weight upload (%d context(s)), reader, xv_forward, writer" % len(devices)}
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+    return out
+
+
 def run_ours(args):
     dc = Dist()
     line = measure_extraction(args, dc, with_pool=not args.no_pool_bench, with_cpu=not args.no_cpu_baseline)
@@ -603,8 +671,13 @@ def run_ours(args):
                 legs[name] = run_leg(name, lambda la=la: compact(measure_extraction(la, solo, with_pool=False, with_cpu=False)))
             la = leg_args(args, steps=200, warmup=20, train_global_batch=0)
             legs["train"] = run_leg("train", lambda: compact(measure_train(la, Solo(dc.local))))
+            legs["ark_e2e"] = run_leg("ark_e2e", leg_ark_e2e, args, [dc.local])
         else:
             legs["train_dp"] = run_leg("train_dp", leg_train_dp, args, dc)
+            dc.barrier()
+            if dc.rank == 0:                                    # one process drives every GPU of the box: the product's shape
+                legs["ark_e2e"] = run_leg("ark_e2e", leg_ark_e2e, args, list(range(dc.world)))
+            dc.barrier()
     if dc.rank == 0:
         if legs:
             line["legs"] = legs

@@ -8,6 +8,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/mman.h>
 #include <sys/stat.h>
 #include <sys/types.h>
 #include <sys/uio.h>
@@ -122,6 +123,34 @@ struct Source {
   size_t pos = 0, end = 0;
   bool eof = false;
   std::string err;
+  // memory-mapped mode (regular uncompressed files, batch reader): every "read" is a memcpy out of the page cache --
+  // no system call per object, and the worker threads copy bodies out of the same mapping in parallel
+  const uint8_t* map = nullptr;
+  size_t map_size = 0, map_pos = 0;
+  bool map_owner = false;
+
+  // logical stream position (bytes consumed so far) of a seekable source
+  int64_t tell() const {
+    if (map) return static_cast<int64_t>(map_pos) - static_cast<int64_t>(end - pos);
+    return static_cast<int64_t>(lseek(fd, 0, SEEK_CUR)) - static_cast<int64_t>(end - pos);
+  }
+
+  bool enable_map() {
+    if (map) return true;
+    if (!seekable || gz || fd < 0) return false;
+    struct stat st;
+    if (fstat(fd, &st) != 0 || st.st_size <= 0) return false;
+    const int64_t at = tell();
+    void* m = mmap(nullptr, static_cast<size_t>(st.st_size), PROT_READ, MAP_SHARED, fd, 0);
+    if (m == MAP_FAILED) return false;
+    madvise(m, static_cast<size_t>(st.st_size), MADV_SEQUENTIAL);
+    map = static_cast<const uint8_t*>(m);
+    map_size = static_cast<size_t>(st.st_size);
+    map_pos = static_cast<size_t>(at);
+    map_owner = true;
+    pos = end = 0;
+    return true;
+  }
 
   int open(const std::string& rspecifier, size_t buf_bytes = kBufBytes) {
     std::string prefix, file;
@@ -155,6 +184,13 @@ struct Source {
 
   // raw read of up to n bytes; 0 at end of stream, -1 on error
   ssize_t raw_read(void* dst, size_t n) {
+    if (map) {
+      const size_t left = map_size - map_pos;
+      const size_t take = n < left ? n : left;
+      memcpy(dst, map + map_pos, take);
+      map_pos += take;
+      return static_cast<ssize_t>(take);
+    }
     if (gz) {
       const int got = gzread(gz, dst, static_cast<unsigned>(n > (1u << 30) ? (1u << 30) : n));
       if (got < 0) { set_err(&err, "gzread failed"); return -1; }
@@ -193,6 +229,12 @@ struct Source {
     dst += take;
     n -= take;
     while (n > 0) {
+      if (map) {
+        if (map_size - map_pos < n) { eof = true; set_err(&err, "unexpected end of stream"); return false; }
+        memcpy(dst, map + map_pos, n);
+        map_pos += n;
+        return true;
+      }
       if (n >= kDirectBytes && !gz) {
         // body: scatter read -- the rest of the body lands in the destination, a short look-ahead (the next key and
         // header) in the bounce buffer; one system call and no second copy per object
@@ -234,6 +276,11 @@ struct Source {
     if (n <= have) { pos += static_cast<size_t>(n); return true; }
     n -= have;
     pos = end = 0;
+    if (map) {
+      if (map_size - map_pos < n) { set_err(&err, "unexpected end of stream"); return false; }
+      map_pos += static_cast<size_t>(n);
+      return true;
+    }
     if (seekable && !gz) {
       struct stat st;
       const off_t cur = lseek(fd, 0, SEEK_CUR);
@@ -274,6 +321,8 @@ struct Source {
 
   int close_all() {
     int rc = XVK_OK;
+    if (map && map_owner) munmap(const_cast<uint8_t*>(map), map_size);
+    map = nullptr;
     if (gz) { gzclose(gz); gz = nullptr; }
     if (fd >= 0) { ::close(fd); fd = -1; }
     if (child > 0) { rc = reap(child, cmd, &err); child = -1; }
@@ -533,7 +582,9 @@ int read_batch_indexed(xvk_reader* r, float* dst, int64_t cap_rows, int32_t dim,
   *n_utts = 0;
   *n_rows = 0;
   Source& s = r->src;
-  s.fill_limit = 4096;
+  static const bool no_map = getenv("XVK_NO_MMAP") != nullptr;      // A/B switch
+  if (!no_map) s.enable_map();
+  s.fill_limit = s.map ? 256 : 4096;          // header scans: a key + header is a few dozen bytes
   for (;;) {
     if (!r->pending) {
       const int rc = xvk_next(r, nullptr, nullptr, nullptr, nullptr);
@@ -558,7 +609,7 @@ int read_batch_indexed(xvk_reader* r, float* dst, int64_t cap_rows, int32_t dim,
     }
     if (bad != XVK_OK) { s.fill_limit = 0; return bad; }
     Item it;
-    it.off = static_cast<int64_t>(lseek(s.fd, 0, SEEK_CUR)) - static_cast<int64_t>(s.end - s.pos);
+    it.off = s.tell();
     it.row0 = rows;
     it.h = h;
     items.push_back(it);
@@ -571,6 +622,22 @@ int read_batch_indexed(xvk_reader* r, float* dst, int64_t cap_rows, int32_t dim,
   }
   s.fill_limit = 0;
   const int threads = std::min<int64_t>(r->threads, std::max<int64_t>(1, static_cast<int64_t>(items.size())));
+  if (s.map) {
+    // bodies are copied (FM) or decoded (DM / CM) straight out of the mapping, one object per task
+    const int mrc = parallel_for(static_cast<int64_t>(items.size()), threads, [&](int64_t i, int, std::vector<uint8_t>* scratch, std::string* err) {
+      const Item& it = items[i];
+      Source w;
+      w.map = s.map;
+      w.map_size = s.map_size;
+      w.map_pos = static_cast<size_t>(it.off);
+      w.seekable = true;
+      return decode_body(w, it.h, 0, it.h.rows, dst + it.row0 * dim, static_cast<int64_t>(dim), scratch, err);
+    }, &r->err);
+    if (mrc != XVK_OK) return mrc;
+    *n_utts = static_cast<int32_t>(items.size());
+    *n_rows = rows;
+    return more;
+  }
   while (static_cast<int>(r->worker_fds.size()) < threads) {
     const int fd = ::open(s.path.c_str(), O_RDONLY | O_CLOEXEC);
     if (fd < 0) { set_err(&r->err, "cannot open %s: %s", s.path.c_str(), strerror(errno)); return XVK_EOPEN; }
