@@ -141,7 +141,8 @@ struct Source {
     struct stat st;
     if (fstat(fd, &st) != 0 || st.st_size <= 0) return false;
     const int64_t at = tell();
-    void* m = mmap(nullptr, static_cast<size_t>(st.st_size), PROT_READ, MAP_SHARED, fd, 0);
+    static const bool populate = getenv("XVK_MAP_POPULATE") != nullptr;     // A/B switch: pre-fault the whole mapping
+    void* m = mmap(nullptr, static_cast<size_t>(st.st_size), PROT_READ, MAP_SHARED | (populate ? MAP_POPULATE : 0), fd, 0);
     if (m == MAP_FAILED) return false;
     madvise(m, static_cast<size_t>(st.st_size), MADV_SEQUENTIAL);
     map = static_cast<const uint8_t*>(m);

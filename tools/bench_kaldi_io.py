@@ -33,7 +33,8 @@ def main():
         for _ in range(2):                                  # second pass: page cache warm
             t0 = time.perf_counter()
             rows = 0
-            for keys, feats, lens in K.BatchReader(path, dim, max_rows=1 << 18, max_utts=4096):
+            for keys, feats, lens in K.BatchReader(path, dim, max_rows=1 << 18, max_utts=4096,
+                                                   threads=int(os.environ.get("XVK_BENCH_THREADS", "8"))):
                 rows += feats.shape[0]
             dt = time.perf_counter() - t0
         assert rows == total
