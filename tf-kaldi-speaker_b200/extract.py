@@ -156,6 +156,26 @@ def default_reader_threads():
     return max(1, min(32, os.cpu_count() or 8))
 
 
+_PIN_RING = {}
+
+
+def _pinned_ring(n_buf, max_rows, dim):
+    """Ring of pinned [max_rows, dim] buffers, kept for the life of the process: cudaHostAlloc of a 63 MB buffer costs tens
+    of milliseconds, a whole extraction call of a few million frames not much more."""
+    from .engine import PinnedArray
+    ring = _PIN_RING.setdefault((int(max_rows), int(dim)), [])
+    while len(ring) < n_buf:
+        ring.append(PinnedArray((max_rows, dim)))
+    return ring[:n_buf]
+
+
+def release_pinned_rings():
+    for ring in _PIN_RING.values():
+        for p in ring:
+            p.close()
+    _PIN_RING.clear()
+
+
 def extract_stream_mgpu(make_trainer, devices, rspecifier, wspecifier, dim, chunk_size=10000, min_chunk_size=25,
                         normalize=False, max_rows=1 << 20, max_utts=4096, threads=None, trainers=None):
     """extract_stream over several GPUs of one box: what `run.pl JOB=1:nj extract_wrapper.sh` does with nj processes
@@ -172,7 +192,7 @@ def extract_stream_mgpu(make_trainer, devices, rspecifier, wspecifier, dim, chun
     threads = threads or default_reader_threads()
     n_dev = len(devices)
     n_buf = 2 * n_dev + 1
-    pins = [PinnedArray((max_rows, dim)) for _ in range(n_buf)]
+    pins = _pinned_ring(n_buf, max_rows, dim)
     free_bufs = queue.Queue()
     for i in range(n_buf):
         free_bufs.put(i)
@@ -262,8 +282,6 @@ def extract_stream_mgpu(make_trainer, devices, rspecifier, wspecifier, dim, chun
         rt.join(timeout=30)
         for t in workers:
             t.join(timeout=30)
-        for p in pins:
-            p.close()
     return written, skipped
 
 
@@ -307,15 +325,11 @@ def main(argv=None):
         t.load()
         return t
 
+    # one pipeline for any number of GPUs: the reader runs ahead of the device(s) through a ring of pinned buffers
     first = max(args.gpu, 0)
-    if args.gpus > 1:
-        written, skipped = extract_stream_mgpu(make_trainer, list(range(first, first + args.gpus)), args.rspecifier, args.wspecifier,
-                                               dim, args.chunk_size, args.min_chunk_size, args.normalize)
-    else:
-        trainer = make_trainer(first)
-        written, skipped = extract_stream(trainer, args.rspecifier, args.wspecifier, dim, args.chunk_size, args.min_chunk_size,
-                                          args.normalize)
-        trainer.close()
+    written, skipped = extract_stream_mgpu(make_trainer, list(range(first, first + max(args.gpus, 1))), args.rspecifier,
+                                           args.wspecifier, dim, args.chunk_size, args.min_chunk_size, args.normalize)
+    release_pinned_rings()
     print("[INFO] wrote %d embeddings, skipped %d short utterances" % (written, skipped))
 
 
