@@ -828,9 +828,9 @@ def measure_train(args, dc, precision=None, comm_bench=False):
         "config": {"workload": "configs[4]: TDNN x-vector + AM-softmax training step fwd+bwd+update, %d x %d frames x %d dims, "
                                "%d speakers, SGD" % (gbatch, frames, dim, speakers), "global_batch": gbatch,
                    "per_gpu_batch": gbatch // world, "weights": "random init, seed 1234",
-                   "parallelism": "dp%d: ncclAllReduce(sum) of the flat gradient buffer (%d fp32) in %d bucket(s) on a side stream, "
-                                  "overlapped with the backward pass; library communicator (xv_comm_init)" % (
-                                      world, info["grad_elems"], info["buckets"]),
+                   "parallelism": "dp%d: ncclAllReduce(sum) of the flat gradient buffer (%d elements, travelling as %s) in %d bucket(s) "
+                                  "on a side stream, overlapped with the backward pass; library communicator (xv_comm_init)" % (
+                                      world, info["grad_elems"], info.get("dtype", "fp32"), info["buckets"]),
                    "comm_nranks": info["world"],
                    "l2_policy": "activations + gradients of a step (0.4 GB) exceed the L2"},
         "e2e": {"value": total_frames * args.steps / wall, "unit": UNIT, "h2d_bytes_per_step": int(xs.nbytes + ys.nbytes),
@@ -862,10 +862,10 @@ def comm_roofline(eng, dc, info, iters=20):
     dc.barrier(eng)
     eng._check(eng.lib.xv_comm_bench(eng._ctx, iters, C.byref(ms)))
     per = dc.max(float(ms.value))
-    payload = info["grad_elems"] * 4
+    payload = info["grad_elems"] * (2 if info.get("dtype") == "bf16" else 4)       # (the fp32 tail of a bf16 exchange is < 0.1 %)
     n = info["world"]
     bus = 2.0 * (n - 1) / n * payload / (per * 1e-3) / 1e9
-    return {"ms_per_allreduce": per, "payload_bytes": payload, "buckets": info["buckets"], "nranks": n,
+    return {"ms_per_allreduce": per, "payload_bytes": payload, "dtype": info.get("dtype", "fp32"), "buckets": info["buckets"], "nranks": n,
             "bus_gbs": bus, "nvlink_peak_gbs_per_direction": 900.0, "frac_of_nvlink": bus / 900.0, "iters": iters}
 
 

@@ -208,6 +208,10 @@ int  xv_comm_init(xv_ctx* ctx, const void* nccl_unique_id, int rank, int world);
  * the communicator (ncclCommAbort); the peers see an asynchronous NCCL error instead of a hang (ncclCommGetAsyncError is
  * polled while a step is waited for) and every context of the job must be re-created. */
 int  xv_comm_info(xv_ctx* ctx, int32_t* rank, int32_t* world, int64_t* grad_elems, int32_t* buckets);
+/* XV_DTYPE_BF16 when the gradients of the trainable variables cross NVLink as bf16 (default of the bf16 precision with
+ * world > 1: fp32 master weights and fp32 sums on arrival, half the bytes in flight; the tail -- moving statistics and the
+ * loss -- always travels as fp32), XV_DTYPE_F32 otherwise.  Config key "grad_allreduce_dtype": "bf16" | "fp32". */
+int  xv_comm_dtype(xv_ctx* ctx);
 /* The exchange step alone (measurement): all-reduces the step's gradient buckets `iters` times back to back on the
  * communication stream and reports the mean time of one full exchange (CUDA events on that stream).  Collective: every
  * rank must call it with the same iters.  The gradient buffer is scratch between steps. */

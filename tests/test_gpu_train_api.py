@@ -138,7 +138,8 @@ def test_trainer_mgpu_matches_two_tower_oracle(tmp_path):
     trainer = TrainerMGPU(_params(tmp_path, cfg), str(tmp_path), dim, num_speakers=speakers, num_gpus=2, precision="fp32")
     trainer.set_weights(w)
     trainer.build("train")
-    assert trainer.engine.comm_info() == {"rank": 0, "world": 2, "grad_elems": trainer.engine.comm_info()["grad_elems"], "buckets": 3}
+    assert trainer.engine.comm_info() == {"rank": 0, "world": 2, "grad_elems": trainer.engine.comm_info()["grad_elems"], "buckets": 3,
+                                          "dtype": "fp32"}
     loss, total = trainer.train_step(x, y, 0.05)
     new_ref, info = train_ref.train_step(x, y, w, numpy_ref.OracleParams(**cfg), 0.05, 0, num_towers=2)
     assert abs(loss - info["loss"]) <= 1e-5 * abs(info["loss"])
@@ -147,3 +148,33 @@ def test_trainer_mgpu_matches_two_tower_oracle(tmp_path):
         np.testing.assert_array_equal(v0[k], v1[k])            # replicas stay bit-identical
         assert np.linalg.norm(v0[k] - new_ref[k].reshape(v0[k].shape)) <= 5e-3 * np.linalg.norm(new_ref[k]), k
     trainer.close()
+
+
+@pytest.mark.skipif(_n_gpus() < 2, reason="needs 2 GPUs (run with gpurun --gpus 2)")
+def test_trainer_mgpu_bf16_exchange_tracks_fp32_exchange(tmp_path):
+    """bf16 precision, two towers: gradients cross NVLink as bf16 by default (fp32 masters; "grad_allreduce_dtype"), the
+    replicas stay bit-identical, and the step stays within bf16 rounding of the same step with an fp32 exchange."""
+    from oracle import synth
+    from xvector_b200.model.trainer import TrainerMGPU
+    dim, speakers = 24, 101
+    x, y = synth.config5_batch(16, 50, dim, speakers, seed=32, speaker_signal=1.0)
+    out = {}
+    for comm in ("bf16", "fp32"):
+        cfg = dict(synth.TDNN_AMSOFTMAX_CONFIG, num_speakers_per_batch=16, num_segments_per_speaker=1, grad_allreduce_dtype=comm)
+        w = synth.add_softmax_weights(synth.make_tdnn_weights(dim, cfg, seed=31), speakers)
+        trainer = TrainerMGPU(_params(tmp_path, cfg), str(tmp_path), dim, num_speakers=speakers, num_gpus=2, precision="bf16")
+        trainer.set_weights(w)
+        trainer.build("train")
+        assert trainer.engine.comm_info()["dtype"] == comm
+        loss, _ = trainer.train_step(x, y, 0.05)
+        v0, v1 = trainer.engines[0].train_variables(), trainer.engines[1].train_variables()
+        for k in v0:
+            np.testing.assert_array_equal(v0[k], v1[k])        # replicas stay bit-identical
+        out[comm] = (loss, {k: trainer.engine.train_grad(k, np.asarray(w[k]).shape) for k in ("tdnn/tdnn3_conv/kernel", "tdnn/tdnn6_dense/kernel", "softmax/output/kernel")},
+                     v0["tdnn/tdnn1_bn/moving_mean"])
+        trainer.close()
+    assert abs(out["bf16"][0] - out["fp32"][0]) <= 1e-6 * abs(out["fp32"][0])      # the loss travels in the fp32 tail
+    np.testing.assert_array_equal(out["bf16"][2], out["fp32"][2])                  # so do the moving statistics
+    for k, g in out["bf16"][1].items():
+        ref = out["fp32"][1][k]
+        assert np.linalg.norm(g - ref) <= 6e-3 * np.linalg.norm(ref), k            # one bf16 rounding per tower gradient + one of the sum

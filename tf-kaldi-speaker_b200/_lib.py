@@ -80,6 +80,7 @@ PROTOTYPES = {
     "xv_train_variable_name": (C.c_int, [_p, C.c_int32, C.c_char_p, C.c_size_t, _i64p]),
     "xv_comm_info": (C.c_int, [_p, _i32p, _i32p, _i64p, _i32p]),
     "xv_comm_bench": (C.c_int, [_p, C.c_int32, _f32p]),
+    "xv_comm_dtype": (C.c_int, [_p]),
     "xv_comm_unique_id": (C.c_int, [_p, _p]),
     "xv_comm_init": (C.c_int, [_p, _p, C.c_int, C.c_int]),
     "xv_vec_normalize_length": (C.c_int, [_p, _f32p, C.c_int64, C.c_int32, C.c_int, _f32p]),

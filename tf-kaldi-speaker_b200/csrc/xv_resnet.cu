@@ -37,44 +37,53 @@ __global__ void __launch_bounds__(256) resnet_stem_kernel(const float* __restric
                                                           const float* __restrict__ scale, const float* __restrict__ shift,
                                                           const float* __restrict__ slope, T* __restrict__ out,
                                                           int64_t out_utt_stride) {
-  __shared__ float sw[9 * 64];
-  __shared__ float ss[3 * 64];
+  __shared__ __align__(16) float sw[9 * 64];
+  __shared__ __align__(16) float ss[3 * 64];
   for (int i = threadIdx.x; i < 9 * 64; i += blockDim.x) sw[i] = w[i];
   for (int i = threadIdx.x; i < 64; i += blockDim.x) { ss[i] = scale[i]; ss[64 + i] = shift[i]; ss[128 + i] = slope[i]; }
   __syncthreads();
-  const int64_t total = static_cast<int64_t>(nb) * t * f * 8;
-  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-    const int cg = static_cast<int>(i & 7);
-    const int64_t pos = i >> 3;
-    const int fi = static_cast<int>(pos % f);
-    const int64_t bt = pos / f;
-    const int ti = static_cast<int>(bt % t);
-    const int b = static_cast<int>(bt / t);
+  // 32-bit index arithmetic (a batch holds < 2^28 positions), weights and BN constants read as 16-byte shared loads:
+  // the kernel is bound by instruction issue, not by its 128 bytes of output per position
+  const uint32_t n_pos = static_cast<uint32_t>(nb) * static_cast<uint32_t>(t) * static_cast<uint32_t>(f);
+  const uint32_t total = n_pos * 8u;
+  const uint32_t cg = threadIdx.x & 7u;                       // blockDim.x and the grid stride are multiples of 8
+  const float4* w4 = reinterpret_cast<const float4*>(sw) + cg * 2;
+  const float4 sc0 = reinterpret_cast<const float4*>(ss)[cg * 2], sc1 = reinterpret_cast<const float4*>(ss)[cg * 2 + 1];
+  const float4 sh0 = reinterpret_cast<const float4*>(ss + 64)[cg * 2], sh1 = reinterpret_cast<const float4*>(ss + 64)[cg * 2 + 1];
+  const float4 sl0 = reinterpret_cast<const float4*>(ss + 128)[cg * 2], sl1 = reinterpret_cast<const float4*>(ss + 128)[cg * 2 + 1];
+  const float scv[8] = {sc0.x, sc0.y, sc0.z, sc0.w, sc1.x, sc1.y, sc1.z, sc1.w};
+  const float shv[8] = {sh0.x, sh0.y, sh0.z, sh0.w, sh1.x, sh1.y, sh1.z, sh1.w};
+  const float slv[8] = {sl0.x, sl0.y, sl0.z, sl0.w, sl1.x, sl1.y, sl1.z, sl1.w};
+  const uint32_t uf = static_cast<uint32_t>(f), ut = static_cast<uint32_t>(t);
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const uint32_t pos = i >> 3;
+    const uint32_t bt = pos / uf;
+    const int fi = static_cast<int>(pos - bt * uf);
+    const uint32_t b = bt / ut;
+    const int ti = static_cast<int>(bt - b * ut);
     float acc[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+    const float* xb = x + static_cast<int64_t>(b) * t * f;
 #pragma unroll
     for (int dt = 0; dt < 3; ++dt) {
       const int tt = ti + dt - 1;
-      if (tt < 0 || tt >= t) continue;
+      const bool tok = tt >= 0 && tt < t;
 #pragma unroll
       for (int df = 0; df < 3; ++df) {
         const int ff = fi + df - 1;
-        if (ff < 0 || ff >= f) continue;
-        const float v = __ldg(x + (static_cast<int64_t>(b) * t + tt) * f + ff);
-        const float* wp = sw + (dt * 3 + df) * 64 + cg * 8;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) acc[k] = fmaf(v, wp[k], acc[k]);
+        const float v = (tok && ff >= 0 && ff < f) ? __ldg(xb + tt * f + ff) : 0.f;
+        const float4 wa = w4[(dt * 3 + df) * 16], wb = w4[(dt * 3 + df) * 16 + 1];
+        acc[0] = fmaf(v, wa.x, acc[0]); acc[1] = fmaf(v, wa.y, acc[1]); acc[2] = fmaf(v, wa.z, acc[2]); acc[3] = fmaf(v, wa.w, acc[3]);
+        acc[4] = fmaf(v, wb.x, acc[4]); acc[5] = fmaf(v, wb.y, acc[5]); acc[6] = fmaf(v, wb.z, acc[6]); acc[7] = fmaf(v, wb.w, acc[7]);
       }
     }
     T* dst = out + static_cast<int64_t>(b) * out_utt_stride + (static_cast<int64_t>(ti) * f + fi) * 64 + cg * 8;
-    T y[8];
+    alignas(16) T y[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      const int ch = cg * 8 + k;
-      float v = fmaf(acc[k], ss[ch], ss[64 + ch]);
-      v = v >= 0.f ? v : v * ss[128 + ch];
+      float v = fmaf(acc[k], scv[k], shv[k]);
+      v = v >= 0.f ? v : v * slv[k];
       y[k] = cvt_out<T>(v);
     }
     // 8 channels = one 16-byte (bf16) or two 16-byte (fp32) stores; consecutive threads write consecutive chunks

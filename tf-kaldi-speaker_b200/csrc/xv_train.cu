@@ -100,6 +100,10 @@ struct TrainState {
   cudaEvent_t ev_ready[kNumBuckets] = {}, ev_done = nullptr;
   int64_t bucket_lo[kNumBuckets] = {}, bucket_hi[kNumBuckets] = {};   // float ranges of the gradient buffer
   bool overlap = true;                   // XV_TRAIN_OVERLAP=0: one allreduce after the backward pass
+  // gradients cross NVLink as bf16 (fp32 masters, fp32 moving statistics / loss in the tail): default for the bf16 path,
+  // config "grad_allreduce_dtype": "fp32" | "bf16" or XV_TRAIN_COMM=fp32|bf16 override; needs the bucketed exchange
+  bool comm_bf16 = false;
+  DevBuf gcomm;                          // bf16 [n_train]: the trainable range of the gradient buffer as it travels
   bool poisoned = false;                 // the communicator was aborted after a failed step
 
   double* scalars() const { return static_cast<double*>(sum_area.p); }
@@ -174,7 +178,7 @@ void train_release(xv_ctx* c) {
   }
   DevBuf* bufs[] = {&t->params, &t->grads, &t->accum, &t->d_segs, &t->d_chunks, &t->const_slope, &t->feats, &t->labels,
                     &t->pooled, &t->logits, &t->gr, &t->coef, &t->rnorm, &t->dbuf[0], &t->dbuf[1], &t->scratch_stats,
-                    &t->sum_area, &t->sqnorms, &t->xb0, &t->dzb, &t->ones_pad, &t->zeros_pad};
+                    &t->sum_area, &t->sqnorms, &t->xb0, &t->dzb, &t->ones_pad, &t->zeros_pad, &t->gcomm};
   for (DevBuf* b : bufs) release(b);
   delete t;
   c->train = nullptr;
@@ -203,6 +207,13 @@ static int train_init(xv_ctx* c, int32_t num_speakers) {
   t->mixed = c->bf16;
   t->fused_stats = !(getenv("XV_TRAIN_FUSED_STATS") && atoi(getenv("XV_TRAIN_FUSED_STATS")) == 0);
   t->overlap = !(getenv("XV_TRAIN_OVERLAP") && atoi(getenv("XV_TRAIN_OVERLAP")) == 0);
+  {
+    const JValue* gd = c->cfg.get("grad_allreduce_dtype");
+    std::string want = (gd && gd->type == JValue::Str) ? gd->str : (c->bf16 ? "bf16" : "fp32");
+    if (getenv("XV_TRAIN_COMM")) want = getenv("XV_TRAIN_COMM");
+    if (want != "bf16" && want != "fp32") return fail(c, XV_EINVAL, "grad_allreduce_dtype must be \"bf16\" or \"fp32\", got \"%s\"", want.c_str());
+    t->comm_bf16 = want == "bf16" && t->overlap;
+  }
   const JValue& cfg = c->cfg;
   const JValue* lf = cfg.get("loss_func");
   const std::string loss = (lf && lf->type == JValue::Str) ? lf->str : "softmax";
@@ -508,6 +519,29 @@ int dp_wait(xv_ctx* c, TrainState* t) {
 
 }  // namespace
 
+// One bucket of the exchange on the communication stream.  fp32: the bucket's range of the gradient buffer in place.
+// bf16: the trainable part is cast to bf16 (on the communication stream, off the compute stream's critical path),
+// all-reduced as bf16, and read back by the update kernel; the tail (moving statistics + loss slot) stays fp32.
+static int exchange_bucket(TrainState* t, int k) {
+  float* G = static_cast<float*>(t->grads.p);
+  const int64_t lo = t->bucket_lo[k], hi = t->bucket_hi[k];
+  if (!t->comm_bf16)
+    return t->nccl.AllReduce(G + lo, G + lo, static_cast<size_t>(hi - lo), /*ncclFloat32*/ 7, /*ncclSum*/ 0, t->comm, t->comm_stream);
+  const int64_t hi_t = std::min(hi, t->n_train);
+  int nrc = 0;
+  if (hi_t > lo) {
+    __nv_bfloat16* gb = static_cast<__nv_bfloat16*>(t->gcomm.p);
+    cudaError_t e = launch_f32_to_bf16(G + lo, gb + lo, static_cast<size_t>(hi_t - lo), t->comm_stream);
+    if (e != cudaSuccess) return 1;       // ncclUnhandledCudaError
+    nrc = t->nccl.AllReduce(gb + lo, gb + lo, static_cast<size_t>(hi_t - lo), /*ncclBfloat16*/ 9, /*ncclSum*/ 0, t->comm, t->comm_stream);
+  }
+  if (nrc == 0 && hi > t->n_train) {
+    const int64_t a = std::max(lo, t->n_train);
+    nrc = t->nccl.AllReduce(G + a, G + a, static_cast<size_t>(hi - a), /*ncclFloat32*/ 7, /*ncclSum*/ 0, t->comm, t->comm_stream);
+  }
+  return nrc;
+}
+
 static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const int32_t* labels, int32_t b, int32_t tt, float lr,
                            int64_t global_step, float* loss_out) {
   int rc = tr_buffers(c, t, b, tt);
@@ -696,8 +730,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     if (!overlap || t->bucket_hi[k] <= t->bucket_lo[k]) return XV_OK;
     TR_CUDA(cudaEventRecord(t->ev_ready[k], s), "cudaEventRecord");
     TR_CUDA(cudaStreamWaitEvent(t->comm_stream, t->ev_ready[k], 0), "cudaStreamWaitEvent");
-    const int nrc = t->nccl.AllReduce(G + t->bucket_lo[k], G + t->bucket_lo[k], static_cast<size_t>(t->bucket_hi[k] - t->bucket_lo[k]),
-                                      /*ncclFloat32*/ 7, /*ncclSum*/ 0, t->comm, t->comm_stream);
+    int nrc = exchange_bucket(t, k);
     if (nrc != 0) return tr_fail_nccl(c, t, nrc, "ncclAllReduce");
     count_launch(c, "train.allreduce");
     return XV_OK;
@@ -826,12 +859,14 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
   }
   const double* sqn = nullptr;
   const int n_chunks = static_cast<int>(t->chunks.size());
+  // bf16 exchange: the summed gradients of the trainable range come back in the bf16 travel buffer
+  const __nv_bfloat16* gsum_bf16 = (dp && overlap && t->comm_bf16) ? static_cast<const __nv_bfloat16*>(t->gcomm.p) : nullptr;
   if (t->clip_norm > 0.f) {
     // clipping acts on the AVERAGED gradient (model/trainer.py:1244-1246), per variable
     double* d_sqn = static_cast<double*>(t->sqnorms.p);
     TR_CUDA(cudaMemsetAsync(d_sqn, 0, sizeof(double) * t->segs.size(), s), "memset norms");
     count_launch(c, "train.grad_norms");
-    grad_sqnorm_kernel<<<n_chunks, 256, 0, s>>>(P, G, static_cast<const ParamSeg*>(t->d_segs.p),
+    grad_sqnorm_kernel<<<n_chunks, 256, 0, s>>>(P, G, gsum_bf16, static_cast<const ParamSeg*>(t->d_segs.p),
                                                 static_cast<const UpdChunk*>(t->d_chunks.p), 1.f / t->world, d_sqn);
     TR_CUDA(cudaGetLastError(), "gradient norm launch");
     sqn = d_sqn;
@@ -843,7 +878,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
                                 (1.0 - std::pow(0.9, static_cast<double>(t->adam_t))));
   }
   count_launch(c, "train.update");
-  apply_update_kernel<<<n_chunks, 256, 0, s>>>(P, G, static_cast<float*>(t->accum.p), static_cast<const ParamSeg*>(t->d_segs.p),
+  apply_update_kernel<<<n_chunks, 256, 0, s>>>(P, G, gsum_bf16, static_cast<float*>(t->accum.p), static_cast<const ParamSeg*>(t->d_segs.p),
                                                static_cast<const UpdChunk*>(t->d_chunks.p), t->n_total, 1.f / t->world, lr_eff,
                                                t->optimizer, t->opt_momentum, t->nesterov, sqn, t->clip_norm, scalars + 1);
   TR_CUDA(cudaGetLastError(), "update launch");
@@ -976,6 +1011,7 @@ int xv_comm_init(xv_ctx* c, const void* nccl_unique_id, int rank, int world) {
   memcpy(id.bytes, nccl_unique_id, sizeof(id.bytes));
   const int nrc = t->nccl.CommInitRank(&t->comm, world, id, rank);
   if (nrc != 0) return tr_fail_nccl(c, t, nrc, "ncclCommInitRank");
+  if (t->comm_bf16 && (rc = ensure(c, &t->gcomm, sizeof(__nv_bfloat16) * static_cast<size_t>(t->n_train))) != XV_OK) return rc;
   if (!t->comm_stream) {
     cudaError_t e = cudaStreamCreateWithFlags(&t->comm_stream, cudaStreamNonBlocking);
     for (int i = 0; i < kNumBuckets && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&t->ev_ready[i], cudaEventDisableTiming);
@@ -1004,9 +1040,7 @@ int xv_comm_bench(xv_ctx* c, int32_t iters, float* ms_per_iter) {
   for (int it = 0; it < iters && nrc == 0; ++it) {
     if (t->overlap) {
       for (int k = 0; k < kNumBuckets && nrc == 0; ++k)
-        if (t->bucket_hi[k] > t->bucket_lo[k])
-          nrc = t->nccl.AllReduce(G + t->bucket_lo[k], G + t->bucket_lo[k], static_cast<size_t>(t->bucket_hi[k] - t->bucket_lo[k]), 7, 0,
-                                  t->comm, t->comm_stream);
+        if (t->bucket_hi[k] > t->bucket_lo[k]) nrc = exchange_bucket(t, k);
     } else {
       nrc = t->nccl.AllReduce(G, G, static_cast<size_t>(t->n_total + 1), 7, 0, t->comm, t->comm_stream);
     }
@@ -1022,6 +1056,11 @@ int xv_comm_bench(xv_ctx* c, int32_t iters, float* ms_per_iter) {
   cudaEventDestroy(b);
   *ms_per_iter = ms / iters;
   return rc;
+}
+
+int xv_comm_dtype(xv_ctx* c) {
+  if (!c || !c->train) return XV_EINVAL;
+  return (c->train->comm_bf16 && c->train->world > 1) ? XV_DTYPE_BF16 : XV_DTYPE_F32;
 }
 
 int xv_comm_info(xv_ctx* c, int32_t* rank, int32_t* world, int64_t* grad_elems, int32_t* buckets) {

@@ -1205,7 +1205,12 @@ struct UpdChunk { int64_t off; int32_t n; int32_t seg; };
 
 // Per-variable squared L2 norm of the final gradient g = gsum/world + wd*p (tf.clip_by_norm works per tensor,
 // model/trainer.py:529-533 and :1245-1246): norms[seg] += sum g^2.
+// gb (may be null): the summed gradients of the trainable range as they came back from a bf16 exchange
+__device__ __forceinline__ float grad_sum(const float* g, const __nv_bfloat16* gb, int64_t i) {
+  return gb != nullptr ? __bfloat162float(gb[i]) : g[i];
+}
 __global__ void __launch_bounds__(256) grad_sqnorm_kernel(const float* __restrict__ p, const float* __restrict__ g,
+                                                          const __nv_bfloat16* __restrict__ gb,
                                                           const ParamSeg* __restrict__ segs, const UpdChunk* __restrict__ chunks,
                                                           float inv_world, double* __restrict__ norms) {
   __shared__ double sh[8];
@@ -1214,7 +1219,7 @@ __global__ void __launch_bounds__(256) grad_sqnorm_kernel(const float* __restric
   double s = 0.0;
   if (!sg.moving)
     for (int i = threadIdx.x; i < ch.n; i += 256) {
-      const double v = fmaf(sg.wd, p[ch.off + i], g[ch.off + i] * inv_world);
+      const double v = fmaf(sg.wd, p[ch.off + i], grad_sum(g, gb, ch.off + i) * inv_world);
       s += v * v;
     }
   s = block_reduce(s, sh, false);
@@ -1227,7 +1232,8 @@ __global__ void __launch_bounds__(256) grad_sqnorm_kernel(const float* __restric
 //   m = b1*m + (1-b1)*g; v = b2*v + (1-b2)*g^2; p -= lr*m/(sqrt(v)+eps), m = accum[0..total), v = accum[total..2 total)
 // The regularisation loss sum_kernels (wd/2)*|W|^2 (tf.contrib.layers.l2_regularizer, model/trainer.py:472-499) of the
 // PRE-update weights is accumulated on the way (reg_out += ...).
-__global__ void __launch_bounds__(256) apply_update_kernel(float* __restrict__ p, float* __restrict__ g, float* __restrict__ accum,
+__global__ void __launch_bounds__(256) apply_update_kernel(float* __restrict__ p, float* __restrict__ g,
+                                                           const __nv_bfloat16* __restrict__ gb, float* __restrict__ accum,
                                                            const ParamSeg* __restrict__ segs, const UpdChunk* __restrict__ chunks,
                                                            int64_t total, float inv_world, float lr, int optimizer, float momentum,
                                                            int nesterov, const double* __restrict__ sqnorms, float clip_norm,
@@ -1246,7 +1252,7 @@ __global__ void __launch_bounds__(256) apply_update_kernel(float* __restrict__ p
     const int64_t i = ch.off + k;
     const float pv = p[i];
     reg += static_cast<double>(pv) * pv;
-    float grad = fmaf(sg.wd, pv, g[i] * inv_world);
+    float grad = fmaf(sg.wd, pv, grad_sum(g, gb, i) * inv_world);
     if (sqnorms != nullptr) grad *= clip;
     g[i] = grad;
     if (optimizer == 0) {

@@ -322,7 +322,9 @@ class Engine(object):
         rank, world, buckets = C.c_int32(), C.c_int32(), C.c_int32()
         elems = C.c_int64()
         self._check(self.lib.xv_comm_info(self._ctx, C.byref(rank), C.byref(world), C.byref(elems), C.byref(buckets)))
-        return {"rank": int(rank.value), "world": int(world.value), "grad_elems": int(elems.value), "buckets": int(buckets.value)}
+        dt = self.lib.xv_comm_dtype(self._ctx)
+        return {"rank": int(rank.value), "world": int(world.value), "grad_elems": int(elems.value), "buckets": int(buckets.value),
+                "dtype": "bf16" if dt == _lib.DTYPE_BF16 else "fp32"}
 
     def comm_unique_id(self):
         buf = C.create_string_buffer(128)
