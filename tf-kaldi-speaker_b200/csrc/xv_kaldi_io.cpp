@@ -4,6 +4,7 @@
 // buffers, and a thread pool for scp random access.
 #include <errno.h>
 #include <fcntl.h>
+#include <spawn.h>
 #include <stdarg.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -24,6 +25,8 @@
 #include <vector>
 
 #include "../../include/xvkaldi.h"
+
+extern char** environ;
 
 namespace {
 
@@ -82,18 +85,23 @@ void parse_specifier(const std::string& spec, std::string* prefix, std::string* 
   }
 }
 
+// posix_spawn, not fork(): the callers live in processes with CUDA contexts and busy threads (the multi-GPU extractor opens
+// "ark:cmd |" while its workers create their contexts).  fork() runs every pthread_atfork handler of the process -- the CUDA
+// driver's among them, which faulted when another thread was inside context creation -- and copies the page tables of a
+// process that maps hundreds of GB; glibc's posix_spawn is clone(CLONE_VM | CLONE_VFORK) + exec and runs no handlers.
 pid_t spawn_shell(const std::string& cmd, bool child_writes, int* fd_out, std::string* err) {
   int p[2];
-  if (pipe(p) != 0) { set_err(err, "pipe(): %s", strerror(errno)); return -1; }
-  const pid_t pid = fork();
-  if (pid < 0) { set_err(err, "fork(): %s", strerror(errno)); close(p[0]); close(p[1]); return -1; }
-  if (pid == 0) {
-    if (child_writes) { dup2(p[1], 1); } else { dup2(p[0], 0); }
-    close(p[0]);
-    close(p[1]);
-    execl("/bin/sh", "sh", "-c", cmd.c_str(), static_cast<char*>(nullptr));
-    _exit(127);
-  }
+  if (pipe2(p, O_CLOEXEC) != 0) { set_err(err, "pipe(): %s", strerror(errno)); return -1; }
+  posix_spawn_file_actions_t fa;
+  posix_spawn_file_actions_init(&fa);
+  // dup2 clears FD_CLOEXEC on the target; the pipe's own descriptors close at exec
+  if (child_writes) posix_spawn_file_actions_adddup2(&fa, p[1], 1);
+  else posix_spawn_file_actions_adddup2(&fa, p[0], 0);
+  char* const argv[] = {const_cast<char*>("sh"), const_cast<char*>("-c"), const_cast<char*>(cmd.c_str()), nullptr};
+  pid_t pid = -1;
+  const int rc = posix_spawn(&pid, "/bin/sh", &fa, nullptr, argv, environ);
+  posix_spawn_file_actions_destroy(&fa);
+  if (rc != 0) { set_err(err, "posix_spawn(): %s", strerror(rc)); close(p[0]); close(p[1]); return -1; }
   if (child_writes) { close(p[1]); *fd_out = p[0]; } else { close(p[0]); *fd_out = p[1]; }
   return pid;
 }

@@ -233,10 +233,19 @@ def extract_stream_mgpu(make_trainer, devices, rspecifier, wspecifier, dim, chun
             if trainer is not None and trainers is None:
                 trainer.close()
 
+    # Both specifiers are opened HERE, before any worker thread exists: "ark:cmd |" and "ark:| cmd" start a child process, and
+    # that must not happen while another thread is inside CUDA context creation (make_trainer in the workers).
+    first_buf = free_bufs.get()
+    rd = kaldi_io.BatchReader(rspecifier, dim, max_rows=max_rows, max_utts=max_utts, buffer=pins[first_buf].array, threads=threads)
+    try:
+        fp_out = kaldi_io.open_or_fd(wspecifier, "wb")
+    except BaseException:
+        rd.close()
+        raise
+
     def reader():
         try:
-            buf = free_bufs.get()
-            rd = kaldi_io.BatchReader(rspecifier, dim, max_rows=max_rows, max_utts=max_utts, buffer=pins[buf].array, threads=threads)
+            buf = first_buf
             seq = 0
             for keys, feats, lengths in rd:
                 work.put((seq, buf, keys, int(feats.shape[0]), lengths))
@@ -262,7 +271,7 @@ def extract_stream_mgpu(make_trainer, devices, rspecifier, wspecifier, dim, chun
     rt.start()
     written = skipped = 0
     try:
-        with kaldi_io.open_or_fd(wspecifier, "wb") as fp_out:
+        with fp_out:
             seq = 0
             while True:
                 with done_cv:
