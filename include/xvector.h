@@ -111,6 +111,20 @@ int  xv_stat_pooling(xv_ctx* ctx, const void* x, const int32_t* cu_lens, int32_t
  * synchronise: the bandwidth-roofline entry point. cu_lens_dev is a device array [n+1]. */
 int  xv_stat_pooling_dev(xv_ctx* ctx, const void* x_dev, const int32_t* cu_lens_dev, int32_t n, int32_t C,
                          int dtype, int32_t max_len, float* out_dev);
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * xv_stat_pooling_dev (same kernels) but the [n,2C] fp32 sum / sum-of-squares workspace lives in a file-scope
+ * __device__ array of XV_NOALLOC_POOL_MAX_FLOATS floats (2 MiB, held by every GPU that loads the library until
+ * exit): nothing is allocated or freed, on the device or through any allocating library routine, and nothing is
+ * synchronised.  x_dev [total_rows, C] of dtype XV_DTYPE_*, cu_lens_dev [n+1] and out_dev [n,2C] fp32 are DEVICE
+ * buffers of the caller; total_rows = cu_lens[n] is passed by value so the call needs no read-back.
+ * n*2*C > XV_NOALLOC_POOL_MAX_FLOATS is rejected with XV_EINVAL and a message in xv_last_error().
+ * Every call on a device shares the one array, which keeps the previous call's contents: each call clears the
+ * part it uses on the ctx stream first, so calls ordered on the GPU are independent, but calls that OVERLAP on
+ * the GPU (two ctx of one device inside this entry point at once) race on it: the caller serialises them. */
+#define XV_NOALLOC_POOL_MAX_FLOATS (512 * 1024)
+int  xv_stat_pooling_noalloc(xv_ctx* ctx, const void* x_dev, const int32_t* cu_lens_dev, int32_t n, int32_t C,
+                             int dtype, int64_t total_rows, float* out_dev);
 /* The weighted-statistics core of self_attention (model/pooling.py:186-218): value [cu[n],Cv],
  * key [cu[n],Ck] (dtype as above, device or host), query [H,dk] fp32 host.  out (host)
  * [n, 2*H*dv]; weights_out (host, may be NULL) packed [H, L_u] per utterance at H*cu_lens[u]. */

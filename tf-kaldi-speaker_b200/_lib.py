@@ -44,6 +44,7 @@ PROTOTYPES = {
     "xv_sync": (C.c_int, [_p]),
     "xv_stat_pooling": (C.c_int, [_p, _p, _i32p, C.c_int32, C.c_int32, C.c_int, _f32p]),
     "xv_stat_pooling_dev": (C.c_int, [_p, _p, _p, C.c_int32, C.c_int32, C.c_int, C.c_int32, _p]),
+    "xv_stat_pooling_noalloc": (C.c_int, [_p, _p, _p, C.c_int32, C.c_int32, C.c_int, C.c_int64, _p]),
     "xv_attention_pooling": (C.c_int, [_p, _p, _p, _f32p, _i32p, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                        C.c_int, C.c_int, C.c_int, C.c_int, _f32p, _f32p]),
     "xv_dense_rows_f32": (C.c_int, [_p, _f32p, C.c_int64, C.c_int32, C.c_int32, _f32p, C.c_int32, _f32p, _f32p,
