@@ -105,6 +105,13 @@ struct TrainState {
   bool comm_bf16 = false;
   DevBuf gcomm;                          // bf16 [n_train]: the trainable range of the gradient buffer as it travels
   bool poisoned = false;                 // the communicator was aborted after a failed step
+  // weight-gradient GEMMs of the bf16 path on a side stream: dW_l needs only dZ_l and the stored forward activations, so it runs
+  // beside the critical chain dgrad_l -> BN backward_{l-1} (fills the idle second wave of the dgrad GEMM and the latency-bound
+  // row-streaming kernels).  dZ is double-buffered by layer parity; XV_TRAIN_WGRAD_STREAM=0 keeps everything on one stream.
+  bool wg_overlap = true, wg_overlap_head = true;
+  cudaStream_t wg_stream = nullptr;
+  cudaEvent_t ev_dz[2] = {}, ev_wg[2] = {}, ev_wg_mark = nullptr, ev_fork = nullptr, ev_side_rd[2] = {}, ev_rnorm = nullptr;
+  size_t dzb_half = 0;                   // elements between the two dZ buffers inside dzb (0: single buffer)
 
   double* scalars() const { return static_cast<double*>(sum_area.p); }
   double* fwd_sums(int layer) const { return static_cast<double*>(sum_area.p) + 8 + static_cast<size_t>(layer) * 5 * sum_ld; }
@@ -173,6 +180,16 @@ void train_release(xv_ctx* c) {
   for (int i = 0; i < kNumBuckets; ++i)
     if (t->ev_ready[i]) cudaEventDestroy(t->ev_ready[i]);
   if (t->ev_done) cudaEventDestroy(t->ev_done);
+  if (t->wg_stream) cudaStreamDestroy(t->wg_stream);
+  for (int i = 0; i < 2; ++i) {
+    if (t->ev_dz[i]) cudaEventDestroy(t->ev_dz[i]);
+    if (t->ev_wg[i]) cudaEventDestroy(t->ev_wg[i]);
+  }
+  if (t->ev_wg_mark) cudaEventDestroy(t->ev_wg_mark);
+  if (t->ev_fork) cudaEventDestroy(t->ev_fork);
+  if (t->ev_rnorm) cudaEventDestroy(t->ev_rnorm);
+  for (int i = 0; i < 2; ++i)
+    if (t->ev_side_rd[i]) cudaEventDestroy(t->ev_side_rd[i]);
   for (TrLayer& l : t->layers) {
     release(&l.z); release(&l.y); release(&l.mean); release(&l.rstd); release(&l.wt_fwd); release(&l.wt_dgrad); release(&l.yb);
   }
@@ -207,6 +224,8 @@ static int train_init(xv_ctx* c, int32_t num_speakers) {
   t->mixed = c->bf16;
   t->fused_stats = !(getenv("XV_TRAIN_FUSED_STATS") && atoi(getenv("XV_TRAIN_FUSED_STATS")) == 0);
   t->overlap = !(getenv("XV_TRAIN_OVERLAP") && atoi(getenv("XV_TRAIN_OVERLAP")) == 0);
+  t->wg_overlap = !(getenv("XV_TRAIN_WGRAD_STREAM") && atoi(getenv("XV_TRAIN_WGRAD_STREAM")) == 0);
+  t->wg_overlap_head = !(getenv("XV_TRAIN_WGRAD_STREAM") && atoi(getenv("XV_TRAIN_WGRAD_STREAM")) == 1);   // 1: frame layers only
   {
     const JValue* gd = c->cfg.get("grad_allreduce_dtype");
     std::string want = (gd && gd->type == JValue::Str) ? gd->str : (c->bf16 ? "bf16" : "fp32");
@@ -430,12 +449,26 @@ int tr_buffers(xv_ctx* c, TrainState* t, int b, int tt) {
   }
   if (t->mixed) {
     if ((rc = ensure(c, &t->xb0, sizeof(__nv_bfloat16) * rows * t->layers[0].a_cin)) != XV_OK) return rc;
-    if ((rc = ensure(c, &t->dzb, sizeof(__nv_bfloat16) * rows * max_ldb)) != XV_OK) return rc;
+    const bool two_dz = t->wg_overlap;
+    t->dzb_half = two_dz ? static_cast<size_t>(rows) * max_ldb : 0;
+    if ((rc = ensure(c, &t->dzb, sizeof(__nv_bfloat16) * rows * max_ldb * (two_dz ? 2 : 1))) != XV_OK) return rc;
+    if (two_dz && !t->wg_stream) {
+      cudaError_t e = cudaStreamCreateWithFlags(&t->wg_stream, cudaStreamNonBlocking);
+      for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+        e = cudaEventCreateWithFlags(&t->ev_dz[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&t->ev_wg[i], cudaEventDisableTiming);
+      }
+      if (e == cudaSuccess) e = cudaEventCreateWithFlags(&t->ev_wg_mark, cudaEventDisableTiming);
+      if (e == cudaSuccess) e = cudaEventCreateWithFlags(&t->ev_fork, cudaEventDisableTiming);
+      if (e == cudaSuccess) e = cudaEventCreateWithFlags(&t->ev_rnorm, cudaEventDisableTiming);
+      for (int i = 0; i < 2 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&t->ev_side_rd[i], cudaEventDisableTiming);
+      if (e != cudaSuccess) return cuda_fail(c, e, "weight-gradient stream / events");
+    }
     for (int i = 0; i < t->n_frame; ++i) {
       TrLayer& l = t->layers[i];
       const void* a = i == 0 ? t->xb0.p : t->layers[i - 1].yb.p;
       const char* err = make_tmap_bf16_2d(&l.tm_af, a, l.a_cin, rows, static_cast<uint64_t>(l.a_cin) * 2, kBK, kBM);
-      if (!err) err = make_tmap_bf16_2d(&l.tm_adz, t->dzb.p, l.ldb, rows, static_cast<uint64_t>(l.ldb) * 2, kBK, kBM);
+      if (!err) err = make_tmap_bf16_2d(&l.tm_adz, static_cast<__nv_bfloat16*>(t->dzb.p) + (i & 1) * t->dzb_half, l.ldb, rows, static_cast<uint64_t>(l.ldb) * 2, kBK, kBM);
       if (err) return fail(c, XV_ECUDA, "%s", err);
     }
   }
@@ -661,6 +694,33 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     in_c = l.cout;
   }
 
+  // Side stream for everything that only PRODUCES parameter gradients (nothing on the critical chain reads them before the
+  // exchange / update): the loss head's weight gradient, the segment layers' and the frame layers' weight gradients.
+  const bool wg_side = t->mixed && t->wg_overlap && t->wg_stream != nullptr;
+  const bool head_side = wg_side && t->wg_overlap_head;
+  bool wg_launched = false;
+  bool wg_reads[2] = {false, false};            // a side-stream wgrad of this step reads dZ buffer [parity]
+  bool side_rd[2] = {false, false};             // a side-stream kernel of this step reads dbuf[i]
+  // side stream <- everything enqueued on the main stream so far
+  auto side_fork = [&]() -> int {
+    TR_CUDA(cudaEventRecord(t->ev_fork, s), "cudaEventRecord");
+    TR_CUDA(cudaStreamWaitEvent(t->wg_stream, t->ev_fork, 0), "cudaStreamWaitEvent");
+    wg_launched = true;
+    return XV_OK;
+  };
+  // the side-stream work enqueued so far reads dbuf[i]: the main stream must not overwrite it earlier
+  auto side_reads_dbuf = [&](int i) -> int {
+    TR_CUDA(cudaEventRecord(t->ev_side_rd[i], t->wg_stream), "cudaEventRecord");
+    side_rd[i] = true;
+    return XV_OK;
+  };
+  auto before_dbuf_write = [&](int i) -> int {
+    if (!side_rd[i]) return XV_OK;
+    TR_CUDA(cudaStreamWaitEvent(s, t->ev_side_rd[i], 0), "cudaStreamWaitEvent");
+    side_rd[i] = false;
+    return XV_OK;
+  };
+
   // ------------------------------------------------------------------ loss (model/loss.py:9-48, 201-286)
   const TrLayer& last = t->layers.back();
   const float* fvec = static_cast<const float*>(last.y.p);
@@ -692,8 +752,13 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
   TR_CUDA(cudaGetLastError(), "loss launch");
   // dW = f^T G (+ the l2_normalize Jacobian for AM-softmax), db = column sums of G; the tower loss goes to the tail slot
   if (E <= kHeadMaxE && E % 32 == 0) {
+    cudaStream_t hs = s;
+    if (head_side) {
+      if ((rc = side_fork()) != XV_OK) return rc;
+      hs = t->wg_stream;
+    }
     count_launch(c, "train.head_wgrad");
-    head_wgrad_kernel<<<(S + 31) / 32, 256, 0, s>>>(fvec, static_cast<const float*>(t->logits.p), b, E, S, P + t->off_w,
+    head_wgrad_kernel<<<(S + 31) / 32, 256, 0, hs>>>(fvec, static_cast<const float*>(t->logits.p), b, E, S, P + t->off_w,
                                                     t->amsoftmax ? static_cast<const float*>(t->rnorm.p) : nullptr, G + t->off_w,
                                                     t->amsoftmax ? nullptr : G + t->off_b, scalars, G + t->n_total);
     TR_CUDA(cudaGetLastError(), "softmax weight-gradient launch");
@@ -730,6 +795,10 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     if (!overlap || t->bucket_hi[k] <= t->bucket_lo[k]) return XV_OK;
     TR_CUDA(cudaEventRecord(t->ev_ready[k], s), "cudaEventRecord");
     TR_CUDA(cudaStreamWaitEvent(t->comm_stream, t->ev_ready[k], 0), "cudaStreamWaitEvent");
+    if (wg_launched) {                          // ... and the weight gradients that were sent to the side stream
+      TR_CUDA(cudaEventRecord(t->ev_wg_mark, t->wg_stream), "cudaEventRecord");
+      TR_CUDA(cudaStreamWaitEvent(t->comm_stream, t->ev_wg_mark, 0), "cudaStreamWaitEvent");
+    }
     int nrc = exchange_bucket(t, k);
     if (nrc != 0) return tr_fail_nccl(c, t, nrc, "ncclAllReduce");
     count_launch(c, "train.allreduce");
@@ -763,7 +832,14 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
       wa.a = i == t->n_frame ? static_cast<const float*>(t->pooled.p) : static_cast<const float*>(t->layers[i - 1].y.p);
       wa.lda = l.cin; wa.dz = dy; wa.ldz = l.cout; wa.out = G + l.off_kernel; wa.ldo = l.cout; wa.rows = b; wa.k = l.cin; wa.n = l.cout;
       count_launch(c, "train.seg_wgrad");
-      TR_CUDA(launch_rowsT_gemm(wa, s), "segment wgrad launch");
+      if (head_side) {
+        if ((rc = side_fork()) != XV_OK) return rc;
+        TR_CUDA(launch_rowsT_gemm(wa, t->wg_stream), "segment wgrad launch");
+        if ((rc = side_reads_dbuf(cur)) != XV_OK) return rc;           // dz lives in dbuf[cur]
+      } else {
+        TR_CUDA(launch_rowsT_gemm(wa, s), "segment wgrad launch");
+      }
+      if ((rc = before_dbuf_write(cur ^ 1)) != XV_OK) return rc;
       float* dx = static_cast<float*>(t->dbuf[cur ^ 1].p);
       SkinnyArgs sa;
       sa.a = dy; sa.lda = l.cout; sa.w = P + l.off_kernel; sa.ldw = l.cout; sa.out = dx; sa.ldo = l.cin;
@@ -795,8 +871,11 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     ba.g_gamma = G + l.off_gamma; ba.g_beta = G + l.off_beta; ba.g_alpha = l.off_alpha >= 0 ? G + l.off_alpha : nullptr;
     ba.ldb = l.ldb;
     float* dz32 = nullptr;
+    __nv_bfloat16* dzb_l = static_cast<__nv_bfloat16*>(t->dzb.p) + (i & 1) * t->dzb_half;
     if (tc) {
-      ba.dz32 = nullptr; ba.dzb = static_cast<__nv_bfloat16*>(t->dzb.p);
+      ba.dz32 = nullptr; ba.dzb = dzb_l;
+      // layer i+2's weight gradient may still be reading this dZ buffer on the side stream
+      if (wg_side && wg_reads[i & 1]) TR_CUDA(cudaStreamWaitEvent(s, t->ev_wg[i & 1], 0), "cudaStreamWaitEvent");
     } else {
       dz32 = from_pool ? static_cast<float*>(t->dbuf[cur ^ 1].p) : dy;      // in place unless the gradient was virtual
       ba.dz32 = dz32; ba.dzb = nullptr;
@@ -808,22 +887,35 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     }
     if (!tc && from_pool) { cur ^= 1; dy = dz32; }
     if (tc) {
-      // dW on the MN-major tcgen05 kernel (xv_wgrad_sm100.cu): layer 0 contracts the pre-spliced features (one tap of width
-      // taps*dim), the others shift the previous layer's bf16 activations by the tap index
-      const void* a_bf16 = i == 0 ? t->xb0.p : t->layers[i - 1].yb.p;
-      cudaError_t ce;
-      count_launch(c, "train.tc_wgrad");
-      const char* we = launch_wgrad(a_bf16, rows, l.a_cin, t->dzb.p, l.ldb, rows, i == 0 ? 1 : l.taps, i == 0 ? l.taps * l.cin : l.cin,
-                                    l.cout, G + l.off_kernel, l.cout, c->sm_count, s, &ce);
-      if (we) return fail(c, XV_ECUDA, "%s", we);
-      TR_CUDA(ce, "tcgen05 wgrad launch");
+      // The data gradient is the critical path (the next layer's BN backward waits for it) and is enqueued first; dW on the
+      // MN-major tcgen05 kernel (xv_wgrad_sm100.cu) follows on the side stream: layer 0 contracts the pre-spliced features
+      // (one tap of width taps*dim), the others shift the previous layer's bf16 activations by the tap index
+      if (wg_side) TR_CUDA(cudaEventRecord(t->ev_dz[i & 1], s), "cudaEventRecord");
       if (i > 0) {
+        if ((rc = before_dbuf_write(cur ^ 1)) != XV_OK) return rc;
         float* dx = static_cast<float*>(t->dbuf[cur ^ 1].p);
         // dX[m, c] = sum_j sum_n dZ[m - j, n] W[j, c, n]: the forward kernel with tap step -1 (rows < 0 are TMA zero fill)
         if ((rc = tr_gemm_tc(c, t, l.tm_adz, l.tm_wd, rows, l.ldb, l.taps, -1, l.c_alloc, static_cast<const float*>(t->zeros_pad.p),
                              dx, l.cin, l.cin, nullptr, 1, 1, "train.tc_dgrad")) != XV_OK) return rc;
         cur ^= 1;
         dy = dx;
+      }
+      cudaStream_t ws = s;
+      if (wg_side) {
+        TR_CUDA(cudaStreamWaitEvent(t->wg_stream, t->ev_dz[i & 1], 0), "cudaStreamWaitEvent");
+        ws = t->wg_stream;
+      }
+      const void* a_bf16 = i == 0 ? t->xb0.p : t->layers[i - 1].yb.p;
+      cudaError_t ce;
+      count_launch(c, "train.tc_wgrad");
+      const char* we = launch_wgrad(a_bf16, rows, l.a_cin, dzb_l, l.ldb, rows, i == 0 ? 1 : l.taps, i == 0 ? l.taps * l.cin : l.cin,
+                                    l.cout, G + l.off_kernel, l.cout, c->sm_count, ws, &ce);
+      if (we) return fail(c, XV_ECUDA, "%s", we);
+      TR_CUDA(ce, "tcgen05 wgrad launch");
+      if (wg_side) {
+        TR_CUDA(cudaEventRecord(t->ev_wg[i & 1], t->wg_stream), "cudaEventRecord");
+        wg_reads[i & 1] = true;
+        wg_launched = true;
       }
     } else {
       const float* a_in = i == 0 ? static_cast<const float*>(t->feats.p) : static_cast<const float*>(t->layers[i - 1].y.p);
@@ -848,6 +940,10 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
   }
 
   // ------------------------------------------------------------------ exchange, update
+  if (wg_launched) {                              // the update (and the next step's forward) follow every weight gradient
+    TR_CUDA(cudaEventRecord(t->ev_wg_mark, t->wg_stream), "cudaEventRecord");
+    TR_CUDA(cudaStreamWaitEvent(s, t->ev_wg_mark, 0), "cudaStreamWaitEvent");
+  }
   if (dp && overlap) {
     TR_CUDA(cudaEventRecord(t->ev_done, t->comm_stream), "cudaEventRecord");
     TR_CUDA(cudaStreamWaitEvent(s, t->ev_done, 0), "cudaStreamWaitEvent");
