@@ -794,23 +794,53 @@ def measure_train(args, dc, precision=None, comm_bench=False):
     losses = []
     for i in range(args.warmup):
         losses.append(eng.train_step(pin.array, ys, 0.01, i)[0])
+    step_no = args.warmup
+    # ---- `value`: the batch is resident in HBM before the timed region; steps are enqueued back to back (loss_out = NULL)
+    d_x = eng.device_alloc(xs.nbytes)
+    d_y = eng.device_alloc(ys.nbytes)
+    eng.h2d(d_x, xs)
+    eng.h2d(d_y, np.ascontiguousarray(ys, np.int32))
+    for i in range(3):
+        eng.train_step_resident(d_x, d_y, xs.shape[0], xs.shape[1], 0.01, step_no)
+        step_no += 1
+    eng.sync()
     dc.barrier(eng)
     sampler = ClockSampler(local)
     sampler.start()
     launches0 = eng.launch_count()
     eng.event_record(0)
-    t0 = time.perf_counter()
     for i in range(args.steps):
-        # the public call: H2D of this step's features/labels, all kernels, the allreduce, D2H of the loss
-        losses.append(eng.train_step(pin.array, ys, 0.01, args.warmup + i)[0])
-    t1 = time.perf_counter()
+        eng.train_step_resident(d_x, d_y, xs.shape[0], xs.shape[1], 0.01, step_no)
+        step_no += 1
     eng.event_record(1)
     eng.sync()
     ms_dev = dc.max(eng.elapsed_ms(0, 1))
-    wall = dc.max(t1 - t0)
     launches = eng.launch_count() - launches0
     dc.barrier(eng)
+    # ---- `e2e`: the public pipelined call on a pinned host batch -- every step copies its features / labels to the device
+    # (copy stream, overlapping the previous step) and brings its loss back; the host collects step k after submitting k+1
+    eng.train_submit(pin.array, ys, 0.01, step_no)
+    step_no += 1
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        eng.train_submit(pin.array, ys, 0.01, step_no)
+        step_no += 1
+        losses.append(eng.train_collect()[0])
+    t1 = time.perf_counter()
+    losses.append(eng.train_collect()[0])
+    wall = dc.max(t1 - t0)
+    dc.barrier(eng)
+    # ---- the synchronous call (xv_train_step with loss_out: H2D, step, D2H, host waits), for comparison
+    n_sync = max(10, args.steps // 4)
+    t0 = time.perf_counter()
+    for i in range(n_sync):
+        losses.append(eng.train_step(pin.array, ys, 0.01, step_no)[0])
+        step_no += 1
+    wall_sync = dc.max(time.perf_counter() - t0) / n_sync
+    dc.barrier(eng)
     sampler.stop()
+    eng.device_free(d_x)
+    eng.device_free(d_y)
     assert np.isfinite(losses).all()
     info = eng.comm_info()
     comm = None
@@ -834,7 +864,9 @@ def measure_train(args, dc, precision=None, comm_bench=False):
                    "comm_nranks": info["world"],
                    "l2_policy": "activations + gradients of a step (0.4 GB) exceed the L2"},
         "e2e": {"value": total_frames * args.steps / wall, "unit": UNIT, "h2d_bytes_per_step": int(xs.nbytes + ys.nbytes),
-                "d2h_bytes_per_step": 16, "steps": args.steps, "api": "xv_train_step (pinned host batch -> loss on the host)"},
+                "d2h_bytes_per_step": 20, "steps": args.steps,
+                "api": "xv_train_submit / xv_train_collect (pinned host batch -> loss on the host, step k collected after k+1 is submitted)",
+                "synchronous_xv_train_step_ms": wall_sync * 1e3},
         "gpu_launches": int(dc.sum(float(launches))), "clocks": sampler.summary(),
         "roofline": {"kernel": ("tcgen05 GEMMs of the frame layers (forward + tap-step -1 dgrad on xv_tdnn_gemm_kernel, MN-major "
                                 "xv_wgrad_kernel) inside the whole step" if mixed else

@@ -201,9 +201,22 @@ int  xv_train_init(xv_ctx* ctx, int32_t num_speakers);
  * int32 (host).  Forward in training mode (BN batch statistics of THIS rank, model/trainer.py:1183-1190), loss +
  * L2 regularisation, backward, gradient average over ranks (one ncclAllReduce when xv_comm_init was called with
  * world > 1; == add_n/N of model/trainer.py:1240-1244), optimizer update, BN moving averages from rank 0.
- * loss_out (may be NULL): [0] = mean tower loss, [1] = [0] + regularisation loss. */
+ * loss_out (may be NULL): [0] = mean tower loss, [1] = [0] + regularisation loss.  With loss_out the call returns when the
+ * step has finished; with NULL it only enqueues the step.  feats / labels may also be DEVICE buffers of the caller
+ * (device labels are not range-checked). */
 int  xv_train_step(xv_ctx* ctx, const float* feats, const int32_t* labels, int32_t batch, int32_t frames,
                    float learning_rate, int64_t global_step, float* loss_out);
+/* The same step as a two-stage pipeline, in place of the reference's queue runners + sess.run(train_op) loop
+ * (model/trainer.py:629-660, dataset/data_loader.py:369-495: there the input queue hides the host work; here the copy of
+ * batch k+1 overlaps the kernels of step k and the host never waits for the step it has just enqueued).
+ * xv_train_submit copies the batch on the copy stream into the alternate batch buffers and enqueues the step behind it
+ * without waiting; xv_train_collect waits for the OLDEST submitted step and returns its loss (loss_out as above, may be
+ * NULL).  At most two steps may be in flight (XV_ESTATE beyond that); the usual loop is submit(0); for k: submit(k+1),
+ * collect(k).  The host buffers of a submit must stay untouched until that step has been collected (pinned memory is
+ * copied asynchronously).  Steps, updates and the data-parallel exchange are ordered exactly as with xv_train_step. */
+int  xv_train_submit(xv_ctx* ctx, const float* feats, const int32_t* labels, int32_t batch, int32_t frames,
+                     float learning_rate, int64_t global_step);
+int  xv_train_collect(xv_ctx* ctx, float* loss_out);
 /* Current value / last averaged gradient (including the wd*W regularisation term) of a variable, by TF name. */
 int  xv_train_get_weight(xv_ctx* ctx, const char* tf_name, float* host, int64_t capacity);
 int  xv_train_get_grad(xv_ctx* ctx, const char* tf_name, float* host, int64_t capacity);

@@ -178,3 +178,74 @@ def test_trainer_mgpu_bf16_exchange_tracks_fp32_exchange(tmp_path):
     for k, g in out["bf16"][1].items():
         ref = out["fp32"][1][k]
         assert np.linalg.norm(g - ref) <= 6e-3 * np.linalg.norm(ref), k            # one bf16 rounding per tower gradient + one of the sum
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_pipelined_steps_match_synchronous_steps(precision):
+    """xv_train_submit / xv_train_collect (batch k+1 copied while step k runs, loss collected one step late) against
+    xv_train_step on the same batches: same losses, same weights; also a step on device-resident buffers, and the state checks."""
+    import xvector_b200
+    from oracle import synth
+    from xvector_b200 import XVectorError
+    cfg = dict(synth.TDNN_AMSOFTMAX_CONFIG)
+    dim, speakers, lr, n_steps = 24, 101, 0.01, 6
+    w = synth.add_softmax_weights(synth.make_tdnn_weights(dim, cfg, seed=41), speakers)
+    # batches of DIFFERENT shapes: the loader draws one segment length per batch (dataset/data_loader.py:322-349)
+    batches = [synth.config5_batch(16 + 4 * (i % 2), 50 + 7 * i, dim, speakers, seed=60 + i, speaker_signal=1.0) for i in range(n_steps)]
+
+    def engine():
+        e = xvector_b200.Engine(cfg, dim, precision=precision)
+        e.set_weights(w)
+        e.train_init(speakers)
+        return e
+
+    a = engine()
+    sync_losses = [a.train_step(x, y, lr, i) for i, (x, y) in enumerate(batches)]
+    a2 = engine()                                               # the run-to-run spread of the synchronous call itself
+    again = [a2.train_step(x, y, lr, i) for i, (x, y) in enumerate(batches)]
+    a2.close()
+    b = engine()
+    with pytest.raises(XVectorError):
+        b.train_collect()                                       # nothing submitted
+    pipe_losses = []
+    b.train_submit(batches[0][0], batches[0][1], lr, 0)
+    for i in range(1, n_steps):
+        b.train_submit(batches[i][0], batches[i][1], lr, i)
+        if i == 1:
+            with pytest.raises(XVectorError):                   # two steps in flight: a third submit is refused ...
+                b.train_submit(batches[i][0], batches[i][1], lr, i)
+            with pytest.raises(XVectorError):                   # ... and so is the synchronous call
+                b.train_step(batches[i][0], batches[i][1], lr, i)
+        pipe_losses.append(b.train_collect())
+    pipe_losses.append(b.train_collect())
+    # Reductions use fp32 atomics, so two runs of the same step agree to rounding only, and training amplifies that from step
+    # to step: measured run-to-run spread of the SYNCHRONOUS call on these batches (printed below as the second run) is 2e-7 /
+    # 1.5e-4 (fp32 / bf16) at step 1 and 1.4e-3 / 1e-2 by step 5.  Step 1 is the first one submitted while another is in
+    # flight: a batch that went to the wrong step, or a copy that raced a running step, shows there at full precision.
+    report = "sync %s\nsync %s (second run)\npipe %s" % tuple(" ".join("%.6f" % l[0] for l in ls) for ls in (sync_losses, again, pipe_losses))
+    print(report)
+    early = 1e-5 if precision == "fp32" else 1e-3
+    late = 1e-2 if precision == "fp32" else 5e-2
+    for i, ((l0, t0), (l1, t1)) in enumerate(zip(sync_losses, pipe_losses)):
+        tol = 1e-5 if i == 0 else (early if i == 1 else late)
+        assert abs(l0 - l1) <= tol * abs(l0) and abs(t0 - t1) <= tol * abs(t0), report
+    k = "tdnn/tdnn3_conv/kernel"
+    wa, wb = a.train_weight(k, w[k].shape), b.train_weight(k, w[k].shape)
+    assert np.linalg.norm(wa - wb) <= 0.5 * np.linalg.norm(wa - w[k]), report
+    tol = late
+    # a step on buffers that already live on the device (loss_out = NULL: enqueued only), then a synchronous one
+    x, y = batches[0]
+    d_x, d_y = b.device_alloc(x.nbytes), b.device_alloc(y.nbytes)
+    try:
+        b.h2d(d_x, x)
+        b.h2d(d_y, np.ascontiguousarray(y, np.int32))
+        a_loss = a.train_step(x, y, lr, n_steps)
+        b.train_step_resident(d_x, d_y, x.shape[0], x.shape[1], lr, n_steps)
+        b.sync()
+        nxt_a, nxt_b = a.train_step(x, y, lr, n_steps + 1), b.train_step(x, y, lr, n_steps + 1)
+        assert np.isfinite(a_loss).all() and abs(nxt_a[0] - nxt_b[0]) <= 4 * tol * abs(nxt_a[0])
+    finally:
+        b.device_free(d_x)
+        b.device_free(d_y)
+    a.close()
+    b.close()

@@ -75,6 +75,8 @@ PROTOTYPES = {
                                       C.c_int32, _p, C.c_int32]),
     "xv_train_init": (C.c_int, [_p, C.c_int32]),
     "xv_train_step": (C.c_int, [_p, _p, _p, C.c_int32, C.c_int32, C.c_float, C.c_int64, _p]),
+    "xv_train_submit": (C.c_int, [_p, _p, _p, C.c_int32, C.c_int32, C.c_float, C.c_int64]),
+    "xv_train_collect": (C.c_int, [_p, _f32p]),
     "xv_train_get_weight": (C.c_int, [_p, C.c_char_p, _p, C.c_int64]),
     "xv_train_get_grad": (C.c_int, [_p, C.c_char_p, _p, C.c_int64]),
     "xv_train_num_variables": (C.c_int, [_p]),

@@ -112,6 +112,16 @@ struct TrainState {
   cudaStream_t wg_stream = nullptr;
   cudaEvent_t ev_dz[2] = {}, ev_wg[2] = {}, ev_wg_mark = nullptr, ev_fork = nullptr, ev_side_rd[2] = {}, ev_rnorm = nullptr;
   size_t dzb_half = 0;                   // elements between the two dZ buffers inside dzb (0: single buffer)
+  // pipelined steps (xv_train_submit / xv_train_collect): the batch of step k+1 is copied on the copy stream into the
+  // alternate feature / label buffers while step k computes; every step leaves its loss in a pinned slot behind an event
+  DevBuf feats_alt, labels_alt;
+  struct PipeSlot {
+    cudaEvent_t copied = nullptr, end = nullptr;   // H2D of the batch done | last command of the step (after the D2H of the loss)
+    float* h_loss = nullptr;                       // pinned: [0] tower-loss sum as float, then two doubles at +2 floats
+    bool used = false;
+  } pipe[2];
+  int pipe_next = 0;                     // slot of the next submit
+  int pipe_inflight = 0;                 // submitted and not yet collected (0..2); the oldest is slot (pipe_next - inflight) & 1
 
   double* scalars() const { return static_cast<double*>(sum_area.p); }
   double* fwd_sums(int layer) const { return static_cast<double*>(sum_area.p) + 8 + static_cast<size_t>(layer) * 5 * sum_ld; }
@@ -186,6 +196,11 @@ void train_release(xv_ctx* c) {
     if (t->ev_wg[i]) cudaEventDestroy(t->ev_wg[i]);
   }
   if (t->ev_wg_mark) cudaEventDestroy(t->ev_wg_mark);
+  for (int i = 0; i < 2; ++i) {
+    if (t->pipe[i].copied) cudaEventDestroy(t->pipe[i].copied);
+    if (t->pipe[i].end) cudaEventDestroy(t->pipe[i].end);
+    if (t->pipe[i].h_loss) cudaFreeHost(t->pipe[i].h_loss);
+  }
   if (t->ev_fork) cudaEventDestroy(t->ev_fork);
   if (t->ev_rnorm) cudaEventDestroy(t->ev_rnorm);
   for (int i = 0; i < 2; ++i)
@@ -195,7 +210,7 @@ void train_release(xv_ctx* c) {
   }
   DevBuf* bufs[] = {&t->params, &t->grads, &t->accum, &t->d_segs, &t->d_chunks, &t->const_slope, &t->feats, &t->labels,
                     &t->pooled, &t->logits, &t->gr, &t->coef, &t->rnorm, &t->dbuf[0], &t->dbuf[1], &t->scratch_stats,
-                    &t->sum_area, &t->sqnorms, &t->xb0, &t->dzb, &t->ones_pad, &t->zeros_pad, &t->gcomm};
+                    &t->sum_area, &t->sqnorms, &t->xb0, &t->dzb, &t->ones_pad, &t->zeros_pad, &t->gcomm, &t->feats_alt, &t->labels_alt};
   for (DevBuf* b : bufs) release(b);
   delete t;
   c->train = nullptr;
@@ -475,6 +490,8 @@ int tr_buffers(xv_ctx* c, TrainState* t, int b, int tt) {
   const int pool_c = t->layers[t->n_frame - 1].cout;
   if ((rc = ensure(c, &t->feats, sizeof(float) * rows * c->dim)) != XV_OK) return rc;
   if ((rc = ensure(c, &t->labels, sizeof(int32_t) * b)) != XV_OK) return rc;
+  if ((rc = ensure(c, &t->feats_alt, sizeof(float) * rows * c->dim)) != XV_OK) return rc;
+  if ((rc = ensure(c, &t->labels_alt, sizeof(int32_t) * b)) != XV_OK) return rc;
   if ((rc = ensure(c, &t->pooled, sizeof(float) * b * 2 * pool_c)) != XV_OK) return rc;
   if ((rc = ensure(c, &t->logits, sizeof(float) * static_cast<size_t>(b) * t->speakers)) != XV_OK) return rc;
   if ((rc = ensure(c, &t->gr, sizeof(float) * static_cast<size_t>(b) * t->speakers)) != XV_OK) return rc;
@@ -517,15 +534,15 @@ int tr_gemm_tc(xv_ctx* c, TrainState* t, const CUtensorMap& tm_a, const CUtensor
 
 // Host wait for the stream of a data-parallel step: polls the communicator for asynchronous errors so that a peer's
 // failure surfaces as an error here instead of a hang inside the collective.
-int dp_wait(xv_ctx* c, TrainState* t) {
+int dp_wait(xv_ctx* c, TrainState* t, cudaEvent_t ev = nullptr) {     // ev: wait for this event instead of the whole stream
   if (t->world <= 1 || !t->comm || !t->nccl.CommGetAsyncError) {
-    cudaError_t e = cudaStreamSynchronize(c->stream);
+    cudaError_t e = ev ? cudaEventSynchronize(ev) : cudaStreamSynchronize(c->stream);
     if (e != cudaSuccess) return cuda_fail(c, e, "stream synchronize");
     return XV_OK;
   }
   int spins = 0;
   for (;;) {
-    cudaError_t q = cudaStreamQuery(c->stream);
+    cudaError_t q = ev ? cudaEventQuery(ev) : cudaStreamQuery(c->stream);
     if (q == cudaSuccess) break;
     if (q != cudaErrorNotReady) return cuda_fail(c, q, "stream query");
     if ((++spins & 63) == 0) {
@@ -576,7 +593,7 @@ static int exchange_bucket(TrainState* t, int k) {
 }
 
 static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const int32_t* labels, int32_t b, int32_t tt, float lr,
-                           int64_t global_step, float* loss_out) {
+                           int64_t global_step, float* loss_out, int pipe_slot = -1) {
   int rc = tr_buffers(c, t, b, tt);
   if (rc != XV_OK) return rc;
   cudaStream_t s = c->stream;
@@ -589,8 +606,10 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
   const float* slope_const = static_cast<const float*>(t->const_slope.p);
   const float* slope_linear = slope_const + maxc;
   const int nl = static_cast<int>(t->layers.size());
-  TR_CUDA(cudaMemcpyAsync(t->feats.p, feats, sizeof(float) * rows * c->dim, cudaMemcpyDefault, s), "H2D features");
-  TR_CUDA(cudaMemcpyAsync(t->labels.p, labels, sizeof(int32_t) * b, cudaMemcpyHostToDevice, s), "H2D labels");
+  if (feats != nullptr) {          // null: the batch was staged into t->feats / t->labels by the caller (pipelined step)
+    TR_CUDA(cudaMemcpyAsync(t->feats.p, feats, sizeof(float) * rows * c->dim, cudaMemcpyDefault, s), "H2D features");
+    TR_CUDA(cudaMemcpyAsync(t->labels.p, labels, sizeof(int32_t) * b, cudaMemcpyDefault, s), "H2D labels");
+  }
   TR_CUDA(cudaMemsetAsync(t->sum_area.p, 0, sizeof(double) * t->sum_area_doubles(), s), "memset sums");
   // gradient buffer: the frame-layer range is accumulated into (tensor-core wgrad = split-K reductions; biases in front
   // of a batch norm keep their exact zero); the tail carries rank 0's moving statistics + the loss slot
@@ -611,6 +630,17 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     return f;
   };
   const PoolGrad no_pg = {nullptr, nullptr, 0.f, 0};
+
+  // 1/|w_s| of the AM-softmax weight columns depends on the weights only: it runs on the side stream beside the forward pass
+  const bool rnorm_early = t->amsoftmax && t->mixed && t->wg_overlap && t->wg_overlap_head && t->wg_stream != nullptr;
+  if (rnorm_early) {
+    TR_CUDA(cudaEventRecord(t->ev_fork, s), "cudaEventRecord");                   // behind the previous step's update
+    TR_CUDA(cudaStreamWaitEvent(t->wg_stream, t->ev_fork, 0), "cudaStreamWaitEvent");
+    count_launch(c, "train.col_rnorm");
+    col_rnorm_kernel<<<(t->speakers + 31) / 32, 256, 0, t->wg_stream>>>(P + t->off_w, t->embed, t->speakers, static_cast<float*>(t->rnorm.p));
+    TR_CUDA(cudaGetLastError(), "column norm launch");
+    TR_CUDA(cudaEventRecord(t->ev_rnorm, t->wg_stream), "cudaEventRecord");
+  }
 
   // ------------------------------------------------------------------ forward
   const float* in = static_cast<const float*>(t->feats.p);
@@ -731,9 +761,13 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
                                 static_cast<double>(t->lam_base) * pow(1.0 + static_cast<double>(t->lam_gamma) * static_cast<double>(global_step),
                                                                         -static_cast<double>(t->lam_power)));
     fa = static_cast<float>(1.0 / (1.0 + lam));
-    count_launch(c, "train.col_rnorm");
-    col_rnorm_kernel<<<(S + 31) / 32, 256, 0, s>>>(P + t->off_w, E, S, static_cast<float*>(t->rnorm.p));
-    TR_CUDA(cudaGetLastError(), "column norm launch");
+    if (rnorm_early) {
+      TR_CUDA(cudaStreamWaitEvent(s, t->ev_rnorm, 0), "cudaStreamWaitEvent");     // launched beside the forward pass (below)
+    } else {
+      count_launch(c, "train.col_rnorm");
+      col_rnorm_kernel<<<(S + 31) / 32, 256, 0, s>>>(P + t->off_w, E, S, static_cast<float*>(t->rnorm.p));
+      TR_CUDA(cudaGetLastError(), "column norm launch");
+    }
   }
   {
     // logits = f . W (softmax: + bias; AM-softmax: columns scaled by 1/|w_s|, model/loss.py:241-243)
@@ -987,27 +1021,78 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     if ((rc = dp_wait(c, t)) != XV_OK) return rc;
     loss_out[0] = loss_sum / t->world;                 // mean of the tower losses (model/trainer.py:1218-1219)
     loss_out[1] = loss_out[0] + static_cast<float>(sc[1]);
+  } else if (pipe_slot >= 0) {
+    TrainState::PipeSlot& ps = t->pipe[pipe_slot];
+    TR_CUDA(cudaMemcpyAsync(ps.h_loss, G + t->n_total, sizeof(float), cudaMemcpyDeviceToHost, s), "D2H loss");
+    TR_CUDA(cudaMemcpyAsync(ps.h_loss + 2, scalars, sizeof(double) * 2, cudaMemcpyDeviceToHost, s), "D2H scalars");
+    TR_CUDA(cudaEventRecord(ps.end, s), "cudaEventRecord");
   }
   return XV_OK;
 }
 
+static bool is_device_pointer(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+// Pipelined step, first half: the batch goes to the alternate feature / label buffers on the COPY stream (it overlaps the step
+// that is still running on the compute stream), then the whole step is enqueued behind it; nothing is waited for.
+static int train_submit_body(xv_ctx* c, TrainState* t, const float* feats, const int32_t* labels, int32_t b, int32_t tt, float lr,
+                             int64_t global_step) {
+  int rc = tr_buffers(c, t, b, tt);
+  if (rc != XV_OK) return rc;
+  const int slot = t->pipe_next;
+  TrainState::PipeSlot& ps = t->pipe[slot];
+  if (!ps.end) {
+    TR_CUDA(cudaEventCreateWithFlags(&ps.copied, cudaEventDisableTiming), "cudaEventCreate");
+    TR_CUDA(cudaEventCreateWithFlags(&ps.end, cudaEventDisableTiming), "cudaEventCreate");
+    TR_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&ps.h_loss), 32, cudaHostAllocDefault), "cudaHostAlloc");
+  }
+  // the buffers about to be overwritten were read by the step two submits ago (same slot): it has been collected, hence
+  // finished, unless the caller never collected it -- the event makes the order explicit either way
+  std::swap(t->feats, t->feats_alt);
+  std::swap(t->labels, t->labels_alt);
+  if (ps.used) TR_CUDA(cudaStreamWaitEvent(c->copy_stream, ps.end, 0), "cudaStreamWaitEvent");
+  const int64_t rows = static_cast<int64_t>(b) * tt;
+  TR_CUDA(cudaMemcpyAsync(t->feats.p, feats, sizeof(float) * rows * c->dim, cudaMemcpyDefault, c->copy_stream), "H2D features");
+  TR_CUDA(cudaMemcpyAsync(t->labels.p, labels, sizeof(int32_t) * b, cudaMemcpyDefault, c->copy_stream), "H2D labels");
+  TR_CUDA(cudaEventRecord(ps.copied, c->copy_stream), "cudaEventRecord");
+  TR_CUDA(cudaStreamWaitEvent(c->stream, ps.copied, 0), "cudaStreamWaitEvent");
+  rc = train_step_body(c, t, nullptr, nullptr, b, tt, lr, global_step, nullptr, slot);
+  if (rc != XV_OK) return rc;
+  ps.used = true;
+  t->pipe_next ^= 1;
+  t->pipe_inflight++;
+  return XV_OK;
+}
+
 static int train_step(xv_ctx* c, const float* feats, const int32_t* labels, int32_t b, int32_t tt, float lr,
-                      int64_t global_step, float* loss_out) {
+                      int64_t global_step, float* loss_out, bool pipelined = false) {
   TrainState* t = c->train;
   if (!t) return fail(c, XV_ESTATE, "xv_train_step: call xv_train_init first");
   if (t->poisoned) return fail(c, XV_ESTATE, "xv_train_step: the communicator was aborted by an earlier failed step; re-create the context");
   if (t->world > 1 && !t->comm) return fail(c, XV_ESTATE, "xv_train_step: world > 1 but no communicator (xv_comm_init)");
+  if (!pipelined && t->pipe_inflight > 0)
+    return fail(c, XV_ESTATE, "xv_train_step: %d submitted step(s) have not been collected (xv_train_collect)", t->pipe_inflight);
+  if (pipelined && t->pipe_inflight >= 2)
+    return fail(c, XV_ESTATE, "xv_train_submit: two steps are in flight; collect one first (xv_train_collect)");
   // Everything that can fail for reasons local to this rank is checked BEFORE any work (and any collective) is enqueued.
   int rc = XV_OK;
   if (b < 1 || tt <= c->total_context) rc = fail(c, XV_EINVAL, "xv_train_step: need B >= 1 and T > %d", c->total_context);
   else if (static_cast<int64_t>(b) * tt >= (1LL << 31)) rc = fail(c, XV_EINVAL, "xv_train_step: B*T must stay below 2^31 rows");
-  else
+  else if (!is_device_pointer(labels))       // labels resident on the device are the caller's responsibility
     for (int u = 0; u < b; ++u)
       if (labels[u] < 0 || labels[u] >= t->speakers) {
         rc = fail(c, XV_EINVAL, "label %d of utterance %d is outside [0,%d)", labels[u], u, t->speakers);
         break;
       }
-  if (rc == XV_OK) rc = train_step_body(c, t, feats, labels, b, tt, lr, global_step, loss_out);
+  if (rc == XV_OK)
+    rc = pipelined ? train_submit_body(c, t, feats, labels, b, tt, lr, global_step)
+                   : train_step_body(c, t, feats, labels, b, tt, lr, global_step, loss_out);
   if (rc != XV_OK && t->world > 1 && t->comm) {
     // The peers are (or will be) inside this step's collectives: abort the communicator so that they get an
     // asynchronous error (dp_wait) instead of waiting forever.  The context cannot train any further.
@@ -1040,6 +1125,35 @@ int xv_train_step(xv_ctx* c, const float* feats, const int32_t* labels, int32_t 
   if (!feats || !labels) return fail(c, XV_EINVAL, "xv_train_step: null argument");
   cudaSetDevice(c->device);
   return train_step(c, feats, labels, batch, frames, learning_rate, global_step, loss_out);
+}
+
+int xv_train_submit(xv_ctx* c, const float* feats, const int32_t* labels, int32_t batch, int32_t frames, float learning_rate,
+                    int64_t global_step) {
+  if (!c) return XV_EINVAL;
+  if (!feats || !labels) return fail(c, XV_EINVAL, "xv_train_submit: null argument");
+  cudaSetDevice(c->device);
+  return train_step(c, feats, labels, batch, frames, learning_rate, global_step, nullptr, true);
+}
+
+int xv_train_collect(xv_ctx* c, float* loss_out) {
+  if (!c) return XV_EINVAL;
+  TrainState* t = c->train;
+  if (!t) return fail(c, XV_ESTATE, "xv_train_collect: call xv_train_init first");
+  if (t->pipe_inflight <= 0) return fail(c, XV_ESTATE, "xv_train_collect: no submitted step is waiting");
+  cudaSetDevice(c->device);
+  const int slot = (t->pipe_next - t->pipe_inflight) & 1;
+  TrainState::PipeSlot& ps = t->pipe[slot];
+  t->pipe_inflight--;
+  if (t->poisoned) return fail(c, XV_ESTATE, "xv_train_collect: the communicator was aborted by an earlier failed step");
+  int rc = dp_wait(c, t, ps.end);
+  if (rc != XV_OK) return rc;
+  if (loss_out) {
+    double sc[2];
+    memcpy(sc, ps.h_loss + 2, sizeof(sc));
+    loss_out[0] = ps.h_loss[0] / t->world;
+    loss_out[1] = loss_out[0] + static_cast<float>(sc[1]);
+  }
+  return XV_OK;
 }
 
 static int train_read(xv_ctx* c, const char* name, float* host, int64_t cap, bool grad) {

@@ -283,6 +283,34 @@ class Engine(object):
                                            int(global_step), _fptr(out)))
         return float(out[0]), float(out[1])
 
+    def train_submit(self, feats, labels, learning_rate, global_step=0):
+        """First half of a pipelined step (xv_train_submit): copies the batch on the copy stream and enqueues the step behind
+        it without waiting.  At most two submitted steps may be uncollected.  The arrays are kept alive until the step is
+        collected; a caller that reuses its own (pinned) buffers must not overwrite them before that."""
+        x = _f32(feats)
+        y = np.ascontiguousarray(labels, dtype=np.int32)
+        assert x.ndim == 3 and y.shape == (x.shape[0],)
+        self._check(self.lib.xv_train_submit(self._ctx, _fptr(x), _i32ptr(y), x.shape[0], x.shape[1], float(learning_rate),
+                                             int(global_step)))
+        if not hasattr(self, "_submitted"):
+            self._submitted = []
+        self._submitted.append((x, y))
+
+    def train_collect(self):
+        """Second half: waits for the oldest submitted step -> (loss, total_loss)."""
+        out = np.zeros(2, np.float32)
+        rc = self.lib.xv_train_collect(self._ctx, _fptr(out))
+        if getattr(self, "_submitted", None):
+            self._submitted.pop(0)
+        self._check(rc)
+        return float(out[0]), float(out[1])
+
+    def train_step_resident(self, feats_dev, labels_dev, batch, frames, learning_rate, global_step=0):
+        """xv_train_step on a batch that already lives in device buffers of the caller (device_alloc + h2d); only enqueues
+        the step (loss_out = NULL): read the loss with a later train_step / train_collect, or sync()."""
+        self._check(self.lib.xv_train_step(self._ctx, feats_dev, labels_dev, int(batch), int(frames), float(learning_rate),
+                                           int(global_step), None))
+
     def _train_read(self, fn, name, shape):
         out = np.empty(shape, np.float32)
         self._check(fn(self._ctx, name.encode("utf-8"), _fptr(out), out.size))

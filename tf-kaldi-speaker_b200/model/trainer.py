@@ -188,6 +188,32 @@ class Trainer(object):
         self._predict_stale = True
         return out
 
+    def train_submit(self, features, labels, learning_rate, global_step=None):
+        """train_step as a two-stage pipeline (xv_train_submit / xv_train_collect): copies the batch and enqueues the step
+        without waiting for it, so that the host prepares batch k+1 while step k runs.  At most two submitted steps may be
+        uncollected; train_collect() returns their (loss, total_loss) in order."""
+        if not self.train_built:
+            sys.exit("The training graph has not been build. Call build('train') first.")
+        features = np.asarray(features, np.float32)
+        if features.shape[-1] != self.dim:
+            features = features[:, :, :self.dim]
+        labels = np.ascontiguousarray(labels, np.int32)
+        step = self.curr_step if global_step is None else int(global_step)
+        world = len(self.engines)
+        if world == 1:
+            self.engine.train_submit(features, labels, learning_rate, step)
+        else:
+            slices = [train_dp.slice_batch(features, labels, r, world) for r in range(world)]
+            list(self._pool.map(lambda r: self.engines[r].train_submit(slices[r][0], slices[r][1], learning_rate, step),
+                                range(world)))
+        self.curr_step = step + 1
+        self._predict_stale = True
+
+    def train_collect(self):
+        if len(self.engines) == 1:
+            return self.engine.train_collect()
+        return list(self._pool.map(lambda e: e.train_collect(), self.engines))[0]
+
     def variables(self):
         """{TF variable name: current value} of the training state (replica 0; replicas are bit-identical)."""
         return self.engine.train_variables()
@@ -211,18 +237,32 @@ class Trainer(object):
                                      max_len=p["max_segment_len"], dim=self.dim, seed=p.get("seed", 0) + self.curr_step,
                                      sample_with_prob=p.get("sample_with_prob", False))
         steps = p["num_steps_per_epoch"]
-        last = (0.0, 0.0)
+        last = [(0.0, 0.0)]
+        pending = []                                     # (global step, step of the epoch) of the submitted, uncollected steps
+
+        def collect_one():
+            curr, step = pending.pop(0)
+            last[0] = self.train_collect()
+            if step % p.get("show_training_progress", 100) == 0:
+                print("Epoch: [%2d] step: [%2d/%2d] raw loss: %f, total loss: %f" % (curr // steps, step, steps, last[0][0], last[0][1]),
+                      file=sys.stderr)
+
+        # two-stage pipeline: while step k runs on the GPU the loader assembles batch k+1 and its copy is already queued
         for step in range(self.curr_step % steps, steps):
             features, labels = loader.fetch()
             curr = self.curr_step
-            last = self.train_step(features, labels, learning_rate)
-            if step % p.get("show_training_progress", 100) == 0:
-                print("Epoch: [%2d] step: [%2d/%2d] raw loss: %f, total loss: %f" % (curr // steps, step, steps, last[0], last[1]),
-                      file=sys.stderr)
+            self.train_submit(features, labels, learning_rate)
+            pending.append((curr, step))
+            if len(pending) == 2:
+                collect_one()
             if step % p.get("save_checkpoints_steps", steps) == 0 and curr != 0:
+                while pending:                           # a checkpoint holds exactly the steps up to and including `curr`
+                    collect_one()
                 self.save(curr)
+        while pending:
+            collect_one()
         self.save(self.curr_step)
-        return last
+        return last[0]
 
     def valid(self, *args, **kwargs):
         raise NotImplementedError("valid(): the validation loop (model/trainer.py:756-884) is outside this build's scope")
