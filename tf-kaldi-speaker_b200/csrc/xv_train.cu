@@ -31,6 +31,7 @@
 
 #include "xv_ctx.h"
 #include "xv_train_kernels.cuh"
+#include "xv_train_stream.cuh"
 
 // ================================================================================================ host side
 namespace xv {
@@ -109,6 +110,12 @@ struct TrainState {
   // beside the critical chain dgrad_l -> BN backward_{l-1} (fills the idle second wave of the dgrad GEMM and the latency-bound
   // row-streaming kernels).  dZ is double-buffered by layer parity; XV_TRAIN_WGRAD_STREAM=0 keeps everything on one stream.
   bool wg_overlap = true, wg_overlap_head = true;
+  // XV_TRAIN_TIMELINE=<global step>: that step records an event in front of every launch of the compute stream and prints the
+  // time between consecutive marks per kernel family (the in-step critical path, warm caches; side-stream work shows as ~0)
+  int64_t timeline_step = -1;
+  std::vector<std::pair<const char*, cudaEvent_t>> marks;
+  bool marking = false;
+  bool bulk_rows = false;                 // XV_TRAIN_BULK=0: per-thread-load versions of the row-streaming kernels (xv_train_stream.cuh)
   cudaStream_t wg_stream = nullptr;
   cudaEvent_t ev_dz[2] = {}, ev_wg[2] = {}, ev_wg_mark = nullptr, ev_fork = nullptr, ev_side_rd[2] = {}, ev_rnorm = nullptr;
   size_t dzb_half = 0;                   // elements between the two dZ buffers inside dzb (0: single buffer)
@@ -218,9 +225,40 @@ void train_release(xv_ctx* c) {
 
 namespace {
 // (Re)builds the bf16 operand layouts of every frame layer from the fp32 masters: one launch.
+void tr_count(xv_ctx* c, TrainState* t, const char* fam) {
+  count_launch(c, fam);
+  if (!t->marking) return;
+  cudaEvent_t e;
+  if (cudaEventCreate(&e) != cudaSuccess) return;
+  cudaEventRecord(e, c->stream);
+  t->marks.push_back(std::make_pair(fam, e));
+}
+
+void tr_timeline_report(xv_ctx* c, TrainState* t) {
+  tr_count(c, t, "end");
+  t->marking = false;
+  cudaStreamSynchronize(c->stream);
+  std::map<std::string, std::pair<double, int>> fam;
+  double total = 0;
+  fprintf(stderr, "[xv_train timeline]");
+  for (size_t i = 0; i + 1 < t->marks.size(); ++i) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, t->marks[i].second, t->marks[i + 1].second);
+    fam[t->marks[i].first].first += ms * 1e3;
+    fam[t->marks[i].first].second++;
+    total += ms * 1e3;
+    fprintf(stderr, " %s=%.1f", t->marks[i].first + 6, ms * 1e3);
+  }
+  fprintf(stderr, "\n[xv_train timeline] total %.1f us:", total);
+  for (const auto& kv : fam) fprintf(stderr, " %s x%d = %.1f;", kv.first.c_str() + 6, kv.second.second, kv.second.first);
+  fprintf(stderr, "\n");
+  for (auto& m : t->marks) cudaEventDestroy(m.second);
+  t->marks.clear();
+}
+
 int launch_recast(xv_ctx* c, TrainState* t) {
   if (!t->mixed || t->recast.n == 0) return XV_OK;
-  count_launch(c, "train.cast_w");
+  tr_count(c, t, "train.cast_w");
   const int grid = std::min(t->recast.total_tiles, c->sm_count * 16);
   recast_weights_kernel<<<grid, 256, 0, c->stream>>>(t->recast);
   cudaError_t e = cudaGetLastError();
@@ -240,6 +278,8 @@ static int train_init(xv_ctx* c, int32_t num_speakers) {
   t->fused_stats = !(getenv("XV_TRAIN_FUSED_STATS") && atoi(getenv("XV_TRAIN_FUSED_STATS")) == 0);
   t->overlap = !(getenv("XV_TRAIN_OVERLAP") && atoi(getenv("XV_TRAIN_OVERLAP")) == 0);
   t->wg_overlap = !(getenv("XV_TRAIN_WGRAD_STREAM") && atoi(getenv("XV_TRAIN_WGRAD_STREAM")) == 0);
+  if (getenv("XV_TRAIN_TIMELINE")) t->timeline_step = atoll(getenv("XV_TRAIN_TIMELINE"));
+  t->bulk_rows = getenv("XV_TRAIN_BULK") && atoi(getenv("XV_TRAIN_BULK")) == 1;     // measured no faster than the per-thread-load kernels (r02w): opt-in
   t->wg_overlap_head = !(getenv("XV_TRAIN_WGRAD_STREAM") && atoi(getenv("XV_TRAIN_WGRAD_STREAM")) == 1);   // 1: frame layers only
   {
     const JValue* gd = c->cfg.get("grad_allreduce_dtype");
@@ -526,7 +566,7 @@ int tr_gemm_tc(xv_ctx* c, TrainState* t, const CUtensorMap& tm_a, const CUtensor
   p.heads = 1; p.head_width = n_alloc;
   p.stat_out = stat; p.stat_ld = t->sum_ld; p.stat_t = stat_t; p.stat_valid = stat_valid;
   g.pool = false;
-  count_launch(c, fam);
+  tr_count(c, t, fam);
   cudaError_t e = launch_gemm(g, c->sm_count, c->stream);
   if (e != cudaSuccess) return cuda_fail(c, e, "tcgen05 training GEMM launch");
   return XV_OK;
@@ -606,6 +646,8 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
   const float* slope_const = static_cast<const float*>(t->const_slope.p);
   const float* slope_linear = slope_const + maxc;
   const int nl = static_cast<int>(t->layers.size());
+  t->marking = t->timeline_step >= 0 && global_step == t->timeline_step;
+  if (t->marking) tr_count(c, t, "train.h2d+memsets");
   if (feats != nullptr) {          // null: the batch was staged into t->feats / t->labels by the caller (pipelined step)
     TR_CUDA(cudaMemcpyAsync(t->feats.p, feats, sizeof(float) * rows * c->dim, cudaMemcpyDefault, s), "H2D features");
     TR_CUDA(cudaMemcpyAsync(t->labels.p, labels, sizeof(int32_t) * b, cudaMemcpyDefault, s), "H2D labels");
@@ -613,7 +655,9 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
   TR_CUDA(cudaMemsetAsync(t->sum_area.p, 0, sizeof(double) * t->sum_area_doubles(), s), "memset sums");
   // gradient buffer: the frame-layer range is accumulated into (tensor-core wgrad = split-K reductions; biases in front
   // of a batch norm keep their exact zero); the tail carries rank 0's moving statistics + the loss slot
-  TR_CUDA(cudaMemsetAsync(G, 0, sizeof(float) * t->layers[t->n_frame].off_kernel, s), "memset frame gradients");
+  // (bf16 path: only the side-stream weight-gradient GEMMs need these zeros, and the side stream clears them itself below)
+  const bool side0 = t->mixed && t->wg_overlap && t->wg_stream != nullptr;
+  if (!side0) TR_CUDA(cudaMemsetAsync(G, 0, sizeof(float) * t->layers[t->n_frame].off_kernel, s), "memset frame gradients");
   TR_CUDA(cudaMemsetAsync(G + t->n_train, 0, sizeof(float) * (t->n_total - t->n_train + 1), s), "memset tail");
   auto slope_of = [&](const TrLayer& l) -> const float* {
     if (!l.act) return slope_linear;
@@ -632,15 +676,18 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
   const PoolGrad no_pg = {nullptr, nullptr, 0.f, 0};
 
   // 1/|w_s| of the AM-softmax weight columns depends on the weights only: it runs on the side stream beside the forward pass
-  const bool rnorm_early = t->amsoftmax && t->mixed && t->wg_overlap && t->wg_overlap_head && t->wg_stream != nullptr;
-  if (rnorm_early) {
+  const bool rnorm_early = t->amsoftmax && side0 && t->wg_overlap_head;
+  if (side0) {
     TR_CUDA(cudaEventRecord(t->ev_fork, s), "cudaEventRecord");                   // behind the previous step's update
     TR_CUDA(cudaStreamWaitEvent(t->wg_stream, t->ev_fork, 0), "cudaStreamWaitEvent");
-    count_launch(c, "train.col_rnorm");
+    TR_CUDA(cudaMemsetAsync(G, 0, sizeof(float) * t->layers[t->n_frame].off_kernel, t->wg_stream), "memset frame gradients");
+  }
+  if (rnorm_early) {
+    tr_count(c, t, "train.col_rnorm");
     col_rnorm_kernel<<<(t->speakers + 31) / 32, 256, 0, t->wg_stream>>>(P + t->off_w, t->embed, t->speakers, static_cast<float*>(t->rnorm.p));
     TR_CUDA(cudaGetLastError(), "column norm launch");
-    TR_CUDA(cudaEventRecord(t->ev_rnorm, t->wg_stream), "cudaEventRecord");
   }
+  if (side0) TR_CUDA(cudaEventRecord(t->ev_rnorm, t->wg_stream), "cudaEventRecord");
 
   // ------------------------------------------------------------------ forward
   const float* in = static_cast<const float*>(t->feats.p);
@@ -659,7 +706,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     bool have_stats = false;
     if (tc) {
       if (i == 0) {
-        count_launch(c, "train.splice_cast");
+        tr_count(c, t, "train.splice_cast");
         TR_CUDA(launch_splice_cast(static_cast<const float*>(t->feats.p), rows, c->dim, l.taps, 1,
                                    static_cast<__nv_bfloat16*>(t->xb0.p), l.a_cin, s), "splice launch");
       }
@@ -673,7 +720,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
       SkinnyArgs sa;
       sa.a = in; sa.lda = l.cin; sa.w = P + l.off_kernel; sa.ldw = l.cout; sa.out = static_cast<float*>(l.z.p); sa.ldo = l.cout;
       sa.col_scale = nullptr; sa.bias = P + l.off_bias; sa.m = b; sa.n = l.cout; sa.k = l.cin; sa.ks = 0;
-      count_launch(c, "train.skinny_fwd");
+      tr_count(c, t, "train.skinny_fwd");
       TR_CUDA(launch_skinny_gemm<false>(sa, c->sm_count, s), "segment-level forward GEMM launch");
     } else {
       SimtGemmArgs ga;
@@ -681,7 +728,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
       ga.w = P + l.off_kernel; ga.n = l.cout; ga.bias = P + l.off_bias;
       ga.bn_scale = nullptr; ga.bn_shift = nullptr; ga.slope = nullptr; ga.act_tanh = 0;
       ga.out_dense = static_cast<float*>(l.z.p); ga.out_bn = nullptr; ga.out_act = nullptr; ga.m_rows = r;
-      count_launch(c, "train.gemm_fwd");
+      tr_count(c, t, "train.gemm_fwd");
       TR_CUDA(launch_simt_gemm(ga, s), "forward GEMM launch");
     }
     if (!l.frame) {
@@ -690,7 +737,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
       fa.fin = finalize_of(l);
       fa.gamma = l.has_bn ? P + l.off_gamma : nullptr; fa.beta = l.has_bn ? P + l.off_beta : nullptr; fa.slope = slope_of(l);
       fa.y = static_cast<float*>(l.y.p);
-      count_launch(c, "train.seg_bn_act");
+      tr_count(c, t, "train.seg_bn_act");
       seg_bn_act_fwd_kernel<<<(l.cout + 31) / 32, dim3(32, 8), 0, s>>>(fa);
       TR_CUDA(cudaGetLastError(), "segment BN/activation launch");
       in = static_cast<const float*>(l.y.p);
@@ -698,7 +745,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
       continue;
     }
     if (!have_stats) {
-      count_launch(c, "train.bn_stats");
+      tr_count(c, t, "train.bn_stats");
       TR_CUDA(launch_col_reduce4<0>(nullptr, static_cast<const float*>(l.z.p), mask, r, l.cout, nullptr, nullptr, nullptr, nullptr,
                                     nullptr, no_pg, t->fwd_sums(i), t->sum_ld, c->sm_count, s), "BN statistics launch");
     }
@@ -710,15 +757,24 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     fa.y = nullptr; fa.yb = nullptr; fa.ldb = l.ldb;
     if (i == t->n_frame - 1) {
       // normalise + activate + statistics pooling (model/pooling.py:40-50) in one pass; y is never stored
-      count_launch(c, "train.bn_act_pool");
+      tr_count(c, t, "train.bn_act_pool");
       bn_act_pool_fwd_kernel<<<dim3((l.cout / 4 + 31) / 32, b), dim3(32, 8), 0, s>>>(fa, static_cast<float*>(t->pooled.p));
       TR_CUDA(cudaGetLastError(), "BN/activation/pooling launch");
     } else {
       if (tc) fa.yb = static_cast<__nv_bfloat16*>(l.yb.p); else fa.y = static_cast<float*>(l.y.p);
-      count_launch(c, "train.bn_act");
-      const RowGrid rg = row_grid(l.cout / 4, c->sm_count);
-      bn_act_fwd_kernel<<<rg.grid, rg.block, 0, s>>>(fa);
-      TR_CUDA(cudaGetLastError(), "BN/activation launch");
+      tr_count(c, t, "train.bn_act");
+      BsArgs sa = {};
+      sa.z = fa.z; sa.dy = nullptr; sa.rows = r; sa.c_total = l.cout; sa.mask = mask;
+      sa.st = fa.st; sa.fin = fa.fin; sa.y = fa.y; sa.yb = fa.yb; sa.ldb = fa.ldb;
+      sa.gamma = fa.gamma; sa.beta = fa.beta; sa.slope = fa.slope;
+      dim3 sg, sb;
+      if (t->bulk_rows && bs_plan(&sa, c->sm_count, &sg, &sb)) {
+        TR_CUDA(bs_launch<kBsFwd>(sa, sg, sb, s), "BN/activation launch");
+      } else {
+        const RowGrid rg = row_grid(l.cout / 4, c->sm_count);
+        bn_act_fwd_kernel<<<rg.grid, rg.block, 0, s>>>(fa);
+        TR_CUDA(cudaGetLastError(), "BN/activation launch");
+      }
       in = static_cast<const float*>(l.y.p);
     }
     in_c = l.cout;
@@ -756,15 +812,16 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
   const float* fvec = static_cast<const float*>(last.y.p);
   const int E = t->embed, S = t->speakers;
   float fa = 0.f;
+  // the side stream's work of the step start (gradient zeros, AM-softmax column norms) is complete before anything below
+  // reads the norms or stores a parameter gradient
+  if (side0) TR_CUDA(cudaStreamWaitEvent(s, t->ev_rnorm, 0), "cudaStreamWaitEvent");
   if (t->amsoftmax) {
     const double lam = std::max(static_cast<double>(t->lam_min),
                                 static_cast<double>(t->lam_base) * pow(1.0 + static_cast<double>(t->lam_gamma) * static_cast<double>(global_step),
                                                                         -static_cast<double>(t->lam_power)));
     fa = static_cast<float>(1.0 / (1.0 + lam));
-    if (rnorm_early) {
-      TR_CUDA(cudaStreamWaitEvent(s, t->ev_rnorm, 0), "cudaStreamWaitEvent");     // launched beside the forward pass (below)
-    } else {
-      count_launch(c, "train.col_rnorm");
+    if (!rnorm_early) {
+      tr_count(c, t, "train.col_rnorm");
       col_rnorm_kernel<<<(S + 31) / 32, 256, 0, s>>>(P + t->off_w, E, S, static_cast<float*>(t->rnorm.p));
       TR_CUDA(cudaGetLastError(), "column norm launch");
     }
@@ -776,10 +833,10 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     sa.col_scale = t->amsoftmax ? static_cast<const float*>(t->rnorm.p) : nullptr;
     sa.bias = t->amsoftmax ? nullptr : P + t->off_b;
     sa.m = b; sa.n = S; sa.k = E; sa.ks = 0;
-    count_launch(c, "train.skinny_fwd");
+    tr_count(c, t, "train.skinny_fwd");
     TR_CUDA(launch_skinny_gemm<false>(sa, c->sm_count, s), "logits GEMM launch");
   }
-  count_launch(c, "train.loss");
+  tr_count(c, t, "train.loss");
   softmax_loss_kernel<<<b, kLossThreads, 0, s>>>(static_cast<float*>(t->logits.p), S, fvec, E, static_cast<const int32_t*>(t->labels.p), b,
                                         t->amsoftmax ? static_cast<const float*>(t->rnorm.p) : nullptr, t->amsoftmax ? 1 : 0,
                                         t->margin, fa, static_cast<float*>(t->gr.p), static_cast<float*>(t->coef.p), scalars);
@@ -791,7 +848,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
       if ((rc = side_fork()) != XV_OK) return rc;
       hs = t->wg_stream;
     }
-    count_launch(c, "train.head_wgrad");
+    tr_count(c, t, "train.head_wgrad");
     head_wgrad_kernel<<<(S + 31) / 32, 256, 0, hs>>>(fvec, static_cast<const float*>(t->logits.p), b, E, S, P + t->off_w,
                                                     t->amsoftmax ? static_cast<const float*>(t->rnorm.p) : nullptr, G + t->off_w,
                                                     t->amsoftmax ? nullptr : G + t->off_b, scalars, G + t->n_total);
@@ -800,7 +857,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     RowsTArgs wa;
     wa.a = fvec; wa.lda = E; wa.dz = static_cast<const float*>(t->logits.p); wa.ldz = S; wa.out = G + t->off_w; wa.ldo = S;
     wa.rows = b; wa.k = E; wa.n = S;
-    count_launch(c, "train.gemm_wgrad");
+    tr_count(c, t, "train.gemm_wgrad");
     TR_CUDA(launch_rowsT_gemm(wa, s), "softmax wgrad launch");
     if (t->amsoftmax) amsoftmax_dw_kernel<<<(S + 31) / 32, 256, 0, s>>>(G + t->off_w, P + t->off_w, static_cast<const float*>(t->rnorm.p), E, S);
     else col_sum_small_kernel<<<(S + 255) / 256, 256, 0, s>>>(static_cast<const float*>(t->logits.p), b, S, G + t->off_b);
@@ -813,10 +870,10 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     SkinnyArgs sa;
     sa.a = static_cast<const float*>(t->gr.p); sa.lda = S; sa.w = P + t->off_w; sa.ldw = S; sa.out = dy; sa.ldo = E;
     sa.col_scale = nullptr; sa.bias = nullptr; sa.m = b; sa.n = E; sa.k = S; sa.ks = 0;
-    count_launch(c, "train.skinny_dgrad");
+    tr_count(c, t, "train.skinny_dgrad");
     TR_CUDA(launch_skinny_gemm<true>(sa, c->sm_count, s), "softmax dgrad launch");
     if (t->amsoftmax) {
-      count_launch(c, "train.axpy");
+      tr_count(c, t, "train.axpy");
       axpy_rows_kernel<<<ew_grid(c), 256, 0, s>>>(dy, fvec, static_cast<const float*>(t->coef.p), b, E);
       TR_CUDA(cudaGetLastError(), "axpy launch");
     }
@@ -835,7 +892,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     }
     int nrc = exchange_bucket(t, k);
     if (nrc != 0) return tr_fail_nccl(c, t, nrc, "ncclAllReduce");
-    count_launch(c, "train.allreduce");
+    tr_count(c, t, "train.allreduce");
     return XV_OK;
   };
 
@@ -859,13 +916,13 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
       ba.mean = mean; ba.rstd = rstd; ba.gamma = gamma; ba.beta = beta; ba.slope = slope_of(l);
       ba.g_gamma = l.has_bn ? G + l.off_gamma : nullptr; ba.g_beta = l.has_bn ? G + l.off_beta : nullptr;
       ba.g_alpha = l.off_alpha >= 0 ? G + l.off_alpha : nullptr; ba.g_bias = G + l.off_bias;
-      count_launch(c, "train.seg_bn_bwd");
+      tr_count(c, t, "train.seg_bn_bwd");
       seg_bn_bwd_kernel<<<(l.cout + 31) / 32, dim3(32, 8), 0, s>>>(ba);
       TR_CUDA(cudaGetLastError(), "segment BN backward launch");
       RowsTArgs wa;
       wa.a = i == t->n_frame ? static_cast<const float*>(t->pooled.p) : static_cast<const float*>(t->layers[i - 1].y.p);
       wa.lda = l.cin; wa.dz = dy; wa.ldz = l.cout; wa.out = G + l.off_kernel; wa.ldo = l.cout; wa.rows = b; wa.k = l.cin; wa.n = l.cout;
-      count_launch(c, "train.seg_wgrad");
+      tr_count(c, t, "train.seg_wgrad");
       if (head_side) {
         if ((rc = side_fork()) != XV_OK) return rc;
         TR_CUDA(launch_rowsT_gemm(wa, t->wg_stream), "segment wgrad launch");
@@ -878,7 +935,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
       SkinnyArgs sa;
       sa.a = dy; sa.lda = l.cout; sa.w = P + l.off_kernel; sa.ldw = l.cout; sa.out = dx; sa.ldo = l.cin;
       sa.col_scale = nullptr; sa.bias = nullptr; sa.m = b; sa.n = l.cin; sa.k = l.cout; sa.ks = 0;
-      count_launch(c, "train.skinny_dgrad");
+      tr_count(c, t, "train.skinny_dgrad");
       TR_CUDA(launch_skinny_gemm<true>(sa, c->sm_count, s), "segment-level dgrad launch");
       cur ^= 1;
       dy = dx;
@@ -895,9 +952,19 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     const bool from_pool = i == t->n_frame - 1;
     const PoolGrad& lpg = from_pool ? pg : no_pg;
     double* bs = t->bwd_sums(i);
-    count_launch(c, "train.bn_bwd");
-    TR_CUDA(launch_col_reduce4<1>(from_pool ? nullptr : dy, static_cast<const float*>(l.z.p), mask, r, l.cout, mean, rstd, gamma, beta,
-                                  slope_of(l), lpg, bs, t->sum_ld, c->sm_count, s), "BN backward reduce launch");
+    tr_count(c, t, "train.bn_bwd");
+    BsArgs sa = {};
+    sa.z = static_cast<const float*>(l.z.p); sa.dy = from_pool ? nullptr : dy; sa.rows = r; sa.c_total = l.cout; sa.mask = mask;
+    sa.mean = mean; sa.rstd = rstd; sa.gamma = gamma; sa.beta = beta; sa.slope = slope_of(l); sa.pg = lpg;
+    sa.sums_out = bs; sa.sums_ld = t->sum_ld; sa.n = n; sa.ldb = l.ldb;
+    dim3 sg, sb;
+    const bool staged = t->bulk_rows && bs_plan(&sa, c->sm_count, &sg, &sb);
+    if (staged) {
+      TR_CUDA(bs_launch<kBsReduce>(sa, sg, sb, s), "BN backward reduce launch");
+    } else {
+      TR_CUDA(launch_col_reduce4<1>(from_pool ? nullptr : dy, static_cast<const float*>(l.z.p), mask, r, l.cout, mean, rstd, gamma, beta,
+                                    slope_of(l), lpg, bs, t->sum_ld, c->sm_count, s), "BN backward reduce launch");
+    }
     BnBwdArgs ba;
     ba.dy = from_pool ? nullptr : dy; ba.z = static_cast<const float*>(l.z.p); ba.rows = r; ba.c_total = l.cout; ba.mask = mask;
     ba.mean = mean; ba.rstd = rstd; ba.gamma = gamma; ba.beta = beta; ba.slope = slope_of(l);
@@ -914,7 +981,11 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
       dz32 = from_pool ? static_cast<float*>(t->dbuf[cur ^ 1].p) : dy;      // in place unless the gradient was virtual
       ba.dz32 = dz32; ba.dzb = nullptr;
     }
-    {
+    if (staged) {
+      sa.dz32 = ba.dz32; sa.dzb = ba.dzb;
+      sa.g_gamma = ba.g_gamma; sa.g_beta = ba.g_beta; sa.g_alpha = ba.g_alpha;
+      TR_CUDA(bs_launch<kBsApply>(sa, sg, sb, s), "BN backward apply launch");
+    } else {
       const RowGrid rg = row_grid(l.cout / 4, c->sm_count);
       bn_bwd_apply_kernel<<<rg.grid, rg.block, 0, s>>>(ba);
       TR_CUDA(cudaGetLastError(), "BN backward apply launch");
@@ -941,7 +1012,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
       }
       const void* a_bf16 = i == 0 ? t->xb0.p : t->layers[i - 1].yb.p;
       cudaError_t ce;
-      count_launch(c, "train.tc_wgrad");
+      tr_count(c, t, "train.tc_wgrad");
       const char* we = launch_wgrad(a_bf16, rows, l.a_cin, dzb_l, l.ldb, rows, i == 0 ? 1 : l.taps, i == 0 ? l.taps * l.cin : l.cin,
                                     l.cout, G + l.off_kernel, l.cout, c->sm_count, ws, &ce);
       if (we) return fail(c, XV_ECUDA, "%s", we);
@@ -956,14 +1027,14 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
       TrGemmArgs wa;
       wa.a = a_in; wa.lda = i == 0 ? c->dim : l.cin; wa.dz = dy; wa.w = nullptr; wa.out = G + l.off_kernel; wa.rows = r; wa.cin = l.cin;
       wa.nz = l.cout; wa.taps = l.taps;
-      count_launch(c, "train.gemm_wgrad");
+      tr_count(c, t, "train.gemm_wgrad");
       TR_CUDA(launch_tr_gemm<kWgrad>(wa, s), "wgrad launch");
       if (i > 0) {
         float* dx = static_cast<float*>(t->dbuf[cur ^ 1].p);
         TrGemmArgs da;
         da.a = nullptr; da.lda = 0; da.dz = dy; da.w = P + l.off_kernel; da.out = dx; da.rows = r; da.cin = l.cin; da.nz = l.cout;
         da.taps = l.taps;
-        count_launch(c, "train.gemm_dgrad");
+        tr_count(c, t, "train.gemm_dgrad");
         TR_CUDA(launch_tr_gemm<kDgrad>(da, s), "dgrad launch");
         cur ^= 1;
         dy = dx;
@@ -985,7 +1056,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     // ONE collective: gradients of every variable + rank 0's moving statistics + the tower loss
     const int nrc = t->nccl.AllReduce(G, G, static_cast<size_t>(t->n_total + 1), /*ncclFloat32*/ 7, /*ncclSum*/ 0, t->comm, s);
     if (nrc != 0) return tr_fail_nccl(c, t, nrc, "ncclAllReduce");
-    count_launch(c, "train.allreduce");
+    tr_count(c, t, "train.allreduce");
   }
   const double* sqn = nullptr;
   const int n_chunks = static_cast<int>(t->chunks.size());
@@ -995,7 +1066,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     // clipping acts on the AVERAGED gradient (model/trainer.py:1244-1246), per variable
     double* d_sqn = static_cast<double*>(t->sqnorms.p);
     TR_CUDA(cudaMemsetAsync(d_sqn, 0, sizeof(double) * t->segs.size(), s), "memset norms");
-    count_launch(c, "train.grad_norms");
+    tr_count(c, t, "train.grad_norms");
     grad_sqnorm_kernel<<<n_chunks, 256, 0, s>>>(P, G, gsum_bf16, static_cast<const ParamSeg*>(t->d_segs.p),
                                                 static_cast<const UpdChunk*>(t->d_chunks.p), 1.f / t->world, d_sqn);
     TR_CUDA(cudaGetLastError(), "gradient norm launch");
@@ -1007,12 +1078,13 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     lr_eff = static_cast<float>(lr * std::sqrt(1.0 - std::pow(0.999, static_cast<double>(t->adam_t))) /
                                 (1.0 - std::pow(0.9, static_cast<double>(t->adam_t))));
   }
-  count_launch(c, "train.update");
+  tr_count(c, t, "train.update");
   apply_update_kernel<<<n_chunks, 256, 0, s>>>(P, G, gsum_bf16, static_cast<float*>(t->accum.p), static_cast<const ParamSeg*>(t->d_segs.p),
                                                static_cast<const UpdChunk*>(t->d_chunks.p), t->n_total, 1.f / t->world, lr_eff,
                                                t->optimizer, t->opt_momentum, t->nesterov, sqn, t->clip_norm, scalars + 1);
   TR_CUDA(cudaGetLastError(), "update launch");
   if ((rc = launch_recast(c, t)) != XV_OK) return rc;      // bf16 operand copies of the NEW weights, for the next step
+  if (t->marking) tr_timeline_report(c, t);
   if (loss_out) {
     float loss_sum = 0.f;
     double sc[2] = {0, 0};

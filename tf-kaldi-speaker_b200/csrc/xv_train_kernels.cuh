@@ -205,6 +205,23 @@ struct RowMask {
   }
 };
 
+// A strided row walk (r, r + step, ...) that knows its utterance and its position inside it without dividing per row (the
+// division -- 64-bit for the utterance index -- was a quarter of the row-streaming kernels' instructions; ncu source view r02t).
+struct RowWalk {
+  uint32_t t, valid_len, rem;
+  int32_t ut;
+  __device__ __forceinline__ RowWalk(const RowMask& m, int64_t first) {
+    t = static_cast<uint32_t>(m.t); valid_len = static_cast<uint32_t>(m.valid_len);
+    const uint32_t f = static_cast<uint32_t>(first);
+    rem = f % t; ut = static_cast<int32_t>(f / t);
+  }
+  __device__ __forceinline__ bool ok() const { return rem < valid_len; }
+  __device__ __forceinline__ void advance(uint32_t step) {
+    rem += step;
+    while (rem >= t) { rem -= t; ++ut; }
+  }
+};
+
 // Batch statistics of one layer as fp64 column sums: sums[c] = sum z, sums[ld + c] = sum z^2 over n rows.
 struct BnStat {
   const double* sums;     // null: the layer has no batch norm
@@ -292,14 +309,14 @@ __device__ __forceinline__ void pool_coef_load(const PoolGrad& pg, int64_t u, in
 // KIND 1 (backward through activation + batch norm): g = dy * act'(pre); v0 = sum g, v1 = sum g*xhat, v2 = sum dy*pre [pre<0].
 // `out` ([NV][out_ld]) must be zero on entry.
 template <int KIND>
-__global__ void __launch_bounds__(256) col_reduce4_kernel(const float* __restrict__ dy, const float* __restrict__ z,
+__global__ void __launch_bounds__(256, 2) col_reduce4_kernel(const float* __restrict__ dy, const float* __restrict__ z,
                                                           const RowMask mask, int64_t rows, int c_total, int64_t rows_per_block,
                                                           const float* __restrict__ mean, const float* __restrict__ rstd,
                                                           const float* __restrict__ gamma, const float* __restrict__ beta,
                                                           const float* __restrict__ slope, const PoolGrad pg,
                                                           double* __restrict__ out, int out_ld) {
   constexpr int NV = KIND == 0 ? 2 : 3;
-  constexpr int U = 4;                                 // rows in flight per thread: loads first, math after
+  constexpr int U = 4;                                 // rows in flight per thread: loads first, math after (2 rows and 3 thinner blocks per SM: 7 % slower step, r02x)
   __shared__ double red[NV][8][129];
   const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
   const int c0 = (blockIdx.x * 32 + cx) * 4;
@@ -325,14 +342,18 @@ __global__ void __launch_bounds__(256) col_reduce4_kernel(const float* __restric
 #pragma unroll
     for (int j = 0; j < 4; ++j) { pc.mu[j] = 0.f; pc.ca[j] = 0.f; pc.cb[j] = 0.f; }
     const bool read_dy = KIND == 1 && !pg.enabled;
+    RowWalk walk(mask, r0 + ry);
     for (int64_t rb = r0 + ry; rb < r1; rb += 8 * U) {
       float zz[U][4], dd[U][4];
       bool ok[U];
+      int32_t uts[U];
       // invalid rows hold finite values (zeros / products of real data): loading them unconditionally keeps U loads in flight
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int64_t r = rb + 8 * u;
-        ok[u] = r < r1 && mask.ok(r);
+        ok[u] = r < r1 && walk.ok();
+        uts[u] = walk.ut;
+        walk.advance(8);
         if (r < r1) {
           VecF<4>::load(z + r * c_total + c0, zz[u]);
           if (read_dy) VecF<4>::load(dy + r * c_total + c0, dd[u]);
@@ -351,7 +372,7 @@ __global__ void __launch_bounds__(256) col_reduce4_kernel(const float* __restric
           }
         } else {
           if (pg.enabled) {
-            const int64_t ut = (rb + 8 * u) / mask.t;
+            const int64_t ut = uts[u];
             if (ut != cur_u) {                        // per-utterance pooling coefficients: reloaded when the row walk enters a new utterance
               cur_u = ut;
               pool_coef_load(pg, ut, c_total, c0, &pc);
@@ -416,7 +437,7 @@ struct BnFwdArgs {
   const float* gamma; const float* beta; const float* slope;
   float* y; __nv_bfloat16* yb; int32_t ldb;
 };
-__global__ void __launch_bounds__(256) bn_act_fwd_kernel(const BnFwdArgs a) {
+__global__ void __launch_bounds__(256, 2) bn_act_fwd_kernel(const BnFwdArgs a) {
   constexpr int U = 4;
   const int nq = a.c_total / 4;
   // block b owns the rows [b*rpb, (b+1)*rpb): few blocks (2 per SM), many rows per thread -- the per-channel set-up (fp64
@@ -437,6 +458,7 @@ __global__ void __launch_bounds__(256) bn_act_fwd_kernel(const BnFwdArgs a) {
       }
       sl[k] = a.slope[c0 + k];
     }
+    RowWalk walk(a.mask, r0 + threadIdx.y);
     for (int64_t rb = r0 + threadIdx.y; rb < r1; rb += static_cast<int64_t>(blockDim.y) * U) {
       float v[U][4];
 #pragma unroll
@@ -447,8 +469,9 @@ __global__ void __launch_bounds__(256) bn_act_fwd_kernel(const BnFwdArgs a) {
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int64_t r = rb + static_cast<int64_t>(u) * blockDim.y;
+        const bool ok = walk.ok();
+        walk.advance(blockDim.y);
         if (r >= r1) continue;
-        const bool ok = a.mask.ok(r);
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           float t = v[u][k];
@@ -552,7 +575,7 @@ struct BnBwdArgs {
   float* dz32; __nv_bfloat16* dzb; int32_t ldb;
   float* g_gamma; float* g_beta; float* g_alpha;     // may be null
 };
-__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnBwdArgs a) {
+__global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(const BnBwdArgs a) {
   constexpr int U = 4;
   const int nq = a.c_total / 4;
   const int64_t rpb = (a.rows + gridDim.x - 1) / gridDim.x;        // contiguous row range per block (see bn_act_fwd_kernel)
@@ -585,6 +608,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnBwdArgs a) {
     float k1f[4], k2f[4], grf[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) { k1f[k] = static_cast<float>(k1[k]); k2f[k] = static_cast<float>(k2[k]); grf[k] = static_cast<float>(gr[k]); }
+    RowWalk walk(a.mask, r0 + threadIdx.y);
     for (int64_t rb = r0 + threadIdx.y; rb < r1; rb += static_cast<int64_t>(blockDim.y) * U) {
       float zz[U][4], d[U][4];
 #pragma unroll
@@ -598,11 +622,13 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const BnBwdArgs a) {
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const int64_t r = rb + static_cast<int64_t>(u) * blockDim.y;
+        const bool row_ok = walk.ok();
+        const int64_t ut = walk.ut;
+        walk.advance(blockDim.y);
         if (r >= r1) continue;
         float out[4] = {0.f, 0.f, 0.f, 0.f};
-        if (a.mask.ok(r)) {
+        if (row_ok) {
           if (a.pg.enabled) {
-            const int64_t ut = r / a.mask.t;
             if (ut != cur_u) {
               cur_u = ut;
               pool_coef_load(a.pg, ut, a.c_total, c0, &pc);
@@ -1160,25 +1186,44 @@ __global__ void __launch_bounds__(256) skinny_gemm_kernel(const SkinnyArgs g) {
     }
     __syncthreads();
   }
+  // split-K partial sums meet in global memory: one vector reduction per row and thread where the layout allows it (four
+  // adjacent columns = 16 bytes, two when only the row pitch is even) instead of four scalar atomics
+  const int nq = n0 + tx * 4;
+  float cs[4] = {1.f, 1.f, 1.f, 1.f}, bi[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    if (nq + j < g.n) {
+      if (g.col_scale != nullptr) cs[j] = g.col_scale[nq + j];
+      if (g.bias != nullptr && blockIdx.y == 0) bi[j] = g.bias[nq + j];
+    }
+  const bool base_ok = (reinterpret_cast<uintptr_t>(g.out) & 15) == 0;
+  const bool vec4 = base_ok && (g.ldo & 3) == 0 && nq + 3 < g.n;
+  const bool vec2 = base_ok && (g.ldo & 1) == 0 && nq + 3 < g.n;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int m = m0 + ty + 16 * i;
     if (m >= g.m) continue;
+    float v[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int n = n0 + tx * 4 + j;
-      if (n >= g.n) continue;
-      float v = acc[i][j];
-      if (g.col_scale != nullptr) v *= g.col_scale[n];
-      if (g.bias != nullptr && blockIdx.y == 0) v += g.bias[n];
-      atomicAdd(g.out + static_cast<int64_t>(m) * g.ldo + n, v);
+    for (int j = 0; j < 4; ++j) v[j] = fmaf(acc[i][j], cs[j], bi[j]);
+    float* dst = g.out + static_cast<int64_t>(m) * g.ldo + nq;
+    if (vec4) {
+      asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]) : "memory");
+    } else if (vec2) {
+      asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(dst), "f"(v[0]), "f"(v[1]) : "memory");
+      asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(dst + 2), "f"(v[2]), "f"(v[3]) : "memory");
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (nq + j < g.n) atomicAdd(dst + j, v[j]);
     }
   }
 }
 
 template <bool TB>
 cudaError_t launch_skinny_gemm(SkinnyArgs g, int sm_count, cudaStream_t s) {
-  cudaError_t e = cudaMemset2DAsync(g.out, sizeof(float) * g.ldo, 0, sizeof(float) * g.n, g.m, s);
+  cudaError_t e = g.ldo == g.n ? cudaMemsetAsync(g.out, 0, sizeof(float) * g.n * g.m, s)
+                              : cudaMemset2DAsync(g.out, sizeof(float) * g.ldo, 0, sizeof(float) * g.n, g.m, s);
   if (e != cudaSuccess) return e;
   const int nb = (g.n + 63) / 64, mb = (g.m + 63) / 64, kb = (g.k + 63) / 64;
   // one 64-wide K step per block when the row count is a single tile (every product of the training step): one memory round
