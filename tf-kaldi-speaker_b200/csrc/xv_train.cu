@@ -92,7 +92,10 @@ struct TrainState {
   bool mixed = false;                    // context precision bf16: frame-layer GEMMs on tcgen05, everything else fp32
   bool fused_stats = true;               // batch statistics from the forward GEMM's epilogue (XV_TRAIN_FUSED_STATS=0: separate pass)
   DevBuf xb0, dzb, ones_pad, zeros_pad;
-  RecastJobs recast;
+  RecastJobs recast;                     // forward operand layouts of the frame layers
+  RecastJobs recast_d;                   // data-gradient layouts ([Cin][taps*Cout]): first needed by the NEXT step's backward pass
+  int chunk_split = 0;                   // first update chunk of the early bucket (segment layers, loss head, tail)
+  bool early_update = true;              // XV_TRAIN_EARLY_UPDATE=0: one update launch at the end of the step
   // data parallel
   NcclApi nccl;
   void* comm = nullptr;
@@ -256,11 +259,11 @@ void tr_timeline_report(xv_ctx* c, TrainState* t) {
   t->marks.clear();
 }
 
-int launch_recast(xv_ctx* c, TrainState* t) {
-  if (!t->mixed || t->recast.n == 0) return XV_OK;
+int launch_recast(xv_ctx* c, TrainState* t, const RecastJobs& jobs, cudaStream_t stream) {
+  if (!t->mixed || jobs.n == 0) return XV_OK;
   tr_count(c, t, "train.cast_w");
-  const int grid = std::min(t->recast.total_tiles, c->sm_count * 16);
-  recast_weights_kernel<<<grid, 256, 0, c->stream>>>(t->recast);
+  const int grid = std::min(jobs.total_tiles, c->sm_count * 16);
+  recast_weights_kernel<<<grid, 256, 0, stream>>>(jobs);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return cuda_fail(c, e, "weight recast launch");
   return XV_OK;
@@ -279,6 +282,7 @@ static int train_init(xv_ctx* c, int32_t num_speakers) {
   t->overlap = !(getenv("XV_TRAIN_OVERLAP") && atoi(getenv("XV_TRAIN_OVERLAP")) == 0);
   t->wg_overlap = !(getenv("XV_TRAIN_WGRAD_STREAM") && atoi(getenv("XV_TRAIN_WGRAD_STREAM")) == 0);
   if (getenv("XV_TRAIN_TIMELINE")) t->timeline_step = atoll(getenv("XV_TRAIN_TIMELINE"));
+  t->early_update = !(getenv("XV_TRAIN_EARLY_UPDATE") && atoi(getenv("XV_TRAIN_EARLY_UPDATE")) == 0);
   t->bulk_rows = getenv("XV_TRAIN_BULK") && atoi(getenv("XV_TRAIN_BULK")) == 1;     // measured no faster than the per-thread-load kernels (r02w): opt-in
   t->wg_overlap_head = !(getenv("XV_TRAIN_WGRAD_STREAM") && atoi(getenv("XV_TRAIN_WGRAD_STREAM")) == 1);   // 1: frame layers only
   {
@@ -401,6 +405,14 @@ static int train_init(xv_ctx* c, int32_t num_speakers) {
     t->bucket_lo[0] = seg0; t->bucket_hi[0] = t->n_total + 1;
     t->bucket_lo[1] = mid;  t->bucket_hi[1] = seg0;
     t->bucket_lo[2] = 0;    t->bucket_hi[2] = mid;
+    // the update of bucket 0 (segment layers, loss head, moving statistics) can run as soon as its gradients are final:
+    // chunks [chunk_split, end) -- valid only if the chunk table is ordered the way the flat buffer is
+    const int n_chunks = static_cast<int>(t->chunks.size());
+    t->chunk_split = n_chunks;
+    for (int i = 0; i < n_chunks; ++i)
+      if (t->chunks[i].off >= seg0) { t->chunk_split = i; break; }
+    for (int i = t->chunk_split; i < n_chunks; ++i)
+      if (t->chunks[i].off < seg0) t->early_update = false;
   }
   int maxc = 4;
   for (const TrLayer& l : t->layers) maxc = std::max(maxc, l.cout);
@@ -418,19 +430,22 @@ static int train_init(xv_ctx* c, int32_t num_speakers) {
   }
   t->recast.n = 0;
   t->recast.total_tiles = 0;
+  t->recast_d.n = 0;
+  t->recast_d.total_tiles = 0;
   if (t->mixed) {
     const char* we = wgrad_init();
     if (we) return fail(c, XV_ECUDA, "%s", we);
     int max_alloc = 256;
     int prev_ldb = 0;
     auto add_job = [&](RecastJob j, int fast, int64_t slow) {
+      RecastJobs& set = j.kind == 0 ? t->recast : t->recast_d;
       const int tile_fast = j.kind == 0 ? 64 : 32;        // forward layout: 64 (k) x 32 (n) tiles, bf16 pairs along k
       j.tiles_x = (fast + tile_fast - 1) / tile_fast;
-      j.tile0 = t->recast.total_tiles;
-      t->recast.total_tiles += j.tiles_x * static_cast<int32_t>((slow + 31) / 32);
-      t->recast.j[t->recast.n++] = j;
+      j.tile0 = set.total_tiles;
+      set.total_tiles += j.tiles_x * static_cast<int32_t>((slow + 31) / 32);
+      set.j[set.n++] = j;
     };
-    if (2 * t->n_frame > kMaxRecastJobs) return fail(c, XV_EUNSUPPORTED, "too many frame layers for the recast table");
+    if (t->n_frame > kMaxRecastJobs) return fail(c, XV_EUNSUPPORTED, "too many frame layers for the recast table");
     for (int i = 0; i < t->n_frame; ++i) {
       TrLayer& l = t->layers[i];
       if (i == 0) { l.a_taps = 1; l.a_cin = (l.taps * l.cin + kBK - 1) / kBK * kBK; }
@@ -463,7 +478,8 @@ static int train_init(xv_ctx* c, int32_t num_speakers) {
     if ((rc = ensure(c, &t->zeros_pad, sizeof(float) * max_alloc)) != XV_OK) return rc;
     fill_f32_kernel<<<64, 256, 0, c->stream>>>(static_cast<float*>(t->ones_pad.p), max_alloc, 1.f);
     cudaMemsetAsync(t->zeros_pad.p, 0, sizeof(float) * max_alloc, c->stream);
-    if ((rc = launch_recast(c, t)) != XV_OK) return rc;
+    if ((rc = launch_recast(c, t, t->recast, c->stream)) != XV_OK) return rc;
+    if ((rc = launch_recast(c, t, t->recast_d, c->stream)) != XV_OK) return rc;
   }
   cudaError_t e = cudaStreamSynchronize(c->stream);
   if (e != cudaSuccess) return cuda_fail(c, e, "xv_train_init");
@@ -655,6 +671,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
   TR_CUDA(cudaMemsetAsync(t->sum_area.p, 0, sizeof(double) * t->sum_area_doubles(), s), "memset sums");
   // gradient buffer: the frame-layer range is accumulated into (tensor-core wgrad = split-K reductions; biases in front
   // of a batch norm keep their exact zero); the tail carries rank 0's moving statistics + the loss slot
+  if (t->clip_norm > 0.f) TR_CUDA(cudaMemsetAsync(t->sqnorms.p, 0, sizeof(double) * t->segs.size(), s), "memset norms");
   // (bf16 path: only the side-stream weight-gradient GEMMs need these zeros, and the side stream clears them itself below)
   const bool side0 = t->mixed && t->wg_overlap && t->wg_stream != nullptr;
   if (!side0) TR_CUDA(cudaMemsetAsync(G, 0, sizeof(float) * t->layers[t->n_frame].off_kernel, s), "memset frame gradients");
@@ -882,6 +899,42 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
   // ------------------------------------------------------------------ exchange plumbing
   const bool dp = t->world > 1;
   const bool overlap = dp && t->overlap;
+  // ---- update of a chunk range on a stream (clipping norms + optimizer), see the end of the step
+  const int n_chunks = static_cast<int>(t->chunks.size());
+  // bf16 exchange: the summed gradients of the trainable range come back in the bf16 travel buffer
+  const __nv_bfloat16* gsum_bf16 = (dp && overlap && t->comm_bf16) ? static_cast<const __nv_bfloat16*>(t->gcomm.p) : nullptr;
+  float lr_eff = lr;
+  if (t->optimizer == 2) {
+    ++t->adam_t;
+    lr_eff = static_cast<float>(lr * std::sqrt(1.0 - std::pow(0.999, static_cast<double>(t->adam_t))) /
+                                (1.0 - std::pow(0.9, static_cast<double>(t->adam_t))));
+  }
+  auto launch_update = [&](int c_lo, int c_hi, cudaStream_t us) -> int {
+    const int nc = c_hi - c_lo;
+    if (nc <= 0) return XV_OK;
+    const UpdChunk* chunks = static_cast<const UpdChunk*>(t->d_chunks.p) + c_lo;
+    const double* sqn = nullptr;
+    if (t->clip_norm > 0.f) {
+      // clipping acts on the AVERAGED gradient (model/trainer.py:1244-1246), per variable; the norms were zeroed at the step start
+      double* d_sqn = static_cast<double*>(t->sqnorms.p);
+      tr_count(c, t, "train.grad_norms");
+      grad_sqnorm_kernel<<<nc, 256, 0, us>>>(P, G, gsum_bf16, static_cast<const ParamSeg*>(t->d_segs.p), chunks, 1.f / t->world, d_sqn);
+      TR_CUDA(cudaGetLastError(), "gradient norm launch");
+      sqn = d_sqn;
+    }
+    tr_count(c, t, "train.update");
+    apply_update_kernel<<<nc, 256, 0, us>>>(P, G, gsum_bf16, static_cast<float*>(t->accum.p), static_cast<const ParamSeg*>(t->d_segs.p),
+                                            chunks, t->n_total, 1.f / t->world, lr_eff, t->optimizer, t->opt_momentum, t->nesterov,
+                                            sqn, t->clip_norm, scalars + 1);
+    TR_CUDA(cudaGetLastError(), "update launch");
+    return XV_OK;
+  };
+  // Bucket 0 (segment layers, loss head, moving statistics: half of the parameters) is updated while the frame layers are still
+  // in their backward pass -- nothing there reads those variables.  Data parallel: on the communication stream behind the
+  // bucket's all-reduce; one GPU: on the side stream behind the weight gradients it holds.
+  const bool early_dp = t->early_update && overlap && t->chunk_split < n_chunks;
+  const bool early_side = t->early_update && !dp && wg_side && head_side && t->chunk_split < n_chunks;
+  const int late_hi = (early_dp || early_side) ? t->chunk_split : n_chunks;
   auto bucket_ready = [&](int k) -> int {       // every gradient of bucket k has been written on the main stream
     if (!overlap || t->bucket_hi[k] <= t->bucket_lo[k]) return XV_OK;
     TR_CUDA(cudaEventRecord(t->ev_ready[k], s), "cudaEventRecord");
@@ -893,6 +946,7 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     int nrc = exchange_bucket(t, k);
     if (nrc != 0) return tr_fail_nccl(c, t, nrc, "ncclAllReduce");
     tr_count(c, t, "train.allreduce");
+    if (k == 0 && early_dp) return launch_update(t->chunk_split, n_chunks, t->comm_stream);
     return XV_OK;
   };
 
@@ -945,6 +999,10 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
         pg.pooled = static_cast<const float*>(t->pooled.p); pg.dpooled = dy;
         pg.inv_l = 1.f / static_cast<float>(tt - pl.context); pg.enabled = 1;
         if ((rc = bucket_ready(0)) != XV_OK) return rc;
+        if (early_side) {
+          if ((rc = side_fork()) != XV_OK) return rc;
+          if ((rc = launch_update(t->chunk_split, n_chunks, t->wg_stream)) != XV_OK) return rc;
+        }
       }
       continue;
     }
@@ -1058,32 +1116,17 @@ static int train_step_body(xv_ctx* c, TrainState* t, const float* feats, const i
     if (nrc != 0) return tr_fail_nccl(c, t, nrc, "ncclAllReduce");
     tr_count(c, t, "train.allreduce");
   }
-  const double* sqn = nullptr;
-  const int n_chunks = static_cast<int>(t->chunks.size());
-  // bf16 exchange: the summed gradients of the trainable range come back in the bf16 travel buffer
-  const __nv_bfloat16* gsum_bf16 = (dp && overlap && t->comm_bf16) ? static_cast<const __nv_bfloat16*>(t->gcomm.p) : nullptr;
-  if (t->clip_norm > 0.f) {
-    // clipping acts on the AVERAGED gradient (model/trainer.py:1244-1246), per variable
-    double* d_sqn = static_cast<double*>(t->sqnorms.p);
-    TR_CUDA(cudaMemsetAsync(d_sqn, 0, sizeof(double) * t->segs.size(), s), "memset norms");
-    tr_count(c, t, "train.grad_norms");
-    grad_sqnorm_kernel<<<n_chunks, 256, 0, s>>>(P, G, gsum_bf16, static_cast<const ParamSeg*>(t->d_segs.p),
-                                                static_cast<const UpdChunk*>(t->d_chunks.p), 1.f / t->world, d_sqn);
-    TR_CUDA(cudaGetLastError(), "gradient norm launch");
-    sqn = d_sqn;
+  if ((rc = launch_update(0, late_hi, s)) != XV_OK) return rc;
+  // bf16 operand copies of the NEW weights for the next step: the forward layouts now, the data-gradient layouts (first read by
+  // the next step's backward pass) on the side stream when there is one -- the main stream meets it again before that step's loss
+  if ((rc = launch_recast(c, t, t->recast, s)) != XV_OK) return rc;
+  if (side0) {
+    TR_CUDA(cudaEventRecord(t->ev_fork, s), "cudaEventRecord");
+    TR_CUDA(cudaStreamWaitEvent(t->wg_stream, t->ev_fork, 0), "cudaStreamWaitEvent");
+    if ((rc = launch_recast(c, t, t->recast_d, t->wg_stream)) != XV_OK) return rc;
+  } else {
+    if ((rc = launch_recast(c, t, t->recast_d, s)) != XV_OK) return rc;
   }
-  float lr_eff = lr;
-  if (t->optimizer == 2) {
-    ++t->adam_t;
-    lr_eff = static_cast<float>(lr * std::sqrt(1.0 - std::pow(0.999, static_cast<double>(t->adam_t))) /
-                                (1.0 - std::pow(0.9, static_cast<double>(t->adam_t))));
-  }
-  tr_count(c, t, "train.update");
-  apply_update_kernel<<<n_chunks, 256, 0, s>>>(P, G, gsum_bf16, static_cast<float*>(t->accum.p), static_cast<const ParamSeg*>(t->d_segs.p),
-                                               static_cast<const UpdChunk*>(t->d_chunks.p), t->n_total, 1.f / t->world, lr_eff,
-                                               t->optimizer, t->opt_momentum, t->nesterov, sqn, t->clip_norm, scalars + 1);
-  TR_CUDA(cudaGetLastError(), "update launch");
-  if ((rc = launch_recast(c, t)) != XV_OK) return rc;      // bf16 operand copies of the NEW weights, for the next step
   if (t->marking) tr_timeline_report(c, t);
   if (loss_out) {
     float loss_sum = 0.f;
