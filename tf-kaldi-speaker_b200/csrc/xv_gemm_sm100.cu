@@ -118,7 +118,9 @@ __device__ __forceinline__ void pool_reduce_atomics(float (&v)[16], uint32_t lan
 // stages instead of four), the leader (cluster rank 0) issues every MMA, commits multicast to both CTAs' barriers, both
 // epilogues read their own TMEM and hand the accumulator back on the LEADER's barrier.  Halves the shared-memory operand
 // reads and the L2 -> SM weight traffic per flop, which is what the power-capped tensor pipe is short of.
-template <bool kPool, bool k2Sm>
+// kWPool: the pooled epilogue with softmax row weights (attention pooling).  A separate instantiation, so that the code of the
+// weighted sums does not enter the register allocation of the unweighted kernel (the headline path's tdnn5) and vice versa.
+template <bool kPool, bool k2Sm, bool kWPool = false>
 __global__ void __launch_bounds__(EpiCfg<kPool>::kThreads, 1)
 xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                     const __grid_constant__ CUtensorMap tm_out, const GemmParams p) {
@@ -412,13 +414,13 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
             w_last = s;
           }
         }
-        w_full = w_first == w_last && w_sg.r0 <= mw && w_sg.r1 >= mw + 32 && p.row_weight == nullptr;
+        w_full = w_first == w_last && w_sg.r0 <= mw && w_sg.r1 >= mw + 32 && !kWPool;
       }
       // attention pooling, common case (one utterance under this warp's 32 rows, heads at least a tile wide): the masked
       // softmax weights of the thread's four rows for the (at most two) heads of this tile, loaded once per tile
       float tw_a[4] = {0.f, 0.f, 0.f, 0.f}, tw_b[4] = {0.f, 0.f, 0.f, 0.f};
       int tile_bound = 0;
-      const bool tile_weights = kPool && p.row_weight != nullptr && w_first == w_last && p.head_width >= kBN;
+      const bool tile_weights = kPool && kWPool && w_first == w_last && p.head_width >= kBN;
       if (tile_weights) {
         const int ha = n0 / p.head_width;
         tile_bound = (ha + 1) * p.head_width - n0;
@@ -443,13 +445,15 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
         // atomics (order-independent at fp32 precision; no cancellation noise in E[x^2] - mean^2).
         const int rq = lane >> 2, cq = (lane & 3) * 2;
         const int c_end = min(8, static_cast<int>(half + 1) * kChunksPerWarp);
-        if (p.row_weight == nullptr) {
-          // ---- statistics pooling (unweighted).  The thread's 4 rows are added into register accumulators that live
+        {
+          // ---- statistics pooling (unweighted), and attention pooling when one utterance lies under the warp's rows.
+          // The thread's 4 rows are added into register accumulators that live
           // across tiles (same utterance, same columns); the butterfly and the atomics run once per utterance and warp
           // instead of once per tile.  All math on packed fp32 pairs.  A warp whose 32 rows straddle an utterance edge
           // makes one masked pass per utterance over the same accumulator tile (re-read from TMEM), flushing in between.
-          auto accumulate = [&](auto masked_c, int lo, int hi, bool release) {
+          auto accumulate = [&](auto masked_c, auto weighted_c, int lo, int hi, bool release) {
             constexpr bool kMasked = decltype(masked_c)::value;
+            constexpr bool kWeighted = decltype(weighted_c)::value;     // attention pooling: sum w*y and sum w*y^2
             uint64_t mk[4];
             if (kMasked) {
 #pragma unroll
@@ -484,6 +488,11 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
                   const ulonglong2 sh = *reinterpret_cast<const ulonglong2*>(ss + col + 8 * ii + cq);   // (s0,s1) | (h0,h1)
                   float2 ng = make_float2(0.f, 0.f);
                   if (!relu_only) ng = *reinterpret_cast<const float2*>(sl + col + 8 * ii + cq);
+                  // weighted: a tile touches at most two heads (head_width >= the tile width), the second one from
+                  // column tile_bound on; only the 16-column half chunk that holds the boundary selects per column
+                  const int rel = tile_bound - col;                  // warp-uniform
+                  const bool w_mixed = kWeighted && rel > 0 && rel < 16;
+                  const bool sec0 = 8 * ii + cq >= rel, sec1 = 8 * ii + cq + 1 >= rel;
 #pragma unroll
                   for (int k = 0; k < 4; ++k) {
                     const uint32_t* src = k < 2 ? r0[h & 1] : r1[h & 1];
@@ -499,14 +508,23 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
                       if (p.act_tanh) { v0 = tanhf(v0); v1 = tanhf(v1); }
                     }
                     v = ptx::f2_pack(v0, v1);
-                    if (kMasked) v = ptx::f2_mul(v, mk[k]);
-                    acc_s[ci][i] = ptx::f2_add(acc_s[ci][i], v);
-                    acc_q[ci][i] = ptx::f2_fma(v, v, acc_q[ci][i]);
+                    if (kWeighted) {
+                      const float wu = rel <= 0 ? tw_b[k] : tw_a[k];          // softmax weights: 0 outside the utterance's valid rows
+                      const uint64_t w = w_mixed ? ptx::f2_pack(sec0 ? tw_b[k] : tw_a[k], sec1 ? tw_b[k] : tw_a[k]) : ptx::f2_pack(wu, wu);
+                      const uint64_t t = ptx::f2_mul(v, w);
+                      acc_s[ci][i] = ptx::f2_add(acc_s[ci][i], t);
+                      acc_q[ci][i] = ptx::f2_fma(t, v, acc_q[ci][i]);
+                    } else {
+                      if (kMasked) v = ptx::f2_mul(v, mk[k]);
+                      acc_s[ci][i] = ptx::f2_add(acc_s[ci][i], v);
+                      acc_q[ci][i] = ptx::f2_fma(v, v, acc_q[ci][i]);
+                    }
                   }
                 }
               }
             }
           };
+          if (!kWPool || tile_weights) {
           bool released = false;
           for (int s = w_first; s <= w_last; ++s) {
             const PoolSeg sg = s == w_first ? w_sg : p.segs[s];
@@ -521,15 +539,16 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
             }
             ++held_tiles;
             released = s == w_last;
-            if (lo == 0 && hi == 32) accumulate(std::false_type{}, lo, hi, released);
-            else accumulate(std::true_type{}, lo, hi, released);
+            if (kWPool) accumulate(std::false_type{}, std::true_type{}, lo, hi, released);   // the weights carry the row mask
+            else if (lo == 0 && hi == 32) accumulate(std::false_type{}, std::false_type{}, lo, hi, released);
+            else accumulate(std::true_type{}, std::false_type{}, lo, hi, released);
           }
           if (!released) {                           // no valid row under this warp: just hand the accumulator back
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) release_acc(as);
           }
-        } else {
+          } else {
 #pragma unroll 1
         for (int c = half * kChunksPerWarp; c < c_end; ++c) {
           uint32_t ra[16], rb[16];
@@ -587,7 +606,7 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
                   for (int k = 0; k < 4; ++k) m[k] = tw_b[k];
                   bound = 32;
                 }
-              } else if (p.row_weight != nullptr) {
+              } else if (kWPool) {
                 const int nbase = n0 + c * 32;
                 const int ha = nbase / p.head_width;
                 bound = (ha + 1) * p.head_width - nbase;
@@ -617,6 +636,7 @@ xv_tdnn_gemm_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
             pool_reduce_atomics(v, lane, p.pool_acc + static_cast<size_t>(sg.utt) * 2 * p.pool_ld, p.pool_ld, n0 + c * 32);
           }
         }
+          }
         }
       } else if (!store_bf16 && p.out_f32 != nullptr && p.dot_out == nullptr) {
       // ---- fp32-only output (training forward / data gradient, segment layers): tcgen05.ld.16x256b gives each thread
@@ -873,6 +893,8 @@ const char* gemm_init() {
   if (e == cudaSuccess) e = cudaFuncSetAttribute(xv_tdnn_gemm_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(xv_tdnn_gemm_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(xv_tdnn_gemm_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(xv_tdnn_gemm_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(xv_tdnn_gemm_kernel<true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
   if (e != cudaSuccess) {
     snprintf(g_err, sizeof(g_err), "cudaFuncSetAttribute(max dynamic smem) failed: %s", cudaGetErrorString(e));
     return g_err;
@@ -943,6 +965,14 @@ int max_cluster_pairs() {
   return cached;
 }
 
+template <bool kPool, bool k2Sm>
+cudaError_t launch_kernel(const cudaLaunchConfig_t& cfg, const GemmPlan& plan, const GemmParams& p) {
+  if constexpr (kPool) {
+    if (p.row_weight != nullptr) return cudaLaunchKernelEx(&cfg, xv_tdnn_gemm_kernel<true, k2Sm, true>, plan.tm_a, plan.tm_b, plan.tm_out, p);
+  }
+  return cudaLaunchKernelEx(&cfg, xv_tdnn_gemm_kernel<kPool, k2Sm, false>, plan.tm_a, plan.tm_b, plan.tm_out, p);
+}
+
 template <bool kPool>
 cudaError_t launch_variant(const GemmPlan& plan, int sm_count, cudaStream_t stream) {
   GemmParams p = plan.p;
@@ -957,9 +987,10 @@ cudaError_t launch_variant(const GemmPlan& plan, int sm_count, cudaStream_t stre
   cudaLaunchAttribute attr;
   attr.id = cudaLaunchAttributeClusterDimension;
   attr.val.clusterDim.x = 2; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
-  // pooled layer with plain (unweighted) sums: column-stationary schedule, floor(clusters / n_tiles) clusters per
+  // pooled layer: column-stationary schedule, floor(clusters / n_tiles) clusters per
   // column tile (144 of 148 SMs at 6 column tiles; the register-resident sums save more than the four idle SMs cost)
-  const bool col_stat = kPool && want_cs && p.row_weight == nullptr;
+  // (attention pooling too since its sums live in registers across tiles; XV_POOL_COLSTAT=2 keeps it on the row-major schedule)
+  const bool col_stat = kPool && want_cs && (p.row_weight == nullptr || want_cs != 2);
   const int groups2 = (p.m_tiles + 1) / 2;         // pairs of row tiles
   // cta_group::2 pairs for every layer with at least two row tiles.  Measured on one box, pairs vs multicast pairs:
   // tdnn2 K=2560 1341 -> 1465, tdnn3 K=3584 1393 -> 1508, pooled tdnn5 K=512 1074 -> 1216, tdnn4 K=512 966 -> 1084,
@@ -979,7 +1010,7 @@ cudaError_t launch_variant(const GemmPlan& plan, int sm_count, cudaStream_t stre
       cfg.gridDim = dim3(2 * n, 1, 1);
       cfg.attrs = &attr;
       cfg.numAttrs = 1;
-      return cudaLaunchKernelEx(&cfg, xv_tdnn_gemm_kernel<kPool, true>, plan.tm_a, plan.tm_b, plan.tm_out, p);
+      return launch_kernel<kPool, true>(cfg, plan, p);
     }
   }
   if (col_stat && p.n_tiles <= sm_count) {
@@ -987,7 +1018,7 @@ cudaError_t launch_variant(const GemmPlan& plan, int sm_count, cudaStream_t stre
     if (cpn > p.m_tiles) cpn = p.m_tiles;
     p.col_stationary = 1;
     cfg.gridDim = dim3(cpn * p.n_tiles, 1, 1);
-    return cudaLaunchKernelEx(&cfg, xv_tdnn_gemm_kernel<kPool, false>, plan.tm_a, plan.tm_b, plan.tm_out, p);
+    return launch_kernel<kPool, false>(cfg, plan, p);
   }
   // multicast pairs (1-SM MMAs, weight tile halves multicast) when the pairs cover (nearly) the whole chip
   // (the pooled kernel gained nothing from them: 880 vs 890 TFLOP/s)
@@ -1006,7 +1037,7 @@ cudaError_t launch_variant(const GemmPlan& plan, int sm_count, cudaStream_t stre
     const int tiles = p.m_tiles * p.n_tiles;
     cfg.gridDim = dim3(tiles < sm_count ? tiles : sm_count, 1, 1);
   }
-  return cudaLaunchKernelEx(&cfg, xv_tdnn_gemm_kernel<kPool, false>, plan.tm_a, plan.tm_b, plan.tm_out, p);
+  return launch_kernel<kPool, false>(cfg, plan, p);
 }
 }  // namespace
 
