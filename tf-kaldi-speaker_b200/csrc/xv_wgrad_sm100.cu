@@ -219,9 +219,23 @@ const char* launch_wgrad(const void* a, int64_t a_rows, int lda, const void* dz,
   p.n_tiles = (n_valid + 255) / 256;
   const int mn = p.m_tiles * p.n_tiles;
   const int64_t kblocks = (rows + 63) / 64;
-  int64_t splits = (2 * static_cast<int64_t>(sm_count) + mn - 1) / mn;
-  if (splits > kblocks / 4) splits = kblocks / 4;
-  if (splits < 1) splits = 1;
+  // Split of the contraction (frame) axis: the persistent grid works through mn * splits units of kb k-blocks each in
+  // ceil(units / SMs) rounds, and every unit ends with a 128 x 256 fp32 reduction into `out` (~6 k-blocks' worth of time).
+  // Taking ~2 units per SM regardless of how they divide into rounds left the last round mostly empty (tdnn3 of the training
+  // step: 336 units = 3 rounds of 34 k-blocks where 280 units = 2 rounds of 40 do; tdnn5: 312 units = 3 rounds where 144 fit
+  // one): pick the split with the shortest schedule.
+  int64_t splits = 1;
+  {
+    const int64_t max_splits = kblocks / 4 > 1 ? kblocks / 4 : 1;       // at least 4 k-blocks per unit
+    int64_t best_cost = -1;
+    for (int64_t sp = 1; sp <= max_splits; ++sp) {
+      const int64_t kb = (kblocks + sp - 1) / sp;
+      const int64_t sp_eff = (kblocks + kb - 1) / kb;
+      const int64_t rounds = (mn * sp_eff + sm_count - 1) / sm_count;
+      const int64_t cost = rounds * (kb + 6);
+      if (best_cost < 0 || cost < best_cost) { best_cost = cost; splits = sp; }
+    }
+  }
   const int64_t kb_per_split = (kblocks + splits - 1) / splits;
   p.rows_per_split = kb_per_split * 64;
   p.splits = static_cast<int32_t>((kblocks + kb_per_split - 1) / kb_per_split);
