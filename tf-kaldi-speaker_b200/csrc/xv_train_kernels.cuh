@@ -256,6 +256,22 @@ __device__ __forceinline__ void bn_finalize_channel(const BnStat& b, const BnFin
   f.new_mv[c] = static_cast<float>(static_cast<double>(f.mov_var[c]) * f.momentum + vm * (1.0 - f.momentum));
 }
 
+// Per-channel constants of y = act(gamma * (z - mean) * rstd + beta), folded so that a row loop pays ONE FMA for the normalised
+// value and ONE (independent) FMA for the pre-activation: xhat = z * xa + xb, pre = z * pa + pb.  Every kernel of the step --
+// forward, pooled forward, backward reduce and apply -- uses this form, so they agree on the sign of `pre` bit for bit.
+// (Against the textbook order the rounding differs by ~6e-8 * |mean| * rstd: the row kernels are bound by dependent-instruction
+// latency, and this removes a third of their arithmetic.)  No batch norm: pre = z, xhat = 0.
+struct BnFold { float xa, xb, pa, pb; };
+__device__ __forceinline__ BnFold bn_fold(bool has_bn, float mu, float rs, float ga, float be) {
+  BnFold f;
+  if (!has_bn) { f.xa = 0.f; f.xb = 0.f; f.pa = 1.f; f.pb = 0.f; return f; }
+  f.xa = rs;
+  f.xb = -mu * rs;
+  f.pa = ga * rs;
+  f.pb = fmaf(ga, f.xb, be);
+  return f;
+}
+
 template <int Q> struct VecF;
 template <> struct VecF<4> {
   static __device__ __forceinline__ void load(const float* p, float* v) { const float4 t = *reinterpret_cast<const float4*>(p); v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w; }
@@ -328,13 +344,15 @@ __global__ void __launch_bounds__(256, 2) col_reduce4_kernel(const float* __rest
 #pragma unroll
     for (int j = 0; j < 4; ++j) v[k][j] = 0.0;
   if (c0 < c_total) {
-    float mu[4], rs[4], ga[4], be[4], sl[4];
+    float sl[4];
+    BnFold bf[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      mu[j] = 0.f; rs[j] = 1.f; ga[j] = 1.f; be[j] = 0.f; sl[j] = 0.f;
+      sl[j] = 0.f;
+      bf[j] = bn_fold(false, 0.f, 1.f, 1.f, 0.f);
       if (KIND == 1) {
         sl[j] = slope[c0 + j];
-        if (mean != nullptr) { mu[j] = mean[c0 + j]; rs[j] = rstd[c0 + j]; ga[j] = gamma[c0 + j]; be[j] = beta[c0 + j]; }
+        if (mean != nullptr) bf[j] = bn_fold(true, mean[c0 + j], rstd[c0 + j], gamma[c0 + j], beta[c0 + j]);
       }
     }
     int64_t cur_u = -1;
@@ -380,8 +398,7 @@ __global__ void __launch_bounds__(256, 2) col_reduce4_kernel(const float* __rest
           }
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            float xh = 0.f, pre = zz[u][j];
-            if (mean != nullptr) { xh = (zz[u][j] - mu[j]) * rs[j]; pre = fmaf(ga[j], xh, be[j]); }
+            const float xh = fmaf(zz[u][j], bf[j].xa, bf[j].xb), pre = fmaf(zz[u][j], bf[j].pa, bf[j].pb);
             float d = dd[u][j];
             if (pg.enabled) d = fmaf(pc.cb[j], (pre >= 0.f ? pre : pre * sl[j]) - pc.mu[j], pc.ca[j]);
             const float g = pre > 0.f ? d : d * sl[j];
@@ -446,15 +463,17 @@ __global__ void __launch_bounds__(256, 2) bn_act_fwd_kernel(const BnFwdArgs a) {
   const int64_t r0 = static_cast<int64_t>(blockIdx.x) * rpb, r1 = min(r0 + rpb, a.rows);
   for (int q = threadIdx.x; q < nq; q += blockDim.x) {
     const int c0 = q * 4;
-    float mu[4], rs[4], ga[4], be[4], sl[4];
+    float sl[4];
+    BnFold bf[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      mu[k] = 0.f; rs[k] = 1.f; ga[k] = 1.f; be[k] = 0.f;
+      bf[k] = bn_fold(false, 0.f, 1.f, 1.f, 0.f);
       if (a.st.sums != nullptr) {
         double var;
-        bn_mean_rstd(a.st, c0 + k, a.fin.eps, &mu[k], &rs[k], &var);
-        ga[k] = a.gamma[c0 + k]; be[k] = a.beta[c0 + k];
-        if (blockIdx.x == 0 && threadIdx.y == 0) bn_finalize_channel(a.st, a.fin, c0 + k, mu[k], rs[k], var);
+        float mu, rs;
+        bn_mean_rstd(a.st, c0 + k, a.fin.eps, &mu, &rs, &var);
+        bf[k] = bn_fold(true, mu, rs, a.gamma[c0 + k], a.beta[c0 + k]);
+        if (blockIdx.x == 0 && threadIdx.y == 0) bn_finalize_channel(a.st, a.fin, c0 + k, mu, rs, var);
       }
       sl[k] = a.slope[c0 + k];
     }
@@ -474,8 +493,7 @@ __global__ void __launch_bounds__(256, 2) bn_act_fwd_kernel(const BnFwdArgs a) {
         if (r >= r1) continue;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-          float t = v[u][k];
-          if (a.st.sums != nullptr) t = fmaf(ga[k], (t - mu[k]) * rs[k], be[k]);      // same expression in every backward kernel
+          const float t = fmaf(v[u][k], bf[k].pa, bf[k].pb);                          // same expression in every backward kernel
           v[u][k] = ok ? (t >= 0.f ? t : t * sl[k]) : 0.f;
         }
         if (a.y != nullptr) VecF<4>::store(a.y + r * a.c_total + c0, v[u]);
@@ -501,15 +519,17 @@ __global__ void __launch_bounds__(256) bn_act_pool_fwd_kernel(const BnFwdArgs a,
   double s1[4] = {0.0, 0.0, 0.0, 0.0}, s2[4] = {0.0, 0.0, 0.0, 0.0};
   float piv[4] = {0.f, 0.f, 0.f, 0.f};
   if (c0 < a.c_total) {
-    float mu[4], rs[4], ga[4], be[4], sl[4];
+    float sl[4];
+    BnFold bf[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      mu[k] = 0.f; rs[k] = 1.f; ga[k] = 1.f; be[k] = 0.f;
+      bf[k] = bn_fold(false, 0.f, 1.f, 1.f, 0.f);
       if (a.st.sums != nullptr) {
         double var;
-        bn_mean_rstd(a.st, c0 + k, a.fin.eps, &mu[k], &rs[k], &var);
-        ga[k] = a.gamma[c0 + k]; be[k] = a.beta[c0 + k];
-        if (u == 0 && ty == 0) bn_finalize_channel(a.st, a.fin, c0 + k, mu[k], rs[k], var);
+        float mu, rs;
+        bn_mean_rstd(a.st, c0 + k, a.fin.eps, &mu, &rs, &var);
+        bf[k] = bn_fold(true, mu, rs, a.gamma[c0 + k], a.beta[c0 + k]);
+        if (u == 0 && ty == 0) bn_finalize_channel(a.st, a.fin, c0 + k, mu, rs, var);
       }
       sl[k] = a.slope[c0 + k];
     }
@@ -517,8 +537,7 @@ __global__ void __launch_bounds__(256) bn_act_pool_fwd_kernel(const BnFwdArgs a,
       VecF<4>::load(a.z + r * a.c_total + c0, v);
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        float t = v[k];
-        if (a.st.sums != nullptr) t = fmaf(ga[k], (t - mu[k]) * rs[k], be[k]);
+        const float t = fmaf(v[k], bf[k].pa, bf[k].pb);
         v[k] = t >= 0.f ? t : t * sl[k];
       }
     };
@@ -534,8 +553,7 @@ __global__ void __launch_bounds__(256) bn_act_pool_fwd_kernel(const BnFwdArgs a,
         float p1[4], p2[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-          float t = v[u][k];
-          if (a.st.sums != nullptr) t = fmaf(ga[k], (t - mu[k]) * rs[k], be[k]);
+          float t = fmaf(v[u][k], bf[k].pa, bf[k].pb);
           t = t >= 0.f ? t : t * sl[k];
           const float d = t - piv[k];
           p1[k] = d; p2[k] = d * d;
@@ -583,16 +601,22 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(const BnBwdArgs a)
   const double inv_n = 1.0 / a.n;
   for (int q = threadIdx.x; q < nq; q += blockDim.x) {
     const int c0 = q * 4;
-    float mu[4], rs[4], ga[4], be[4], sl[4];
-    double k1[4], k2[4], gr[4];
+    float sl[4];
+    BnFold bf[4];
+    // dz = gr * (g - k1 - xhat * k2) = g * gr + (e0 + xhat * e1): the fp64 sums only enter through the three constants
+    float grf[4], e0[4], e1[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       sl[k] = a.slope[c0 + k];
-      mu[k] = 0.f; rs[k] = 1.f; ga[k] = 1.f; be[k] = 0.f; k1[k] = 0.0; k2[k] = 0.0; gr[k] = 1.0;
+      bf[k] = bn_fold(false, 0.f, 1.f, 1.f, 0.f);
+      grf[k] = 1.f; e0[k] = 0.f; e1[k] = 0.f;
       if (a.mean != nullptr) {
-        mu[k] = a.mean[c0 + k]; rs[k] = a.rstd[c0 + k]; ga[k] = a.gamma[c0 + k]; be[k] = a.beta[c0 + k];
-        k1[k] = a.sums[c0 + k] * inv_n; k2[k] = a.sums[a.sums_ld + c0 + k] * inv_n;
-        gr[k] = static_cast<double>(ga[k]) * rs[k];
+        const float ga = a.gamma[c0 + k], rs = a.rstd[c0 + k];
+        bf[k] = bn_fold(true, a.mean[c0 + k], rs, ga, a.beta[c0 + k]);
+        const double gr = static_cast<double>(ga) * rs;
+        grf[k] = static_cast<float>(gr);
+        e0[k] = static_cast<float>(-gr * (a.sums[c0 + k] * inv_n));
+        e1[k] = static_cast<float>(-gr * (a.sums[a.sums_ld + c0 + k] * inv_n));
       }
       if (blockIdx.x == 0 && threadIdx.y == 0) {
         if (a.g_beta != nullptr) a.g_beta[c0 + k] = static_cast<float>(a.sums[c0 + k]);
@@ -604,10 +628,6 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(const BnBwdArgs a)
     PoolCoef pc;
 #pragma unroll
     for (int k = 0; k < 4; ++k) { pc.mu[k] = 0.f; pc.ca[k] = 0.f; pc.cb[k] = 0.f; }
-    // per-element arithmetic in fp32 (the fp64 sums only enter through k1, k2): dz = gr * (g - k1 - xhat * k2)
-    float k1f[4], k2f[4], grf[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) { k1f[k] = static_cast<float>(k1[k]); k2f[k] = static_cast<float>(k2[k]); grf[k] = static_cast<float>(gr[k]); }
     RowWalk walk(a.mask, r0 + threadIdx.y);
     for (int64_t rb = r0 + threadIdx.y; rb < r1; rb += static_cast<int64_t>(blockDim.y) * U) {
       float zz[U][4], d[U][4];
@@ -636,12 +656,11 @@ __global__ void __launch_bounds__(256, 2) bn_bwd_apply_kernel(const BnBwdArgs a)
           }
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            float xh = 0.f, pre = zz[u][k];
-            if (a.mean != nullptr) { xh = (zz[u][k] - mu[k]) * rs[k]; pre = fmaf(ga[k], xh, be[k]); }
+            const float xh = fmaf(zz[u][k], bf[k].xa, bf[k].xb), pre = fmaf(zz[u][k], bf[k].pa, bf[k].pb);
             float dk = d[u][k];
             if (a.pg.enabled) dk = fmaf(pc.cb[k], (pre >= 0.f ? pre : pre * sl[k]) - pc.mu[k], pc.ca[k]);
             const float g = pre > 0.f ? dk : dk * sl[k];
-            out[k] = a.mean != nullptr ? grf[k] * (g - k1f[k] - xh * k2f[k]) : g;
+            out[k] = fmaf(g, grf[k], fmaf(xh, e1[k], e0[k]));          // no batch norm: grf = 1, e0 = e1 = 0
           }
         }
         if (a.dz32 != nullptr) VecF<4>::store(a.dz32 + r * a.c_total + c0, out);

@@ -93,11 +93,12 @@ __global__ void __launch_bounds__(kBsMaxThreads) bn_stream_kernel(const BsArgs a
   const int nq = a.c_total >> 2;
   const bool active = q < nq && rl < n_lanes;
   const int c0 = q * 4;
-  float mu[4], rs[4], ga[4], be[4], sl[4];
-  float k1f[4], k2f[4], grf[4];
+  float sl[4], grf[4], e0[4], e1[4];         // apply: dz = g * grf + (e0 + xhat * e1), see bn_bwd_apply_kernel
+  BnFold bf[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    mu[k] = 0.f; rs[k] = 1.f; ga[k] = 1.f; be[k] = 0.f; sl[k] = 0.f; k1f[k] = 0.f; k2f[k] = 0.f; grf[k] = 1.f;
+    sl[k] = 0.f; grf[k] = 1.f; e0[k] = 0.f; e1[k] = 0.f;
+    bf[k] = bn_fold(false, 0.f, 1.f, 1.f, 0.f);
   }
   const bool has_bn = MODE == kBsFwd ? a.st.sums != nullptr : a.mean != nullptr;
   if (active) {
@@ -107,17 +108,20 @@ __global__ void __launch_bounds__(kBsMaxThreads) bn_stream_kernel(const BsArgs a
       if (MODE == kBsFwd) {
         if (has_bn) {
           double var;
-          bn_mean_rstd(a.st, c0 + k, a.fin.eps, &mu[k], &rs[k], &var);
-          ga[k] = a.gamma[c0 + k]; be[k] = a.beta[c0 + k];
-          if (blockIdx.x == 0 && rl == 0) bn_finalize_channel(a.st, a.fin, c0 + k, mu[k], rs[k], var);
+          float mu, rs;
+          bn_mean_rstd(a.st, c0 + k, a.fin.eps, &mu, &rs, &var);
+          bf[k] = bn_fold(true, mu, rs, a.gamma[c0 + k], a.beta[c0 + k]);
+          if (blockIdx.x == 0 && rl == 0) bn_finalize_channel(a.st, a.fin, c0 + k, mu, rs, var);
         }
       } else if (has_bn) {
-        mu[k] = a.mean[c0 + k]; rs[k] = a.rstd[c0 + k]; ga[k] = a.gamma[c0 + k]; be[k] = a.beta[c0 + k];
+        const float ga = a.gamma[c0 + k], rs = a.rstd[c0 + k];
+        bf[k] = bn_fold(true, a.mean[c0 + k], rs, ga, a.beta[c0 + k]);
         if (MODE == kBsApply) {
           const double inv_n = 1.0 / a.n;
-          k1f[k] = static_cast<float>(a.sums_out[c0 + k] * inv_n);
-          k2f[k] = static_cast<float>(a.sums_out[a.sums_ld + c0 + k] * inv_n);
-          grf[k] = static_cast<float>(static_cast<double>(ga[k]) * rs[k]);
+          const double gr = static_cast<double>(ga) * rs;
+          grf[k] = static_cast<float>(gr);
+          e0[k] = static_cast<float>(-gr * (a.sums_out[c0 + k] * inv_n));
+          e1[k] = static_cast<float>(-gr * (a.sums_out[a.sums_ld + c0 + k] * inv_n));
         }
       }
       if (MODE == kBsApply && blockIdx.x == 0 && rl == 0) {
@@ -175,8 +179,7 @@ __global__ void __launch_bounds__(kBsMaxThreads) bn_stream_kernel(const BsArgs a
           float v[4];
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            float t = zz[k];
-            if (has_bn) t = fmaf(ga[k], (t - mu[k]) * rs[k], be[k]);          // same expression in every backward kernel
+            const float t = fmaf(zz[k], bf[k].pa, bf[k].pb);                  // same expression in every backward kernel
             v[k] = ok ? (t >= 0.f ? t : t * sl[k]) : 0.f;
           }
           if (y_p != nullptr) { VecF<4>::store(y_p, v); y_p += f32_step; }
@@ -197,8 +200,7 @@ __global__ void __launch_bounds__(kBsMaxThreads) bn_stream_kernel(const BsArgs a
             }
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-              float xh = 0.f, pre = zz[k];
-              if (has_bn) { xh = (zz[k] - mu[k]) * rs[k]; pre = fmaf(ga[k], xh, be[k]); }
+              const float xh = fmaf(zz[k], bf[k].xa, bf[k].xb), pre = fmaf(zz[k], bf[k].pa, bf[k].pb);
               float d = dd[k];
               if (virt) d = fmaf(pc.cb[k], (pre >= 0.f ? pre : pre * sl[k]) - pc.mu[k], pc.ca[k]);
               const float g = pre > 0.f ? d : d * sl[k];
@@ -207,7 +209,7 @@ __global__ void __launch_bounds__(kBsMaxThreads) bn_stream_kernel(const BsArgs a
                 acc[1][k] = fmaf(g, xh, acc[1][k]);
                 if (pre < 0.f) acc[2][k] = fmaf(d, pre, acc[2][k]);
               } else {
-                out[k] = has_bn ? grf[k] * (g - k1f[k] - xh * k2f[k]) : g;
+                out[k] = fmaf(g, grf[k], fmaf(xh, e1[k], e0[k]));
               }
             }
           }

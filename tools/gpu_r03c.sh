@@ -1,6 +1,6 @@
 #!/bin/bash
-# r03c (1 GPU): round-aware split of the wgrad contraction axis
-out=gpurun_out; tag=r03c
+# r03c-d (1 GPU): round-aware wgrad split (r03c); folded batch-norm constants in the row kernels (r03d)
+out=gpurun_out; tag=r03d
 timeout 900 python -m pytest tests/test_gpu_wgrad.py tests/test_gpu_train.py -m gpu -q > $out/${tag}_pytest.log 2>&1; tail -4 $out/${tag}_pytest.log | cut -c1-600
 for v in 1 2; do
 python bench.py --workload train --steps 300 --warmup 30 --no-cpu-baseline > $out/${tag}_train_$v.json 2>/dev/null
