@@ -215,6 +215,16 @@ class Dist(object):
             torch.cuda.set_device(self.local)
             dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
             self.dist = dist
+            self.host_group = dist.new_group(backend="gloo")
+
+    def barrier_host(self):
+        """Ranks meet on the HOST (gloo): a rank that waits here keeps its GPU idle.  An NCCL barrier is a kernel that spins on
+        the GPU until the last rank arrives -- while rank 0 drove all eight GPUs from one process (the ark_e2e leg) the seven
+        waiting ranks' barrier kernels sat on the SMs its persistent one-CTA-per-SM GEMMs count on, and halved their rate."""
+        if self.dist is not None:
+            import torch
+            torch.cuda.synchronize()
+            self.dist.barrier(group=self.host_group)
 
     def barrier(self, eng=None):
         if eng is not None:
@@ -598,7 +608,7 @@ def leg_ark_e2e(args, devices):
     import tempfile
     from oracle import kaldi_io_ref, synth                     # generators / format writers for the INPUT files only
     from xvector_b200 import kaldi_io
-    from xvector_b200.extract import extract_stream_mgpu
+    from xvector_b200.extract import CLI_BATCH_ROWS, extract_stream_mgpu      # the CLI's own batch cut
     from xvector_b200.model.trainer import Trainer
     dim = DIM
     cfg = dict(synth.TDNN_STAT_CONFIG)
@@ -642,7 +652,7 @@ def leg_ark_e2e(args, devices):
                 for _ in range(reps):                          # the first pass also warms buffers and the page cache
                     t0 = time.perf_counter()
                     written, skipped = extract_stream_mgpu(None, devices, path, os.path.join(tmp, "xvector.ark"), dim,
-                                                           max_rows=1 << 19, trainers=trainers)
+                                                           trainers=trainers, batch_rows=int(os.environ.get("XV_ARK_ROWS", CLI_BATCH_ROWS)))
                     dt = time.perf_counter() - t0
                     best = dt if best is None else min(best, dt)
                 # the reader alone (decode into one buffer, nothing else)
@@ -650,7 +660,8 @@ def leg_ark_e2e(args, devices):
                 for _ in range(2):
                     t0 = time.perf_counter()
                     rows = 0
-                    for _, feats, _ in kaldi_io.BatchReader(path, dim, max_rows=1 << 19, max_utts=4096, threads=default_reader_threads()):
+                    for _, feats, _ in kaldi_io.BatchReader(path, dim, max_rows=1 << 20, max_utts=4096, threads=default_reader_threads(),
+                                                            batch_rows=CLI_BATCH_ROWS):
                         rows += feats.shape[0]
                     dt = time.perf_counter() - t0
                     rd = dt if rd is None else min(rd, dt)
@@ -684,10 +695,10 @@ def run_ours(args):
             legs["ark_e2e"] = run_leg("ark_e2e", leg_ark_e2e, args, [dc.local])
         else:
             legs["train_dp"] = run_leg("train_dp", leg_train_dp, args, dc)
-            dc.barrier()
+            dc.barrier_host()
             if dc.rank == 0:                                    # one process drives every GPU of the box: the product's shape
                 legs["ark_e2e"] = run_leg("ark_e2e", leg_ark_e2e, args, list(range(dc.world)))
-            dc.barrier()
+            dc.barrier_host()
     if dc.rank == 0:
         if legs:
             line["legs"] = legs

@@ -221,3 +221,29 @@ def test_error_behaviour(K, tmp_path):
     assert list(K.read_mat_ark("ark:true |")) == []
     with pytest.raises(ValueError):
         K.open_or_fd(bad, "x")
+
+
+def test_batch_reader_soft_batch_cut(tmp_path):
+    """batch_rows cuts the batches below the buffer capacity; an utterance longer than a batch still gets through (its batch is
+    filled to the capacity), and the keys of every batch come back without the padding of the key buffer."""
+    from xvector_b200 import kaldi_io as K
+    rng = np.random.default_rng(0)
+    mats = [rng.standard_normal((n, 5)).astype(np.float32) for n in (10, 300, 20, 7, 120, 500, 3)]
+    path = str(tmp_path / "soft.ark")
+    with K.open_or_fd(path, "wb") as f:
+        for i, m in enumerate(mats):
+            K.write_mat(f, m, key="u%d" % i)
+    batches = []
+    for keys, feats, lens in K.BatchReader(path, 5, max_rows=600, max_utts=16, threads=2, batch_rows=128):
+        batches.append(keys)
+        assert len(keys) == len(lens) and feats.shape[0] == int(lens.sum())
+        off = 0
+        for k, n in zip(keys, lens):
+            assert np.array_equal(feats[off:off + n], mats[int(k[1:])])
+            off += n
+    assert batches == [["u0"], ["u1", "u2", "u3", "u4"], ["u5", "u6"]]
+    # without the soft cut: capacity only
+    assert [k for k, _, _ in K.BatchReader(path, 5, max_rows=600, max_utts=16, threads=2)] == [["u0", "u1", "u2", "u3", "u4"], ["u5", "u6"]]
+    # an utterance longer than the capacity is an error, not a truncation
+    with pytest.raises(K.KaldiIOError):
+        list(K.BatchReader(path, 5, max_rows=400, max_utts=16, threads=2, batch_rows=128))

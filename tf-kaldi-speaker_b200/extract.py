@@ -115,7 +115,7 @@ def extract_packed(trainer, feats, lengths, chunk_size=10000, min_chunk_size=25,
 
 
 def extract_stream(trainer, rspecifier, wspecifier, dim, chunk_size=10000, min_chunk_size=25, normalize=False,
-                   max_rows=1 << 20, max_utts=4096, pinned=True, threads=None):
+                   max_rows=1 << 20, max_utts=4096, pinned=True, threads=None, batch_rows=None):
     """The reference's extraction loop (extract.py:63-93) as a stream of packed batches: the native ark reader
     (kaldi_io.BatchReader, lib/libxvkaldi.so) decodes whole batches into one pinned buffer, xv_forward embeds the
     batch, the native writer emits the vectors.  Batches whose utterances all lie in [min_chunk_size, chunk_size]
@@ -131,7 +131,7 @@ def extract_stream(trainer, rspecifier, wspecifier, dim, chunk_size=10000, min_c
     try:
         with kaldi_io.open_or_fd(wspecifier, "wb") as fp_out:
             for keys, feats, lengths in kaldi_io.BatchReader(rspecifier, dim, max_rows=max_rows, max_utts=max_utts, buffer=buffer,
-                                                             threads=threads or default_reader_threads()):
+                                                             threads=threads or default_reader_threads(), batch_rows=batch_rows):
                 if lengths.min() >= min_chunk_size and lengths.max() <= chunk_size:
                     emb = np.asarray(trainer.predict_packed(feats, lengths), np.float32)
                     if normalize:
@@ -156,6 +156,11 @@ def default_reader_threads():
     return max(1, min(32, os.cpu_count() or 8))
 
 
+# Where the CLI cuts its batches (the pinned buffers keep their 1 M-row capacity for long recordings): a quarter of a million
+# frames is 1.7 ms of one B200, so the fill and drain of the reader -> GPU -> writer pipeline cost little, and a batch costs the
+# reader ~50 us of fixed work.
+CLI_BATCH_ROWS = 1 << 18
+
 _PIN_RING = {}
 
 
@@ -177,7 +182,7 @@ def release_pinned_rings():
 
 
 def extract_stream_mgpu(make_trainer, devices, rspecifier, wspecifier, dim, chunk_size=10000, min_chunk_size=25,
-                        normalize=False, max_rows=1 << 20, max_utts=4096, threads=None, trainers=None):
+                        normalize=False, max_rows=1 << 20, max_utts=4096, threads=None, trainers=None, batch_rows=None):
     """extract_stream over several GPUs of one box: what `run.pl JOB=1:nj extract_wrapper.sh` does with nj processes
     (egs/voxceleb/v1/nnet/run_extract_embeddings.sh:68-71), as ONE process -- one reader (native ark decoder into a ring of
     pinned buffers), one host thread + one xv_ctx per GPU pulling batches from a queue (utterances are independent: no
@@ -191,7 +196,8 @@ def extract_stream_mgpu(make_trainer, devices, rspecifier, wspecifier, dim, chun
     from .engine import PinnedArray
     threads = threads or default_reader_threads()
     n_dev = len(devices)
-    n_buf = 2 * n_dev + 1
+    # two batches per GPU (one running, one queued) + the one being read; XV_EXTRACT_RING overrides (measurement)
+    n_buf = int(os.environ.get("XV_EXTRACT_RING", 0)) or 2 * n_dev + 1
     pins = _pinned_ring(n_buf, max_rows, dim)
     free_bufs = queue.Queue()
     for i in range(n_buf):
@@ -236,7 +242,8 @@ def extract_stream_mgpu(make_trainer, devices, rspecifier, wspecifier, dim, chun
     # Both specifiers are opened HERE, before any worker thread exists: "ark:cmd |" and "ark:| cmd" start a child process, and
     # that must not happen while another thread is inside CUDA context creation (make_trainer in the workers).
     first_buf = free_bufs.get()
-    rd = kaldi_io.BatchReader(rspecifier, dim, max_rows=max_rows, max_utts=max_utts, buffer=pins[first_buf].array, threads=threads)
+    rd = kaldi_io.BatchReader(rspecifier, dim, max_rows=max_rows, max_utts=max_utts, buffer=pins[first_buf].array, threads=threads,
+                              batch_rows=batch_rows)
     try:
         fp_out = kaldi_io.open_or_fd(wspecifier, "wb")
     except BaseException:
@@ -337,7 +344,8 @@ def main(argv=None):
     # one pipeline for any number of GPUs: the reader runs ahead of the device(s) through a ring of pinned buffers
     first = max(args.gpu, 0)
     written, skipped = extract_stream_mgpu(make_trainer, list(range(first, first + max(args.gpus, 1))), args.rspecifier,
-                                           args.wspecifier, dim, args.chunk_size, args.min_chunk_size, args.normalize)
+                                           args.wspecifier, dim, args.chunk_size, args.min_chunk_size, args.normalize,
+                                           batch_rows=CLI_BATCH_ROWS)
     release_pinned_rings()
     print("[INFO] wrote %d embeddings, skipped %d short utterances" % (written, skipped))
 

@@ -23,6 +23,7 @@ import numpy as np
 LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libxvkaldi.so")
 
 XVK_OK = 0
+XVK_ECAPACITY = -5
 MAT_F32, MAT_F64, MAT_CM, MAT_TEXT, VEC_F32, VEC_F64, VEC_TEXT = 1, 2, 3, 4, 5, 6, 7
 
 
@@ -466,7 +467,11 @@ class BatchReader(object):
     `max_rows` rows / `max_utts` utterances each, decoded natively into `buffer` (pass a pinned array to make the
     H2D copy of xv_forward asynchronous).  The arrays of a batch are views: consume them before the next one."""
 
-    def __init__(self, rspecifier, dim, max_rows=1 << 20, max_utts=4096, buffer=None, threads=8):
+    def __init__(self, rspecifier, dim, max_rows=1 << 20, max_utts=4096, buffer=None, threads=8, batch_rows=None):
+        """max_rows: capacity of the buffer (the longest utterance that can be read); batch_rows: where a batch is cut
+        (default: at the capacity).  A batch holds at most batch_rows rows; one whose first utterance alone is longer than that
+        is filled up to the capacity instead."""
+        self.batch_rows = None if batch_rows is None else max(int(batch_rows), 1)
         self.fd = open_or_fd(rspecifier)
         self.fd._check(self.fd._lib.xvk_reader_set_threads(self.fd._h, max(int(threads), 1)))   # regular files: parallel decode
         self.dim = int(dim)
@@ -482,11 +487,18 @@ class BatchReader(object):
         n, rows = C.c_int32(), C.c_int64()
         more = 1
         while more:
-            more = fd._check(lib.xvk_read_batch_f32(fd._h, _ptr(self.buffer), self.buffer.shape[0], self.dim, self.max_utts,
-                                                    self._lengths.ctypes.data_as(_i32p), self._keys, len(self._keys),
-                                                    C.byref(n), C.byref(rows)))
+            full = self.buffer.shape[0]
+            cap = full if self.batch_rows is None else min(self.batch_rows, full)
+            rc = lib.xvk_read_batch_f32(fd._h, _ptr(self.buffer), cap, self.dim, self.max_utts,
+                                        self._lengths.ctypes.data_as(_i32p), self._keys, len(self._keys), C.byref(n), C.byref(rows))
+            if rc == XVK_ECAPACITY and cap < full:       # one utterance longer than a batch: it gets the whole buffer
+                rc = lib.xvk_read_batch_f32(fd._h, _ptr(self.buffer), full, self.dim, self.max_utts,
+                                            self._lengths.ctypes.data_as(_i32p), self._keys, len(self._keys), C.byref(n), C.byref(rows))
+            more = fd._check(rc)
             if n.value:
-                keys = self._keys.raw.split(b"\0")[:n.value]
+                # maxsplit: the rest of the 64 * max_utts byte buffer is NULs -- an unbounded split makes a list entry of
+                # every one of them (2-3 ms per batch, a third of the reader's time on 0.5 M-row batches)
+                keys = self._keys.raw.split(b"\0", n.value)[:n.value]
                 yield [k.decode("latin1") for k in keys], self.buffer[:rows.value], self._lengths[:n.value].copy()
         self.close()
 
