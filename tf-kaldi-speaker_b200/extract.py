@@ -156,10 +156,11 @@ def default_reader_threads():
     return max(1, min(32, os.cpu_count() or 8))
 
 
-# Where the CLI cuts its batches (the pinned buffers keep their 1 M-row capacity for long recordings): a quarter of a million
-# frames is 1.7 ms of one B200, so the fill and drain of the reader -> GPU -> writer pipeline cost little, and a batch costs the
-# reader ~50 us of fixed work.
-CLI_BATCH_ROWS = 1 << 18
+# Where the CLI cuts its batches (the pinned buffers keep their 1 M-row capacity for long recordings).  Measured on the
+# ark -> x-vector ark leg (7 M frames, 1 / 2 GPUs): 2^19 rows 125 / 202 M frames/s, 2^18 rows 115 / 166 M -- a batch costs
+# ~0.45 ms on the GPU side (the first slice's H2D before any kernel can start, the last D2H), which outweighs the shorter
+# fill and drain of the reader -> GPU -> writer pipeline.
+CLI_BATCH_ROWS = 1 << 19
 
 _PIN_RING = {}
 
