@@ -1,12 +1,12 @@
 #!/bin/bash
 # r02i (8 GPUs): the driver's N=8 launch of the default bench (train_dp + ark_e2e legs)
-out=gpurun_out; tag=r02i2
+out=gpurun_out; tag=r03j
 nvidia-smi -L | wc -l
 ( time python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus 8 > $out/${tag}_bench_n8.json 2> $out/${tag}_bench_n8.err ) 2>&1 | tail -3; tail -6 $out/${tag}_bench_n8.err | cut -c1-300
 python - <<'PY'
 import json
 try:
-    d=json.load(open('gpurun_out/r02i2_bench_n8.json'))
+    d=json.load(open('gpurun_out/r03j_bench_n8.json'))
     print('N=8 headline', d['value'], d['ms_per_step'], 'e2e', d['e2e']['value'])
     l=d['legs']
     t=l['train_dp']
