@@ -181,3 +181,21 @@ def test_extract_packed_views_match_extract_many():
             np.testing.assert_allclose(row, ref[i], rtol=2e-6, atol=1e-7)
     got, kept = extract_packed(Fake(), feats, lengths, chunk_size=10000, min_chunk_size=2000)
     assert got.shape[0] == 0 and len(kept) == 0
+
+
+def test_plan_arrays_equals_the_per_utterance_chunk_plan():
+    """scheduler.plan_arrays (the vectorised plan of extract_packed) against extract.plan_many (chunk_plan per utterance,
+    egs/voxceleb/v1/nnet/lib/extract.py:65-78) over edge lengths: below the minimum, exactly chunk_size, one frame over, exact
+    multiples of the half-chunk hop, odd chunk sizes (Python-2 integer division of chunk_size / 2)."""
+    from xvector_b200.extract import plan_many
+    from xvector_b200.scheduler import plan_arrays
+    rng = np.random.default_rng(3)
+    for chunk, min_len in ((2000, 25), (300, 50), (301, 25), (10000, 25), (7, 3)):
+        half = chunk // 2
+        lens = np.concatenate([[0, 1, min_len - 1, min_len, chunk - 1, chunk, chunk + 1, chunk + half, chunk + half + 1,
+                                chunk + 2 * half, 3 * chunk, 10 * chunk + 3], rng.integers(1, 6 * chunk, 200)])
+        work = plan_many(lens, chunk, min_len)
+        owners, starts, sizes = plan_arrays(lens, chunk, min_len)
+        assert [(int(u), int(s), int(z)) for u, s, z in zip(owners, starts, sizes)] == [(u, s, z) for u, s, z in work]
+    o, s, z = plan_arrays(np.array([3, 5]), 100, 25)
+    assert o.size == 0 and s.size == 0 and z.size == 0

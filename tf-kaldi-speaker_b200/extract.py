@@ -13,7 +13,7 @@ import sys
 
 import numpy as np
 
-from .scheduler import chunk_plan
+from .scheduler import chunk_plan, plan_arrays
 
 
 def extract_one(trainer, feature, chunk_size=10000, min_chunk_size=25, normalize=False):
@@ -86,29 +86,29 @@ def extract_packed(trainer, feats, lengths, chunk_size=10000, min_chunk_size=25,
     min_chunk_size are left out (:65-67)."""
     lengths = np.asarray(lengths)
     offs = np.concatenate([[0], np.cumsum(lengths, dtype=np.int64)])
-    work = plan_many(lengths, chunk_size, min_chunk_size)
-    if not work:
+    owners, starts, sizes = plan_arrays(lengths, chunk_size, min_chunk_size)
+    if owners.size == 0:
         return np.zeros((0, 0), np.float32), np.zeros(0, np.int64)
-    owners = np.fromiter((u for u, _, _ in work), np.int64, len(work))
-    sizes = np.fromiter((z for _, _, z in work), np.int32, len(work))
-    row0 = offs[owners] + np.fromiter((s for _, s, _ in work), np.int64, len(work))
+    sizes = sizes.astype(np.int32)
+    row0 = offs[owners] + starts
     emb = trainer.predict_views(feats, row0, sizes)
     first = np.concatenate([[0], np.nonzero(np.diff(owners))[0] + 1])             # pieces of an utterance are consecutive
     kept = owners[first]
-    counts = np.diff(np.concatenate([first, [len(work)]]))
+    counts = np.diff(np.concatenate([first, [owners.size]]))
+    out = np.array(emb[first], np.float32)                                        # unchunked utterances: the embedding itself, bit for bit
     if counts.max() > 1:
-        e = emb.astype(np.float64)
-        if normalize:
-            multi = np.repeat(counts > 1, counts)
-            nrm = np.sqrt(np.sum(np.square(e), axis=1, keepdims=True))
-            e = np.where(multi[:, None], e / nrm, e)                              # per-chunk normalisation (:80-81) of chunked utterances only
-        w = sizes.astype(np.float64)[:, None]
-        out = np.add.reduceat(e * w, first, axis=0) / np.add.reduceat(w, first, axis=0)
-        single = counts == 1
-        out[single] = emb[first[single]]                                          # unchunked utterances: the embedding itself, bit for bit
-        out = out.astype(np.float32)
-    else:
-        out = emb
+        # chunked utterances only, grouped by their number of pieces (a handful of groups): [n, k, E] gathers summed over k in
+        # fp64.  (np.add.reduceat over all 3432 x 512 piece rows of a 2048-utterance batch took 50 ms -- its axis-0 path is
+        # a strided scalar loop -- against 3 ms here.)
+        multi = np.nonzero(counts > 1)[0]
+        for k in np.unique(counts[multi]):
+            sel = multi[counts[multi] == k]
+            rows = first[sel][:, None] + np.arange(int(k))[None, :]
+            e = emb[rows].astype(np.float64)
+            if normalize:
+                e = e / np.sqrt(np.sum(np.square(e), axis=2, keepdims=True))      # per-chunk normalisation (:80-81) of chunked utterances only
+            w = sizes[rows].astype(np.float64)[:, :, None]
+            out[sel] = (np.sum(e * w, axis=1) / np.sum(w, axis=1)).astype(np.float32)
     if normalize:
         out = out / np.sqrt(np.sum(np.square(out), axis=1, keepdims=True))
     return out.astype(np.float32), kept

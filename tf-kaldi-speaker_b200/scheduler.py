@@ -21,6 +21,23 @@ def chunk_plan(length, chunk_size):
     return plan
 
 
+def plan_arrays(lengths, chunk_size, min_chunk_size):
+    """chunk_plan over a whole batch without a Python loop: -> (owners, starts, sizes), int64 arrays with one entry per piece
+    in utterance order; utterances shorter than min_chunk_size own no piece (extract.py:65-78)."""
+    n = np.asarray(lengths, np.int64)
+    keep = n >= min_chunk_size
+    half = chunk_size // 2
+    chunked = keep & (n > chunk_size)
+    pieces = keep.astype(np.int64)
+    if chunked.any():
+        pieces = np.where(chunked, -(-(n - chunk_size) // half) + 1, pieces)
+    owners = np.repeat(np.arange(len(n), dtype=np.int64), pieces)
+    first = np.cumsum(pieces) - pieces
+    starts = (np.arange(owners.size, dtype=np.int64) - first[owners]) * half
+    left = n[owners] - starts
+    return owners, starts, np.where(left > chunk_size, chunk_size, left)
+
+
 def utterance_flops(t, d, pool_nodes=1500):
     """Algorithmic FLOPs up to tdnn6_dense."""
     t = np.asarray(t, np.float64)
