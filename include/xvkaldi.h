@@ -96,6 +96,13 @@ int xvk_scp_read_f32(xvk_scp* s, int64_t i, float* dst, int64_t ld);
  * row_off[k] (row stride ld); rows_out[k] receives the row count.  cap_rows bounds dst. */
 int xvk_scp_read_many_f32(xvk_scp* s, const int64_t* idx, int64_t n, float* dst, int64_t ld, const int64_t* row_off,
                           int64_t cap_rows, int32_t* rows_out, int32_t threads);
+/* Rows [start[k], start[k] + length[k]) of entries idx[k], k in [0, n), decoded by `threads` workers into dst at row offsets
+ * row_off[k]: the random segments of a training batch (KaldiDataRandomQueue's FeatureReader.read_segment calls,
+ * dataset/data_loader.py:336-345 over dataset/kaldi_io.py:1034-1053) in one call -- only the bytes of the segments are read
+ * (FM / DM; a compressed matrix is decoded row range by row range).  A segment that does not lie inside its matrix is
+ * XVK_EINVAL ("The number of frames is not enough for length ..."). */
+int xvk_scp_read_segments_f32(xvk_scp* s, const int64_t* idx, const int32_t* start, const int32_t* length, int64_t n, float* dst,
+                              int64_t ld, const int64_t* row_off, int64_t cap_rows, int32_t threads);
 /* Row / column counts of entries idx[0..n) (headers only), `threads` workers. */
 int xvk_scp_dims_many(xvk_scp* s, const int64_t* idx, int64_t n, int32_t* rows_out, int32_t* cols_out, int32_t threads);
 const char* xvk_scp_error(const xvk_scp* s);

@@ -247,3 +247,95 @@ def test_batch_reader_soft_batch_cut(tmp_path):
     # an utterance longer than the capacity is an error, not a truncation
     with pytest.raises(K.KaldiIOError):
         list(K.BatchReader(path, 5, max_rows=400, max_utts=16, threads=2, batch_rows=128))
+
+
+def test_worker_pool_concurrent_readers_and_fork(tmp_path):
+    """The native reader's parked worker threads: two Python threads reading at once (one gets the pool, the other starts its
+    own threads), and a forked child that reads after the parent has used the pool (the parent's threads do not exist there)."""
+    import signal
+    import threading
+    from xvector_b200 import kaldi_io as K
+    rng = np.random.default_rng(4)
+    mats = [rng.standard_normal((int(n), 6)).astype(np.float32) for n in rng.integers(20, 200, 60)]
+    path = str(tmp_path / "pool.ark")
+    with K.open_or_fd(path, "wb") as f:
+        for i, m in enumerate(mats):
+            K.write_mat(f, m, key="u%02d" % i)
+
+    def read_all():
+        total = 0
+        for keys, feats, lens in K.BatchReader(path, 6, max_rows=1000, max_utts=16, threads=4):
+            off = 0
+            for k, n in zip(keys, lens):
+                assert np.array_equal(feats[off:off + n], mats[int(k[1:])])
+                off += n
+            total += len(keys)
+        assert total == len(mats)
+
+    read_all()                                             # the pool exists from here on
+    errors = []
+
+    def guarded():
+        try:
+            for _ in range(5):
+                read_all()
+        except BaseException as e:                         # noqa: BLE001 -- reported in the main thread
+            errors.append(e)
+
+    threads = [threading.Thread(target=guarded) for _ in range(3)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(60)
+    assert not errors and not any(t.is_alive() for t in threads)
+    pid = os.fork()
+    if pid == 0:                                           # child: must not wait for threads that were never copied
+        signal.alarm(30)
+        try:
+            read_all()
+            os._exit(0)
+        except BaseException:                              # noqa: BLE001
+            os._exit(1)
+    _, status = os.waitpid(pid, 0)
+    assert os.WIFEXITED(status) and os.WEXITSTATUS(status) == 0, status
+    read_all()                                             # and the parent's pool is still fine
+
+
+def test_scp_read_segments(tmp_path):
+    """xvk_scp_read_segments_f32 (FeatureReader.read_segment over an scp, dataset/kaldi_io.py:1034-1053): every segment is
+    the slice of its matrix, for float and compressed matrices, mapped and unmapped files, and a segment that does not fit
+    is an error that names the key."""
+    from oracle import kaldi_io_ref
+    from xvector_b200 import kaldi_io as K
+    rng = np.random.default_rng(6)
+    mats = [rng.standard_normal((int(n), 5)).astype(np.float32) for n in rng.integers(30, 90, 12)]
+    ark, scp = str(tmp_path / "seg.ark"), str(tmp_path / "seg.scp")
+    with K.open_or_fd("ark,scp:%s,%s" % (ark, scp), "wb") as f:
+        for i, m in enumerate(mats):
+            K.write_mat(f, m, key="u%02d" % i)
+    table = K.ScpTable(scp)
+    idx = rng.integers(0, len(mats), 40)
+    length = 17
+    starts = np.array([rng.integers(0, mats[i].shape[0] - length + 1) for i in idx], np.int32)
+    for threads in (1, 4):
+        got = table.read_segments(idx, starts, length, threads=threads)
+        assert got.shape == (40, length, 5) and got.dtype == np.float32
+        for k, (i, s) in enumerate(zip(idx, starts)):
+            assert np.array_equal(got[k], mats[i][s:s + length])
+    with pytest.raises(K.KaldiIOError, match="not enough"):
+        table.read_segments([0], [mats[0].shape[0] - length + 1], length)
+    table.close()
+    # compressed matrices: the rows of a segment decode to what the whole-matrix decode gives
+    cm_ark, cm_scp = str(tmp_path / "cm.ark"), str(tmp_path / "cm.scp")
+    with open(cm_ark, "wb") as f, open(cm_scp, "w") as g:
+        for i, m in enumerate(mats[:4]):
+            rec = kaldi_io_ref.write_cm_bytes(m, "c%d" % i)
+            g.write("c%d %s:%d\n" % (i, cm_ark, f.tell() + len("c%d " % i)))
+            f.write(rec)
+    t2 = K.ScpTable(cm_scp)
+    whole, lens = t2.read_many(np.arange(4))
+    off = np.concatenate([[0], np.cumsum(lens)])
+    seg = t2.read_segments([2, 0, 3], [5, 0, 11], 9)
+    for k, (i, s) in enumerate(((2, 5), (0, 0), (3, 11))):
+        assert np.array_equal(seg[k], whole[off[i] + s:off[i] + s + 9])
+    t2.close()

@@ -20,6 +20,9 @@
 #include <algorithm>
 #include <atomic>
 #include <map>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -795,29 +798,165 @@ struct xvk_scp {
   std::vector<ScpEntry> entries;
   std::string err;
   std::vector<uint8_t> scratch;
+  // "file:offset" targets in regular uncompressed files are served out of one read-only mapping per file, created on first
+  // use and kept until the table is closed: a random-access read is then a header parse and a memcpy -- no open / lseek /
+  // read / close per entry (a training batch is 64 such reads per millisecond).  p == nullptr: the file cannot be mapped.
+  struct FileMap { const uint8_t* p; size_t size; };
+  std::mutex map_mu;
+  std::map<std::string, FileMap> maps;
+  ~xvk_scp() {
+    for (auto& kv : maps)
+      if (kv.second.p) munmap(const_cast<uint8_t*>(kv.second.p), kv.second.size);
+  }
 };
 
 namespace {
 
 // One scp target: open (with its byte offset), parse the header; optionally decode.
-int scp_fetch(const ScpEntry& e, ObjHeader* h, float* dst, int64_t ld, int64_t cap_rows, std::vector<uint8_t>* scratch,
-              std::string* err) {
+// start < 0: the whole matrix; else rows [start, start + length) of it (FeatureReader.read_segment, dataset/kaldi_io.py:1034-1053)
+// The mapping of an scp target's file (see xvk_scp::maps); false: not a plain "file:offset" target or not mappable.
+bool scp_mapping(xvk_scp* owner, const std::string& rxfile, xvk_scp::FileMap* out, int64_t* offset) {
+  static const bool no_map = getenv("XVK_NO_MMAP") != nullptr;      // A/B switch
+  if (!owner || no_map) return false;
+  std::string prefix, file;
+  parse_specifier(rxfile, &prefix, &file, offset);
+  file = trim(file);
+  if (*offset < 0 || file.empty() || file.back() == '|' || ends_with(file, ".gz")) return false;
+  std::lock_guard<std::mutex> lock(owner->map_mu);
+  auto it = owner->maps.find(file);
+  if (it == owner->maps.end()) {
+    xvk_scp::FileMap m = {nullptr, 0};
+    const int fd = ::open(file.c_str(), O_RDONLY | O_CLOEXEC);
+    if (fd >= 0) {
+      struct stat st;
+      if (fstat(fd, &st) == 0 && S_ISREG(st.st_mode) && st.st_size > 0) {
+        void* p = mmap(nullptr, static_cast<size_t>(st.st_size), PROT_READ, MAP_SHARED, fd, 0);
+        if (p != MAP_FAILED) {
+          madvise(p, static_cast<size_t>(st.st_size), MADV_RANDOM);
+          m.p = static_cast<const uint8_t*>(p);
+          m.size = static_cast<size_t>(st.st_size);
+        }
+      }
+      ::close(fd);
+    }
+    it = owner->maps.emplace(file, m).first;
+  }
+  if (!it->second.p || static_cast<size_t>(*offset) >= it->second.size) return false;
+  *out = it->second;
+  return true;
+}
+
+int scp_fetch(xvk_scp* owner, const ScpEntry& e, ObjHeader* h, float* dst, int64_t ld, int64_t cap_rows, std::vector<uint8_t>* scratch,
+              std::string* err, int32_t start = -1, int32_t length = 0) {
   Source s;
-  int rc = s.open(e.rxfile, 1 << 16);            // random access: small read-ahead
-  if (rc != XVK_OK) { *err = s.err; s.close_all(); return rc; }
+  xvk_scp::FileMap fm;
+  int64_t offset = -1;
+  int rc = XVK_OK;
+  if (scp_mapping(owner, e.rxfile, &fm, &offset)) {
+    s.map = fm.p;
+    s.map_size = fm.size;
+    s.map_pos = static_cast<size_t>(offset);
+    s.seekable = true;                           // map_owner stays false: the table owns the mapping
+    s.buf.resize(256);                           // look-ahead of the header parse (a token and two int32 fields)
+  } else {
+    rc = s.open(e.rxfile, 1 << 16);              // random access: small read-ahead
+    if (rc != XVK_OK) { *err = s.err; s.close_all(); return rc; }
+  }
   rc = parse_header(s, h, err);
   if (rc == XVK_OK && dst != nullptr) {
-    if (h->rows > cap_rows) {
-      set_err(err, "key %s: %d rows do not fit the %lld rows left in the destination", e.key.c_str(), h->rows, (long long)cap_rows);
+    const int32_t first = start < 0 ? 0 : start;
+    const int32_t count = start < 0 ? h->rows : length;
+    if (count > cap_rows) {
+      set_err(err, "key %s: %d rows do not fit the %lld rows left in the destination", e.key.c_str(), count, (long long)cap_rows);
       rc = XVK_ECAPACITY;
     } else {
-      rc = decode_body(s, *h, 0, h->rows, dst, ld, scratch, err);
+      rc = decode_body(s, *h, first, count, dst, ld, scratch, err);
+      if (rc != XVK_OK && err->find("key ") != 0) *err = "key " + e.key + ": " + *err;
     }
   }
   const int rc2 = s.close_all();
   if (rc == XVK_OK && rc2 != XVK_OK) { *err = s.err; rc = rc2; }
   return rc;
 }
+
+// Parked worker threads shared by every reader of the process: a batch of the ark reader and the segments of a training batch
+// are ~1 ms jobs, and starting 8-32 threads for each of them cost a quarter of that.  One job at a time (a caller that finds
+// the pool busy starts its own threads as before); the caller works as thread 0.  A forked child finds the parent's pid
+// recorded and starts over with no workers (the parent's threads do not exist there).
+class WorkerPool {
+  // Everything the workers touch lives in one heap object: a forked child cannot reuse the parent's (its condition variables
+  // were copied with waiters that do not exist in the child), so it abandons that object and starts a fresh one.
+  struct State {
+    std::mutex mu;
+    std::condition_variable cv_start, cv_done;
+    std::vector<std::thread> workers;
+    const std::function<void(int)>* job = nullptr;
+    int job_n = 0, pending = 0;
+    uint64_t gen = 0;
+    bool stop = false;
+  };
+
+ public:
+  bool run(int n, const std::function<void(int)>& fn) {
+    std::unique_lock<std::mutex> use(use_mu_, std::try_to_lock);
+    if (!use.owns_lock()) return false;
+    if (owner_pid_ != getpid()) {                         // first use, or a forked child (the old state is leaked on purpose)
+      st_ = new State();
+      owner_pid_ = getpid();
+    }
+    State* st = st_;
+    while (static_cast<int>(st->workers.size()) < n - 1) {
+      const int w = static_cast<int>(st->workers.size()) + 1;
+      st->workers.emplace_back([st, w] { loop(st, w); });
+    }
+    {
+      std::lock_guard<std::mutex> lock(st->mu);
+      st->job = &fn;
+      st->job_n = n;
+      st->pending = n - 1;
+      ++st->gen;
+    }
+    st->cv_start.notify_all();
+    fn(0);
+    std::unique_lock<std::mutex> lock(st->mu);
+    st->cv_done.wait(lock, [st] { return st->pending == 0; });
+    st->job = nullptr;
+    return true;
+  }
+  ~WorkerPool() {
+    if (!st_ || owner_pid_ != getpid()) return;           // never used here, or a forked child: nothing to join
+    {
+      std::lock_guard<std::mutex> lock(st_->mu);
+      st_->stop = true;
+    }
+    st_->cv_start.notify_all();
+    for (auto& t : st_->workers) t.join();
+    delete st_;
+  }
+
+ private:
+  static void loop(State* st, int w) {
+    uint64_t seen = 0;
+    for (;;) {
+      const std::function<void(int)>* job = nullptr;
+      {
+        std::unique_lock<std::mutex> lock(st->mu);
+        st->cv_start.wait(lock, [&] { return st->stop || st->gen != seen; });
+        if (st->stop) return;
+        seen = st->gen;
+        if (w < st->job_n) job = st->job;
+      }
+      if (!job) continue;
+      (*job)(w);
+      std::lock_guard<std::mutex> lock(st->mu);
+      if (--st->pending == 0) st->cv_done.notify_one();
+    }
+  }
+  std::mutex use_mu_;
+  State* st_ = nullptr;
+  pid_t owner_pid_ = -1;
+};
+WorkerPool g_pool;
 
 template <class Fn>
 int parallel_for(int64_t n, int threads, Fn fn, std::string* err) {
@@ -826,8 +965,8 @@ int parallel_for(int64_t n, int threads, Fn fn, std::string* err) {
   std::atomic<int64_t> next(0);
   std::atomic<int> status(XVK_OK);
   std::vector<std::string> errs(threads);
-  auto work = [&](int tid) {
-    std::vector<uint8_t> scratch;
+  const std::function<void(int)> work = [&](int tid) {
+    static thread_local std::vector<uint8_t> scratch;       // decode scratch of this thread, kept across jobs
     for (;;) {
       const int64_t i = next.fetch_add(1);
       if (i >= n || status.load() != XVK_OK) return;
@@ -835,9 +974,10 @@ int parallel_for(int64_t n, int threads, Fn fn, std::string* err) {
       if (rc != XVK_OK) { int expect = XVK_OK; status.compare_exchange_strong(expect, rc); return; }
     }
   };
+  static const bool no_pool = getenv("XVK_NO_POOL") != nullptr;      // A/B switch: a fresh set of threads per job
   if (threads == 1) {
     work(0);
-  } else {
+  } else if (no_pool || !g_pool.run(threads, work)) {
     std::vector<std::thread> pool;
     for (int t = 0; t < threads; ++t) pool.emplace_back(work, t);
     for (auto& th : pool) th.join();
@@ -893,7 +1033,7 @@ const char* xvk_scp_rxfile(const xvk_scp* s, int64_t i) {
 int xvk_scp_dims(xvk_scp* s, int64_t i, int32_t* kind, int32_t* rows, int32_t* cols) {
   if (!s || i < 0 || i >= static_cast<int64_t>(s->entries.size())) return XVK_EINVAL;
   ObjHeader h;
-  const int rc = scp_fetch(s->entries[i], &h, nullptr, 0, 0, &s->scratch, &s->err);
+  const int rc = scp_fetch(s, s->entries[i], &h, nullptr, 0, 0, &s->scratch, &s->err);
   if (rc != XVK_OK) return rc;
   if (kind) *kind = h.kind;
   if (rows) *rows = h.rows;
@@ -904,7 +1044,7 @@ int xvk_scp_dims(xvk_scp* s, int64_t i, int32_t* kind, int32_t* rows, int32_t* c
 int xvk_scp_read_f32(xvk_scp* s, int64_t i, float* dst, int64_t ld) {
   if (!s || !dst || i < 0 || i >= static_cast<int64_t>(s->entries.size())) return XVK_EINVAL;
   ObjHeader h;
-  return scp_fetch(s->entries[i], &h, dst, ld, INT64_MAX, &s->scratch, &s->err);
+  return scp_fetch(s, s->entries[i], &h, dst, ld, INT64_MAX, &s->scratch, &s->err);
 }
 
 int xvk_scp_read_many_f32(xvk_scp* s, const int64_t* idx, int64_t n, float* dst, int64_t ld, const int64_t* row_off,
@@ -915,9 +1055,24 @@ int xvk_scp_read_many_f32(xvk_scp* s, const int64_t* idx, int64_t n, float* dst,
     if (idx[k] < 0 || idx[k] >= count || row_off[k] < 0 || row_off[k] > cap_rows) { s->err = "index or row offset out of range"; return XVK_EINVAL; }
   return parallel_for(n, threads, [&](int64_t k, int, std::vector<uint8_t>* scratch, std::string* err) {
     ObjHeader h;
-    const int rc = scp_fetch(s->entries[idx[k]], &h, dst + row_off[k] * ld, ld, cap_rows - row_off[k], scratch, err);
+    const int rc = scp_fetch(s, s->entries[idx[k]], &h, dst + row_off[k] * ld, ld, cap_rows - row_off[k], scratch, err);
     if (rc == XVK_OK && rows_out) rows_out[k] = h.rows;
     return rc;
+  }, &s->err);
+}
+
+int xvk_scp_read_segments_f32(xvk_scp* s, const int64_t* idx, const int32_t* start, const int32_t* length, int64_t n, float* dst,
+                              int64_t ld, const int64_t* row_off, int64_t cap_rows, int32_t threads) {
+  if (!s || !idx || !start || !length || !dst || !row_off || n < 0) return XVK_EINVAL;
+  const int64_t count = static_cast<int64_t>(s->entries.size());
+  for (int64_t k = 0; k < n; ++k)
+    if (idx[k] < 0 || idx[k] >= count || start[k] < 0 || length[k] < 0 || row_off[k] < 0 || row_off[k] > cap_rows) {
+      s->err = "index, segment or row offset out of range";
+      return XVK_EINVAL;
+    }
+  return parallel_for(n, threads, [&](int64_t k, int, std::vector<uint8_t>* scratch, std::string* err) {
+    ObjHeader h;
+    return scp_fetch(s, s->entries[idx[k]], &h, dst + row_off[k] * ld, ld, cap_rows - row_off[k], scratch, err, start[k], length[k]);
   }, &s->err);
 }
 
@@ -928,7 +1083,7 @@ int xvk_scp_dims_many(xvk_scp* s, const int64_t* idx, int64_t n, int32_t* rows_o
     if (idx[k] < 0 || idx[k] >= count) { s->err = "index out of range"; return XVK_EINVAL; }
   return parallel_for(n, threads, [&](int64_t k, int, std::vector<uint8_t>* scratch, std::string* err) {
     ObjHeader h;
-    const int rc = scp_fetch(s->entries[idx[k]], &h, nullptr, 0, 0, scratch, err);
+    const int rc = scp_fetch(s, s->entries[idx[k]], &h, nullptr, 0, 0, scratch, err);
     if (rc == XVK_OK) {
       if (rows_out) rows_out[k] = h.rows;
       if (cols_out) cols_out[k] = h.cols;

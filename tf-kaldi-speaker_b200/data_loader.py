@@ -73,52 +73,68 @@ class RandomSegmentLoader(object):
         self.threads = threads
         self.sample_with_prob = sample_with_prob
         self.rd = random.Random(seed)
+        self.rng = np.random.default_rng(seed)
         self.spk_frames = np.array([int(self.frames[self.spk_utts[s]].sum()) for s in self.speakers], np.float64)
-        self.pool = list(self.speakers)
+        # [speaker, slot] tables of scp entry indices and frame counts (-1 / 0 beyond a speaker's utterances): a batch is
+        # drawn with a handful of array operations instead of a Python loop over its speakers
+        width = max(len(self.spk_utts[s]) for s in self.speakers)
+        self.utt_table = np.full((len(self.speakers), width), -1, np.int64)
+        self.len_table = np.zeros((len(self.speakers), width), np.int64)
+        for row, spk in enumerate(self.speakers):
+            u = self.spk_utts[spk]
+            self.utt_table[row, :len(u)] = u
+            self.len_table[row, :len(u)] = self.frames[u]
+        self.spk_labels = np.asarray(self.speakers, np.int32)
+        self.max_frames = self.len_table.max(axis=1)
+        self.pool = np.arange(len(self.speakers))
         if len(self.pool) < self.num_speakers:            # dataset/data_loader.py:293-297: duplicate speakers
-            self.pool = self.pool * (self.num_speakers // len(self.pool) + 1)
+            self.pool = np.tile(self.pool, self.num_speakers // len(self.pool) + 1)
 
-    def _draw_speakers(self):
-        if self.sample_with_prob:
-            p = self.spk_frames / self.spk_frames.sum()
-            rng = np.random.default_rng(self.rd.getrandbits(32))
-            if len(self.speakers) >= self.num_speakers:
-                return [self.speakers[i] for i in rng.choice(len(self.speakers), self.num_speakers, replace=False, p=p)]
-        return self.rd.sample(self.pool, self.num_speakers)
+    def _draw_speakers(self, length):
+        """Row indices (into self.speakers) of the batch's speakers: drawn without replacement (optionally with probability
+        proportional to their frame count), speakers without an utterance longer than `length` replaced by others that have
+        one (dataset/data_loader.py:322-333)."""
+        n = self.num_speakers
+        if self.sample_with_prob and len(self.speakers) >= n:
+            rows = self.rng.choice(len(self.speakers), n, replace=False, p=self.spk_frames / self.spk_frames.sum())
+        else:
+            rows = self.rng.permutation(self.pool)[:n]
+        bad = self.max_frames[rows] <= length
+        if bad.any():
+            usable = np.nonzero(self.max_frames > length)[0]
+            if usable.size == 0:
+                raise DataOutOfRange("no utterance longer than %d frames" % length)
+            fresh = np.setdiff1d(usable, rows[~bad])
+            cand = fresh if fresh.size >= bad.sum() else usable
+            rows = rows.copy()
+            rows[bad] = self.rng.choice(cand, int(bad.sum()), replace=cand.size < bad.sum())
+        return rows
 
     def fetch(self):
         """-> (features [B, L, dim] float32, labels [B] int32), B = num_speakers * num_segments."""
-        batch_speakers = self._draw_speakers()
-        length = self.rd.randint(self.min_len, self.max_len)
-        b = self.num_speakers * self.num_segments
-        labels = np.zeros(b, np.int32)
-        picks = []
-        for i, spk in enumerate(batch_speakers):
-            for _ in range(1000):
-                utts = self.spk_utts[spk]
-                ok = utts[self.frames[utts] > length]
-                if len(ok):
-                    break
-                # the speaker has no utterance long enough for this batch: resample it (dataset/data_loader.py:330-333)
-                rest = list(set(self.speakers) - set(batch_speakers)) or self.speakers
-                spk = self.rd.choice(rest)
-                batch_speakers[i] = spk
-            else:
-                raise DataOutOfRange("no utterance longer than %d frames" % length)
-            labels[i * self.num_segments:(i + 1) * self.num_segments] = spk
-            ok = list(ok)
-            if len(ok) < self.num_segments:
-                ok = ok * (self.num_segments // len(ok) + 1)
-            picks.extend(self.rd.sample(ok, self.num_segments))
-        idx = np.asarray(picks, np.int64)
-        rows = self.frames[idx]
-        packed, _ = self.table.read_many(idx, rows=rows, threads=self.threads,
-                                         out=np.empty((int(rows.sum()), self.feat_dim), np.float32))
-        off = np.concatenate([[0], np.cumsum(rows, dtype=np.int64)])
-        features = np.empty((b, length, self.dim), np.float32)
-        for j in range(b):
-            start = self.rd.randint(0, int(rows[j]) - length) if self.shuffle else 0
-            features[j] = packed[off[j] + start:off[j] + start + length, :self.dim]
+        length = int(self.rng.integers(self.min_len, self.max_len + 1))
+        rows = self._draw_speakers(length)
+        m = self.num_segments
+        # per speaker: m utterances longer than L, without replacement while there are enough of them (the reference repeats
+        # the list when it is short): random keys, invalid slots last, the first m slots of the order (cycled over the valid ones)
+        ok = self.len_table[rows] > length
+        keys = self.rng.random(ok.shape)
+        keys[~ok] = 2.0
+        order = np.argsort(keys, axis=1)
+        n_ok = ok.sum(axis=1)
+        slot = order[np.arange(len(rows))[:, None], np.arange(m)[None, :] % n_ok[:, None]]
+        idx = self.utt_table[rows[:, None], slot].reshape(-1)
+        frames = self.len_table[rows[:, None], slot].reshape(-1)
+        labels = np.repeat(self.spk_labels[rows], m)
+        b = idx.size
+        starts = (self.rng.random(b) * (frames - length + 1)).astype(np.int32) if self.shuffle else np.zeros(b, np.int32)
+        if self.dim == self.feat_dim:
+            features = self.table.read_segments(idx, starts, length, threads=self.threads,
+                                                out=np.empty((b, length, self.dim), np.float32))
+        else:
+            full = self.table.read_segments(idx, starts, length, threads=self.threads,
+                                            out=np.empty((b, length, self.feat_dim), np.float32))
+            features = np.ascontiguousarray(full[:, :, :self.dim])
         return features, labels
 
     def stop(self):

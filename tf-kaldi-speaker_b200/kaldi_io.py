@@ -73,6 +73,7 @@ PROTOTYPES = {
     "xvk_scp_dims": (C.c_int, [_p, C.c_int64, _i32p, _i32p, _i32p]),
     "xvk_scp_read_f32": (C.c_int, [_p, C.c_int64, _p, C.c_int64]),
     "xvk_scp_read_many_f32": (C.c_int, [_p, _i64p, C.c_int64, _p, C.c_int64, _i64p, C.c_int64, _i32p, C.c_int32]),
+    "xvk_scp_read_segments_f32": (C.c_int, [_p, _i64p, _i32p, _i32p, C.c_int64, _p, C.c_int64, _i64p, C.c_int64, C.c_int32]),
     "xvk_scp_dims_many": (C.c_int, [_p, _i64p, C.c_int64, _i32p, _i32p, C.c_int32]),
     "xvk_scp_error": (C.c_char_p, [_p]),
     "xvk_scp_close": (None, [_p]),
@@ -449,6 +450,24 @@ class ScpTable(object):
         if not np.array_equal(got, rows):
             raise KaldiIOError("scp entries changed size between the header pass and the read")
         return out[:total], rows
+
+    def read_segments(self, idx, starts, length, out=None, threads=8):
+        """Rows [starts[k], starts[k] + length) of entries idx[k] -> [n, length, dim] float32 (`out`: a C-contiguous array of
+        that shape to fill in place): the random segments of a training batch in one native call."""
+        idx = np.ascontiguousarray(idx, np.int64)
+        starts = np.ascontiguousarray(starts, np.int32)
+        n, length = len(idx), int(length)
+        if out is None:
+            dim = int(self.dims(idx[:1])[1][0]) if n else 0
+            out = np.empty((n, length, dim), np.float32)
+        if out.shape[:2] != (n, length) or out.dtype != np.float32 or not out.flags.c_contiguous:
+            raise ValueError("read_segments: destination must be C-contiguous float32 [%d, %d, dim]" % (n, length))
+        lens = np.full(n, length, np.int32)
+        off = np.arange(n, dtype=np.int64) * length
+        self._check(self._lib.xvk_scp_read_segments_f32(self._h, idx.ctypes.data_as(_i64p), starts.ctypes.data_as(_i32p),
+                                                        lens.ctypes.data_as(_i32p), n, _ptr(out), out.shape[2],
+                                                        off.ctypes.data_as(_i64p), n * length, threads))
+        return out
 
     def close(self):
         if self._h:
