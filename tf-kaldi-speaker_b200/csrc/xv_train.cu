@@ -18,6 +18,13 @@
 // stream as soon as its last gradient is written, so all but the last (small) bucket overlap the rest of the backward
 // pass.  ncclCommGetAsyncError is polled while the host waits for a step; a failing rank aborts the communicator.
 //
+// Streams of a step (bf16 path): the compute stream carries the critical chain (forward, loss, data gradients, batch-norm
+// backward); a side stream carries everything that only produces parameter gradients (weight-gradient GEMMs of all layers,
+// the loss head's weight gradient), the work with slack at the step boundaries (gradient zeros, AM-softmax column norms,
+// the recast of the data-gradient weight layouts) and the early update of bucket 0; the communication stream carries the
+// bucketed all-reduces (and bucket 0's update behind its all-reduce); the copy stream carries the next batch of a
+// pipelined step (xv_train_submit / xv_train_collect).  Events order every buffer reuse across them.
+//
 // Two precisions: "bf16" (product path: the 14 frame-layer GEMMs on tcgen05 with bf16 operands, fp32 masters) and
 // "fp32" (validation path: SIMT FFMA GEMMs); both share every other kernel (xv_train_kernels.cuh).
 #include <dlfcn.h>
