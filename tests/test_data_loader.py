@@ -64,3 +64,32 @@ def test_random_segment_loader_batch_contract(tmp_path):
     os.remove(os.path.join(data, "utt2num_frames"))
     ld3 = RandomSegmentLoader(data, spklist, num_speakers=3, num_segments=1, min_len=35, max_len=35, seed=2)
     assert ld3.fetch()[0].shape == (3, 35, 7)
+
+
+def test_sequential_segment_loader_contract(tmp_path):
+    """KaldiDataSeqQueue / batch_sequence (dataset/data_loader.py:498-549): len // batch + 1 full batches in spk2utt order, the
+    list wrapping around, one length per batch cut to the shortest utterance, segments from frame 0, DataOutOfRange at the end."""
+    import pytest
+    from xvector_b200.data_loader import DataOutOfRange, SequentialSegmentLoader
+    data, spklist, mats = _make_data(tmp_path)
+    keys = list(mats)                                           # spk2utt order: speaker by speaker
+    ld = SequentialSegmentLoader(data, spklist, batch_size=4, min_len=35, max_len=35)
+    assert ld.num_total_speakers == 6 and ld.num_batches == len(keys) // 4 + 1 and ld.batch_size == 4
+    seen = []
+    for i in range(ld.num_batches):
+        x, y = ld.fetch()
+        want = [keys[(4 * i + j) % len(keys)] for j in range(4)]
+        length = min(35, min(mats[k].shape[0] for k in want))   # speaker 5's utterances have 30 frames
+        assert x.shape == (4, length, 7) and y.dtype == np.int32
+        for j, k in enumerate(want):
+            assert np.array_equal(x[j], mats[k][:length]) and y[j] == int(k[3])
+        seen += want
+    assert set(seen) == set(keys)
+    with pytest.raises(DataOutOfRange):
+        ld.fetch()
+    # fewer utterances than a batch: one batch of all of them (min(batch_size, len)), twice over the list (num_batches = 1)
+    ld2 = SequentialSegmentLoader(data, spklist, batch_size=64, min_len=20, max_len=20, dim=5)
+    x, y = ld2.fetch()
+    assert x.shape == (len(keys), 20, 5) and ld2.num_batches == 1
+    with pytest.raises(DataOutOfRange):
+        ld2.fetch()

@@ -127,6 +127,58 @@ def test_trainer_train_epoch_over_a_kaldi_directory(tmp_path):
     trainer.close()
 
 
+def test_trainer_valid_matches_oracle(tmp_path):
+    """Trainer.valid (model/trainer.py:756-884) after two training steps: the eval-mode network output of the CURRENT
+    variables from the device, the loss head on the host -- against the oracle's eval-mode forward of the same variables
+    and the oracle's loss, batch by batch in the sequential loader's order."""
+    from oracle import numpy_ref, synth, train_ref
+    from xvector_b200 import kaldi_io
+    from xvector_b200.data_loader import DataOutOfRange, SequentialSegmentLoader
+    from xvector_b200.model.trainer import Trainer
+    rng = np.random.default_rng(1)
+    data = tmp_path / "data"
+    data.mkdir()
+    dim, n_spk = 24, 6
+    with kaldi_io.open_or_fd("ark,scp:%s,%s" % (data / "feats.ark", data / "feats.scp"), "wb") as fd:
+        for s in range(n_spk):
+            for u in range(3):
+                m = (rng.standard_normal((int(rng.integers(60, 100)), dim)) + 0.5 * np.sin(s + np.arange(dim))).astype(np.float32)
+                kaldi_io.write_mat(fd, m, "s%02d-u%d" % (s, u))
+    (data / "spk2utt").write_text("".join("s%02d s%02d-u0 s%02d-u1 s%02d-u2\n" % (s, s, s, s) for s in range(n_spk)))
+    spklist = tmp_path / "spklist"
+    spklist.write_text("".join("s%02d %d\n" % (s, s) for s in range(n_spk)))
+    cfg = dict(synth.TDNN_AMSOFTMAX_CONFIG, num_speakers_per_batch=4, num_segments_per_speaker=2, min_segment_len=40,
+               max_segment_len=60, valid_max_iterations=100, seed=2)
+    w = synth.add_softmax_weights(synth.make_tdnn_weights(dim, cfg, seed=33), n_spk)
+    trainer = Trainer(_params(tmp_path, cfg), str(tmp_path), dim, num_speakers=n_spk, precision="fp32")
+    trainer.set_weights(w)
+    trainer.build("train")
+    trainer.build("valid")
+    x, y = synth.config5_batch(8, 50, dim, n_spk, seed=34, speaker_signal=1.0)
+    for _ in range(2):
+        trainer.train_step(x, y, 0.05)
+    loss, emb, labels = trainer.valid(str(data), str(spklist), output_embeddings=True)
+    got = trainer.variables()
+    upd = {k: np.asarray(v).reshape(np.asarray(w[k]).shape) for k, v in got.items()}
+    oparams = numpy_ref.OracleParams(**cfg)
+    ld = SequentialSegmentLoader(str(data), str(spklist), batch_size=8, min_len=50, max_len=50, dim=dim)
+    ref_losses, ref_emb, ref_labels = [], [], []
+    while True:
+        try:
+            f, lab = ld.fetch()
+        except DataOutOfRange:
+            break
+        out = numpy_ref.predict(f, oparams, upd, dim, node="output")
+        ref_losses.append(train_ref.loss_forward_backward(out, lab, upd, oparams, trainer.curr_step, want_grad=False)[0])
+        ref_emb.append(numpy_ref.predict(f, oparams, upd, dim))
+        ref_labels.append(lab)
+    assert len(ref_losses) == 18 // 8 + 1
+    assert abs(loss - np.mean(ref_losses)) <= 1e-4 * abs(np.mean(ref_losses)), (loss, ref_losses)
+    assert emb.shape == (24, 512) and np.array_equal(labels, np.concatenate(ref_labels))
+    assert max_rel(emb, np.concatenate(ref_emb)) <= TOL["fp32"]
+    trainer.close()
+
+
 @pytest.mark.skipif(_n_gpus() < 2, reason="needs 2 GPUs (run with gpurun --gpus 2)")
 def test_trainer_mgpu_matches_two_tower_oracle(tmp_path):
     from oracle import numpy_ref, synth, train_ref

@@ -199,3 +199,101 @@ def test_plan_arrays_equals_the_per_utterance_chunk_plan():
         assert [(int(u), int(s), int(z)) for u, s, z in zip(owners, starts, sizes)] == [(u, s, z) for u, s, z in work]
     o, s, z = plan_arrays(np.array([3, 5]), 100, 25)
     assert o.size == 0 and s.size == 0 and z.size == 0
+
+
+def test_host_losses_match_the_training_oracle():
+    """model/loss.py of the package (validation) against oracle/train_ref.loss_forward_backward, which is pinned on the
+    reference's own numpy AM-softmax (tests/test_train_oracle.py)."""
+    from oracle import numpy_ref, synth, train_ref
+    from xvector_b200.model import loss as L
+    rng = np.random.default_rng(8)
+    f = rng.standard_normal((16, 48)) * 3
+    y = rng.integers(0, 37, 16)
+    w = {"softmax/output/kernel": rng.standard_normal((48, 37)).astype(np.float32),
+         "softmax/output/bias": rng.standard_normal(37).astype(np.float32)}
+    for cfg, step in ((dict(synth.TDNN_AMSOFTMAX_CONFIG), 0), (dict(synth.TDNN_AMSOFTMAX_CONFIG), 12345),
+                      (dict(synth.TDNN_AMSOFTMAX_CONFIG, loss_func="softmax"), 7)):
+        params = numpy_ref.OracleParams(**cfg)
+        ref, _, _ = train_ref.loss_forward_backward(f, y, w, params, step, want_grad=False)
+        got = L.valid_loss(cfg["loss_func"], f.astype(np.float32), y, w, cfg, step)
+        assert abs(got - ref) <= 1e-6 * abs(ref), (cfg["loss_func"], got, ref)
+    with pytest.raises(NotImplementedError):
+        L.valid_loss("asoftmax", f, y, w, {}, 0)
+
+
+def test_trainer_valid_with_a_stub_engine(tmp_path):
+    """Trainer.valid (model/trainer.py:756-884): sequential batches of (min + max) / 2 frames, eval-mode network output from
+    the device path (a stub here: the mean over frames, projected), host loss head, mean of the batch losses, embeddings
+    and labels on request, at most valid_max_iterations batches."""
+    from oracle import synth
+    from test_data_loader import _make_data
+    from xvector_b200.misc.utils import ParamsPlain
+    from xvector_b200.model import loss as L
+    from xvector_b200.model.trainer import Trainer
+    data, spklist, mats = _make_data(tmp_path)
+    cfg = dict(synth.TDNN_AMSOFTMAX_CONFIG, min_segment_len=30, max_segment_len=40, num_speakers_per_batch=2,
+               num_segments_per_speaker=2, valid_max_iterations=3)
+    params = ParamsPlain()
+    params.dict.update(cfg)
+    rng = np.random.default_rng(9)
+    proj = rng.standard_normal((7, 12)).astype(np.float32)
+    weights = {"softmax/output/kernel": rng.standard_normal((12, 6)).astype(np.float32)}
+
+    class StubEngine(object):
+        calls = []
+
+        def forward(self, packed, lengths, node):
+            self.calls.append(node)
+            t = int(lengths[0])
+            pooled = packed.reshape(len(lengths), t, -1).mean(axis=1)
+            return pooled @ proj if node == "output" else pooled
+
+        def close(self):
+            pass
+
+    tr = Trainer(params, str(tmp_path / "model"), 7, num_speakers=6, single_cpu=True)
+    tr.engine, tr.is_built, tr.is_loaded, tr._weights = StubEngine(), True, True, weights
+    tr._has_model = lambda: False
+    loss, emb, labels = tr.valid(data, spklist, output_embeddings=True)
+    keys = list(mats)
+    want, want_labels = [], []
+    for i in range(3):                                          # valid_max_iterations of the 5 batches
+        ks = [keys[(4 * i + j) % len(keys)] for j in range(4)]
+        length = min(35, min(mats[k].shape[0] for k in ks))
+        feats = np.stack([mats[k][:length] for k in ks])
+        lab = np.array([int(k[3]) for k in ks])
+        want.append(L.additive_margin_softmax(feats.mean(axis=1) @ proj, lab, weights["softmax/output/kernel"], cfg, 0))
+        want_labels.append(lab)
+    assert abs(loss - np.mean(want)) <= 1e-6 * abs(np.mean(want))
+    assert emb.shape == (12, 7) and np.array_equal(labels, np.concatenate(want_labels))
+    loss2, emb2, labels2 = tr.valid(data, spklist)
+    assert abs(loss2 - loss) < 1e-12 and emb2 is None and labels2 is None
+    with pytest.raises(NotImplementedError):
+        tr.valid(data, spklist, batch_type="end2end")
+
+
+def test_compute_cos_pairwise_eer():
+    """misc/utils.py:307-346: separable speakers -> 0, labels independent of the embeddings -> about one half, and the value
+    agrees with a direct threshold sweep of the same pair scores."""
+    from xvector_b200.misc.utils import compute_cos_pairwise_eer
+    rng = np.random.default_rng(10)
+    centers = np.eye(8, 16) * 5
+    labels = np.repeat(np.arange(8), 6)
+    tight = centers[labels] + 0.01 * rng.standard_normal((48, 16))
+    keep = tight.copy()
+    assert compute_cos_pairwise_eer(tight, labels) < 1e-6
+    assert np.array_equal(tight, keep)                          # the caller's array is left alone
+    noise = rng.standard_normal((200, 16))
+    assert 0.4 < compute_cos_pairwise_eer(noise, rng.integers(0, 5, 200)) < 0.6
+    # overlapping clusters: compare with the crossing of the empirical miss / false-alarm curves
+    loose = centers[labels] + 2.5 * rng.standard_normal((48, 16))
+    eer = compute_cos_pairwise_eer(loose, labels)
+    e = loose / np.linalg.norm(loose, axis=1, keepdims=True)
+    i, j = np.triu_indices(48, k=1)
+    sc, tgt = np.sum(e[i] * e[j], axis=1), labels[i] == labels[j]
+    best = min((abs(np.mean(sc[tgt] < t) - np.mean(sc[~tgt] >= t)), 0.5 * (np.mean(sc[tgt] < t) + np.mean(sc[~tgt] >= t)))
+               for t in np.sort(sc))
+    assert abs(eer - best[1]) < 0.02
+    # more embeddings than max_num_embeddings: subsampled every n // max
+    big = rng.standard_normal((2500, 8))
+    assert 0.4 < compute_cos_pairwise_eer(big, rng.integers(0, 3, 2500), max_num_embeddings=500) < 0.6

@@ -139,3 +139,81 @@ class RandomSegmentLoader(object):
 
     def stop(self):
         self.table.close()
+
+
+class SequentialSegmentLoader(object):
+    """Validation batches: the rule of the reference's KaldiDataSeqQueue / batch_sequence (dataset/data_loader.py:498-549,
+    :554-660) over the native scp reader.  Every utterance of the speakers in `spklist` appears once per pass, speaker by
+    speaker in spk2utt order; there are len // batch_size + 1 batches of min(batch_size, len) utterances, the list wrapping
+    around to fill the last one (:528-532); a batch takes ONE length in [min_len, max_len], shortened to its shortest
+    utterance (:535-541), and with shuffle=False every segment starts at frame 0.  fetch() raises DataOutOfRange after the
+    last batch (:642-657).  (The reference splits the list over `num_parallel` processes whose batches interleave in queue
+    order; here one stream yields them in list order.)"""
+
+    def __init__(self, data, spklist, batch_size=128, min_len=200, max_len=400, dim=None, shuffle=False, seed=0, threads=8):
+        self.table = kaldi_io.ScpTable(os.path.join(data, "feats.scp"))
+        keys = self.table.keys()
+        index_of = {k: i for i, k in enumerate(keys)}
+        n2f = os.path.join(data, "utt2num_frames")
+        if os.path.isfile(n2f):
+            frames = np.zeros(len(keys), np.int32)
+            with open(n2f) as f:
+                for line in f:
+                    u, n = line.split()
+                    if u in index_of:
+                        frames[index_of[u]] = int(n)
+            cols = self.table.dims(np.arange(1, dtype=np.int64))[1]
+        else:
+            frames, cols = self.table.dims(threads=threads)
+        self.feat_dim = int(cols[0])
+        self.dim = int(dim) if dim else self.feat_dim
+        spk2index = read_spklist(spklist)
+        self.num_total_speakers = len(spk2index)
+        order, labels = [], []
+        with open(os.path.join(data, "spk2utt")) as f:
+            for line in f:
+                parts = line.split()
+                if not parts or parts[0] not in spk2index:
+                    continue
+                for u in parts[1:]:
+                    if u in index_of:
+                        order.append(index_of[u])
+                        labels.append(spk2index[parts[0]])
+        if not order:
+            raise ValueError("no speaker of %s has features in %s" % (spklist, data))
+        self.rng = np.random.default_rng(seed)
+        order, labels = np.asarray(order, np.int64), np.asarray(labels, np.int32)
+        if shuffle:
+            perm = self.rng.permutation(len(order))
+            order, labels = order[perm], labels[perm]
+        self.num_batches = len(order) // int(batch_size) + 1
+        self.batch_size = min(int(batch_size), len(order))
+        need = self.num_batches * self.batch_size
+        reps = -(-need // len(order))
+        self.order, self.labels = np.tile(order, reps)[:need], np.tile(labels, reps)[:need]
+        self.frames = frames
+        self.min_len, self.max_len = int(min_len), int(max_len)
+        self.shuffle = shuffle
+        self.threads = threads
+        self.next_batch = 0
+
+    def fetch(self):
+        """-> (features [batch_size, L, dim] float32, labels [batch_size] int32); DataOutOfRange when the pass is over."""
+        if self.next_batch >= self.num_batches:
+            raise DataOutOfRange("the sequential loader has delivered its %d batches" % self.num_batches)
+        lo = self.next_batch * self.batch_size
+        self.next_batch += 1
+        idx = self.order[lo:lo + self.batch_size]
+        length = int(self.rng.integers(self.min_len, self.max_len + 1))
+        length = min(length, int(self.frames[idx].min()))
+        if self.shuffle:
+            starts = (self.rng.random(len(idx)) * (self.frames[idx] - length + 1)).astype(np.int32)
+        else:
+            starts = np.zeros(len(idx), np.int32)
+        full = self.table.read_segments(idx, starts, length, threads=self.threads,
+                                        out=np.empty((len(idx), length, self.feat_dim), np.float32))
+        features = full if self.dim == self.feat_dim else np.ascontiguousarray(full[:, :, :self.dim])
+        return features, self.labels[lo:lo + self.batch_size].copy()
+
+    def stop(self):
+        self.table.close()

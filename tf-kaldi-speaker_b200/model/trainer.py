@@ -108,7 +108,7 @@ class Trainer(object):
     def build(self, mode, noupdate_var_list=None):
         """model/trainer.py:309-376.  "predict" builds the embedding path; "train" builds the training step (network in
         training mode + loss + gradients + optimizer, :340-376); "valid" is accepted after "train" for call-site
-        compatibility (train.py:105-106 builds both) but valid() itself is outside this build's scope."""
+        compatibility (train.py:105-106 builds both): valid() runs the embedding path in eval mode and the loss head on the host."""
         assert (mode == "train" or mode == "valid" or mode == "predict")
         if mode == "predict":
             if self.engine is None:
@@ -264,8 +264,59 @@ class Trainer(object):
         self.save(self.curr_step)
         return last[0]
 
-    def valid(self, *args, **kwargs):
-        raise NotImplementedError("valid(): the validation loop (model/trainer.py:756-884) is outside this build's scope")
+    def valid(self, data, spklist, batch_type="softmax", output_embeddings=False, aux_data=None):
+        """model/trainer.py:756-884: the loss of the CURRENT variables over one sequential pass of the validation set, in
+        eval mode (batch norm on its moving statistics) -- batches of num_speakers_per_batch * num_segments_per_speaker
+        utterances cut to (min_segment_len + max_segment_len) / 2 frames from frame 0, at most valid_max_iterations of
+        them, the mean of the batch losses (tf.metrics.mean).  -> (valid_loss, embeddings, labels); the last two are None
+        unless output_embeddings (the caller computes EER from them, train.py:119-123).  The network output comes from
+        the device path (node "output"), the loss head runs on the host (model/loss.py here).  batch_type "end2end"
+        belongs to the end-to-end losses, which this build does not train."""
+        from ..data_loader import DataOutOfRange, SequentialSegmentLoader
+        from . import loss as host_loss
+        assert batch_type == "softmax" or batch_type == "end2end", "The batch_type can only be softmax or end2end"
+        if batch_type == "end2end":
+            raise NotImplementedError("valid(batch_type='end2end'): the end-to-end losses are outside this build's scope")
+        loss_func = self.params.dict.get("loss_func", "softmax")
+        if loss_func not in _TRAINABLE_LOSSES:
+            raise NotImplementedError("Not implement %s loss" % loss_func)
+        curr_step = self.curr_step if self.train_built else 0
+        if self.train_built:
+            self._refresh_predict_weights()
+        else:
+            if not self.is_built:
+                self.build("predict")
+            if self._has_model():
+                curr_step = self.load()
+            elif self._weights is None:
+                sys.exit("Cannot find model in %s" % self.model)
+        variables = self._weights
+        p = self.params.dict
+        length = (int(p["min_segment_len"]) + int(p["max_segment_len"])) // 2
+        loader = SequentialSegmentLoader(data, spklist, batch_size=int(p["num_speakers_per_batch"]) * int(p["num_segments_per_speaker"]),
+                                         min_len=length, max_len=length, dim=self.dim, shuffle=False)
+        losses, embeddings, all_labels = [], [], []
+        try:
+            for _ in range(int(p.get("valid_max_iterations", 1 << 30))):
+                try:
+                    features, labels = loader.fetch()
+                except DataOutOfRange:
+                    break
+                b, t, d = features.shape
+                packed = features.reshape(b * t, d)
+                lengths = np.full(b, t, np.int32)
+                out = self.engine.forward(packed, lengths, "output")
+                losses.append(host_loss.valid_loss(loss_func, out, labels, variables, p, curr_step))
+                if output_embeddings:
+                    embeddings.append(np.asarray(self.engine.forward(packed, lengths, self.params.embedding_node), np.float32))
+                    all_labels.append(labels)
+        finally:
+            loader.stop()
+        valid_loss = float(np.mean(losses)) if losses else 0.0
+        print("[Validation %d batches] valid loss: %f" % (len(losses), valid_loss), file=sys.stderr)
+        if output_embeddings and embeddings:
+            return valid_loss, np.concatenate(embeddings, axis=0), np.concatenate(all_labels, axis=0)
+        return valid_loss, None, None
 
     def set_embedding(self, embedding_node):
         """model/trainer.py:305-307."""
