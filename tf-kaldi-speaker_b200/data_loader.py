@@ -13,7 +13,6 @@ a random offset.
 Files read from the data directory: feats.scp, spk2utt, utt2num_frames (optional: lengths are otherwise taken from the
 matrix headers); spklist = "<speaker> <index>" lines (egs/voxceleb/v1/nnet/lib/train.py:83-84)."""
 import os
-import random
 
 import numpy as np
 
@@ -72,7 +71,6 @@ class RandomSegmentLoader(object):
         self.shuffle = shuffle
         self.threads = threads
         self.sample_with_prob = sample_with_prob
-        self.rd = random.Random(seed)
         self.rng = np.random.default_rng(seed)
         self.spk_frames = np.array([int(self.frames[self.spk_utts[s]].sum()) for s in self.speakers], np.float64)
         # [speaker, slot] tables of scp entry indices and frame counts (-1 / 0 beyond a speaker's utterances): a batch is

@@ -11,7 +11,6 @@ libxvector.so.
 Validation (build("valid") / valid()), summaries and the insight/finetune variants are outside this build's scope."""
 import concurrent.futures
 import os
-import re
 import sys
 
 import numpy as np
