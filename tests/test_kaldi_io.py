@@ -339,3 +339,41 @@ def test_scp_read_segments(tmp_path):
     for k, (i, s) in enumerate(((2, 5), (0, 0), (3, 11))):
         assert np.array_equal(seg[k], whole[off[i] + s:off[i] + s + 9])
     t2.close()
+
+
+def test_feature_reader_interface(tmp_path):
+    """FeatureReader (dataset/kaldi_io.py:40-150): get_dim, read / read_segment by "utt path:offset" strings with the
+    reference's length / shuffle / start rules."""
+    from xvector_b200 import kaldi_io as K
+    rng = np.random.default_rng(12)
+    data = tmp_path / "data"
+    data.mkdir()
+    mats = {}
+    with K.open_or_fd("ark,scp:%s,%s" % (data / "feats.ark", data / "feats.scp"), "wb") as f:
+        for i in range(5):
+            m = rng.standard_normal((int(rng.integers(30, 60)), 9)).astype(np.float32)
+            mats["utt%d" % i] = m
+            K.write_mat(f, m, key="utt%d" % i)
+    (data / "utt2num_frames").write_text("".join("%s %d\n" % (k, m.shape[0]) for k, m in mats.items()))
+    lines = [l.strip() for l in open(data / "feats.scp")]
+    fr = K.FeatureReader(str(data))
+    assert fr.get_dim() == 9 and fr.dim == 9 and fr.utt2num_frames["utt3"] == mats["utt3"].shape[0]
+    for line in lines:
+        utt = line.split(" ")[0]
+        m, start = fr.read(line)
+        assert start is None and np.array_equal(m, mats[utt])
+        seg, start = fr.read_segment(line, 20)                       # no shuffle: from frame 0
+        assert start == 0 and np.array_equal(seg, mats[utt][:20])
+        seg, start = fr.read_segment(line, 20, shuffle=True)
+        assert 0 <= start <= mats[utt].shape[0] - 20 and np.array_equal(seg, mats[utt][start:start + 20])
+        seg, start = fr.read_segment(line, 10, start=7)
+        assert start == 7 and np.array_equal(seg, mats[utt][7:17])
+        whole, start = fr.read_segment(line, 1000)                   # longer than the utterance: cut to it
+        assert start == 0 and np.array_equal(whole, mats[utt])
+        part, start = fr.read(line, length=15, shuffle=True)
+        assert np.array_equal(part, mats[utt][start:start + 15])
+    with pytest.raises(AssertionError):
+        fr.read_segment(lines[0], 10, shuffle=True, start=3)
+    with pytest.raises(IOError):
+        fr.read("nokey /nonexistent:0")
+    fr.close()

@@ -523,3 +523,75 @@ class BatchReader(object):
 
     def close(self):
         self.fd.close()
+
+
+class FeatureReader(object):
+    """dataset/kaldi_io.py:40-150: random access to the features of a Kaldi data directory by "utt path:offset" strings (the
+    lines of feats.scp), whole matrices (read) or segments (read_segment), with the reference's argument rules: `length` longer
+    than the utterance is cut to it, `shuffle` draws the start, an explicit `start` forbids shuffle.  -> (matrix, start).
+    Reads go through the native table (one mapping per ark, no descriptor juggling); segments read only their own rows.
+    FeatureReaderV2's byte-offset arithmetic (dataset/kaldi_io.py:152-338) exists for the same purpose and is covered by the
+    same calls."""
+
+    def __init__(self, data):
+        import random
+        self.data = data
+        self._rd = random.Random()
+        scp = os.path.join(data, "feats.scp")
+        self._table = ScpTable(scp)
+        self._index = {}
+        for i in range(len(self._table)):
+            self._index[self._table.key(i) + " " + self._table.rxfile(i)] = i
+        self.dim = self.get_dim()
+        self.utt2num_frames = {}
+        n2f = os.path.join(data, "utt2num_frames")
+        assert os.path.exists(n2f), "[Error] Expect utt2num_frames exists in %s " % data
+        with open(n2f) as f:
+            for line in f:
+                utt, length = line.strip().split(" ")
+                self.utt2num_frames[utt] = int(length)
+
+    def get_dim(self):
+        return int(self._table.dims(np.arange(1, dtype=np.int64))[1][0])
+
+    def close(self):
+        self._table.close()
+
+    def _entry(self, file_or_fd):
+        try:
+            return self._index[file_or_fd.strip()]
+        except KeyError:
+            raise IOError("Cannot read features from %s" % file_or_fd)
+
+    def read(self, file_or_fd, length=None, shuffle=False, start=None):
+        i = self._entry(file_or_fd)
+        try:
+            mat, _ = self._table.read_many(np.array([i], np.int64), threads=1)
+        except KaldiIOError:
+            raise IOError("Cannot read features from %s" % file_or_fd)
+        if length is not None:
+            if start is None:
+                num = mat.shape[0]
+                length = num if length > num else length
+                start = self._rd.randint(0, num - length) if shuffle else 0
+            else:
+                assert not shuffle, "The start point is specified, thus shuffling is invalid."
+            mat = mat[start:start + length, :]
+        return mat, start
+
+    def read_segment(self, file_or_fd, length=None, shuffle=False, start=None):
+        if length is None:
+            return self.read(file_or_fd)
+        i = self._entry(file_or_fd)
+        utt = file_or_fd.strip().split(" ")[0]
+        if start is None:
+            num = self.utt2num_frames[utt]
+            length = num if length > num else length
+            start = self._rd.randint(0, num - length) if shuffle else 0
+        else:
+            assert not shuffle, "The start point is specified, thus shuffling is invalid."
+        try:
+            mat = self._table.read_segments(np.array([i], np.int64), np.array([start], np.int32), int(length), threads=1)[0]
+        except KaldiIOError:
+            raise IOError("Cannot read features from %s" % file_or_fd)
+        return mat, start
