@@ -93,3 +93,31 @@ def test_sequential_segment_loader_contract(tmp_path):
     assert x.shape == (len(keys), 20, 5) and ld2.num_batches == 1
     with pytest.raises(DataOutOfRange):
         ld2.fetch()
+
+
+def test_reference_queue_names(tmp_path):
+    """KaldiDataRandomQueue / KaldiDataSeqQueue by the reference's names and signatures (dataset/data_loader.py:369, :554):
+    num_total_speakers before start(), set_batch / set_length, start / fetch / stop, DataOutOfRange at the end of a pass."""
+    import pytest
+    from xvector_b200.data_loader import DataOutOfRange, KaldiDataRandomQueue, KaldiDataSeqQueue
+    data, spklist, mats = _make_data(tmp_path)
+    q = KaldiDataRandomQueue(data, spklist, num_parallel=8, max_qsize=10, num_speakers=3, num_segments=2, min_len=32, max_len=36)
+    assert q.num_total_speakers == 6
+    q.set_batch(2, 2)
+    q.set_length(33, 33)
+    q.start()
+    x, y = q.fetch()
+    assert x.shape == (4, 33, 7) and y.shape == (4,) and y[0] == y[1] and y[2] == y[3] and y[0] != y[2]
+    q.stop()
+    s = KaldiDataSeqQueue(data, spklist, num_parallel=2, max_qsize=20, batch_size=5, min_len=35, max_len=35, shuffle=False)
+    s.start()
+    n = 0
+    while True:
+        try:
+            x, y = s.fetch()
+        except DataOutOfRange:
+            break
+        assert x.shape[0] == 5 and x.shape[2] == 7
+        n += 1
+    assert n == len(mats) // 5 + 1
+    s.stop()

@@ -54,6 +54,7 @@ class RandomSegmentLoader(object):
         self.dim = int(dim) if dim else self.feat_dim
         self.frames = frames
         spk2index = read_spklist(spklist)
+        self.num_total_speakers = len(spk2index)         # dataset/data_loader.py:425 (train.py:86 sizes the softmax with it)
         self.spk_utts = {}                               # speaker index -> scp entry indices
         with open(os.path.join(data, "spk2utt")) as f:
             for line in f:
@@ -215,3 +216,73 @@ class SequentialSegmentLoader(object):
 
     def stop(self):
         self.table.close()
+
+
+class KaldiDataRandomQueue(object):
+    """The reference's class by name and signature (dataset/data_loader.py:369-495) over RandomSegmentLoader: the queue
+    parameters (num_parallel, max_qsize) are accepted and unused -- batches are produced on demand by fetch(), fast enough to
+    stay ahead of the training step -- and start() / stop() keep their places in the caller's loop.  The batch shape may be
+    set after construction (set_batch / set_length) as in the reference; the loader is built at start()."""
+
+    def __init__(self, data_dir, spklist, num_parallel=1, max_qsize=20, num_speakers=None, num_segments=None, min_len=None,
+                 max_len=None, shuffle=True, sample_with_prob=False):
+        self.data, self.spklist = data_dir, spklist
+        self.num_parallel_datasets = num_parallel
+        self.num_speakers, self.num_segments = num_speakers, num_segments
+        self.min_len, self.max_len = min_len, max_len
+        self.shuffle, self.sample_with_prob = shuffle, sample_with_prob
+        self.num_total_speakers = len(read_spklist(spklist))
+        self._loader = None
+
+    def set_batch(self, num_speakers, num_segments):
+        self.num_speakers, self.num_segments = num_speakers, num_segments
+
+    def set_length(self, min_len, max_len):
+        self.min_len, self.max_len = min_len, max_len
+
+    def start(self):
+        self._loader = RandomSegmentLoader(self.data, self.spklist, num_speakers=self.num_speakers, num_segments=self.num_segments,
+                                           min_len=self.min_len, max_len=self.max_len, shuffle=self.shuffle,
+                                           sample_with_prob=self.sample_with_prob, seed=int.from_bytes(os.urandom(4), "little"))
+
+    def fetch(self):
+        if self._loader is None:
+            self.start()
+        return self._loader.fetch()
+
+    def stop(self):
+        if self._loader is not None:
+            self._loader.stop()
+            self._loader = None
+
+
+class KaldiDataSeqQueue(object):
+    """dataset/data_loader.py:554-660 by name and signature over SequentialSegmentLoader (see KaldiDataRandomQueue)."""
+
+    def __init__(self, data_dir, spklist, num_parallel=1, max_qsize=20, batch_size=128, min_len=None, max_len=None, shuffle=True):
+        self.data, self.spklist = data_dir, spklist
+        self.num_parallel_datasets = num_parallel
+        self.batch_size, self.min_len, self.max_len, self.shuffle = batch_size, min_len, max_len, shuffle
+        self.num_total_speakers = len(read_spklist(spklist))
+        self._loader = None
+
+    def set_batch(self, batch_size):
+        self.batch_size = batch_size
+
+    def set_length(self, min_len, max_len):
+        self.min_len, self.max_len = min_len, max_len
+
+    def start(self):
+        self._loader = SequentialSegmentLoader(self.data, self.spklist, batch_size=self.batch_size, min_len=self.min_len,
+                                               max_len=self.max_len, shuffle=self.shuffle,
+                                               seed=int.from_bytes(os.urandom(4), "little"))
+
+    def fetch(self):
+        if self._loader is None:
+            self.start()
+        return self._loader.fetch()
+
+    def stop(self):
+        if self._loader is not None:
+            self._loader.stop()
+            self._loader = None
